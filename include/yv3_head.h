@@ -1,0 +1,158 @@
+/* yv3_head.h -- C ABI of the B200-native YOLOv3 detection-head path.
+ *
+ * One shared library (libyv3head.so), plain C linkage, plain pointers and sizes.  The reference
+ * (zheng-yuwei/YOLOv3-tensorflow) has no FFI for this path: its boundary is a Python class surface
+ * executed by TensorFlow.  Each entry point below names the reference interface it replaces
+ * (paths relative to the reference repo root).
+ *
+ * Conventions
+ *  - every tensor pointer is a DEVICE pointer unless the name ends in `_host`;
+ *  - the caller owns every buffer, including the workspace; the library allocates nothing on the
+ *    device, keeps no global state and never synchronises the stream (except yv3_read_status);
+ *  - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *  - functions return 0 (YV3_OK) or a negative yv3_error; nothing throws across the ABI;
+ *  - all arithmetic is fp32, one rounding per operator in the reference's operator order
+ *    (no FMA contraction), except NMS IoU which is fp64 like the reference's NumPy code.
+ *
+ * Packed head layout (yolov3/yolov3_detector.py:80-85, yolov3/yolov3_decoder.py:99-117):
+ *   predicts[n][r][c][k], r < H/32, c < W/32, k < Ctot; every /32 row holds 16*B8 records of the /8
+ *   head (16 raster-consecutive cells), then 4*B16 records of /16, then B32 records of /32; a record is
+ *   L = 5 + class_num floats [t_x, t_y, t_w, t_h, t_conf, z_0 .. z_{C-1}].  The whole tensor is thus a
+ *   flat array of N * (H/32*W/32) * (16*B8 + 4*B16 + B32) records.  Gradients use the same layout.
+ */
+#ifndef YV3_HEAD_H_
+#define YV3_HEAD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YV3_ABI_VERSION 1
+#define YV3_MAX_BOX 8      /* anchors per head (reference ships 3 / 2 / 3, configs.py:37-41) */
+#define YV3_MAX_GT 256     /* label slots per image (M) */
+
+typedef enum yv3_error {
+    YV3_OK = 0,
+    YV3_ERR_NULL = -1,          /* required pointer is NULL */
+    YV3_ERR_SHAPE = -2,         /* grids are not /8,/16,/32 of one input; N, M, box_num out of range */
+    YV3_ERR_CONFIG = -3,        /* weights / thresholds / eps not finite or out of range */
+    YV3_ERR_ALIGN = -4,         /* device pointer not aligned as documented */
+    YV3_ERR_WORKSPACE = -5,     /* workspace NULL or smaller than yv3_query_workspace reports */
+    YV3_ERR_CUDA = -6,          /* a CUDA runtime call failed (launch error, wrong device, ...) */
+    YV3_ERR_CAPACITY = -7,      /* candidate capacity exceeded / problem too large for the kernel */
+    YV3_ERR_GT_RANGE = -8,      /* (status) a valid label's centre falls outside the grid; TF's
+                                   gather_nd raises here on CPU (yolov3/yolov3_loss.py:271) */
+    YV3_ERR_NONFINITE = -9      /* (status) inf/NaN met in the loss (reported, not "fixed") */
+} yv3_error;
+
+/* The switch surface the path consumes: YOLOv3Loss.__init__ (yolov3/yolov3_loss.py:16-67),
+ * YOLOv3Decoder.__init__ (yolov3/yolov3_decoder.py:14-45), configs.py:36-72, and
+ * keras.backend.epsilon() as set by run.py:26.  Heads are ordered /8, /16, /32. */
+typedef struct yv3_config {
+    int32_t grid_h[3];
+    int32_t grid_w[3];
+    int32_t box_num[3];
+    int32_t class_num;
+    float anchors[3][YV3_MAX_BOX][2];   /* normalised (w, h) priors, fp32-rounded like tf.constant */
+    float iou_thresh;
+    float loss_weights[3][5];           /* per head: xy, wh, noobj, obj, cls  (configs.py:52) */
+    float rectified_loss_weight[3];     /* yolov3_loss.py:63-67 */
+    int32_t is_focal_loss;
+    float focal_alpha;
+    float focal_gamma;
+    int32_t is_tiou_recall;
+    double eps;                         /* keras.backend.epsilon(): clip_by_value(x, fp32(eps),
+                                           fp32(1 - eps)), the Python doubles rounded once */
+} yv3_config;
+
+int yv3_abi_version(void);
+const char* yv3_strerror(int code);
+
+/* Validates a config; replaces the ValueError checks of YOLOv3Loss.__init__ (yolov3_loss.py:63-66)
+ * and the implicit "input is a multiple of 32" contract of configs.py:46-48. */
+int yv3_config_check(const yv3_config* cfg);
+
+/* Floats per image in the packed layout ((H/32)*(W/32)*Ctot) and records (anchors) per image. */
+int64_t yv3_packed_floats_per_image(const yv3_config* cfg);
+int64_t yv3_records_per_image(const yv3_config* cfg);
+
+/* Workspace needed by yv3_assign / yv3_loss_fwd_bwd for a local batch of n images, m label slots. */
+int yv3_query_workspace(const yv3_config* cfg, int n, int m, size_t* bytes);
+
+/* YOLOv3Decoder.decode (yolov3/yolov3_decoder.py:62-87): out[3*h + 0] = raw[...,0:4] (N,H,W,B,4),
+ * out[3*h + 1] = decoded (N,H,W,B,L) in grid units, out[3*h + 2] = corner boxes (N,H,W,B,4). */
+int yv3_decode(const yv3_config* cfg, const float* predicts, int n, float* const out[9], void* stream);
+
+/* LabelDecoder.decode (yolov3/label_decoder.py:26-60): targets (N, M*5) ->
+ * out[2*h] = (N,M,5) labels in head-h grid units, out[2*h + 1] = (N,M,4) corner boxes. */
+int yv3_label_decode(const yv3_config* cfg, const float* targets, int n, int m, float* const out[6],
+                     void* stream);
+
+/* Ground-truth -> cell / anchor / head assignment: YOLOv3Loss._get_valid_target, _calc_iou (response
+ * part) and the cross-head ownership test (yolov3/yolov3_loss.py:225-252, :269-302, :203-208).
+ * table[n][j][h] = {row, col, best_anchor, owned} (int32; all -1/-1/-1/0 for a padding slot),
+ * iou[n][j][h] = best IoU of the centre cell's anchors (0 for padding).  Either output may be NULL.
+ * Tie rules: lowest anchor index among equal IoUs; `>=` both ways across heads (ties -> every tied
+ * head owns the label). */
+int yv3_assign(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
+               int32_t* table, float* iou, void* workspace, size_t workspace_bytes, void* stream);
+
+/* YOLOv3Loss.loss forward (yolov3/yolov3_loss.py:81-138, :140-164, :166-222, :305-369) fused with
+ * the backward TensorFlow autodiff derives from it.
+ *   n_global           images in the whole (all-rank) batch: the reduce_mean denominator (:112)
+ *   rectified_active   value of `current_num <= rectified_coord_num` for this step (:125)
+ *   upstream           d(final objective)/d(loss) (1.0 under Keras)
+ *   loss_detail18      device, 18 floats = rows [xy, wh, noobj, obj, cls, rectified] x heads
+ *                      [/8,/16,/32]; THIS RANK's share of the batch mean (sum over local images /
+ *                      n_global); the scalar loss is the sum of the 18 (all-reduced over ranks)
+ *   grad_predicts      device, packed layout, n images; must be 16-byte aligned; may be NULL
+ *                      (forward only).  Every element is written. */
+int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
+                     int n_global, int rectified_active, float upstream, float* loss_detail18,
+                     float* grad_predicts, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Deferred status of the last yv3_assign / yv3_loss_fwd_bwd that used `workspace`: synchronises the
+ * stream and returns YV3_OK, YV3_ERR_GT_RANGE or YV3_ERR_NONFINITE (the errors TF would raise /
+ * the NaNs it would silently propagate). */
+int yv3_read_status(void* workspace, void* stream);
+
+/* ---- post-process ---------------------------------------------------------------------------- */
+
+/* One candidate row = the 8 columns of YOLOv3PostProcessor._filter_single_head_boxes
+ * (yolov3/yolov3_post_process.py:65-75): x0/W, y0/H, x1/W, y1/H, conf, prob, class, score. */
+#define YV3_CAND_COLS 8
+
+/* YOLOv3PostProcessor.filter_boxes on already-decoded heads of ONE image
+ * (yolov3/yolov3_post_process.py:21-76).  decoded[h] is (H,W,B,L), boxes[h] is (H,W,B,4).
+ * cand (capacity x 8 fp32) receives the survivors in the reference's order (head /8,/16,/32, raster
+ * (y,x,b) within a head); counts[h] (device int32[3]) their number per head.  score > fp32(thresh),
+ * class = lowest index among equal maxima. */
+int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], const float* const boxes[3],
+                       float score_thresh, float* cand, int32_t capacity, int32_t* counts,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* Fused decode + score + threshold straight from the packed logits of n images (the inference path
+ * run.py:59-69 takes, without materialising the decoded tensors).  cand is (n, capacity, 8) fp32,
+ * counts (n, 3) int32.  Per image the order is the reference's. */
+int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float score_thresh,
+                      float* cand, int32_t capacity, int32_t* counts, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
+/* Class-aware greedy NMS, YOLOv3PostProcessor._apply_nms (yolov3/yolov3_post_process.py:108-159), for
+ * n independent candidate lists.  cand is (n, capacity, 8) fp32 or fp64 (`cand_is_f64`), count[i]
+ * (device int32) rows valid in list i.  keep (n, capacity) uint8 receives 1 for the TRUE greedy
+ * survivors: walking candidates by score descending (ties: lower row index first, i.e. the
+ * reference's stable sort), a box is dropped iff an already kept box of the same class has
+ * IoU_f64 > nms_thresh.  The id-collision quirk of apply_nms (:81-104) is layered on the host. */
+int yv3_nms(const void* cand, int cand_is_f64, const int32_t* count, int n, int32_t capacity,
+            double nms_thresh, uint8_t* keep, void* workspace, size_t workspace_bytes, void* stream);
+
+size_t yv3_query_postprocess_workspace(int n, int32_t capacity);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YV3_HEAD_H_ */
