@@ -122,35 +122,45 @@ int yv3_read_status(void* workspace, void* stream);
 /* ---- post-process ---------------------------------------------------------------------------- */
 
 /* One candidate row = the 8 columns of YOLOv3PostProcessor._filter_single_head_boxes
- * (yolov3/yolov3_post_process.py:65-75): x0/W, y0/H, x1/W, y1/H, conf, prob, class, score. */
+ * (yolov3/yolov3_post_process.py:65-75): x0/W, y0/H, x1/W, y1/H, conf, prob, class, score -- fp32.
+ * The reference's rows are float64 only because NumPy promotes fp32 columns next to the int64
+ * arg-max column (:58, :74); every value is exactly an fp32, so fp32 rows lose nothing. */
 #define YV3_CAND_COLS 8
+#define YV3_MAX_CANDIDATES (1 << 18)   /* rows per candidate list (NMS sort key keeps the row in 18 bits) */
+
+/* Workspace for the three calls below for n lists of `capacity` rows; cfg may be NULL when only
+ * yv3_nms is used. */
+int yv3_query_postprocess_workspace(const yv3_config* cfg, int n, int32_t capacity, size_t* bytes);
 
 /* YOLOv3PostProcessor.filter_boxes on already-decoded heads of ONE image
- * (yolov3/yolov3_post_process.py:21-76).  decoded[h] is (H,W,B,L), boxes[h] is (H,W,B,4).
- * cand (capacity x 8 fp32) receives the survivors in the reference's order (head /8,/16,/32, raster
- * (y,x,b) within a head); counts[h] (device int32[3]) their number per head.  score > fp32(thresh),
- * class = lowest index among equal maxima. */
+ * (yolov3/yolov3_post_process.py:21-76).  decoded[h] is (H,W,B,L), boxes[h] is (H,W,B,4), 16-B aligned.
+ * cand (capacity x 8 fp32, 16-B aligned) receives the survivors in the reference's order (head
+ * /8,/16,/32, raster (y,x,b) within a head); counts (device int32[3]) their number per head (the TRUE
+ * number: if their sum exceeds capacity the surplus rows are dropped and yv3_read_status reports
+ * YV3_ERR_CAPACITY).  Keep iff score > fp32(thresh); class = lowest index among equal maxima. */
 int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], const float* const boxes[3],
                        float score_thresh, float* cand, int32_t capacity, int32_t* counts,
                        void* workspace, size_t workspace_bytes, void* stream);
 
 /* Fused decode + score + threshold straight from the packed logits of n images (the inference path
  * run.py:59-69 takes, without materialising the decoded tensors).  cand is (n, capacity, 8) fp32,
- * counts (n, 3) int32.  Per image the order is the reference's. */
+ * counts (n, 3) int32.  Per image the order is the reference's; results are identical to
+ * yv3_decode followed by yv3_filter_decoded. */
 int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float score_thresh,
                       float* cand, int32_t capacity, int32_t* counts, void* workspace,
                       size_t workspace_bytes, void* stream);
 
 /* Class-aware greedy NMS, YOLOv3PostProcessor._apply_nms (yolov3/yolov3_post_process.py:108-159), for
- * n independent candidate lists.  cand is (n, capacity, 8) fp32 or fp64 (`cand_is_f64`), count[i]
- * (device int32) rows valid in list i.  keep (n, capacity) uint8 receives 1 for the TRUE greedy
- * survivors: walking candidates by score descending (ties: lower row index first, i.e. the
- * reference's stable sort), a box is dropped iff an already kept box of the same class has
- * IoU_f64 > nms_thresh.  The id-collision quirk of apply_nms (:81-104) is layered on the host. */
-int yv3_nms(const void* cand, int cand_is_f64, const int32_t* count, int n, int32_t capacity,
-            double nms_thresh, uint8_t* keep, void* workspace, size_t workspace_bytes, void* stream);
-
-size_t yv3_query_postprocess_workspace(int n, int32_t capacity);
+ * n independent candidate lists.  cand is (n, capacity, 8) fp32; list i holds
+ * sum(counts[i*count_cols .. +count_cols)) rows (pass yv3_filter_packed's (n,3) counts with
+ * count_cols = 3).  Class ids must be integers in [0, num_classes).  keep (n, capacity) uint8 receives
+ * 1 for the TRUE greedy survivors: walking candidates by score descending (ties: lower row first, i.e.
+ * the reference's stable sort), a box is dropped iff an already kept box of the same class has
+ * IoU > nms_thresh, IoU evaluated in float64 in the reference's operation order.  The id-collision
+ * quirk of apply_nms (:81-104) is layered on the host. */
+int yv3_nms(const yv3_config* cfg, const float* cand, const int32_t* counts, int count_cols, int n,
+            int32_t capacity, int num_classes, double nms_thresh, uint8_t* keep, void* workspace,
+            size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -8,21 +8,10 @@
 //
 // One CTA per image, one thread per (head, label slot).  The work is ~9 gathered records per label;
 // the kernel is latency-bound and tiny next to the dense pass it feeds (loss_dense.cu).
-#include "yv3_common.cuh"
+#include "yv3_kernels.cuh"
 
 namespace yv3 {
 
-struct AssignArgs {
-    const float* predicts;
-    const float* targets;
-    int n, m;
-    float kappa;          // upstream / n_global
-    OwnEntry* own;        // [n][3][m]
-    float* img_terms;     // [n][3][3]  weighted xy, wh, obj sums per head
-    int32_t* status;
-    int32_t* table;       // optional public output [n][m][3][4]
-    float* iou_out;       // optional public output [n][m][3]
-};
 
 __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a) {
     extern __shared__ float sm[];
@@ -50,7 +39,6 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
     float rho = 0.0f;
     int best = 0;
     BoxDec bd = {};
-    float braw2 = 0.f, braw3 = 0.f;
     if (inside) {
         RecLoc p; p.h = h; p.y = row; p.x = col; p.b = 0;
         int rec0 = record_of(g, h, row, col, 0);
@@ -63,7 +51,7 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
             BoxDec d = decode_box(g, p, t0, t1, t2, t3, t4);
             float parea = __fmul_rn(d.w, d.h);                          // :267
             float v = iou_ref(d.x0, d.y0, d.x1, d.y1, parea, T.box, g.tiou);
-            if (b == 0 || v > rho) { rho = v; best = b; bd = d; braw2 = t2; braw3 = t3; }   // first max (:301)
+            if (b == 0 || v > rho) { rho = v; best = b; bd = d; }   // first max (:301)
         }
     }
     if (active) rho_s[h * m + j] = inside ? rho : 0.0f;
@@ -113,7 +101,6 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
         e.g[2] = k * g.lw[h][1] * sc * (-2.0f * dw / bd.w) * g.aw[h][best] * bd.ew;
         e.g[3] = k * g.lw[h][1] * sc * (-2.0f * dh / bd.h) * g.ah[h][best] * bd.eh;
         e.g[4] = k * g.lw[h][3] * gp * pass_c * bd.sc * (one - bd.sc);
-        (void)braw2; (void)braw3;
     }
     if (active) {
         a.own[((size_t)n * 3 + h) * m + j] = e;

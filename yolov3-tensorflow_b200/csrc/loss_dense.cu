@@ -21,7 +21,7 @@
 //    shared memory: only the class channels a fix-up dirtied are re-zeroed before reuse;
 //  * loss sums: registers -> warp shuffles -> one partial row per CTA -> the last CTA to finish adds
 //    the rows in index order (double) and writes the 18 detail values.  No float atomics anywhere.
-#include "yv3_common.cuh"
+#include "yv3_kernels.cuh"
 
 namespace yv3 {
 
@@ -29,24 +29,6 @@ constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kSlots = 2;             // images a tile may touch (TR <= records per image)
 
-struct DenseArgs {
-    const float* predicts;
-    const float* targets;
-    float* grad;                      // may be NULL: forward only
-    const OwnEntry* own;
-    const float* img_terms;
-    float* partials;
-    int32_t* status;
-    float* detail;                    // 18 floats
-    int n, m, n_global;
-    int tr;                           // records per tile (multiple of 4, <= kThreads * RPT, <= rpi)
-    int num_tiles;
-    long long total_rec;
-    float kappa;                      // upstream / n_global
-    float upstream;
-    int rect_active;
-    int tma_labels;                   // label rows are 16-B aligned: stage them with a bulk copy
-};
 
 struct DenseSmem {
     float* stage[2];                  // [tr * L]
@@ -416,8 +398,12 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
 
 cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream) {
     const bool with_stage = a.grad != nullptr;
-    // records per tile: as many as fit a 2 x ~86 KB pair of tile images, at most 8 per thread
-    const size_t budget = 87040;
+    // records per tile: as many as fit two tile images next to the label / list areas in the 227 KB
+    // of shared memory a CTA may own, at most 8 per thread
+    const size_t fixed = dense_smem_bytes(kThreads * 8, g.L, a.m, false);
+    const size_t limit = 232448 - 1024;
+    if (fixed + 64 * (size_t)g.L > limit) return cudaErrorInvalidValue;
+    const size_t budget = with_stage ? ((limit - fixed) / 2 - 128) : ((size_t)1 << 30);
     long long tr = (long long)(budget / ((size_t)g.L * 4));
     tr = min(tr, (long long)kThreads * 8);
     tr = min(tr, (long long)g.rpi);

@@ -1,0 +1,387 @@
+// C ABI of the head path (include/yv3_head.h): argument checks, geometry, workspace carving, launches.
+// No device allocation, no global state, no stream synchronisation except yv3_read_status.
+#include <math.h>
+#include <string.h>
+
+#include "yv3_kernels.cuh"
+
+using namespace yv3;
+
+namespace {
+
+int sm_count_cached() {
+    // one attribute query per process and device; not "state" of the path (a hardware constant)
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        cached[dev] = v;
+    }
+    return cached[dev];
+}
+
+bool finite_f(float v) { return isfinite(v); }
+
+int check_shape(const yv3_config* c) {
+    for (int h = 0; h < 3; ++h) {
+        if (c->grid_h[h] <= 0 || c->grid_w[h] <= 0) return YV3_ERR_SHAPE;
+        if (c->box_num[h] < 1 || c->box_num[h] > YV3_MAX_BOX) return YV3_ERR_SHAPE;
+    }
+    // /8, /16, /32 of one input that is a multiple of 32 (configs.py:46-48; the Reshape of
+    // yolov3_detector.py:80-85 is impossible otherwise)
+    if (c->grid_h[0] != 4 * c->grid_h[2] || c->grid_w[0] != 4 * c->grid_w[2]) return YV3_ERR_SHAPE;
+    if (c->grid_h[1] != 2 * c->grid_h[2] || c->grid_w[1] != 2 * c->grid_w[2]) return YV3_ERR_SHAPE;
+    if (c->class_num < 0 || c->class_num > 16383) return YV3_ERR_SHAPE;
+    long long rpi = (long long)c->grid_h[2] * c->grid_w[2] *
+                    (16LL * c->box_num[0] + 4LL * c->box_num[1] + c->box_num[2]);
+    if (rpi > (1LL << 22)) return YV3_ERR_SHAPE;       // record ids are packed into 22-bit fields
+    return YV3_OK;
+}
+
+int check_values(const yv3_config* c) {
+    if (!finite_f(c->iou_thresh)) return YV3_ERR_CONFIG;
+    for (int h = 0; h < 3; ++h) {
+        for (int k = 0; k < 5; ++k)
+            if (!finite_f(c->loss_weights[h][k])) return YV3_ERR_CONFIG;
+        if (!finite_f(c->rectified_loss_weight[h])) return YV3_ERR_CONFIG;
+        for (int b = 0; b < c->box_num[h]; ++b) {
+            float w = c->anchors[h][b][0], hh = c->anchors[h][b][1];
+            if (!finite_f(w) || !finite_f(hh) || w <= 0.f || hh <= 0.f) return YV3_ERR_CONFIG;
+        }
+    }
+    if (!finite_f(c->focal_alpha) || !finite_f(c->focal_gamma)) return YV3_ERR_CONFIG;
+    if (!(c->eps >= 0.0) || !(c->eps < 0.5)) return YV3_ERR_CONFIG;
+    return YV3_OK;
+}
+
+Geo make_geo(const yv3_config* c) {
+    Geo g;
+    memset(&g, 0, sizeof(g));
+    const int fold[3] = {16, 4, 1};
+    g.C = c->class_num;
+    g.L = 5 + c->class_num;
+    g.rows32 = c->grid_h[2] * c->grid_w[2];
+    int base = 0;
+    for (int h = 0; h < 3; ++h) {
+        g.H[h] = c->grid_h[h];
+        g.W[h] = c->grid_w[h];
+        g.B[h] = c->box_num[h];
+        g.fold[h] = fold[h];
+        g.seg_base[h] = base;
+        base += fold[h] * g.B[h];
+        g.head_rec[h] = g.H[h] * g.W[h] * g.B[h];
+        g.fW[h] = (float)g.W[h];
+        g.fH[h] = (float)g.H[h];
+        g.fHW[h] = (float)(g.H[h] * g.W[h]);             // python int height*width -> fp32 (:350)
+        for (int b = 0; b < g.B[h]; ++b) {
+            // tf.constant(anchors, fp32) * np.array([W, H]) -> fp32 product (yolov3_decoder.py:35-40)
+            g.aw[h][b] = c->anchors[h][b][0] * g.fW[h];
+            g.ah[h][b] = c->anchors[h][b][1] * g.fH[h];
+        }
+        for (int k = 0; k < 5; ++k) g.lw[h][k] = c->loss_weights[h][k];
+        g.rw[h] = c->rectified_loss_weight[h];
+    }
+    g.rpr = base;
+    g.rpi = g.rows32 * g.rpr;
+    g.lo = (float)c->eps;                                 // python double -> fp32 constant
+    g.hi = (float)(1.0 - c->eps);
+    g.iou_thresh = c->iou_thresh;
+    g.focal = c->is_focal_loss ? 1 : 0;
+    g.alpha = c->focal_alpha;
+    g.gamma = c->focal_gamma;
+    g.tiou = c->is_tiou_recall ? 1 : 0;
+    return g;
+}
+
+bool aligned16(const void* p) { return ((uintptr_t)p & 15u) == 0; }
+bool aligned4(const void* p) { return ((uintptr_t)p & 3u) == 0; }
+
+}  // namespace
+
+extern "C" {
+
+int yv3_abi_version(void) { return YV3_ABI_VERSION; }
+
+const char* yv3_strerror(int code) {
+    switch (code) {
+        case YV3_OK: return "ok";
+        case YV3_ERR_NULL: return "required pointer is NULL";
+        case YV3_ERR_SHAPE: return "bad shape: grids must be /8,/16,/32 of an input that is a multiple of 32; "
+                                   "box_num in [1,8]; n, m in range";
+        case YV3_ERR_CONFIG: return "bad config value (non-finite weight/threshold, anchor <= 0, eps outside [0,0.5))";
+        case YV3_ERR_ALIGN: return "device pointer not aligned as documented";
+        case YV3_ERR_WORKSPACE: return "workspace NULL or smaller than the query function reports";
+        case YV3_ERR_CUDA: return "CUDA runtime error";
+        case YV3_ERR_CAPACITY: return "candidate capacity exceeded / problem too large";
+        case YV3_ERR_GT_RANGE: return "a valid label's centre lies outside the grid (tf.gather_nd would raise)";
+        case YV3_ERR_NONFINITE: return "inf/NaN in the loss";
+        default: return "unknown yv3 error";
+    }
+}
+
+int yv3_config_check(const yv3_config* cfg) {
+    if (!cfg) return YV3_ERR_NULL;
+    int rc = check_shape(cfg);
+    if (rc != YV3_OK) return rc;
+    return check_values(cfg);
+}
+
+int64_t yv3_records_per_image(const yv3_config* cfg) {
+    if (!cfg || check_shape(cfg) != YV3_OK) return -1;
+    return (int64_t)make_geo(cfg).rpi;
+}
+
+int64_t yv3_packed_floats_per_image(const yv3_config* cfg) {
+    if (!cfg || check_shape(cfg) != YV3_OK) return -1;
+    Geo g = make_geo(cfg);
+    return (int64_t)g.rpi * g.L;
+}
+
+int yv3_query_workspace(const yv3_config* cfg, int n, int m, size_t* bytes) {
+    if (!cfg || !bytes) return YV3_ERR_NULL;
+    int rc = yv3_config_check(cfg);
+    if (rc != YV3_OK) return rc;
+    if (n < 1 || m < 1 || m > YV3_MAX_GT) return YV3_ERR_SHAPE;
+    *bytes = carve_workspace(nullptr, n, m).bytes;
+    return YV3_OK;
+}
+
+}  // extern "C"
+
+// ---- assignment and loss ---------------------------------------------------------------------
+namespace {
+
+int loss_common_checks(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
+                       void* workspace, size_t workspace_bytes) {
+    if (!cfg || !predicts || !targets) return YV3_ERR_NULL;
+    int rc = yv3_config_check(cfg);
+    if (rc != YV3_OK) return rc;
+    if (n < 1 || m < 1 || m > YV3_MAX_GT) return YV3_ERR_SHAPE;
+    if (!workspace) return YV3_ERR_WORKSPACE;
+    if (!aligned16(workspace)) return YV3_ERR_ALIGN;
+    if (workspace_bytes < carve_workspace(nullptr, n, m).bytes) return YV3_ERR_WORKSPACE;
+    if (!aligned4(predicts) || !aligned4(targets)) return YV3_ERR_ALIGN;
+    return YV3_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int yv3_assign(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
+               int32_t* table, float* iou, void* workspace, size_t workspace_bytes, void* stream) {
+    int rc = loss_common_checks(cfg, predicts, targets, n, m, workspace, workspace_bytes);
+    if (rc != YV3_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const Geo g = make_geo(cfg);
+    Workspace ws = carve_workspace(workspace, n, m);
+    if (cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st) != cudaSuccess) return YV3_ERR_CUDA;
+    AssignArgs a;
+    a.predicts = predicts; a.targets = targets; a.n = n; a.m = m;
+    a.kappa = 1.0f / (float)n;
+    a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
+    a.table = table; a.iou_out = iou;
+    if (launch_assign(g, a, st) != cudaSuccess) return YV3_ERR_CUDA;
+    return YV3_OK;
+}
+
+int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
+                     int n_global, int rectified_active, float upstream, float* loss_detail18,
+                     float* grad_predicts, void* workspace, size_t workspace_bytes, void* stream) {
+    int rc = loss_common_checks(cfg, predicts, targets, n, m, workspace, workspace_bytes);
+    if (rc != YV3_OK) return rc;
+    if (!loss_detail18) return YV3_ERR_NULL;
+    if (n_global < n) return YV3_ERR_SHAPE;
+    if (grad_predicts && !aligned16(grad_predicts)) return YV3_ERR_ALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    const Geo g = make_geo(cfg);
+    Workspace ws = carve_workspace(workspace, n, m);
+    if (cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st) != cudaSuccess) return YV3_ERR_CUDA;
+    const float kappa = upstream / (float)n_global;
+
+    AssignArgs a;
+    a.predicts = predicts; a.targets = targets; a.n = n; a.m = m;
+    a.kappa = kappa;
+    a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
+    a.table = nullptr; a.iou_out = nullptr;
+    if (launch_assign(g, a, st) != cudaSuccess) return YV3_ERR_CUDA;
+
+    DenseArgs d;
+    memset(&d, 0, sizeof(d));
+    d.predicts = predicts; d.targets = targets; d.grad = grad_predicts;
+    d.own = ws.own; d.img_terms = ws.img_terms; d.partials = ws.partials; d.status = ws.status;
+    d.detail = loss_detail18;
+    d.n = n; d.m = m; d.n_global = n_global;
+    d.total_rec = (long long)n * g.rpi;
+    d.kappa = kappa; d.upstream = upstream;
+    d.rect_active = rectified_active ? 1 : 0;
+    // a label row is m*20 bytes: bulk copies need 16-B aligned source rows and sizes
+    d.tma_labels = (aligned16(targets) && (m % 4) == 0) ? 1 : 0;
+    if (launch_loss_dense(g, d, sm_count_cached(), st) != cudaSuccess) return YV3_ERR_CUDA;
+    return YV3_OK;
+}
+
+int yv3_read_status(void* workspace, void* stream) {
+    if (!workspace) return YV3_ERR_WORKSPACE;
+    int32_t host[kStatusInts];
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemcpyAsync(host, workspace, sizeof(host), cudaMemcpyDeviceToHost, st) != cudaSuccess) return YV3_ERR_CUDA;
+    if (cudaStreamSynchronize(st) != cudaSuccess) return YV3_ERR_CUDA;
+    unsigned bits = (unsigned)host[0];
+    if (bits & kStatusGtRange) return YV3_ERR_GT_RANGE;
+    if (bits & kStatusNonFinite) return YV3_ERR_NONFINITE;
+    if (bits & kStatusCapacity) return YV3_ERR_CAPACITY;
+    return YV3_OK;
+}
+
+}  // extern "C"
+
+// ---- decode, labels, post-process ------------------------------------------------------------------
+namespace {
+
+PostWs carve_post(void* base, long long rpi, int n, int capacity) {
+    PostWs w;
+    size_t off = 0;
+    char* p = (char*)base;
+    auto take = [&](size_t bytes) {
+        char* r = p + off;
+        off = align_up(off + bytes, 256);
+        return r;
+    };
+    const size_t recs = (size_t)n * (size_t)rpi;
+    const size_t rows = (size_t)n * (size_t)capacity;
+    w.status = (int32_t*)take(sizeof(int32_t) * kStatusInts);
+    w.score = (float*)take(recs * 4);
+    w.prob = (float*)take(recs * 4);
+    w.cls = (int32_t*)take(recs * 4);
+    w.keys = (unsigned long long*)take((size_t)n * nms_cap2(capacity) * 8);
+    w.sbox = (float4*)take(rows * 16);
+    w.sidx = (int32_t*)take(rows * 4);
+    w.kspill = (float4*)take(rows * 16);
+    w.bytes = off;
+    return w;
+}
+
+}  // namespace
+
+extern "C" {
+
+int yv3_decode(const yv3_config* cfg, const float* predicts, int n, float* const out[9], void* stream) {
+    if (!cfg || !predicts || !out) return YV3_ERR_NULL;
+    int rc = yv3_config_check(cfg);
+    if (rc != YV3_OK) return rc;
+    if (n < 1) return YV3_ERR_SHAPE;
+    if (!aligned4(predicts)) return YV3_ERR_ALIGN;
+    const Geo g = make_geo(cfg);
+    DecodeArgs a;
+    a.predicts = predicts;
+    a.n = n;
+    for (int h = 0; h < 3; ++h) {
+        a.raw4[h] = out[3 * h + 0];
+        a.decoded[h] = out[3 * h + 1];
+        a.boxes[h] = out[3 * h + 2];
+        if ((a.raw4[h] && !aligned16(a.raw4[h])) || (a.boxes[h] && !aligned16(a.boxes[h]))) return YV3_ERR_ALIGN;
+        if (a.decoded[h] && !aligned4(a.decoded[h])) return YV3_ERR_ALIGN;
+    }
+    if (launch_decode(g, a, sm_count_cached(), (cudaStream_t)stream) != cudaSuccess) return YV3_ERR_CUDA;
+    return YV3_OK;
+}
+
+int yv3_label_decode(const yv3_config* cfg, const float* targets, int n, int m, float* const out[6],
+                     void* stream) {
+    if (!cfg || !targets || !out) return YV3_ERR_NULL;
+    int rc = yv3_config_check(cfg);
+    if (rc != YV3_OK) return rc;
+    if (n < 1 || m < 1) return YV3_ERR_SHAPE;
+    for (int h = 0; h < 3; ++h)
+        if (out[2 * h + 1] && !aligned16(out[2 * h + 1])) return YV3_ERR_ALIGN;
+    const Geo g = make_geo(cfg);
+    if (launch_label_decode(g, targets, n, m, out, (cudaStream_t)stream) != cudaSuccess) return YV3_ERR_CUDA;
+    return YV3_OK;
+}
+
+int yv3_query_postprocess_workspace(const yv3_config* cfg, int n, int32_t capacity, size_t* bytes) {
+    if (!bytes) return YV3_ERR_NULL;
+    if (n < 1 || capacity < 1 || capacity > (1 << 18)) return YV3_ERR_CAPACITY;
+    long long rpi = 0;
+    if (cfg) {
+        int rc = yv3_config_check(cfg);
+        if (rc != YV3_OK) return rc;
+        rpi = make_geo(cfg).rpi;
+    }
+    *bytes = carve_post(nullptr, rpi, n, capacity).bytes;
+    return YV3_OK;
+}
+
+static int post_checks(const yv3_config* cfg, int n, int32_t capacity, void* workspace, size_t workspace_bytes,
+                       PostWs* ws) {
+    if (n < 1) return YV3_ERR_SHAPE;
+    if (capacity < 1 || capacity > (1 << 18)) return YV3_ERR_CAPACITY;
+    if (!workspace) return YV3_ERR_WORKSPACE;
+    if (!aligned16(workspace)) return YV3_ERR_ALIGN;
+    long long rpi = 0;
+    if (cfg) {
+        int rc = yv3_config_check(cfg);
+        if (rc != YV3_OK) return rc;
+        rpi = make_geo(cfg).rpi;
+    }
+    *ws = carve_post(workspace, rpi, n, capacity);
+    if (workspace_bytes < ws->bytes) return YV3_ERR_WORKSPACE;
+    return YV3_OK;
+}
+
+int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float score_thresh, float* cand,
+                      int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!cfg || !predicts || !cand || !counts) return YV3_ERR_NULL;
+    PostWs ws;
+    int rc = post_checks(cfg, n, capacity, workspace, workspace_bytes, &ws);
+    if (rc != YV3_OK) return rc;
+    if (!aligned4(predicts) || !aligned16(cand)) return YV3_ERR_ALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st) != cudaSuccess) return YV3_ERR_CUDA;
+    const Geo g = make_geo(cfg);
+    if (launch_filter_packed(g, predicts, n, score_thresh, cand, capacity, counts, ws.status, ws.score, ws.prob,
+                             ws.cls, sm_count_cached(), st) != cudaSuccess)
+        return YV3_ERR_CUDA;
+    return YV3_OK;
+}
+
+int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], const float* const boxes[3],
+                       float score_thresh, float* cand, int32_t capacity, int32_t* counts, void* workspace,
+                       size_t workspace_bytes, void* stream) {
+    if (!cfg || !decoded || !boxes || !cand || !counts) return YV3_ERR_NULL;
+    for (int h = 0; h < 3; ++h) {
+        if (!decoded[h] || !boxes[h]) return YV3_ERR_NULL;
+        if (!aligned16(boxes[h]) || !aligned4(decoded[h])) return YV3_ERR_ALIGN;
+    }
+    PostWs ws;
+    int rc = post_checks(cfg, 1, capacity, workspace, workspace_bytes, &ws);
+    if (rc != YV3_OK) return rc;
+    if (!aligned16(cand)) return YV3_ERR_ALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st) != cudaSuccess) return YV3_ERR_CUDA;
+    const Geo g = make_geo(cfg);
+    if (launch_filter_decoded(g, decoded, boxes, score_thresh, cand, capacity, counts, ws.status, ws.score,
+                              ws.prob, ws.cls, sm_count_cached(), st) != cudaSuccess)
+        return YV3_ERR_CUDA;
+    return YV3_OK;
+}
+
+int yv3_nms(const yv3_config* cfg, const float* cand, const int32_t* counts, int count_cols, int n,
+            int32_t capacity, int num_classes, double nms_thresh, uint8_t* keep, void* workspace,
+            size_t workspace_bytes, void* stream) {
+    if (!cand || !counts || !keep) return YV3_ERR_NULL;
+    if (count_cols < 1 || count_cols > 8 || num_classes < 1 || num_classes > 16384) return YV3_ERR_SHAPE;
+    PostWs ws;
+    int rc = post_checks(cfg, n, capacity, workspace, workspace_bytes, &ws);
+    if (rc != YV3_OK) return rc;
+    if (!aligned16(cand)) return YV3_ERR_ALIGN;
+    if (launch_nms(cand, counts, count_cols, n, capacity, num_classes, nms_thresh, keep, ws,
+                   (cudaStream_t)stream) != cudaSuccess)
+        return YV3_ERR_CUDA;
+    return YV3_OK;
+}
+
+}  // extern "C"

@@ -218,6 +218,7 @@ static_assert(sizeof(OwnEntry) == 32, "OwnEntry must stay 32 bytes");
 constexpr int kStatusInts = 8;
 constexpr unsigned kStatusGtRange = 1u;
 constexpr unsigned kStatusNonFinite = 2u;
+constexpr unsigned kStatusCapacity = 4u;
 
 struct Workspace {
     int32_t* status;
@@ -229,7 +230,7 @@ struct Workspace {
 constexpr int kMaxGrid = 1024;          // upper bound on CTAs of the dense pass
 constexpr int kPartialFloats = 12;      // noobj[3], cls[3], rect[3], pad[3]
 
-inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+__host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 inline Workspace carve_workspace(void* base, int n, int m) {
     Workspace w;
     size_t off = 0;

@@ -1,0 +1,77 @@
+// Launcher declarations shared between the kernel translation units and the C-ABI (yv3_api.cu).
+#pragma once
+#include "yv3_common.cuh"
+
+namespace yv3 {
+
+// ---- assign.cu ---------------------------------------------------------------------------------
+struct AssignArgs {
+    const float* predicts;
+    const float* targets;
+    int n, m;
+    float kappa;          // upstream / n_global
+    OwnEntry* own;        // [n][3][m]
+    float* img_terms;     // [n][3][3]  weighted xy, wh, obj sums per head
+    int32_t* status;
+    int32_t* table;       // optional public output [n][m][3][4]
+    float* iou_out;       // optional public output [n][m][3]
+};
+cudaError_t launch_assign(const Geo& g, const AssignArgs& a, cudaStream_t stream);
+
+// ---- loss_dense.cu -----------------------------------------------------------------------------
+struct DenseArgs {
+    const float* predicts;
+    const float* targets;
+    float* grad;                      // may be NULL: forward only
+    const OwnEntry* own;
+    const float* img_terms;
+    float* partials;
+    int32_t* status;
+    float* detail;                    // 18 floats
+    int n, m, n_global;
+    int tr;                           // records per tile (multiple of 4, <= kThreads * RPT, <= rpi)
+    int num_tiles;
+    long long total_rec;
+    float kappa;                      // upstream / n_global
+    float upstream;
+    int rect_active;
+    int tma_labels;                   // label rows are 16-B aligned: stage them with a bulk copy
+};
+cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream);
+
+// ---- decode.cu ---------------------------------------------------------------------------------
+struct DecodeArgs {
+    const float* predicts;
+    int n;
+    float* raw4[3];       // (N,H,W,B,4) or NULL
+    float* decoded[3];    // (N,H,W,B,L) or NULL
+    float* boxes[3];      // (N,H,W,B,4) or NULL
+};
+cudaError_t launch_decode(const Geo& g, const DecodeArgs& a, int sm_count, cudaStream_t stream);
+cudaError_t launch_label_decode(const Geo& g, const float* targets, int n, int m, float* const out[6],
+                                cudaStream_t stream);
+
+// ---- postprocess.cu ----------------------------------------------------------------------------
+struct PostWs {
+    int32_t* status;            // [kStatusInts]
+    float* score;               // [n][rpi]  head-raster order (filter only)
+    float* prob;                // [n][rpi]
+    int32_t* cls;               // [n][rpi]
+    unsigned long long* keys;   // [n][cap2] sorted keys (class | ~score | row)
+    float4* sbox;               // [n][capacity] boxes in sorted order
+    int32_t* sidx;              // [n][capacity] original row of a sorted position
+    float4* kspill;             // [n][capacity] kept boxes beyond the shared-memory list
+    size_t bytes;
+};
+int nms_cap2(int capacity);
+cudaError_t launch_filter_packed(const Geo& g, const float* predicts, int n, float thresh, float* cand,
+                                 int capacity, int32_t* counts, int32_t* status, float* score, float* prob,
+                                 int32_t* cls, int sm_count, cudaStream_t stream);
+cudaError_t launch_filter_decoded(const Geo& g, const float* const decoded[3], const float* const boxes[3],
+                                  float thresh, float* cand, int capacity, int32_t* counts, int32_t* status,
+                                  float* score, float* prob, int32_t* cls, int sm_count, cudaStream_t stream);
+cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, int n, int capacity,
+                       int num_classes, double thresh, unsigned char* keep, const PostWs& ws,
+                       cudaStream_t stream);
+
+}  // namespace yv3
