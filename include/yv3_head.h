@@ -105,13 +105,16 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
  *   n_global           images in the whole (all-rank) batch: the reduce_mean denominator (:112)
  *   rectified_active   value of `current_num <= rectified_coord_num` for this step (:125)
  *   upstream           d(final objective)/d(loss) (1.0 under Keras)
- *   loss_detail18      device, 18 floats = rows [xy, wh, noobj, obj, cls, rectified] x heads
- *                      [/8,/16,/32]; THIS RANK's share of the batch mean (sum over local images /
- *                      n_global); the scalar loss is the sum of the 18 (all-reduced over ranks)
+ *   loss_out20         device, 20 floats.  [0..17] = the (6,3) loss detail: rows [xy, wh, noobj,
+ *                      obj, cls, rectified] x heads [/8,/16,/32] (the loss_detail variables of
+ *                      :71-79, :115-134); THIS RANK's share of the batch mean (sum over local
+ *                      images / n_global).  [18] = their sum = this rank's share of the scalar
+ *                      loss (:137).  [19] = 0.  Summing (all-reducing) the 20 floats over the
+ *                      ranks of a batch-sharded job gives the global values.
  *   grad_predicts      device, packed layout, n images; must be 16-byte aligned; may be NULL
  *                      (forward only).  Every element is written. */
 int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
-                     int n_global, int rectified_active, float upstream, float* loss_detail18,
+                     int n_global, int rectified_active, float upstream, float* loss_out20,
                      float* grad_predicts, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Deferred status of the last yv3_assign / yv3_loss_fwd_bwd that used `workspace`: synchronises the

@@ -1,0 +1,20 @@
+"""B200-native detection-head path of zheng-yuwei/YOLOv3-tensorflow.
+
+Host-side mirror of the reference's interface for the path (same class names, arguments, return
+structures) over the C-ABI library ``lib/libyv3head.so`` (include/yv3_head.h):
+
+    YOLOv3Decoder        yolov3/yolov3_decoder.py
+    LabelDecoder         yolov3/label_decoder.py
+    YOLOv3Loss           yolov3/yolov3_loss.py   (forward + analytic backward, fused)
+    YOLOv3PostProcessor  yolov3/yolov3_post_process.py
+    HeadPostProcessor    batched device-resident filter + NMS (the run.py:59-74 loop as one call)
+    backend              keras.backend.epsilon() / set_epsilon()
+    configs              the configs.py switches the path consumes
+"""
+from . import backend  # noqa: F401
+from .label_decoder import LabelDecoder  # noqa: F401
+from .yolov3_decoder import YOLOv3Decoder  # noqa: F401
+from .yolov3_loss import YOLOv3Loss  # noqa: F401
+from .yolov3_post_process import HeadPostProcessor, YOLOv3PostProcessor  # noqa: F401
+
+__all__ = ["YOLOv3Decoder", "LabelDecoder", "YOLOv3Loss", "YOLOv3PostProcessor", "HeadPostProcessor", "backend"]

@@ -146,6 +146,7 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
         // (1) labels of the touched images -> shared memory (bulk copy when rows are 16-B aligned)
         if (a.tma_labels) {
             if (tid == 0) {
+                fence_async_smem();       // earlier generic reads of lab_raw are ordered before the async writes
                 for (int sl = 0; sl < nslots; ++sl) {
                     mbar_expect_tx(&s.bar[sl], (unsigned)(m * 20));
                     bulk_g2s(s.lab_raw[sl], a.targets + (size_t)(n_first + sl) * m * 5, (unsigned)(m * 20), &s.bar[sl]);
@@ -163,10 +164,11 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
         // (3) the stage buffer must have left for global memory (store of two tiles ago)
         if (with_stage && tid == 0) bulk_wait_read<1>();
         if (a.tma_labels) {
-            for (int sl = 0; sl < nslots; ++sl) mbar_wait(&s.bar[sl], bar_phase);
+            // each slot's barrier flips only in the tiles that use it: one phase bit per slot
+            for (int sl = 0; sl < nslots; ++sl) mbar_wait(&s.bar[sl], (bar_phase >> sl) & 1u);
+            bar_phase ^= (1u << nslots) - 1u;
         }
         __syncthreads();
-        bar_phase ^= 1u;
 
         // (4) warp sl compacts image slot sl's valid labels (order kept) into per-head boxes;
         //     warp 2 collects the owned entries that fall into this tile (order kept)
@@ -376,6 +378,7 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
     __syncthreads();
     if (!is_last) return;
     __threadfence();
+    __shared__ float fin[18];
     if (tid < 18) {
         const int row = tid / 3, h = tid - row * 3;       // rows: xy, wh, noobj, obj, cls, rect
         double acc = 0.0;
@@ -389,11 +392,19 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
             else if (row == 4) acc *= (double)g.lw[h][4];
             else acc = a.rect_active ? acc * (double)g.rw[h] : 0.0;
         }
-        float out = (float)(acc / (double)a.n_global);
+        const float out = (float)(acc / (double)a.n_global);
         a.detail[tid] = out;
+        fin[tid] = out;
         if (!isfinite(out)) atomicOr((unsigned*)a.status, kStatusNonFinite);
     }
-    if (tid == 0) a.status[1] = 0;     // re-arm the ticket for the next launch
+    __syncthreads();
+    if (tid == 0) {
+        float total = 0.f;                                // reduce_sum of the (6,3) detail (:137)
+        for (int i = 0; i < 18; ++i) total += fin[i];
+        a.detail[18] = total;
+        a.detail[19] = 0.f;
+        a.status[1] = 0;                                  // re-arm the ticket for the next launch
+    }
 }
 
 cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream) {

@@ -188,11 +188,11 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
 }
 
 int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
-                     int n_global, int rectified_active, float upstream, float* loss_detail18,
+                     int n_global, int rectified_active, float upstream, float* loss_out20,
                      float* grad_predicts, void* workspace, size_t workspace_bytes, void* stream) {
     int rc = loss_common_checks(cfg, predicts, targets, n, m, workspace, workspace_bytes);
     if (rc != YV3_OK) return rc;
-    if (!loss_detail18) return YV3_ERR_NULL;
+    if (!loss_out20) return YV3_ERR_NULL;
     if (n_global < n) return YV3_ERR_SHAPE;
     if (grad_predicts && !aligned16(grad_predicts)) return YV3_ERR_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
@@ -212,7 +212,7 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
     memset(&d, 0, sizeof(d));
     d.predicts = predicts; d.targets = targets; d.grad = grad_predicts;
     d.own = ws.own; d.img_terms = ws.img_terms; d.partials = ws.partials; d.status = ws.status;
-    d.detail = loss_detail18;
+    d.detail = loss_out20;
     d.n = n; d.m = m; d.n_global = n_global;
     d.total_rec = (long long)n * g.rpi;
     d.kappa = kappa; d.upstream = upstream;

@@ -27,7 +27,7 @@ struct DenseArgs {
     const float* img_terms;
     float* partials;
     int32_t* status;
-    float* detail;                    // 18 floats
+    float* detail;                    // 20 floats: 18 detail values, their sum, pad
     int n, m, n_global;
     int tr;                           // records per tile (multiple of 4, <= kThreads * RPT, <= rpi)
     int num_tiles;

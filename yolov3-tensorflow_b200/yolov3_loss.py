@@ -1,0 +1,180 @@
+"""Drop-in for yolov3/yolov3_loss.py::YOLOv3Loss backed by yv3_loss_fwd_bwd (CUDA, sm_100a).
+
+The reference builds the loss as ~150 small TF ops per image inside tf.map_fn and lets autodiff derive
+the backward; here one assignment kernel plus one fused sweep produce the loss detail AND
+d loss / d predicts in a single pass, so ``loss()`` hands torch.autograd a ready gradient.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+
+_DETAIL_NAMES = ("coord_loss_xy", "coord_loss_wh", "noobj_iou_loss", "obj_iou_loss", "class_loss",
+                 "rectified_coord_loss")
+
+
+class _FusedLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, predicts, owner, targets):
+        total, grad = owner._run(targets, predicts, want_grad=True)
+        ctx.save_for_backward(grad)
+        return total
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        (grad,) = ctx.saved_tensors
+        # upstream is 1 under Keras (the loss IS the objective, trainer.py:84); the product is kept so
+        # that any other use of the scalar stays correct
+        return grad * grad_output, None, None
+
+
+class YOLOv3Loss(object):
+    """Same constructor arguments and ``loss(targets, predicts)`` contract as the reference
+    (yolov3_loss.py:16-18, :81).  Side contract kept: the six ``loss_detail`` vectors (shape (3,),
+    heads /8,/16,/32) are refreshed by every call, and ``current_num`` counts the images seen while the
+    train-from-scratch correction term is active (:69, :125-134, :152).
+
+    Multi-GPU: one process per GPU, each holding a contiguous shard of the batch.  When
+    torch.distributed is initialised (or ``process_group`` is given) the batch mean runs over the
+    GLOBAL batch: gradients are scaled by 1/N_global locally and the 20 loss floats are all-reduced
+    (NCCL); no other data crosses NVLink."""
+
+    def __init__(self, head_grid_sizes, class_num, anchor_boxes, iou_thresh, loss_weights,
+                 rectified_coord_num=0, rectified_loss_weight=None,
+                 is_focal_loss=False, focal_alpha=0.25, focal_gamma=2.0, is_tiou_recall=False,
+                 process_group=None):
+        self.head_grid_sizes = [(int(h), int(w)) for (h, w) in head_grid_sizes]
+        self.class_num = int(class_num)
+        self.box_len = 5 + self.class_num
+        self.iou_thresh = iou_thresh
+        self.is_focal_loss = is_focal_loss
+        self.focal_alpha = focal_alpha
+        self.focal_gamma = focal_gamma
+        self.is_tiou_recall = is_tiou_recall
+        self.rectified_coord_num = int(rectified_coord_num)
+        self._cfg = _lib.make_config(self.head_grid_sizes, self.class_num, anchor_boxes, iou_thresh,
+                                     loss_weights, rectified_loss_weight, is_focal_loss, focal_alpha,
+                                     focal_gamma, is_tiou_recall)
+        self._lib = _lib.lib()
+        self.records_per_image = int(self._lib.yv3_records_per_image(ctypes.byref(self._cfg)))
+        self.packed_floats_per_image = int(self._lib.yv3_packed_floats_per_image(ctypes.byref(self._cfg)))
+        self.process_group = process_group
+        # host-visible state of the tf.cond at yolov3_loss.py:125 (a bare backend variable there, :69)
+        self.current_num = 0
+        self._ws = {}
+        self._last_ws = None
+        self.loss_detail = None
+        for name in _DETAIL_NAMES:
+            setattr(self, name, None)
+
+    # ---- distributed plumbing --------------------------------------------------------------------
+    def _world(self):
+        import torch.distributed as dist
+        if self.process_group is not None:
+            return dist.get_world_size(self.process_group)
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_world_size()
+        return 1
+
+    def _all_reduce(self, t):
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.process_group)
+
+    # ---- the fused call --------------------------------------------------------------------------
+    def _workspace(self, n, m, device):
+        key = (n, m, device)
+        ws = self._ws.get(key)
+        if ws is None:
+            size = ctypes.c_size_t(0)
+            _lib.check(self._lib.yv3_query_workspace(ctypes.byref(self._cfg), n, m, ctypes.byref(size)),
+                       "yv3_query_workspace")
+            ws = torch.empty(size.value, dtype=torch.uint8, device=device)
+            self._ws[key] = ws
+        return ws
+
+    def _prepare(self, targets, predicts):
+        p = _lib.to_device_f32(predicts)
+        t = _lib.to_device_f32(targets, p.device)
+        if p.dim() != 4 or p[0].numel() != self.packed_floats_per_image:
+            raise ValueError("predicts must be (N, H/32, W/32, %d floats per image in total), got %s" %
+                             (self.packed_floats_per_image, tuple(p.shape)))
+        if t.dim() != 2 or t.shape[0] != p.shape[0] or t.shape[1] % 5 != 0 or t.shape[1] == 0:
+            raise ValueError("targets must be (N, M*5) with the same N as predicts")
+        return t, p
+
+    def _run(self, targets, predicts, want_grad, upstream=1.0):
+        t, p = self._prepare(targets, predicts)
+        n, m = p.shape[0], t.shape[1] // 5
+        world = self._world()
+        n_global = n * world
+        rect_active = self.current_num <= self.rectified_coord_num            # :125 (read before the add)
+        ws = self._workspace(n, m, p.device)
+        out = torch.empty(20, dtype=torch.float32, device=p.device)
+        grad = torch.empty_like(p) if want_grad else None
+        rc = self._lib.yv3_loss_fwd_bwd(ctypes.byref(self._cfg), _lib.ptr(p), _lib.ptr(t), n, m, n_global,
+                                        1 if rect_active else 0, float(upstream), _lib.ptr(out),
+                                        _lib.ptr(grad), _lib.ptr(ws), ws.numel(),
+                                        _lib.current_stream_ptr(p.device))
+        _lib.check(rc, "yv3_loss_fwd_bwd")
+        if rect_active:
+            self.current_num += n_global                                       # update_add (:152)
+        if world > 1:
+            self._all_reduce(out)
+        self._last_ws = ws
+        detail = out[:18].view(6, 3)
+        self.loss_detail = detail
+        for i, name in enumerate(_DETAIL_NAMES):
+            setattr(self, name, detail[i])
+        return out[18], grad
+
+    # ---- public surface --------------------------------------------------------------------------
+    def loss(self, targets, predicts):
+        """Scalar total loss (a 0-dim CUDA tensor).  Differentiable with respect to ``predicts`` when it
+        requires grad: the gradient was produced by the same fused pass."""
+        if isinstance(predicts, torch.Tensor) and predicts.requires_grad:
+            return _FusedLoss.apply(predicts, self, targets)
+        total, _ = self._run(targets, predicts, want_grad=False)
+        return total
+
+    __call__ = loss
+
+    def loss_and_grad(self, targets, predicts, upstream=1.0):
+        """(total loss, d(upstream * loss)/d predicts in the packed layout) from one fused pass."""
+        return self._run(targets, predicts, want_grad=True, upstream=upstream)
+
+    def assign(self, targets, predicts):
+        """The integer decisions of the loss: (table (N,M,3,4) int32 [row, col, best_anchor, owned] per
+        label slot and head, -1/-1/-1/0 for padding; iou (N,M,3) fp32 best centre-cell IoU)."""
+        t, p = self._prepare(targets, predicts)
+        n, m = p.shape[0], t.shape[1] // 5
+        ws = self._workspace(n, m, p.device)
+        table = torch.empty((n, m, 3, 4), dtype=torch.int32, device=p.device)
+        iou = torch.empty((n, m, 3), dtype=torch.float32, device=p.device)
+        rc = self._lib.yv3_assign(ctypes.byref(self._cfg), _lib.ptr(p), _lib.ptr(t), n, m, _lib.ptr(table),
+                                  _lib.ptr(iou), _lib.ptr(ws), ws.numel(), _lib.current_stream_ptr(p.device))
+        _lib.check(rc, "yv3_assign")
+        self._last_ws = ws
+        return table, iou
+
+    def check_status(self):
+        """Synchronises and raises what TensorFlow would have raised for the last call: IndexError for a
+        label centre outside the grid (gather_nd, yolov3_loss.py:271); FloatingPointError for inf/NaN
+        in the loss (which TF silently propagates)."""
+        if self._last_ws is None:
+            return
+        rc = self._lib.yv3_read_status(_lib.ptr(self._last_ws),
+                                       _lib.current_stream_ptr(self._last_ws.device))
+        if rc == _lib.YV3_ERR_GT_RANGE:
+            raise IndexError(_lib.strerror(rc))
+        if rc == _lib.YV3_ERR_NONFINITE:
+            raise FloatingPointError(_lib.strerror(rc))
+        _lib.check(rc, "yv3_read_status")
+
+    def state_dict(self):
+        """``current_num`` is not checkpointed by the reference (it is not a model weight); exposing it
+        lets a trainer resume the correction phase where it stopped."""
+        return {"current_num": int(self.current_num)}
+
+    def load_state_dict(self, state):
+        self.current_num = int(state["current_num"])
