@@ -31,12 +31,23 @@ def _nvcc():
     raise RuntimeError("nvcc not found: libyv3head.so cannot be built")
 
 
+def _fingerprint():
+    """Content hash of every source, header and flag: mtimes do not survive the copy to the GPU box."""
+    import hashlib
+    h = hashlib.sha256()
+    h.update(" ".join(NVCC_FLAGS).encode())
+    for d in [os.path.join(CSRC, s) for s in SOURCES + HEADERS]:
+        with open(d, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
 def _stale():
-    if not os.path.exists(LIB_PATH):
+    stamp = os.path.join(LIB_DIR, "build.hash")
+    if not os.path.exists(LIB_PATH) or not os.path.exists(stamp):
         return True
-    t = os.path.getmtime(LIB_PATH)
-    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
-    return any(os.path.getmtime(d) > t for d in deps)
+    with open(stamp) as f:
+        return f.read().strip() != _fingerprint()
 
 
 def build_library(force=False, verbose=False):
@@ -64,6 +75,8 @@ def build_library(force=False, verbose=False):
         raise RuntimeError("link failed")
     with open(os.path.join(LIB_DIR, "build.log"), "w") as f:
         f.write("\n".join(log))
+    with open(os.path.join(LIB_DIR, "build.hash"), "w") as f:
+        f.write(_fingerprint())
     if verbose:
         print("\n".join(log))
     return LIB_PATH
