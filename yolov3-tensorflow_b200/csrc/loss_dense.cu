@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
                 }
             }
             if (lane == 0) s.nlist[0] = count;
-        } else if (with_stage && C > 0) {
+        } else if (warp >= 3 && with_stage && C > 0) {
             // (5) re-zero the class channels the fix-ups of two tiles ago dirtied in this buffer
             const int nd = s.ndirty[buf];
             for (int d = warp - 3; d < nd; d += kWarps - 3) {
@@ -287,7 +287,7 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
         __syncthreads();
 
         // ---- fix-up: records that own a label (one warp per record, entries in label order) ----
-        const int nl = s.nlist[0];
+        const int nl = (a.debug & 4) ? 0 : s.nlist[0];
         for (int i = 0; i < nl; ++i) {
             const int rt = s.list_rec[i];
             if ((rt & (kWarps - 1)) != warp) continue;
@@ -340,12 +340,17 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
             const size_t bytes = (size_t)nrec * L * 4;
             const unsigned bulk = (unsigned)(bytes & ~(size_t)15);
             float* gdst = a.grad + (size_t)rec0 * L;
+            if (a.debug & 8) {
+            } else if (a.debug & 2) {
+                for (int i = tid; i < (int)(bytes / 4); i += kThreads) gdst[i] = s.stage[buf][i];
+            } else {
             if (tid == 0) {
                 if (bulk) bulk_s2g(gdst, s.stage[buf], bulk);
                 bulk_commit();
             }
             const int tail = (int)((bytes - bulk) / 4);          // only the very last tile can have one
             if (tid < tail) gdst[bulk / 4 + tid] = s.stage[buf][bulk / 4 + tid];
+            }
         }
 #pragma unroll
         for (int r = 0; r < RPT; ++r)

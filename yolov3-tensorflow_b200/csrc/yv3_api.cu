@@ -1,6 +1,8 @@
 // C ABI of the head path (include/yv3_head.h): argument checks, geometry, workspace carving, launches.
 // No device allocation, no global state, no stream synchronisation except yv3_read_status.
 #include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "yv3_kernels.cuh"
@@ -23,6 +25,13 @@ int sm_count_cached() {
 }
 
 bool finite_f(float v) { return isfinite(v); }
+
+// YV3_TRACE=1 in the environment: say which CUDA call failed (stderr) before returning YV3_ERR_CUDA.
+bool cuda_ok(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return true;
+    if (getenv("YV3_TRACE")) fprintf(stderr, "[yv3] %s failed: %s\n", what, cudaGetErrorString(e));
+    return false;
+}
 
 int check_shape(const yv3_config* c) {
     for (int h = 0; h < 3; ++h) {
@@ -177,13 +186,13 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
     cudaStream_t st = (cudaStream_t)stream;
     const Geo g = make_geo(cfg);
     Workspace ws = carve_workspace(workspace, n, m);
-    if (cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st) != cudaSuccess) return YV3_ERR_CUDA;
+    if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
     AssignArgs a;
     a.predicts = predicts; a.targets = targets; a.n = n; a.m = m;
     a.kappa = 1.0f / (float)n;
     a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
     a.table = table; a.iou_out = iou;
-    if (launch_assign(g, a, st) != cudaSuccess) return YV3_ERR_CUDA;
+    if (!cuda_ok(launch_assign(g, a, st), "launch_assign")) return YV3_ERR_CUDA;
     return YV3_OK;
 }
 
@@ -198,7 +207,7 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
     cudaStream_t st = (cudaStream_t)stream;
     const Geo g = make_geo(cfg);
     Workspace ws = carve_workspace(workspace, n, m);
-    if (cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st) != cudaSuccess) return YV3_ERR_CUDA;
+    if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
     const float kappa = upstream / (float)n_global;
 
     AssignArgs a;
@@ -206,7 +215,7 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
     a.kappa = kappa;
     a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
     a.table = nullptr; a.iou_out = nullptr;
-    if (launch_assign(g, a, st) != cudaSuccess) return YV3_ERR_CUDA;
+    if (!cuda_ok(launch_assign(g, a, st), "launch_assign")) return YV3_ERR_CUDA;
 
     DenseArgs d;
     memset(&d, 0, sizeof(d));
@@ -219,7 +228,12 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
     d.rect_active = rectified_active ? 1 : 0;
     // a label row is m*20 bytes: bulk copies need 16-B aligned source rows and sizes
     d.tma_labels = (aligned16(targets) && (m % 4) == 0) ? 1 : 0;
-    if (launch_loss_dense(g, d, sm_count_cached(), st) != cudaSuccess) return YV3_ERR_CUDA;
+    {
+        const char* dbg = getenv("YV3_DEBUG");
+        d.debug = dbg ? atoi(dbg) : 0;
+        if (d.debug & 1) d.tma_labels = 0;
+    }
+    if (!cuda_ok(launch_loss_dense(g, d, sm_count_cached(), st), "launch_loss_dense")) return YV3_ERR_CUDA;
     return YV3_OK;
 }
 
@@ -227,8 +241,8 @@ int yv3_read_status(void* workspace, void* stream) {
     if (!workspace) return YV3_ERR_WORKSPACE;
     int32_t host[kStatusInts];
     cudaStream_t st = (cudaStream_t)stream;
-    if (cudaMemcpyAsync(host, workspace, sizeof(host), cudaMemcpyDeviceToHost, st) != cudaSuccess) return YV3_ERR_CUDA;
-    if (cudaStreamSynchronize(st) != cudaSuccess) return YV3_ERR_CUDA;
+    if (!cuda_ok(cudaMemcpyAsync(host, workspace, sizeof(host), cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync")) return YV3_ERR_CUDA;
+    if (!cuda_ok(cudaStreamSynchronize(st), "cudaStreamSynchronize")) return YV3_ERR_CUDA;
     unsigned bits = (unsigned)host[0];
     if (bits & kStatusGtRange) return YV3_ERR_GT_RANGE;
     if (bits & kStatusNonFinite) return YV3_ERR_NONFINITE;
@@ -285,7 +299,7 @@ int yv3_decode(const yv3_config* cfg, const float* predicts, int n, float* const
         if ((a.raw4[h] && !aligned16(a.raw4[h])) || (a.boxes[h] && !aligned16(a.boxes[h]))) return YV3_ERR_ALIGN;
         if (a.decoded[h] && !aligned4(a.decoded[h])) return YV3_ERR_ALIGN;
     }
-    if (launch_decode(g, a, sm_count_cached(), (cudaStream_t)stream) != cudaSuccess) return YV3_ERR_CUDA;
+    if (!cuda_ok(launch_decode(g, a, sm_count_cached(), (cudaStream_t)stream), "launch_decode")) return YV3_ERR_CUDA;
     return YV3_OK;
 }
 
@@ -298,7 +312,7 @@ int yv3_label_decode(const yv3_config* cfg, const float* targets, int n, int m, 
     for (int h = 0; h < 3; ++h)
         if (out[2 * h + 1] && !aligned16(out[2 * h + 1])) return YV3_ERR_ALIGN;
     const Geo g = make_geo(cfg);
-    if (launch_label_decode(g, targets, n, m, out, (cudaStream_t)stream) != cudaSuccess) return YV3_ERR_CUDA;
+    if (!cuda_ok(launch_label_decode(g, targets, n, m, out, (cudaStream_t)stream), "launch_label_decode")) return YV3_ERR_CUDA;
     return YV3_OK;
 }
 
@@ -340,11 +354,10 @@ int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float
     if (rc != YV3_OK) return rc;
     if (!aligned4(predicts) || !aligned16(cand)) return YV3_ERR_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
-    if (cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st) != cudaSuccess) return YV3_ERR_CUDA;
+    if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
     const Geo g = make_geo(cfg);
-    if (launch_filter_packed(g, predicts, n, score_thresh, cand, capacity, counts, ws.status, ws.score, ws.prob,
-                             ws.cls, sm_count_cached(), st) != cudaSuccess)
-        return YV3_ERR_CUDA;
+    if (!cuda_ok(launch_filter_packed(g, predicts, n, score_thresh, cand, capacity, counts, ws.status, ws.score, ws.prob,
+                             ws.cls, sm_count_cached(), st), "launch_filter_packed")) return YV3_ERR_CUDA;
     return YV3_OK;
 }
 
@@ -361,11 +374,10 @@ int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], con
     if (rc != YV3_OK) return rc;
     if (!aligned16(cand)) return YV3_ERR_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
-    if (cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st) != cudaSuccess) return YV3_ERR_CUDA;
+    if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
     const Geo g = make_geo(cfg);
-    if (launch_filter_decoded(g, decoded, boxes, score_thresh, cand, capacity, counts, ws.status, ws.score,
-                              ws.prob, ws.cls, sm_count_cached(), st) != cudaSuccess)
-        return YV3_ERR_CUDA;
+    if (!cuda_ok(launch_filter_decoded(g, decoded, boxes, score_thresh, cand, capacity, counts, ws.status, ws.score,
+                              ws.prob, ws.cls, sm_count_cached(), st), "launch_filter_decoded")) return YV3_ERR_CUDA;
     return YV3_OK;
 }
 
@@ -378,9 +390,8 @@ int yv3_nms(const yv3_config* cfg, const float* cand, const int32_t* counts, int
     int rc = post_checks(cfg, n, capacity, workspace, workspace_bytes, &ws);
     if (rc != YV3_OK) return rc;
     if (!aligned16(cand)) return YV3_ERR_ALIGN;
-    if (launch_nms(cand, counts, count_cols, n, capacity, num_classes, nms_thresh, keep, ws,
-                   (cudaStream_t)stream) != cudaSuccess)
-        return YV3_ERR_CUDA;
+    if (!cuda_ok(launch_nms(cand, counts, count_cols, n, capacity, num_classes, nms_thresh, keep, ws,
+                   (cudaStream_t)stream), "launch_nms")) return YV3_ERR_CUDA;
     return YV3_OK;
 }
 

@@ -36,6 +36,7 @@ struct DenseArgs {
     float upstream;
     int rect_active;
     int tma_labels;                   // label rows are 16-B aligned: stage them with a bulk copy
+    int debug;                        // developer switches (YV3_DEBUG): 2 plain stores, 4 skip fix-up, 8 skip store
 };
 cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream);
 
