@@ -1,0 +1,340 @@
+"""Benchmark of the detection-head hot path (BASELINE.json): fused head loss fwd+bwd and decode+filter+NMS.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step = one pass of the hot path over one synthetic batch: assignment + fused loss forward/backward
+(gradient written) followed by fused decode + score threshold + class-aware NMS of the same head tensors.
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOADS = {
+    # BASELINE.json configs[1]: the configuration the metric is quoted on at N=1
+    "cfg2_416_c80_b64": dict(size=(416, 416), class_num=80, batch=64, m=16, anchors="coco", iou_thresh=0.8,
+                             focal=False, rect=-1, score_thresh=0.1, nms_thresh=0.45,
+                             desc="416x416 80-class head (10647 boxes/img), batch 64 per GPU, loss fwd+bwd + "
+                                  "decode+filter+NMS"),
+    # configs[2] per-GPU shard at 8 GPUs
+    "cfg3_608_c80_b64": dict(size=(608, 608), class_num=80, batch=64, m=16, anchors="coco", iou_thresh=0.8,
+                             focal=False, rect=-1, score_thresh=0.1, nms_thresh=0.45,
+                             desc="608x608 80-class head (22743 boxes/img), batch 64 per GPU"),
+    # configs[3]: post-process stress
+    "cfg4_416_c80_b256_dense": dict(size=(416, 416), class_num=80, batch=256, m=16, anchors="coco", iou_thresh=0.8,
+                                    focal=False, rect=-1, score_thresh=0.001, nms_thresh=0.45,
+                                    desc="416x416 batch 256, score thresh 0.001, per-class NMS IoU 0.45 (dense)"),
+    # configs[4]: single class, focal + rectified
+    "cfg5_512_c0_b16": dict(size=(512, 512), class_num=0, batch=16, m=16, anchors="shipped3", iou_thresh=0.8,
+                            focal=True, rect=1 << 30, score_thresh=0.5, nms_thresh=0.4,
+                            desc="512x512 single-class head (class_num 0), focal + prior-box correction on, "
+                                 "batch 16 per GPU"),
+}
+
+
+def build_spec(w):
+    from helpers import three_anchor_shipped
+    from oracle.head_spec import SHIPPED_LOSS_WEIGHTS, HeadSpec, coco_anchors
+    anchors = coco_anchors() if w["anchors"] == "coco" else three_anchor_shipped()
+    return HeadSpec.from_input(w["size"][0], w["size"][1], w["class_num"], anchors, iou_thresh=w["iou_thresh"],
+                               loss_weights=SHIPPED_LOSS_WEIGHTS, rectified_loss_weight=(1.0, 1.0, 1.0),
+                               is_focal_loss=w["focal"], focal_alpha=1.0, focal_gamma=2.0, eps=1e-8)
+
+
+def synth(spec, n, m, rank):
+    """logits iid N(0,1) clipped to [-8,8], seed 1234+rank; labels V~U{1..M}, seed 4321+rank."""
+    from helpers import make_predicts, make_targets
+    return make_predicts(spec, n, seed=1234 + rank), make_targets(spec, n, m, seed=4321 + rank, min_valid=1)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi's clocks line through NVML, polled while the benchmark runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag, self.mark = index, [], False, None
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_sm = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.max_sm = None
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+                self.samples.append((time.time(), sm, reasons, util, self.mark))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def summary(self):
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_sm, "reasons": ["unavailable"]}
+        nv = self.nv
+        timed = [s for s in self.samples if s[4] == "timed"] or [s for s in self.samples if s[4] is not None] \
+            or self.samples
+        names = {
+            "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4),
+            "hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+            "hw_power_brake": getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80),
+        }
+        seen = sorted({k for s in timed for k, bit in names.items() if s[2] & bit})
+        return {"sm_mhz": float(np.median([s[1] for s in timed])), "sm_max_mhz": self.max_sm, "reasons": seen,
+                "samples": len(timed)}
+
+
+def cpu_port_step(spec, p, t, w):
+    """The oracle port of the reference's CPU path for the same step: serial per-image loss with autograd
+    backward (tf.map_fn(parallel_iterations=1) + TF autodiff), decode, filter_boxes, apply_nms per image
+    (run.py:59-74).  Returns nothing; timed by the caller."""
+    import torch
+    from oracle import ref_numpy as rn, ref_postprocess as rp, ref_torch as rt
+    rt.loss_and_grad(t, p, spec, rectified_active=w["rect"] >= 0, dtype=torch.float32)
+    dec = rn.decode(p, spec)
+    for i in range(p.shape[0]):
+        filt = rp.filter_boxes(dec[0][1][i], dec[0][2][i], dec[1][1][i], dec[1][2][i], dec[2][1][i], dec[2][2][i],
+                               w["score_thresh"])
+        rp.apply_nms(filt, w["nms_thresh"])
+
+
+def time_cpu_port(spec, p, t, w, budget_s):
+    """images/s of the oracle port on a bounded sample of the batch (about budget_s seconds of CPU work)."""
+    import torch
+    t0 = time.time()
+    cpu_port_step(spec, p[:1], t[:1], w)
+    one = max(time.time() - t0, 1e-3)
+    s = int(max(1, min(p.shape[0], budget_s / one)))
+    t0 = time.time()
+    cpu_port_step(spec, p[:s], t[:s], w)
+    dt = time.time() - t0
+    return s / dt, s, torch.get_num_threads()
+
+
+def run_reference(args, w, spec, rank, world):
+    if rank != 0:
+        return
+    import torch
+    p, t = synth(spec, w["batch"], w["m"], 0)
+    cpu_port_step(spec, p[:1], t[:1], w)                       # import / first-touch warm-up
+    t0 = time.time()
+    cpu_port_step(spec, p[:1], t[:1], w)
+    one = max(time.time() - t0, 1e-3)
+    total_steps = args.steps + args.warmup
+    s = int(max(1, min(w["batch"], (120.0 / total_steps) / one)))     # whole run within a few minutes
+    for _ in range(args.warmup):
+        cpu_port_step(spec, p[:s], t[:s], w)
+    t0 = time.time()
+    for _ in range(args.steps):
+        cpu_port_step(spec, p[:s], t[:s], w)
+    dt = time.time() - t0
+    value = s * args.steps / dt
+    cores = torch.get_num_threads()
+    sample = "%d of %d images per step, fp32 torch-CPU restatement of the TF graph + NumPy post-process" % (s, w["batch"])
+    print(json.dumps({
+        "impl": "reference", "metric": "head loss fwd+bwd + decode+filter+NMS throughput", "value": value,
+        "unit": "images/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "desc": w["desc"], "images_per_step": s},
+        "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "TensorFlow is not installable on this image (no network); the reference's TF loss/decoder "
+                "cannot run, so the timed CPU arm is the oracle port (oracle/ref_torch.py, ref_numpy.py, "
+                "ref_postprocess.py) on all host threads.",
+    }), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2_416_c80_b64", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    w = WORKLOADS[args.workload]
+    spec = build_spec(w)
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, w, spec, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    import yolov3_tensorflow_b200 as yv3
+    from helpers import product_loss_args
+
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU path in the product)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    yv3.backend.set_epsilon(spec.eps)
+    n, m = w["batch"], w["m"]
+    p_np, t_np = synth(spec, n, m, rank)
+    p_host = torch.from_numpy(p_np).pin_memory()
+    t_host = torch.from_numpy(t_np).pin_memory()
+    pd, td = p_host.to(dev), t_host.to(dev)
+    loss = yv3.YOLOv3Loss(rectified_coord_num=w["rect"], **product_loss_args(spec))
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    grad = torch.empty_like(pd)
+    cand = torch.empty((n, post.capacity, 8), dtype=torch.float32, device=dev)
+    counts = torch.empty((n, 3), dtype=torch.int32, device=dev)
+    keep = torch.empty((n, post.capacity), dtype=torch.uint8, device=dev)
+
+    def step(events=None):
+        total, _ = loss.loss_and_grad(td, pd, events=events, grad_out=grad)
+        post.filter(pd, w["score_thresh"], out=(cand, counts))
+        post.nms(cand, counts, w["nms_thresh"], out=keep)
+        return total
+
+    def fence():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # owned-label count for the algorithmic byte figure: R = sum of `owned` flags
+    table, _ = loss.assign(td, pd)
+    owned = int(table[..., 3].sum().item())
+    loss.check_status()
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    sampler.mark = "warmup"
+    for _ in range(args.warmup):
+        step()
+    fence()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    post_ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.mark = "timed"
+    start.record()
+    for k in range(args.steps):
+        step(ev[k])
+        post_ev[k].record()
+    stop.record()
+    fence()
+    sampler.mark = "after"
+    total_ms = start.elapsed_time(stop)
+    dense_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    post_ms = float(np.mean([ev[k][1].elapsed_time(post_ev[k]) for k in range(args.steps)]))
+    loss.check_status()
+    post.check_status()
+    cand_per_image = float(counts.sum().item()) / n
+    kept_per_image = float(sum(int(keep[i, :int(counts[i].sum())].sum()) for i in range(min(n, 8)))) / min(n, 8)
+
+    # ---- end to end through the public API with host buffers -------------------------------------------
+    out_host = torch.empty(20, dtype=torch.float32).pin_memory()
+    counts_host = torch.empty((n, 3), dtype=torch.int32).pin_memory()
+    keep_host = torch.empty((n, post.capacity), dtype=torch.uint8).pin_memory()
+
+    def e2e_step():
+        pdev = yv3.to_device(p_host)                     # pinned host -> device, every step
+        tdev = yv3.to_device(t_host)
+        total, _ = loss.loss_and_grad(tdev, pdev, grad_out=grad)
+        post.filter(pdev, w["score_thresh"], out=(cand, counts))
+        post.nms(cand, counts, w["nms_thresh"], out=keep)
+        out_host[:18].copy_(loss.loss_detail.reshape(-1), non_blocking=True)
+        out_host[18:19].copy_(total.reshape(1), non_blocking=True)
+        counts_host.copy_(counts, non_blocking=True)
+        keep_host.copy_(keep, non_blocking=True)
+        torch.cuda.current_stream().synchronize()        # the caller reads the loss and the detections
+        return float(out_host[18])
+
+    sampler.mark = "e2e"
+    for _ in range(3):
+        e2e_step()
+    fence()
+    e2e_steps = args.steps
+    s2, t2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s2.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    t2.record()
+    fence()
+    e2e_ms = s2.elapsed_time(t2)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    times = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(times[0]), float(times[1])
+
+    if rank == 0:
+        A, L, C = spec.anchors_per_image, spec.box_len, spec.class_num
+        alg_per_image = 4 * A * 5 + 4 * A * L + 4 * (owned / n) * C + 4 * m * 5
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        else:
+            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        achieved = alg_per_image * n / (dense_ms * 1e-3) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(args.workload, {}).get("loss_dense_kernel_dram_bytes_per_launch")
+        line = {
+            "metric": "head loss fwd+bwd + decode+filter+NMS throughput",
+            "value": world * n * args.steps / (total_ms * 1e-3), "unit": "images/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "desc": w["desc"], "per_gpu_batch": n, "global_batch": n * world,
+                       "label_slots": m, "score_thresh": w["score_thresh"], "nms_thresh": w["nms_thresh"],
+                       "parallelism": "batch-sharded dp%d, one 20-float NCCL all-reduce per step" % world,
+                       "l2": "inputs larger than L2: predicts %.0f MB + gradient %.0f MB per GPU vs 126 MB L2" % (
+                           pd.numel() * 4 / 1e6, grad.numel() * 4 / 1e6),
+                       "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image},
+            "stage_ms": {"loss_dense_kernel": dense_ms, "filter_plus_nms": post_ms,
+                         "assign_and_launch_gaps": total_ms / args.steps - dense_ms - post_ms},
+            "roofline": {"kernel": "loss_dense_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg_per_image * n, "avg_launch_ms": dense_ms,
+                         "dense_2x4AL_bytes_per_launch_for_context": 8 * A * L * n},
+            "e2e": {"value": world * n * e2e_steps / (e2e_ms * 1e-3), "unit": "images/s",
+                    "h2d_bytes_per_step": int(p_host.numel() * 4 + t_host.numel() * 4),
+                    "d2h_bytes_per_step": int(19 * 4 + counts_host.numel() * 4 + keep_host.numel()),
+                    "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
+            "gpu_launches": 6 * args.steps,
+            "clocks": sampler.summary(),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            v, s, cores = time_cpu_port(spec, p_np, t_np, w, args.cpu_budget)
+            line["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
+                                    "sample": "%d of %d images, one pass (oracle port: torch-CPU fp32 loss + autograd, "
+                                              "NumPy decode/filter, Python NMS as run.py runs it)" % (s, n)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

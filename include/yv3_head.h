@@ -111,11 +111,15 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
  *                      images / n_global).  [18] = their sum = this rank's share of the scalar
  *                      loss (:137).  [19] = 0.  Summing (all-reducing) the 20 floats over the
  *                      ranks of a batch-sharded job gives the global values.
+ *   phases             3 = the whole loss.  The path is two launches -- 1: the per-label assignment
+ *                      kernel (centre-cell IoU, ownership, owner-side terms; latency-bound, tiny),
+ *                      2: the fused dense sweep (HBM-bound) -- and a caller that wants to time them
+ *                      separately may issue them as two calls with the same arguments (1 then 2).
  *   grad_predicts      device, packed layout, n images; must be 16-byte aligned; may be NULL
  *                      (forward only).  Every element is written. */
 int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
                      int n_global, int rectified_active, float upstream, float* loss_out20,
-                     float* grad_predicts, void* workspace, size_t workspace_bytes, void* stream);
+                     float* grad_predicts, void* workspace, size_t workspace_bytes, int phases, void* stream);
 
 /* Deferred status of the last yv3_assign / yv3_loss_fwd_bwd that used `workspace`: synchronises the
  * stream and returns YV3_OK, YV3_ERR_GT_RANGE or YV3_ERR_NONFINITE (the errors TF would raise /

@@ -1,0 +1,319 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via the reference-shaped Python classes) against
+the CPU oracle on the same seeded inputs.
+
+Tolerances (north_star: 1e-5 relative in fp32; bit-exact assignment and NMS indices):
+  * decode            rtol 1e-5 on every decoded value; corner boxes are differences of decoded values, so
+                      their absolute tolerance is 1e-5 * (|centre| + |size|).
+  * labels            bit-exact (same fp32 multiplies/subtractions).
+  * assignment        bit-exact wherever the oracle's decision margin exceeds 1e-5 (kernel and oracle use
+                      different libm exp implementations, a couple of ulp apart); near-ties are counted.
+  * loss detail       rtol 1e-5 against the fp64 twin of the oracle (+ atol 1e-6 for terms that are 0).
+  * gradient          |g - g64| <= 1e-5 |g64| + 1e-6 max|g64|.  The absolute part covers entries that went
+                      through the reference's own (sigmoid + cell) - cell cancellation: the fp32
+                      oracle is equally far from fp64 there, which the test also checks.
+  * NMS               kept set identical to the oracle's greedy NMS on the very same candidate rows.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import CASES, expected_table, make_predicts, make_spec, make_targets, product_loss_args
+from oracle import nms_c, ref_numpy as rn, ref_postprocess as rp, ref_torch as rt
+
+pytestmark = pytest.mark.gpu
+
+SMALL = ["tiny_32_c2", "coco_64x96_c4", "coco_128_c3_focal_tiou", "shipped_384x480_c0", "single_160_c1_focal"]
+GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "postprocess_*.npz")))
+
+
+@pytest.fixture(scope="module")
+def yv3():
+    import yolov3_tensorflow_b200 as pkg
+    from yolov3_tensorflow_b200 import _lib
+    _lib.lib()          # fail loudly here if the CUDA library is missing
+    return pkg
+
+
+def _inputs(name, n, m, seed=11, **kw):
+    spec = make_spec(name)
+    p = make_predicts(spec, n, seed=seed)
+    t = make_targets(spec, n, m, seed=seed + 1, min_valid=0, pad_in_middle=True, **kw)
+    return spec, p, t
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_decode_matches_oracle(yv3, name):
+    spec, p, _ = _inputs(name, 3, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    dec = yv3.YOLOv3Decoder(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes).decode(torch.from_numpy(p).cuda())
+    ref = rn.decode(p, spec)
+    for h in range(3):
+        raw, d, b = (x.cpu().numpy() for x in dec[h])
+        assert np.array_equal(raw, ref[h][0])
+        np.testing.assert_allclose(d, ref[h][1], rtol=1e-5, atol=0)
+        scale = np.abs(ref[h][1][..., 0:2]) + np.abs(ref[h][1][..., 2:4])
+        assert np.all(np.abs(b - ref[h][2]) <= 1e-5 * np.concatenate([scale, scale], -1))
+
+
+def test_decode_numpy_in_numpy_out(yv3):
+    spec, p, _ = _inputs("coco_64x96_c4", 2, 4)
+    out = yv3.YOLOv3Decoder(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes).decode(p)
+    assert isinstance(out[0][1], np.ndarray) and out[2][2].shape == (2, 2, 3, 3, 4)
+
+
+@pytest.mark.parametrize("name", ["coco_64x96_c4", "shipped_384x480_c0"])
+def test_label_decode_bit_exact(yv3, name):
+    spec, _, t = _inputs(name, 4, 7)
+    lab = yv3.LabelDecoder(spec.head_grid_sizes).decode(torch.from_numpy(t).cuda())
+    ref = rn.label_decode(t, spec)
+    for h in range(3):
+        assert np.array_equal(lab[h][0].cpu().numpy(), ref[h][0])
+        assert np.array_equal(lab[h][1].cpu().numpy(), ref[h][1])
+
+
+def _assert_table(spec, table, iou, decisions, n, m, margin=1e-5):
+    et, ei = expected_table(decisions, n, m)
+    tb = table.cpu().numpy()
+    near = 0
+    for i in range(n):
+        d = decisions[i]
+        vidx = d["valid_index"]
+        pad = np.setdiff1d(np.arange(m), vidx)
+        assert np.array_equal(tb[i, pad], et[i, pad])                       # padding slots: exact
+        for k, j in enumerate(vidx):
+            for h in range(3):
+                assert tb[i, j, h, 0] == et[i, j, h, 0] and tb[i, j, h, 1] == et[i, j, h, 1]   # cell: exact
+                if d["heads"][h]["margin_best"][k] > margin:
+                    assert tb[i, j, h, 2] == et[i, j, h, 2]
+                else:
+                    near += 1
+                if d["margin_own"][k] > margin:
+                    assert tb[i, j, h, 3] == et[i, j, h, 3]
+                else:
+                    near += 1
+    np.testing.assert_allclose(iou.cpu().numpy(), ei, rtol=1e-5, atol=1e-6)
+    return near
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_assignment_bit_exact(yv3, name):
+    spec, p, t = _inputs(name, 4, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    loss = yv3.YOLOv3Loss(**product_loss_args(spec))
+    table, iou = loss.assign(torch.from_numpy(t).cuda(), torch.from_numpy(p).cuda())
+    loss.check_status()
+    _, _, decisions = rn.loss(t, p, spec)
+    near = _assert_table(spec, table, iou, decisions, 4, 8)
+    assert near <= 2, "too many near-tie decisions for a meaningful test"
+
+
+def test_assignment_tie_rules(yv3):
+    """T1 (lowest anchor among equal IoUs), T2 (>= both ways: every tied head owns), T3 (two labels on one
+    anchor), T5 (padding in the middle).  Identical logits for every anchor make exact ties certain."""
+    spec = make_spec("coco_64x96_c4")
+    yv3.backend.set_epsilon(spec.eps)
+    # anchors of a head identical => identical decoded boxes per cell => exact IoU ties between anchors
+    anchors = [[(0.2, 0.2)] * 3, [(0.4, 0.4)] * 3, [(0.8, 0.8)] * 3]
+    args = product_loss_args(spec)
+    args["anchor_boxes"] = anchors
+    loss = yv3.YOLOv3Loss(**args)
+    h32, w32 = spec.head_grid_sizes[2]
+    p = np.zeros((1, h32, w32, spec.ctot), np.float32)
+    t = np.full((1, 4, 5), -1.0, np.float32)
+    t[0, 0] = [0.51, 0.52, 0.01, 0.01, 1]      # far smaller than any prediction
+    t[0, 2] = [0.51, 0.52, 0.01, 0.01, 2]      # padding at slot 1, duplicate of slot 0 at slot 2
+    t[0, 3] = [2.0, 0.5, 0.1, 0.1, 0]          # outside the grid -> status error, rows -1
+    table, iou = loss.assign(torch.from_numpy(t.reshape(1, 20)).cuda(), torch.from_numpy(p).cuda())
+    tb = table.cpu().numpy()[0]
+    assert np.all(tb[1] == [-1, -1, -1, 0])
+    assert np.all(tb[[0, 2], :, 2] == 0)                      # T1: first anchor wins the tie
+    assert np.array_equal(tb[0], tb[2])                       # T3: both labels map to the same anchors
+    with pytest.raises(IndexError):
+        loss.check_status()
+    # T2: all three heads see IoU 0 for a label no prediction touches
+    t2 = np.full((1, 1, 5), -1.0, np.float32)
+    t2[0, 0] = [0.5, 0.5, 1e-30, 1e-30, 0]
+    p2 = np.full_like(p, -8.0)
+    p2[..., :] = -8.0
+    table2, iou2 = loss.assign(torch.from_numpy(t2.reshape(1, 5)).cuda(), torch.from_numpy(p2).cuda())
+    if float(iou2.abs().max()) == 0.0:
+        assert np.all(table2.cpu().numpy()[0, 0, :, 3] == 1)
+
+
+@pytest.mark.parametrize("rect", [False, True])
+@pytest.mark.parametrize("name", SMALL)
+def test_loss_and_gradient_match_oracle(yv3, name, rect):
+    spec, p, t = _inputs(name, 3, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    loss = yv3.YOLOv3Loss(rectified_coord_num=(0 if rect else -1), **product_loss_args(spec))
+    total, grad = loss.loss_and_grad(torch.from_numpy(t).cuda(), torch.from_numpy(p).cuda())
+    loss.check_status()
+    total64, detail64, grad64 = rt.loss_and_grad(t, p, spec, rectified_active=rect, dtype=torch.float64)
+    _, _, grad32 = rt.loss_and_grad(t, p, spec, rectified_active=rect, dtype=torch.float32)
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), detail64, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(total.item(), float(total64), rtol=1e-5)
+    g = grad.cpu().numpy()
+    gmax = np.abs(grad64).max()
+    assert np.all(np.abs(g - grad64) <= 1e-5 * np.abs(grad64) + 1e-6 * gmax)
+    assert np.array_equal(g == 0, grad64 == 0)                 # untouched entries are exactly 0.0
+    # the kernel is no further from fp64 than the fp32 oracle is (x4 slack)
+    assert np.abs(g - grad64).max() <= 4 * max(np.abs(grad32 - grad64).max(), 1e-7 * gmax)
+    # detail names of the reference (yolov3_loss.py:71-79)
+    np.testing.assert_allclose(loss.coord_loss_xy.cpu().numpy(), detail64[0], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(loss.rectified_coord_loss.cpu().numpy(), detail64[5], rtol=1e-5, atol=1e-6)
+
+
+def test_loss_autograd_and_forward_only(yv3):
+    spec, p, t = _inputs("coco_64x96_c4", 2, 6)
+    yv3.backend.set_epsilon(spec.eps)
+    loss = yv3.YOLOv3Loss(rectified_coord_num=-1, **product_loss_args(spec))
+    pd = torch.from_numpy(p).cuda().requires_grad_(True)
+    total = loss.loss(torch.from_numpy(t).cuda(), pd)
+    (3.0 * total).backward()
+    _, _, grad64 = rt.loss_and_grad(t, p, spec, dtype=torch.float64)
+    g = pd.grad.cpu().numpy()
+    assert np.all(np.abs(g - 3.0 * grad64) <= 1e-5 * np.abs(3.0 * grad64) + 3e-6 * np.abs(grad64).max())
+    fwd = loss.loss(torch.from_numpy(t).cuda(), torch.from_numpy(p).cuda())       # no grad: forward-only kernel
+    assert abs(fwd.item() - total.item()) <= 1e-6 * abs(total.item())
+
+
+def test_rectified_counter_semantics(yv3):
+    """tf.cond(current_num <= rectified_coord_num) read before update_add (yolov3_loss.py:125,152)."""
+    spec, p, t = _inputs("tiny_32_c2", 3, 4)
+    pd, td = torch.from_numpy(p).cuda(), torch.from_numpy(t).cuda()
+    loss = yv3.YOLOv3Loss(rectified_coord_num=3, **product_loss_args(spec))
+    seen = []
+    for _ in range(4):
+        loss.loss(td, pd)
+        seen.append((loss.current_num, float(loss.rectified_coord_loss.abs().sum()) > 0))
+    assert seen == [(3, True), (6, True), (6, False), (6, False)]
+    off = yv3.YOLOv3Loss(rectified_coord_num=-1, **product_loss_args(spec))
+    off.loss(td, pd)
+    assert off.current_num == 0 and float(off.rectified_coord_loss.abs().sum()) == 0
+    assert off.state_dict() == {"current_num": 0}
+
+
+def test_empty_images_and_duplicates(yv3):
+    spec = make_spec("coco_64x96_c4")
+    yv3.backend.set_epsilon(spec.eps)
+    p = make_predicts(spec, 3, seed=5)
+    t = make_targets(spec, 3, 6, seed=6, min_valid=2).reshape(3, 6, 5)
+    t[1] = -1.0                                 # V = 0: every anchor is background
+    t[2, 1] = t[2, 0]                           # duplicate label: counted twice (T3)
+    t[2, 2, 4] = spec.class_num + 2             # class id outside [0, C): zero one-hot row
+    t = t.reshape(3, 30)
+    loss = yv3.YOLOv3Loss(rectified_coord_num=-1, **product_loss_args(spec))
+    total, grad = loss.loss_and_grad(torch.from_numpy(t).cuda(), torch.from_numpy(p).cuda())
+    loss.check_status()
+    total64, detail64, grad64 = rt.loss_and_grad(t, p, spec, dtype=torch.float64)
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), detail64, rtol=1e-5, atol=1e-6)
+    g = grad.cpu().numpy()
+    assert np.all(np.abs(g - grad64) <= 1e-5 * np.abs(grad64) + 1e-6 * np.abs(grad64).max())
+
+
+def test_unaligned_label_rows_take_the_scalar_path(yv3):
+    """M not a multiple of 4 => label rows are not 16-B multiples => no bulk copy; results unchanged."""
+    spec, p, t = _inputs("coco_64x96_c4", 3, 5)
+    yv3.backend.set_epsilon(spec.eps)
+    loss = yv3.YOLOv3Loss(rectified_coord_num=-1, **product_loss_args(spec))
+    total, grad = loss.loss_and_grad(torch.from_numpy(t).cuda(), torch.from_numpy(p).cuda())
+    total64, detail64, grad64 = rt.loss_and_grad(t, p, spec, dtype=torch.float64)
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), detail64, rtol=1e-5, atol=1e-6)
+    assert np.all(np.abs(grad.cpu().numpy() - grad64) <= 1e-5 * np.abs(grad64) + 1e-6 * np.abs(grad64).max())
+
+
+# ---- post-process -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p)[12:-4] for p in GOLD])
+def test_postprocess_matches_reference_outputs(yv3, path):
+    """Bit-exact against outputs of the REFERENCE's own NumPy post-processor (tests/golden)."""
+    z = np.load(path)
+    args = []
+    for h in range(3):
+        args += [z["pred%d" % h], z["boxes%d" % h]]
+    filt = yv3.YOLOv3PostProcessor.filter_boxes(*args, float(z["score_thresh"]))
+    for h in range(3):
+        ref = z["filt%d" % h]
+        assert filt[h].shape == ref.shape and filt[h].dtype == ref.dtype
+        assert np.array_equal(filt[h], ref)
+    mask = yv3.YOLOv3PostProcessor.true_keep_mask([f.copy() for f in filt], float(z["nms_thresh"]))
+    assert np.array_equal(np.nonzero(mask)[0], np.sort(z["true_keep"]))
+    nms = yv3.YOLOv3PostProcessor.apply_nms([f.copy() for f in filt], float(z["nms_thresh"]))
+    for h in range(3):
+        assert np.array_equal(np.asarray(nms[h]).reshape(-1, 9), z["nms%d" % h])
+    true = yv3.YOLOv3PostProcessor.apply_nms([f.copy() for f in filt], float(z["nms_thresh"]), bug_compat=False)
+    assert sum(len(x) for x in true) == len(z["true_keep"])
+    h8, w8 = z["pred0"].shape[0:2]
+    res = yv3.YOLOv3PostProcessor.resize_boxes(nms, np.array([w8 * 8, h8 * 8] * 2))
+    for h in range(3):
+        assert np.array_equal(np.asarray(res[h]).reshape(-1, 9), z["resized%d" % h])
+
+
+@pytest.mark.parametrize("name", SMALL)
+@pytest.mark.parametrize("thr", [0.3, 0.001])
+def test_fused_filter_nms_from_packed_logits(yv3, name, thr):
+    spec, p, _ = _inputs(name, 3, 4)
+    yv3.backend.set_epsilon(spec.eps)
+    pd = torch.from_numpy(p).cuda()
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    res = post.run(pd, thr, 0.45)
+    post.check_status()
+    dec = yv3.YOLOv3Decoder(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes).decode(pd)
+    for i in range(3):
+        counts = res["counts"][i].cpu().numpy()
+        k = int(counts.sum())
+        rows = res["cand"][i, :k].cpu().numpy()
+        # (1) identical to filter_boxes on the materialised decode of the same logits
+        args = []
+        for h in range(3):
+            args += [dec[h][1][i], dec[h][2][i]]
+        filt = yv3.YOLOv3PostProcessor.filter_boxes(*args, thr)
+        assert [len(f) for f in filt] == counts.tolist()
+        if k:
+            assert np.array_equal(np.concatenate([f.reshape(-1, 8) for f in filt], 0).astype(np.float32), rows)
+        # (2) survivors identical to the oracle's greedy NMS on the same rows
+        keep = np.nonzero(res["keep"][i, :k].cpu().numpy())[0]
+        assert np.array_equal(keep, np.sort(nms_c.greedy_nms(rows.astype(np.float64), 0.45)))
+        # (3) run.py-shaped lists equal the oracle's apply_nms (quirk included) on the same rows
+        heads = np.split(rows.astype(np.float64 if spec.class_num else np.float32), np.cumsum(counts)[:-1])
+        heads = [h_ if len(h_) else np.empty((0, 8)) for h_ in heads]
+        ref_lists = rp.apply_nms([h_.copy() for h_ in heads], 0.45, bug_compat=True)
+        got_lists = post.to_reference(res, i)
+        for h in range(3):
+            assert np.array_equal(np.asarray(got_lists[h]).reshape(-1, 9), np.asarray(ref_lists[h]).reshape(-1, 9))
+
+
+def test_filter_rows_close_to_oracle_decode(yv3):
+    """From logits, rows agree with the NumPy oracle to fp32 noise and the kept counts are equal away from
+    the threshold."""
+    spec, p, _ = _inputs("coco_128_c3_focal_tiou", 2, 4)
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    res = post.run(torch.from_numpy(p).cuda(), 0.2, 0.45)
+    refd = rn.decode(p, spec)
+    for i in range(2):
+        filt = rp.filter_boxes(refd[0][1][i], refd[0][2][i], refd[1][1][i], refd[1][2][i], refd[2][1][i], refd[2][2][i], 0.2)
+        counts = res["counts"][i].cpu().numpy().tolist()
+        assert counts == [len(f) for f in filt]
+        rows = res["cand"][i, :sum(counts)].cpu().numpy()
+        ref_rows = np.concatenate([f.reshape(-1, 8) for f in filt], 0)
+        assert np.array_equal(rows[:, 6], ref_rows[:, 6])
+        np.testing.assert_allclose(rows, ref_rows, rtol=1e-5, atol=1e-6)
+
+
+def test_capacity_overflow_is_reported(yv3):
+    spec, p, _ = _inputs("coco_64x96_c4", 1, 4)
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes, capacity=16)
+    post.filter(torch.from_numpy(p).cuda(), 0.0001)
+    from yolov3_tensorflow_b200._lib import Yv3Error
+    with pytest.raises(Yv3Error):
+        post.check_status()
+
+
+def test_config_errors(yv3):
+    with pytest.raises(ValueError):
+        yv3.YOLOv3Loss([(5, 5), (2, 2), (1, 1)], 0, CASES["tiny_32_c2"][3], 0.5, [(1, 1, 1, 1, 1)] * 3)
+    with pytest.raises(ValueError):
+        yv3.YOLOv3Loss([(4, 4), (2, 2), (1, 1)], 0, CASES["tiny_32_c2"][3], 0.5, [(1, 1, 1, 1, 1)] * 3,
+                       rectified_loss_weight=[1, 1])

@@ -12,9 +12,10 @@ structures) over the C-ABI library ``lib/libyv3head.so`` (include/yv3_head.h):
     configs              the configs.py switches the path consumes
 """
 from . import backend  # noqa: F401
+from ._lib import to_device_f32 as to_device  # noqa: F401
 from .label_decoder import LabelDecoder  # noqa: F401
 from .yolov3_decoder import YOLOv3Decoder  # noqa: F401
 from .yolov3_loss import YOLOv3Loss  # noqa: F401
 from .yolov3_post_process import HeadPostProcessor, YOLOv3PostProcessor  # noqa: F401
 
-__all__ = ["YOLOv3Decoder", "LabelDecoder", "YOLOv3Loss", "YOLOv3PostProcessor", "HeadPostProcessor", "backend"]
+__all__ = ["YOLOv3Decoder", "LabelDecoder", "YOLOv3Loss", "YOLOv3PostProcessor", "HeadPostProcessor", "backend", "to_device"]

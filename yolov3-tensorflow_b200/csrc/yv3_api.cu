@@ -198,7 +198,7 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
 
 int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
                      int n_global, int rectified_active, float upstream, float* loss_out20,
-                     float* grad_predicts, void* workspace, size_t workspace_bytes, void* stream) {
+                     float* grad_predicts, void* workspace, size_t workspace_bytes, int phases, void* stream) {
     int rc = loss_common_checks(cfg, predicts, targets, n, m, workspace, workspace_bytes);
     if (rc != YV3_OK) return rc;
     if (!loss_out20) return YV3_ERR_NULL;
@@ -207,15 +207,18 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
     cudaStream_t st = (cudaStream_t)stream;
     const Geo g = make_geo(cfg);
     Workspace ws = carve_workspace(workspace, n, m);
-    if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
+    if ((phases & 3) == 0) return YV3_ERR_SHAPE;
     const float kappa = upstream / (float)n_global;
-
-    AssignArgs a;
-    a.predicts = predicts; a.targets = targets; a.n = n; a.m = m;
-    a.kappa = kappa;
-    a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
-    a.table = nullptr; a.iou_out = nullptr;
-    if (!cuda_ok(launch_assign(g, a, st), "launch_assign")) return YV3_ERR_CUDA;
+    if (phases & 1) {
+        if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
+        AssignArgs a;
+        a.predicts = predicts; a.targets = targets; a.n = n; a.m = m;
+        a.kappa = kappa;
+        a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
+        a.table = nullptr; a.iou_out = nullptr;
+        if (!cuda_ok(launch_assign(g, a, st), "launch_assign")) return YV3_ERR_CUDA;
+    }
+    if (!(phases & 2)) return YV3_OK;
 
     DenseArgs d;
     memset(&d, 0, sizeof(d));

@@ -103,7 +103,7 @@ class YOLOv3Loss(object):
             raise ValueError("targets must be (N, M*5) with the same N as predicts")
         return t, p
 
-    def _run(self, targets, predicts, want_grad, upstream=1.0):
+    def _run(self, targets, predicts, want_grad, upstream=1.0, events=None, grad_out=None):
         t, p = self._prepare(targets, predicts)
         n, m = p.shape[0], t.shape[1] // 5
         world = self._world()
@@ -111,12 +111,22 @@ class YOLOv3Loss(object):
         rect_active = self.current_num <= self.rectified_coord_num            # :125 (read before the add)
         ws = self._workspace(n, m, p.device)
         out = torch.empty(20, dtype=torch.float32, device=p.device)
-        grad = torch.empty_like(p) if want_grad else None
-        rc = self._lib.yv3_loss_fwd_bwd(ctypes.byref(self._cfg), _lib.ptr(p), _lib.ptr(t), n, m, n_global,
-                                        1 if rect_active else 0, float(upstream), _lib.ptr(out),
-                                        _lib.ptr(grad), _lib.ptr(ws), ws.numel(),
-                                        _lib.current_stream_ptr(p.device))
-        _lib.check(rc, "yv3_loss_fwd_bwd")
+        grad = None
+        if want_grad:
+            grad = torch.empty_like(p) if grad_out is None else grad_out
+            if grad.shape != p.shape or grad.dtype != torch.float32 or not grad.is_contiguous() or grad.device != p.device:
+                raise ValueError("grad_out must be a contiguous fp32 tensor shaped like predicts on the same device")
+        args = (ctypes.byref(self._cfg), _lib.ptr(p), _lib.ptr(t), n, m, n_global, 1 if rect_active else 0,
+                float(upstream), _lib.ptr(out), _lib.ptr(grad), _lib.ptr(ws), ws.numel())
+        stream = _lib.current_stream_ptr(p.device)
+        if events is None:
+            _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 3, stream), "yv3_loss_fwd_bwd")
+        else:
+            # (start, stop) torch.cuda.Event pair bracketing the dense sweep alone (bench.py's roofline)
+            _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 1, stream), "yv3_loss_fwd_bwd[assign]")
+            events[0].record()
+            _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 2, stream), "yv3_loss_fwd_bwd[dense]")
+            events[1].record()
         if rect_active:
             self.current_num += n_global                                       # update_add (:152)
         if world > 1:
@@ -139,9 +149,11 @@ class YOLOv3Loss(object):
 
     __call__ = loss
 
-    def loss_and_grad(self, targets, predicts, upstream=1.0):
-        """(total loss, d(upstream * loss)/d predicts in the packed layout) from one fused pass."""
-        return self._run(targets, predicts, want_grad=True, upstream=upstream)
+    def loss_and_grad(self, targets, predicts, upstream=1.0, events=None, grad_out=None):
+        """(total loss, d(upstream * loss)/d predicts in the packed layout) from one fused pass.
+        ``grad_out`` reuses a caller-owned gradient buffer; ``events`` = (start, stop) CUDA events recorded
+        around the dense sweep alone."""
+        return self._run(targets, predicts, want_grad=True, upstream=upstream, events=events, grad_out=grad_out)
 
     def assign(self, targets, predicts):
         """The integer decisions of the loss: (table (N,M,3,4) int32 [row, col, best_anchor, owned] per
