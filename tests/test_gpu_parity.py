@@ -75,9 +75,12 @@ def test_label_decode_bit_exact(yv3, name):
 
 
 def _assert_table(spec, table, iou, decisions, n, m, margin=1e-5):
+    """Every decision must equal the oracle's; a mismatch is tolerated only where the oracle's own margin
+    for that decision is below `margin` (a near-tie that a 1-ulp libm difference can flip).  Exact ties
+    (margin 0, e.g. all-zero IoUs) are decided by rules T1/T2 and must match.  Returns the mismatch count."""
     et, ei = expected_table(decisions, n, m)
     tb = table.cpu().numpy()
-    near = 0
+    flipped = 0
     for i in range(n):
         d = decisions[i]
         vidx = d["valid_index"]
@@ -86,16 +89,14 @@ def _assert_table(spec, table, iou, decisions, n, m, margin=1e-5):
         for k, j in enumerate(vidx):
             for h in range(3):
                 assert tb[i, j, h, 0] == et[i, j, h, 0] and tb[i, j, h, 1] == et[i, j, h, 1]   # cell: exact
-                if d["heads"][h]["margin_best"][k] > margin:
-                    assert tb[i, j, h, 2] == et[i, j, h, 2]
-                else:
-                    near += 1
-                if d["margin_own"][k] > margin:
-                    assert tb[i, j, h, 3] == et[i, j, h, 3]
-                else:
-                    near += 1
+                if tb[i, j, h, 2] != et[i, j, h, 2]:
+                    assert 0 < d["heads"][h]["margin_best"][k] <= margin
+                    flipped += 1
+                if tb[i, j, h, 3] != et[i, j, h, 3]:
+                    assert 0 < d["margin_own"][k] <= margin
+                    flipped += 1
     np.testing.assert_allclose(iou.cpu().numpy(), ei, rtol=1e-5, atol=1e-6)
-    return near
+    return flipped
 
 
 @pytest.mark.parametrize("name", SMALL)
@@ -106,8 +107,8 @@ def test_assignment_bit_exact(yv3, name):
     table, iou = loss.assign(torch.from_numpy(t).cuda(), torch.from_numpy(p).cuda())
     loss.check_status()
     _, _, decisions = rn.loss(t, p, spec)
-    near = _assert_table(spec, table, iou, decisions, 4, 8)
-    assert near <= 2, "too many near-tie decisions for a meaningful test"
+    flipped = _assert_table(spec, table, iou, decisions, 4, 8)
+    assert flipped == 0, "near-tie decisions flipped by libm differences: %d" % flipped
 
 
 def test_assignment_tie_rules(yv3):
