@@ -7,7 +7,7 @@
 //
 // Bound: HBM.  4*A*L bytes in, 4*A*(L+8) bytes out per image.  A CTA stages a tile of TR consecutive
 // records (a 16-B aligned span of the packed stream) in shared memory with one bulk (TMA) copy, decodes
-// it in place -- a thread per record for the box part, a warp per record for the softmax -- and streams
+// it in place -- one thread per record, box part and class softmax -- and streams
 // it to the three per-head tensors with coalesced stores.  Several CTAs are resident per SM, so the
 // load of one tile overlaps the arithmetic and stores of another.
 #include "tile_ops.cuh"
@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(kDecThreads) decode_kernel(const __grid_consta
 
     tile_load<kDecThreads>(tile, src, nfl, q.tma, &bar);
 
-    // ---- box part: one thread per record ---------------------------------------------------------
+    // ---- one thread per record: box part, then the class probabilities in place ---------------------
     for (int ri = tid; ri < nrec; ri += kDecThreads) {
         const long long grec = rec0 + ri;
         const int n_img = (int)(grec / g.rpi);
@@ -48,11 +48,10 @@ __global__ void __launch_bounds__(kDecThreads) decode_kernel(const __grid_consta
         r[0] = d.x; r[1] = d.y; r[2] = d.w; r[3] = d.h; r[4] = d.conf;
         if (a.raw4[p.h]) reinterpret_cast<float4*>(a.raw4[p.h])[rih] = make_float4(t0, t1, t2, t3);
         if (a.boxes[p.h]) reinterpret_cast<float4*>(a.boxes[p.h])[rih] = make_float4(d.x0, d.y0, d.x1, d.y1);
-    }
-    // ---- class part: one warp per record (decoder :189-191) ---------------------------------------
-    if (C > 0) {
-        for (int ri = warp; ri < nrec; ri += kDecThreads / 32) {
-            softmax_clip_inplace(tile + (size_t)ri * L + 5, C, lane, g.lo, g.hi);
+        if (C > 0) {
+            float* z = r + 5;
+            const ClassStats cs = class_stats(z, C);                     // decoder :189-190
+            for (int k = 0; k < C; ++k) z[k] = class_prob(z[k], cs, g.lo, g.hi);   // :190-191
         }
     }
     __syncthreads();

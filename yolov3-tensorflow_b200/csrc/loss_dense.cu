@@ -1,26 +1,27 @@
-// The fused, memory-bound pass of the head loss: decode + max-IoU + masks + noobj / rectified loss
-// terms + the complete gradient tensor, one sweep over the packed predicts.
+// The fused, memory-bound pass of the head loss: decode + max-IoU + masks + noobj / rectified / class
+// loss terms + the complete gradient tensor, one sweep over the packed predicts.
 //
 // Follows yolov3/yolov3_loss.py: the all-anchor part of _calc_iou :267-294, the masks of
 // _single_head_loss :328-332, the noobj term :335-338, the class term :361-364, the rectified term
 // :140-164, the batch mean :112 and the detail rows :115-138.  The backward is the closed form TF
 // autodiff yields for those operators; no gradient flows through IoU or masks.
 //
-// Shape of the kernel (B200):
-//  * the packed tensor is a flat array of records of L floats; a tile = TR consecutive records, whose
-//    byte offset is a multiple of 16, so the gradient of a tile is ONE contiguous, 16-B aligned span;
-//  * persistent CTAs (one per SM) walk tiles round-robin.  A thread owns one record of the tile (or
-//    RPT of them when L is small): it reads the record's 5 box/conf logits (20 B out of L*4 -- class
-//    logits of non-responsible anchors are never read, their gradient is identically 0), decodes,
-//    takes the max IoU over the image's labels held in shared memory, and writes 5 gradient values
-//    into a shared-memory image of the tile that is otherwise all zeros;
-//  * labels of the <= 2 images a tile touches are staged in shared memory by a 1-D bulk (TMA) copy;
-//  * the few records that own a label get their full gradient (box + softmax-CE) added by a warp;
-//  * the finished tile leaves with one cp.async.bulk shared->global (TMA) store; two tile images
-//    alternate so the store of tile i overlaps the arithmetic of tile i+1.  The zeros persist in
-//    shared memory: only the class channels a fix-up dirtied are re-zeroed before reuse;
+// Shape of the kernel (B200), v2 -- profiles/r01_v1_ncu_summary.md says why v1 (two 87 KB tile images per
+// SM pushed out by TMA, one 8-warp CTA per SM) was latency-bound:
+//  * the packed tensor is a flat array of records of L floats; a tile = TR (<= 256) consecutive records,
+//    whose byte offset is a multiple of 16, so the gradient of a tile is one 16-B aligned span;
+//  * a 256-thread CTA keeps only 20 B per record in shared memory (the five box/conf gradient values); the
+//    other L-5 floats of a record's gradient are zeros that are never staged: the span is written with
+//    128-bit streaming stores whose payload is composed on the fly (zero for the ~94 % of chunks that lie
+//    inside a record's class channels).  Small shared memory => several CTAs per SM => the 20-B logit
+//    gathers of one CTA overlap the arithmetic and the stores of the others;
+//  * a thread owns one record: it reads the record's 5 box/conf logits (class logits of non-responsible
+//    anchors are never read, their gradient is identically 0), decodes, takes the max IoU over the
+//    image's labels held in shared memory, accumulates the loss terms and leaves 5 gradient values;
+//  * the few records that own a label get the owner terms added in label order, and their softmax-CE
+//    class gradient written by a warp after the tile's zeros are out;
 //  * loss sums: registers -> warp shuffles -> one partial row per CTA -> the last CTA to finish adds
-//    the rows in index order (double) and writes the 18 detail values.  No float atomics anywhere.
+//    the rows in index order (double) and writes the 18 detail values + their sum.  No float atomics.
 #include "yv3_kernels.cuh"
 
 namespace yv3 {
@@ -29,113 +30,82 @@ constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kSlots = 2;             // images a tile may touch (TR <= records per image)
 
-
 struct DenseSmem {
-    float* stage[2];                  // [tr * L]
-    float* gt[kSlots];                // [3][m][5]  (x0, y0, x1, y1, area) compacted, label order
-    float* lab_raw[kSlots];           // [m*5] raw label row (bulk-copy landing zone)
+    float* gv;                        // [tr][5] gradient of t0..t4 per record of the tile
+    float* gt0;                       // slot 0: [3][m][5]  (x0, y0, x1, y1, area) of the valid labels
+    float* gt1;                       // slot 1
     int* gt_count;                    // [kSlots]
     int* list_rec;                    // [cap] tile-relative record of an owned entry
     int* list_idx;                    // [cap] index into own[]
     int* nlist;                       // [1]
-    int* dirty[2];                    // [cap] per stage buffer: records whose class channels are dirty
-    int* ndirty;                      // [2]
     unsigned char* objflag;           // [tr]
     float* red;                       // [kWarps][12]
-    uint64_t* bar;                    // [kSlots] mbarriers of the label copies
 };
 
-__host__ __device__ inline size_t dense_smem_bytes(int tr, int L, int m, bool with_stage) {
+__host__ __device__ inline size_t dense_smem_bytes(int tr, int m) {
     size_t b = 0;
-    if (with_stage) b += 2 * align_up((size_t)tr * L * 4, 128);
+    b += align_up((size_t)tr * 5 * 4, 16);
     b += kSlots * align_up((size_t)3 * m * 5 * 4, 16);
-    b += kSlots * align_up((size_t)m * 5 * 4, 16);
     b += 16;                                          // gt_count
-    size_t cap = (size_t)kSlots * 3 * m;
+    const size_t cap = (size_t)kSlots * 3 * m;
     b += 2 * align_up(cap * 4, 16);                   // list_rec, list_idx
     b += 16;                                          // nlist
-    b += 2 * align_up(cap * 4, 16);                   // dirty
-    b += 16;                                          // ndirty
     b += align_up((size_t)tr, 16);                    // objflag
     b += kWarps * 12 * 4;
-    b += 16 * kSlots;                                 // barriers
-    return b + 128;
+    return b + 16;
 }
 
-__device__ inline DenseSmem carve(unsigned char* base, int tr, int L, int m, bool with_stage) {
+__device__ __forceinline__ DenseSmem carve(unsigned char* base, int tr, int m) {
     DenseSmem s;
-    size_t o = (128 - ((size_t)smem_u32(base) & 127)) & 127;
-    auto take = [&](size_t bytes, size_t al) {
-        o = (o + al - 1) / al * al;
+    size_t o = (16 - ((size_t)smem_u32(base) & 15)) & 15;
+    auto take = [&](size_t bytes) {
         unsigned char* p = base + o;
-        o += bytes;
+        o += (bytes + 15) / 16 * 16;
         return p;
     };
-    size_t stage_b = with_stage ? (size_t)tr * L * 4 : 0;
-    s.stage[0] = (float*)take(stage_b, 128);
-    s.stage[1] = (float*)take(stage_b, 128);
-    for (int i = 0; i < kSlots; ++i) s.gt[i] = (float*)take((size_t)3 * m * 5 * 4, 16);
-    for (int i = 0; i < kSlots; ++i) s.lab_raw[i] = (float*)take((size_t)m * 5 * 4, 16);
-    s.gt_count = (int*)take(16, 16);
-    size_t cap = (size_t)kSlots * 3 * m;
-    s.list_rec = (int*)take(cap * 4, 16);
-    s.list_idx = (int*)take(cap * 4, 16);
-    s.nlist = (int*)take(16, 16);
-    s.dirty[0] = (int*)take(cap * 4, 16);
-    s.dirty[1] = (int*)take(cap * 4, 16);
-    s.ndirty = (int*)take(16, 16);
-    s.objflag = (unsigned char*)take((size_t)tr, 16);
-    s.red = (float*)take(kWarps * 12 * 4, 16);
-    s.bar = (uint64_t*)take(16 * kSlots, 16);
+    s.gv = (float*)take((size_t)tr * 5 * 4);
+    s.gt0 = (float*)take((size_t)3 * m * 5 * 4);
+    s.gt1 = (float*)take((size_t)3 * m * 5 * 4);
+    s.gt_count = (int*)take(16);
+    const size_t cap = (size_t)kSlots * 3 * m;
+    s.list_rec = (int*)take(cap * 4);
+    s.list_idx = (int*)take(cap * 4);
+    s.nlist = (int*)take(16);
+    s.objflag = (unsigned char*)take((size_t)tr);
+    s.red = (float*)take(kWarps * 12 * 4);
     return s;
 }
 
-template <int RPT>
-__global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_constant__ Geo g, const DenseArgs a) {
+__global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_constant__ Geo g, const DenseArgs a) {
     extern __shared__ unsigned char smem_raw[];
-    const bool with_stage = a.grad != nullptr;
-    const DenseSmem s = carve(smem_raw, a.tr, g.L, a.m, with_stage);
+    const bool with_grad = a.grad != nullptr;
+    const DenseSmem s = carve(smem_raw, a.tr, a.m);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int L = g.L, C = g.C, m = a.m, tr = a.tr;
     const int cap_entries = 3 * m;
 
-    // ---- one-time init: zero tile images, flags, lists; arm the label barriers -----------------
-    if (with_stage) {
-        float4* z = (float4*)s.stage[0];
-        const int n4 = (int)(((size_t)(s.stage[1] - s.stage[0]) * 4 + (size_t)tr * L * 4) / 16);
-        for (int i = tid; i < n4; i += kThreads) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
     for (int i = tid; i < tr; i += kThreads) s.objflag[i] = 0;
-    if (tid == 0) {
-        s.nlist[0] = 0; s.ndirty[0] = 0; s.ndirty[1] = 0;
-        s.gt_count[0] = 0; s.gt_count[1] = 0;
-        for (int i = 0; i < kSlots; ++i) mbar_init(&s.bar[i], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
+    if (tid == 0) s.nlist[0] = 0;
     __syncthreads();
 
     float acc_noobj[3] = {0.f, 0.f, 0.f}, acc_rect[3] = {0.f, 0.f, 0.f}, acc_cls[3] = {0.f, 0.f, 0.f};
     const float thr = g.iou_thresh;
     const float nf = (float)a.n_global;
+    const float one = 1.0f;
+    // chunk walk of the gradient span: a thread's chunk index advances by kThreads (= 4*kThreads floats)
+    const int step_q = (4 * kThreads) / L, step_r = (4 * kThreads) - step_q * L;
 
-    float cur[RPT][5];
-    auto load_tile = [&](int tile, float (&dst)[RPT][5]) {
+    float cur[5];
+    auto load_rec = [&](int tile, float (&dst)[5]) {
+        const long long grec = (long long)tile * tr + tid;
+        const bool ok = tile < a.num_tiles && tid < tr && grec < a.total_rec;
+        const float* p = a.predicts + (size_t)(ok ? grec : 0) * L;
 #pragma unroll
-        for (int r = 0; r < RPT; ++r) {
-            int ri = r * kThreads + tid;
-            long long grec = (long long)tile * tr + ri;
-            bool ok = tile < a.num_tiles && ri < tr && grec < a.total_rec;
-            const float* p = a.predicts + (size_t)(ok ? grec : 0) * L;
-#pragma unroll
-            for (int c = 0; c < 5; ++c) dst[r][c] = ok ? __ldg(p + c) : 0.f;
-        }
+        for (int c = 0; c < 5; ++c) dst[c] = ok ? __ldg(p + c) : 0.f;
     };
-    load_tile(blockIdx.x, cur);
+    load_rec(blockIdx.x, cur);
 
-    unsigned bar_phase = 0;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x, ++it) {
-        const int buf = it & 1;
+    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
         const long long rec0 = (long long)tile * tr;
         const int nrec = (int)min((long long)tr, a.total_rec - rec0);
         const int n_first = (int)(rec0 / g.rpi);
@@ -143,53 +113,28 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
         const int nslots = n_last - n_first + 1;          // 1 or 2
 
         // ---- tile setup ------------------------------------------------------------------------
-        // (1) labels of the touched images -> shared memory (bulk copy when rows are 16-B aligned)
-        if (a.tma_labels) {
-            if (tid == 0) {
-                fence_async_smem();       // earlier generic reads of lab_raw are ordered before the async writes
-                for (int sl = 0; sl < nslots; ++sl) {
-                    mbar_expect_tx(&s.bar[sl], (unsigned)(m * 20));
-                    bulk_g2s(s.lab_raw[sl], a.targets + (size_t)(n_first + sl) * m * 5, (unsigned)(m * 20), &s.bar[sl]);
-                }
-            }
-        } else {
-            for (int i = tid; i < nslots * m * 5; i += kThreads) {
-                int sl = i / (m * 5), k = i - sl * (m * 5);
-                s.lab_raw[sl][k] = __ldg(a.targets + (size_t)(n_first + sl) * m * 5 + k);
-            }
-        }
-        // (2) prefetch the next tile's logits while this one is processed
-        float nxt[RPT][5];
-        load_tile(tile + gridDim.x, nxt);
-        // (3) the stage buffer must have left for global memory (store of two tiles ago)
-        if (with_stage && tid == 0) bulk_wait_read<1>();
-        if (a.tma_labels) {
-            // each slot's barrier flips only in the tiles that use it: one phase bit per slot
-            for (int sl = 0; sl < nslots; ++sl) mbar_wait(&s.bar[sl], (bar_phase >> sl) & 1u);
-            bar_phase ^= (1u << nslots) - 1u;
-        }
-        __syncthreads();
-
-        // (4) warp sl compacts image slot sl's valid labels (order kept) into per-head boxes;
-        //     warp 2 collects the owned entries that fall into this tile (order kept)
+        // warp sl (< nslots): valid labels of image slot sl -> per-head boxes, order kept (:239-247);
+        // warp 2: the owned entries that fall into this tile, order kept
         if (warp < nslots) {
             const int sl = warp;
+            float* gts = sl == 0 ? s.gt0 : s.gt1;
+            const float* lab = a.targets + (size_t)(n_first + sl) * m * 5;
             int count = 0;
             for (int base = 0; base < m; base += 32) {
-                int j = base + lane;
+                const int j = base + lane;
                 float xn = -1.f, yn = 0.f, wn = 0.f, hn = 0.f;
                 if (j < m) {
-                    const float* t = s.lab_raw[sl] + j * 5;
-                    xn = t[0]; yn = t[1]; wn = t[2]; hn = t[3];
+                    const float* t = lab + j * 5;
+                    xn = __ldg(t); yn = __ldg(t + 1); wn = __ldg(t + 2); hn = __ldg(t + 3);
                 }
-                bool valid = (j < m) && (__fmul_rn(xn, g.fW[0]) >= 0.0f);
-                unsigned mask = __ballot_sync(0xffffffffu, valid);
-                int pos = count + __popc(mask & ((1u << lane) - 1u));
+                const bool valid = (j < m) && (__fmul_rn(xn, g.fW[0]) >= 0.0f);
+                const unsigned mask = __ballot_sync(0xffffffffu, valid);
+                const int pos = count + __popc(mask & ((1u << lane) - 1u));
                 if (valid) {
 #pragma unroll
                     for (int h = 0; h < 3; ++h) {
-                        GtDec T = decode_label(g, h, xn, yn, wn, hn);
-                        float* o = s.gt[sl] + ((size_t)h * m + pos) * 5;
+                        const GtDec T = decode_label(g, h, xn, yn, wn, hn);
+                        float* o = gts + ((size_t)h * m + pos) * 5;
                         o[0] = T.box.x0; o[1] = T.box.y0; o[2] = T.box.x1; o[3] = T.box.y1; o[4] = T.box.area;
                     }
                 }
@@ -202,13 +147,13 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
                 const int n_img = n_first + sl;
                 const long long img_rec0 = (long long)n_img * g.rpi;
                 for (int base = 0; base < cap_entries; base += 32) {
-                    int e = base + lane;
+                    const int e = base + lane;
                     int rec = -1;
                     if (e < cap_entries) rec = a.own[(size_t)n_img * cap_entries + e].rec;
-                    long long grec = img_rec0 + rec;
-                    bool in = rec >= 0 && grec >= rec0 && grec < rec0 + nrec;
-                    unsigned mask = __ballot_sync(0xffffffffu, in);
-                    int pos = count + __popc(mask & ((1u << lane) - 1u));
+                    const long long grec = img_rec0 + rec;
+                    const bool in = rec >= 0 && grec >= rec0 && grec < rec0 + nrec;
+                    const unsigned mask = __ballot_sync(0xffffffffu, in);
+                    const int pos = count + __popc(mask & ((1u << lane) - 1u));
                     if (in) {
                         s.list_rec[pos] = (int)(grec - rec0);
                         s.list_idx[pos] = n_img * cap_entries + e;
@@ -218,87 +163,123 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
                 }
             }
             if (lane == 0) s.nlist[0] = count;
-        } else if (warp >= 3 && with_stage && C > 0) {
-            // (5) re-zero the class channels the fix-ups of two tiles ago dirtied in this buffer
-            const int nd = s.ndirty[buf];
-            for (int d = warp - 3; d < nd; d += kWarps - 3) {
-                float* rp = s.stage[buf] + (size_t)s.dirty[buf][d] * L + 5;
-                for (int k = lane; k < C; k += 32) rp[k] = 0.f;
-            }
         }
-        __syncthreads();
-        if (tid == 0) s.ndirty[buf] = 0;
-
-        // ---- record phase ----------------------------------------------------------------------
-#pragma unroll
-        for (int r = 0; r < RPT; ++r) {
-            const int ri = r * kThreads + tid;
-            if (ri < nrec) {
-                const long long grec = rec0 + ri;
-                const int n_img = (int)(grec / g.rpi);
-                const int r_img = (int)(grec - (long long)n_img * g.rpi);
-                const RecLoc p = locate(g, r_img);
-                const BoxDec d = decode_box(g, p, cur[r][0], cur[r][1], cur[r][2], cur[r][3], cur[r][4]);
-                const float parea = __fmul_rn(d.w, d.h);                                   // :267
-                const int sl = n_img - n_first;
-                const int V = s.gt_count[sl];
-                const float* gt = s.gt[sl] + (size_t)p.h * m * 5;
-                float maxiou = -INFINITY;                                                  // reduce_max over V = 0
-                for (int j = 0; j < V; ++j) {
-                    GtBox t;
-                    t.x0 = gt[j * 5 + 0]; t.y0 = gt[j * 5 + 1]; t.x1 = gt[j * 5 + 2]; t.y1 = gt[j * 5 + 3];
-                    t.area = gt[j * 5 + 4];
-                    maxiou = fmaxf(maxiou, iou_ref(d.x0, d.y0, d.x1, d.y1, parea, t, g.tiou));   // :294
-                }
-                const float objf = s.objflag[ri] ? 1.0f : 0.0f;
-                const float bg = ((maxiou < thr) ? 1.0f : 0.0f) * (1.0f - objf);           // :331-332
-                const float pc = d.conf;
-                const float one = 1.0f;
-                float l = -logf(one - pc);                                                 // :335
-                float fprime;
-                if (g.focal) {
-                    float pg = powf(pc, g.gamma);
-                    fprime = pg / (one - pc) - g.gamma * powf(pc, g.gamma - one) * logf(one - pc);
-                    l = l * pg;                                                            // :337
-                } else {
-                    fprime = one / (one - pc);
-                }
-                const float contrib = l * bg;                                              // :338 (0 * inf = NaN kept)
-                const float sq = cur[r][0] * cur[r][0] + cur[r][1] * cur[r][1] + cur[r][2] * cur[r][2] +
-                                 cur[r][3] * cur[r][3];                                    // :153-155
-                if (p.h == 0) { acc_noobj[0] += contrib; acc_rect[0] += sq; }
-                else if (p.h == 1) { acc_noobj[1] += contrib; acc_rect[1] += sq; }
-                else { acc_noobj[2] += contrib; acc_rect[2] += sq; }
-                if (with_stage) {
-                    const float pass = (d.sc >= g.lo && d.sc <= g.hi) ? one : 0.f;
-                    const float g4 = a.kappa * bg * g.lw[p.h][2] * fprime * pass * d.sc * (one - d.sc);
-                    float* o = s.stage[buf] + (size_t)ri * L;
-                    if (a.rect_active) {
-                        const float rg = a.upstream * g.rw[p.h] * 2.0f;
-                        o[0] = rg * cur[r][0] / nf; o[1] = rg * cur[r][1] / nf;
-                        o[2] = rg * cur[r][2] / nf; o[3] = rg * cur[r][3] / nf;
-                    } else {
-                        o[0] = 0.f; o[1] = 0.f; o[2] = 0.f; o[3] = 0.f;
-                    }
-                    o[4] = g4;
-                }
-            }
-        }
-        __syncthreads();
-
-        // ---- fix-up: records that own a label (one warp per record, entries in label order) ----
+        // prefetch the next tile's logits while this one is processed
+        float nxt[5];
+        load_rec(tile + gridDim.x, nxt);
+        __syncthreads();                                                                   // (A)
         const int nl = (a.debug & 4) ? 0 : s.nlist[0];
-        for (int i = 0; i < nl; ++i) {
-            const int rt = s.list_rec[i];
-            if ((rt & (kWarps - 1)) != warp) continue;
-            const OwnEntry* e = a.own + s.list_idx[i];
-            const long long grec = rec0 + rt;
-            const int r_img = (int)(grec % g.rpi);
-            const int h = locate(g, r_img).h;
-            float* o = with_stage ? s.stage[buf] + (size_t)rt * L : nullptr;
-            if (with_stage && lane < 5) o[lane] += e->g[lane];
-            if (C > 0) {
+
+        // ---- record phase: thread = record ---------------------------------------------------------
+        if (tid < nrec) {
+            const long long grec = rec0 + tid;
+            const int n_img = (int)(grec / g.rpi);
+            const int r_img = (int)(grec - (long long)n_img * g.rpi);
+            const RecLoc p = locate(g, r_img);
+            const BoxDec d = decode_box(g, p, cur[0], cur[1], cur[2], cur[3], cur[4]);
+            const float parea = __fmul_rn(d.w, d.h);                                       // :267
+            const int sl = n_img - n_first;
+            const int V = s.gt_count[sl];
+            const float* gt = (sl == 0 ? s.gt0 : s.gt1) + (size_t)p.h * m * 5;
+            float maxiou = -INFINITY;                                                      // reduce_max over V = 0
+            for (int j = 0; j < V; ++j) {
+                GtBox t;
+                t.x0 = gt[j * 5 + 0]; t.y0 = gt[j * 5 + 1]; t.x1 = gt[j * 5 + 2]; t.y1 = gt[j * 5 + 3];
+                t.area = gt[j * 5 + 4];
+                maxiou = fmaxf(maxiou, iou_ref(d.x0, d.y0, d.x1, d.y1, parea, t, g.tiou));   // :294
+            }
+            const bool is_obj = s.objflag[tid] != 0;
+            const float bg = ((maxiou < thr) ? one : 0.0f) * (one - (is_obj ? one : 0.0f));   // :331-332
+            const float pc = d.conf;
+            float l = -logf(one - pc);                                                     // :335
+            float fprime;
+            if (g.focal) {
+                const float pg = powf(pc, g.gamma);
+                fprime = pg / (one - pc) - g.gamma * powf(pc, g.gamma - one) * logf(one - pc);
+                l = l * pg;                                                                // :337
+            } else {
+                fprime = one / (one - pc);
+            }
+            const float contrib = l * bg;                                                  // :338 (0 * inf = NaN kept)
+            const float sq = cur[0] * cur[0] + cur[1] * cur[1] + cur[2] * cur[2] + cur[3] * cur[3];   // :153-155
+            if (p.h == 0) { acc_noobj[0] += contrib; acc_rect[0] += sq; }
+            else if (p.h == 1) { acc_noobj[1] += contrib; acc_rect[1] += sq; }
+            else { acc_noobj[2] += contrib; acc_rect[2] += sq; }
+            if (with_grad) {
+                const float pass = (d.sc >= g.lo && d.sc <= g.hi) ? one : 0.f;
+                float gv[5];
+                if (a.rect_active) {
+                    const float rg = a.upstream * g.rw[p.h] * 2.0f;
+                    gv[0] = rg * cur[0] / nf; gv[1] = rg * cur[1] / nf;
+                    gv[2] = rg * cur[2] / nf; gv[3] = rg * cur[3] / nf;
+                } else {
+                    gv[0] = 0.f; gv[1] = 0.f; gv[2] = 0.f; gv[3] = 0.f;
+                }
+                gv[4] = a.kappa * bg * g.lw[p.h][2] * fprime * pass * d.sc * (one - d.sc);
+                if (is_obj) {
+                    // owner terms of every label assigned here, in label order (duplicates add, rule T3)
+                    for (int i = 0; i < nl; ++i) {
+                        if (s.list_rec[i] != tid) continue;
+                        const OwnEntry* e = a.own + s.list_idx[i];
+#pragma unroll
+                        for (int c = 0; c < 5; ++c) gv[c] += e->g[c];
+                    }
+                }
+                float* o = s.gv + tid * 5;
+#pragma unroll
+                for (int c = 0; c < 5; ++c) o[c] = gv[c];
+            }
+        }
+        __syncthreads();                                                                   // (B)
+        if (warp == 2) {
+            for (int i = lane; i < nl; i += 32) s.objflag[s.list_rec[i]] = 0;              // re-arm for the next tile
+        }
+
+        // ---- the tile's gradient span leaves as 128-bit streaming stores -----------------------------
+        if (with_grad && !(a.debug & 8)) {
+            const int nfl = nrec * L;
+            const int nchunks = nfl >> 2;
+            float4* gdst = reinterpret_cast<float4*>(a.grad + (size_t)rec0 * L);
+            int r = (4 * tid) / L;
+            int o = 4 * tid - r * L;
+            for (int c = tid; c < nchunks; c += kThreads) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (o < 5 || o + 3 >= L) {
+                    // the chunk touches the box/conf channels of record r and/or of record r + 1
+                    float e[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        int pos = o + k, rr = r;
+                        if (pos >= L) { pos -= L; ++rr; }
+                        e[k] = pos < 5 ? s.gv[rr * 5 + pos] : 0.f;
+                    }
+                    v = make_float4(e[0], e[1], e[2], e[3]);
+                }
+                __stcs(gdst + c, v);
+                r += step_q;
+                o += step_r;
+                if (o >= L) { o -= L; ++r; }
+            }
+            // only the very last tile of the tensor can end off a 16-byte boundary
+            const int tail = nfl & 3;
+            if (tid < tail) {
+                const int i = (nchunks << 2) + tid;
+                const int rr = i / L, pos = i - rr * L;
+                a.grad[(size_t)rec0 * L + i] = pos < 5 ? s.gv[rr * 5 + pos] : 0.f;
+            }
+        }
+
+        // ---- records that own a label: class term and its gradient (one warp per record) ------------
+        if (nl > 0 && C > 0) {
+            __syncthreads();                                                               // (D) zeros are out
+            for (int i = 0; i < nl; ++i) {
+                const int rt = s.list_rec[i];
+                if ((rt & (kWarps - 1)) != warp) continue;      // same record -> same warp, label order
+                const OwnEntry* e = a.own + s.list_idx[i];
                 const int cls = e->cls;
+                if (cls < 0 || cls >= C) continue;               // zero one-hot row: no loss, no gradient
+                const long long grec = rec0 + rt;
+                const int h = locate(g, (int)(grec % g.rpi)).h;
                 const float* z = a.predicts + (size_t)grec * L + 5;
                 float mx = -INFINITY;
                 for (int k = lane; k < C; k += 32) mx = fmaxf(mx, __ldg(z + k));
@@ -307,64 +288,32 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
                 for (int k = lane; k < C; k += 32) sum += expf(__ldg(z + k) - mx);
                 sum = warp_sum(sum);
                 const float inv = 1.0f / sum;
-                if (cls >= 0 && cls < C) {
-                    const float qc = expf(__ldg(z + cls) - mx) * inv;                       // softmax :190
-                    const float qcc = clip_ref(qc, g.lo, g.hi);                            // :191
-                    if (lane == 0) acc_cls[h] += -logf(qcc);                               // loss :363-364
-                    if (with_stage) {
-                        const float pass = (qc >= g.lo && qc <= g.hi) ? 1.0f : 0.f;
-                        const float coef = a.kappa * g.lw[h][4] * (-1.0f / qcc) * pass * qc;
-                        for (int k = lane; k < C; k += 32) {
-                            float qk = expf(__ldg(z + k) - mx) * inv;
-                            o[5 + k] += coef * ((k == cls ? 1.0f : 0.f) - qk);
-                        }
+                const float qc = expf(__ldg(z + cls) - mx) * inv;                          // softmax :190
+                const float qcc = clip_ref(qc, g.lo, g.hi);                                // :191
+                if (lane == 0) acc_cls[h] += -logf(qcc);                                   // loss :363-364
+                if (with_grad && !(a.debug & 8)) {
+                    const float pass = (qc >= g.lo && qc <= g.hi) ? 1.0f : 0.f;
+                    const float coef = a.kappa * g.lw[h][4] * (-1.0f / qcc) * pass * qc;
+                    float* go = a.grad + (size_t)grec * L + 5;
+                    for (int k = lane; k < C; k += 32) {
+                        const float qk = expf(__ldg(z + k) - mx) * inv;
+                        go[k] = __ldcg(go + k) + coef * ((k == cls ? 1.0f : 0.f) - qk);
                     }
                 }
-                if (with_stage && lane == 0) {
-                    int dpos = atomicAdd(&s.ndirty[buf], 1);
-                    s.dirty[buf][dpos] = rt;
-                }
+                __syncwarp();
             }
-            __syncwarp();
-        }
-        __syncthreads();
-        // reset the per-tile list state (warp 2 owns it)
-        if (warp == 2) {
-            for (int i = lane; i < nl; i += 32) s.objflag[s.list_rec[i]] = 0;
-        }
-
-        // ---- the tile leaves: one bulk shared->global store -------------------------------------
-        if (with_stage) {
-            fence_async_smem();
-            __syncthreads();
-            const size_t bytes = (size_t)nrec * L * 4;
-            const unsigned bulk = (unsigned)(bytes & ~(size_t)15);
-            float* gdst = a.grad + (size_t)rec0 * L;
-            if (a.debug & 8) {
-            } else if (a.debug & 2) {
-                for (int i = tid; i < (int)(bytes / 4); i += kThreads) gdst[i] = s.stage[buf][i];
-            } else {
-            if (tid == 0) {
-                if (bulk) bulk_s2g(gdst, s.stage[buf], bulk);
-                bulk_commit();
-            }
-            const int tail = (int)((bytes - bulk) / 4);          // only the very last tile can have one
-            if (tid < tail) gdst[bulk / 4 + tid] = s.stage[buf][bulk / 4 + tid];
-            }
+            __syncthreads();                                                               // (E) list is free again
         }
 #pragma unroll
-        for (int r = 0; r < RPT; ++r)
-#pragma unroll
-            for (int c = 0; c < 5; ++c) cur[r][c] = nxt[r][c];
+        for (int c = 0; c < 5; ++c) cur[c] = nxt[c];
     }
-    if (with_stage && tid == 0) bulk_wait_all<0>();
 
     // ---- reduction: thread -> warp -> CTA partial row -> last CTA --------------------------------
     float v[9] = {acc_noobj[0], acc_noobj[1], acc_noobj[2], acc_cls[0], acc_cls[1], acc_cls[2],
                   acc_rect[0], acc_rect[1], acc_rect[2]};
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
-        float w = warp_sum(v[k]);
+        const float w = warp_sum(v[k]);
         if (lane == 0) s.red[warp * 12 + k] = w;
     }
     __syncthreads();
@@ -377,7 +326,7 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
     __threadfence();
     __syncthreads();
     if (tid == 0) {
-        int ticket = atomicAdd(&a.status[1], 1);
+        const int ticket = atomicAdd(&a.status[1], 1);
         is_last = (ticket == (int)gridDim.x - 1);
     }
     __syncthreads();
@@ -413,41 +362,22 @@ __global__ void __launch_bounds__(kThreads, 1) loss_dense_kernel(const __grid_co
 }
 
 cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream) {
-    const bool with_stage = a.grad != nullptr;
-    // records per tile: as many as fit two tile images next to the label / list areas in the 227 KB
-    // of shared memory a CTA may own, at most 8 per thread
-    const size_t fixed = dense_smem_bytes(kThreads * 8, g.L, a.m, false);
-    const size_t limit = 232448 - 1024;
-    if (fixed + 64 * (size_t)g.L > limit) return cudaErrorInvalidValue;
-    const size_t budget = with_stage ? ((limit - fixed) / 2 - 128) : ((size_t)1 << 30);
-    long long tr = (long long)(budget / ((size_t)g.L * 4));
-    tr = min(tr, (long long)kThreads * 8);
-    tr = min(tr, (long long)g.rpi);
+    // a tile = one record per thread, never more than an image holds (a tile touches <= 2 images)
+    long long tr = min((long long)kThreads, (long long)g.rpi);
     tr &= ~3LL;
     if (tr < 4) return cudaErrorInvalidValue;
-    if (tr > kThreads) tr = tr / kThreads * kThreads;      // whole records-per-thread
     a.tr = (int)tr;
     a.num_tiles = (int)((a.total_rec + tr - 1) / tr);
-    const int rpt = (int)((tr + kThreads - 1) / kThreads);
-    const int grid = (int)min((long long)min(sm_count, kMaxGrid), (long long)a.num_tiles);
-    const size_t smem = dense_smem_bytes(a.tr, g.L, a.m, with_stage);
-    cudaError_t err = cudaSuccess;
-#define YV3_LAUNCH(R)                                                                                    \
-    do {                                                                                                 \
-        err = cudaFuncSetAttribute(loss_dense_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
-                                   (int)smem);                                                           \
-        if (err != cudaSuccess) return err;                                                              \
-        loss_dense_kernel<R><<<grid, kThreads, smem, stream>>>(g, a);                                    \
-    } while (0)
-    switch (rpt) {
-        case 1: YV3_LAUNCH(1); break;
-        case 2: YV3_LAUNCH(2); break;
-        case 3: YV3_LAUNCH(3); break;
-        case 4: YV3_LAUNCH(4); break;
-        case 5: case 6: case 7: case 8: YV3_LAUNCH(8); break;
-        default: return cudaErrorInvalidValue;
-    }
-#undef YV3_LAUNCH
+    const size_t smem = dense_smem_bytes(a.tr, a.m);
+    if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    cudaError_t err = cudaFuncSetAttribute(loss_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    int per_sm = 1;
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_dense_kernel, kThreads, smem);
+    if (err != cudaSuccess) return err;
+    if (per_sm < 1) per_sm = 1;
+    const int grid = (int)min((long long)min(sm_count * per_sm, kMaxGrid), (long long)a.num_tiles);
+    loss_dense_kernel<<<grid, kThreads, smem, stream>>>(g, a);
     return cudaGetLastError();
 }
 

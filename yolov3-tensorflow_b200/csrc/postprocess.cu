@@ -8,7 +8,7 @@
 //
 // Kernels:
 //   score_packed_kernel   one sweep over the packed logits (HBM-bound, 4*A*L bytes/image): tile in shared
-//                         memory by bulk copy, softmax per warp, (score, prob, class) per record written in
+//                         memory by bulk copy, one thread per record, (score, prob, class) written in
 //                         head-raster order (12 B/record).
 //   compact_kernel        one CTA per image: order-preserving compaction (block scan per head) of the
 //                         records that pass the threshold; survivors' boxes are re-decoded from 5 logits.
@@ -25,7 +25,7 @@
 
 namespace yv3 {
 
-constexpr int kScoreThreads = 256;
+constexpr int kScoreThreads = 128;
 
 // ---- (score, prob, class) of every record -----------------------------------------------------------
 __global__ void __launch_bounds__(kScoreThreads) score_packed_kernel(const __grid_constant__ Geo g,
@@ -36,40 +36,30 @@ __global__ void __launch_bounds__(kScoreThreads) score_packed_kernel(const __gri
     __shared__ uint64_t bar;
     const int L = g.L, C = g.C, tr = q.tr;
     float* tile = (float*)ssm;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     const long long rec0 = (long long)blockIdx.x * tr;
     const int nrec = (int)min((long long)tr, q.total_rec - rec0);
     tile_load<kScoreThreads>(tile, predicts + (size_t)rec0 * L, nrec * L, q.tma, &bar);
 
     const int off1 = g.head_rec[0], off2 = g.head_rec[0] + g.head_rec[1];
-    if (C > 0) {
-        for (int ri = warp; ri < nrec; ri += kScoreThreads / 32) {
-            float* r = tile + (size_t)ri * L;
-            softmax_clip_inplace(r + 5, C, lane, g.lo, g.hi);
-            __syncwarp();
+    // one thread per record: records are L floats apart in shared memory (bank-conflict free for odd L)
+    for (int ri = tid; ri < nrec; ri += kScoreThreads) {
+        const long long grec = rec0 + ri;
+        const int n_img = (int)(grec / g.rpi);
+        const RecLoc p = locate(g, (int)(grec - (long long)n_img * g.rpi));
+        const int rih = (p.y * g.W[p.h] + p.x) * g.B[p.h] + p.b;
+        const size_t o = (size_t)n_img * g.rpi + (p.h == 0 ? 0 : (p.h == 1 ? off1 : off2)) + rih;
+        const float* r = tile + (size_t)ri * L;
+        const float conf = clip_ref(sigmoid_ref(r[4]), g.lo, g.hi);
+        if (C > 0) {
+            const ClassStats cs = class_stats(r + 5, C);
             float best;
             int arg;
-            warp_max_argmax(r + 5, C, lane, best, arg);
-            if (lane == 0) {
-                const long long grec = rec0 + ri;
-                const int n_img = (int)(grec / g.rpi);
-                const RecLoc p = locate(g, (int)(grec - (long long)n_img * g.rpi));
-                const int rih = (p.y * g.W[p.h] + p.x) * g.B[p.h] + p.b;
-                const size_t o = (size_t)n_img * g.rpi + (p.h == 0 ? 0 : (p.h == 1 ? off1 : off2)) + rih;
-                const float conf = clip_ref(sigmoid_ref(r[4]), g.lo, g.hi);
-                score[o] = __fmul_rn(best, conf);                       // :59
-                prob[o] = best;
-                cls[o] = arg;
-            }
-        }
-    } else {
-        for (int ri = tid; ri < nrec; ri += kScoreThreads) {
-            const long long grec = rec0 + ri;
-            const int n_img = (int)(grec / g.rpi);
-            const RecLoc p = locate(g, (int)(grec - (long long)n_img * g.rpi));
-            const int rih = (p.y * g.W[p.h] + p.x) * g.B[p.h] + p.b;
-            const size_t o = (size_t)n_img * g.rpi + (p.h == 0 ? 0 : (p.h == 1 ? off1 : off2)) + rih;
-            const float conf = clip_ref(sigmoid_ref(tile[(size_t)ri * L + 4]), g.lo, g.hi);
+            class_best(r + 5, C, cs, g.lo, g.hi, best, arg);
+            score[o] = __fmul_rn(best, conf);                           // :59
+            prob[o] = best;
+            cls[o] = arg;
+        } else {
             score[o] = conf;                                            // :53-55 (prob 1, class 0)
             prob[o] = 1.0f;
             cls[o] = 0;
@@ -382,8 +372,9 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const unsigned long lo
 static TileLaunch score_tiles(const Geo& g, const float* predicts, int n) {
     TileLaunch q;
     q.total_rec = (long long)n * g.rpi;
-    long long tr = (long long)(65536 / ((size_t)g.L * 4));
+    long long tr = (long long)(45056 / ((size_t)g.L * 4));       // ~44 KB per CTA: five CTAs per SM
     tr = min(tr, (long long)kScoreThreads * 4);
+    if (tr > kScoreThreads) tr = tr / kScoreThreads * kScoreThreads;
     tr &= ~3LL;
     if (tr < 4) tr = 4;
     q.tr = (int)tr;

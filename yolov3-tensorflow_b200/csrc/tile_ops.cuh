@@ -36,24 +36,72 @@ __device__ __forceinline__ void tile_load(float* tile, const float* __restrict__
     __syncthreads();
 }
 
-// Class probabilities of one record, in place, by one warp: z -> clip(exp(z - max z) * (1 / sum))
-// (yolov3_decoder.py:189-191; tf.nn.softmax's CPU functor multiplies by the reciprocal of the sum).
-__device__ __forceinline__ void softmax_clip_inplace(float* z, int C, int lane, float lo, float hi) {
-    float mx = -INFINITY;
-    for (int k = lane; k < C; k += 32) mx = fmaxf(mx, z[k]);
-    mx = warp_max(mx);
-    float sum = 0.f;
-    for (int k = lane; k < C; k += 32) {
-        const float e = expf(__fsub_rn(z[k], mx));
-        z[k] = e;
-        sum += e;
+// ---- class probabilities of one record, by ONE THREAD reading its record from shared memory ---------
+// (yolov3_decoder.py:189-191).  tf.nn.softmax's CPU functor computes exp(z - max z) * (1 / sum); the sum
+// here runs over four interleaved partial sums, (s0 + s1) + (s2 + s3), the same in every kernel that
+// needs class probabilities so that the fused filter and the materialised decode agree bit for bit.
+// A record is L floats apart from its neighbour's, so for odd L (85) the 32 lanes of a warp hit 32
+// different banks.
+struct ClassStats {
+    float mx;       // max logit
+    float inv;      // 1 / sum exp(z - mx)
+    int arg;        // first index of the max logit
+    int near;       // logits within 2.4e-7 of the max (including it): > 1 means a rounding tie is possible
+};
+
+__device__ __forceinline__ ClassStats class_stats(const float* __restrict__ z, int C) {
+    ClassStats s;
+    float mx = z[0];
+    int arg = 0;
+    for (int k = 1; k < C; ++k) {
+        const float v = z[k];
+        if (v > mx) { mx = v; arg = k; }
     }
-    sum = warp_sum(sum);
-    const float inv = __fdiv_rn(1.0f, sum);
-    for (int k = lane; k < C; k += 32) z[k] = clip_ref(__fmul_rn(z[k], inv), lo, hi);
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int near = 0;
+    int k = 0;
+    for (; k + 4 <= C; k += 4) {
+        const float d0 = __fsub_rn(z[k], mx), d1 = __fsub_rn(z[k + 1], mx);
+        const float d2 = __fsub_rn(z[k + 2], mx), d3 = __fsub_rn(z[k + 3], mx);
+        near += (d0 >= -2.4e-7f) + (d1 >= -2.4e-7f) + (d2 >= -2.4e-7f) + (d3 >= -2.4e-7f);
+        s0 += expf(d0); s1 += expf(d1); s2 += expf(d2); s3 += expf(d3);
+    }
+    for (; k < C; ++k) {
+        const float d = __fsub_rn(z[k], mx);
+        near += (d >= -2.4e-7f);
+        const float e = expf(d);
+        const int m = k & 3;
+        if (m == 0) s0 += e; else if (m == 1) s1 += e; else if (m == 2) s2 += e; else s3 += e;
+    }
+    const float sum = __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
+    s.mx = mx;
+    s.inv = __fdiv_rn(1.0f, sum);
+    s.arg = arg;
+    s.near = near;
+    return s;
 }
 
-// max and FIRST arg-max of q[0..C) by one warp (np.max / np.argmax, yolov3_post_process.py:57-58)
+// clip(exp(z - mx) * inv): one class probability
+__device__ __forceinline__ float class_prob(float z, const ClassStats& s, float lo, float hi) {
+    return clip_ref(__fmul_rn(expf(__fsub_rn(z, s.mx)), s.inv), lo, hi);
+}
+
+// np.max / np.argmax over the clipped probabilities (yolov3_post_process.py:57-58) without materialising
+// them.  The max logit has exp(0) = 1 and multiplying by inv is monotone, so max prob = clip(1 * inv).
+// The arg-max is the FIRST index whose rounded probability equals that value: the first max logit, unless
+// a logit within rounding distance of the max sits at a lower index and rounds to the same probability.
+__device__ __forceinline__ void class_best(const float* __restrict__ z, int C, const ClassStats& s, float lo, float hi,
+                                           float& best, int& arg) {
+    best = clip_ref(s.inv, lo, hi);
+    arg = s.arg;
+    if (s.near > 1) {
+        for (int k = 0; k < s.arg; ++k) {
+            if (class_prob(z[k], s, lo, hi) == best) { arg = k; break; }
+        }
+    }
+}
+
+// max and FIRST arg-max of q[0..C) by one warp (np.max / np.argmax on materialised probabilities)
 __device__ __forceinline__ void warp_max_argmax(const float* q, int C, int lane, float& best, int& arg) {
     float v = -INFINITY;
     int a = 0x7fffffff;
