@@ -10,16 +10,18 @@
 // SM pushed out by TMA, one 8-warp CTA per SM) was latency-bound:
 //  * the packed tensor is a flat array of records of L floats; a tile = TR (<= 256) consecutive records,
 //    whose byte offset is a multiple of 16, so the gradient of a tile is one 16-B aligned span;
-//  * a 256-thread CTA keeps only 20 B per record in shared memory (the five box/conf gradient values); the
-//    other L-5 floats of a record's gradient are zeros that are never staged: the span is written with
-//    128-bit streaming stores whose payload is composed on the fly (zero for the ~94 % of chunks that lie
-//    inside a record's class channels).  Small shared memory => several CTAs per SM => the 20-B logit
-//    gathers of one CTA overlap the arithmetic and the stores of the others;
+//  * nothing of the gradient is staged: a tile's span is first covered with 128-bit streaming ZERO stores
+//    (fire-and-forget, issued before the arithmetic so they overlap it), and after the CTA barrier every
+//    thread overwrites the five box/conf floats of its own record with their values.  L-5 of a record's L
+//    gradient floats are zeros, so this is ~94 % of the bytes at ~3 instructions per 16 B;
 //  * a thread owns one record: it reads the record's 5 box/conf logits (class logits of non-responsible
 //    anchors are never read, their gradient is identically 0), decodes, takes the max IoU over the
-//    image's labels held in shared memory, accumulates the loss terms and leaves 5 gradient values;
-//  * the few records that own a label get the owner terms added in label order, and their softmax-CE
-//    class gradient written by a warp after the tile's zeros are out;
+//    image's labels held in shared memory, accumulates the loss terms and stores 5 gradient values;
+//  * shared memory holds only the decoded labels of the <= 2 images a tile touches and the list of owned
+//    entries falling into the tile, double-buffered by tile parity => ONE barrier per tile and several
+//    CTAs per SM, so the 20-B logit gathers of one CTA overlap the arithmetic and stores of the others;
+//  * the few records that own a label get the owner terms added in label order by their thread, and
+//    their softmax-CE class gradient added on top of the zeros by a warp;
 //  * loss sums: registers -> warp shuffles -> one partial row per CTA -> the last CTA to finish adds
 //    the rows in index order (double) and writes the 18 detail values + their sum.  No float atomics.
 #include "yv3_kernels.cuh"
@@ -30,32 +32,24 @@ constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kSlots = 2;             // images a tile may touch (TR <= records per image)
 
-struct DenseSmem {
-    float* gv;                        // [tr][5] gradient of t0..t4 per record of the tile
-    float* gt0;                       // slot 0: [3][m][5]  (x0, y0, x1, y1, area) of the valid labels
-    float* gt1;                       // slot 1
-    int* gt_count;                    // [kSlots]
+struct DenseBuf {                     // one per tile parity
+    float* gt[kSlots];                // [3][m][5]  (x0, y0, x1, y1, area) of the valid labels, label order
     int* list_rec;                    // [cap] tile-relative record of an owned entry
     int* list_idx;                    // [cap] index into own[]
-    int* nlist;                       // [1]
-    unsigned char* objflag;           // [tr]
+    int* meta;                        // [0..1] valid-label count per slot, [2] entries in the list
+};
+struct DenseSmem {
+    DenseBuf buf[2];
     float* red;                       // [kWarps][12]
 };
 
-__host__ __device__ inline size_t dense_smem_bytes(int tr, int m) {
-    size_t b = 0;
-    b += align_up((size_t)tr * 5 * 4, 16);
-    b += kSlots * align_up((size_t)3 * m * 5 * 4, 16);
-    b += 16;                                          // gt_count
+__host__ __device__ inline size_t dense_smem_bytes(int m) {
     const size_t cap = (size_t)kSlots * 3 * m;
-    b += 2 * align_up(cap * 4, 16);                   // list_rec, list_idx
-    b += 16;                                          // nlist
-    b += align_up((size_t)tr, 16);                    // objflag
-    b += kWarps * 12 * 4;
-    return b + 16;
+    size_t per = kSlots * align_up((size_t)3 * m * 5 * 4, 16) + 2 * align_up(cap * 4, 16) + 16;
+    return 2 * per + kWarps * 12 * 4 + 16;
 }
 
-__device__ __forceinline__ DenseSmem carve(unsigned char* base, int tr, int m) {
+__device__ __forceinline__ DenseSmem carve(unsigned char* base, int m) {
     DenseSmem s;
     size_t o = (16 - ((size_t)smem_u32(base) & 15)) & 15;
     auto take = [&](size_t bytes) {
@@ -63,37 +57,31 @@ __device__ __forceinline__ DenseSmem carve(unsigned char* base, int tr, int m) {
         o += (bytes + 15) / 16 * 16;
         return p;
     };
-    s.gv = (float*)take((size_t)tr * 5 * 4);
-    s.gt0 = (float*)take((size_t)3 * m * 5 * 4);
-    s.gt1 = (float*)take((size_t)3 * m * 5 * 4);
-    s.gt_count = (int*)take(16);
     const size_t cap = (size_t)kSlots * 3 * m;
-    s.list_rec = (int*)take(cap * 4);
-    s.list_idx = (int*)take(cap * 4);
-    s.nlist = (int*)take(16);
-    s.objflag = (unsigned char*)take((size_t)tr);
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+        s.buf[b].gt[0] = (float*)take((size_t)3 * m * 5 * 4);
+        s.buf[b].gt[1] = (float*)take((size_t)3 * m * 5 * 4);
+        s.buf[b].list_rec = (int*)take(cap * 4);
+        s.buf[b].list_idx = (int*)take(cap * 4);
+        s.buf[b].meta = (int*)take(16);
+    }
     s.red = (float*)take(kWarps * 12 * 4);
     return s;
 }
 
 __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_constant__ Geo g, const DenseArgs a) {
     extern __shared__ unsigned char smem_raw[];
-    const bool with_grad = a.grad != nullptr;
-    const DenseSmem s = carve(smem_raw, a.tr, a.m);
+    const bool with_grad = a.grad != nullptr && !(a.debug & 8);
+    const DenseSmem s = carve(smem_raw, a.m);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int L = g.L, C = g.C, m = a.m, tr = a.tr;
     const int cap_entries = 3 * m;
-
-    for (int i = tid; i < tr; i += kThreads) s.objflag[i] = 0;
-    if (tid == 0) s.nlist[0] = 0;
-    __syncthreads();
 
     float acc_noobj[3] = {0.f, 0.f, 0.f}, acc_rect[3] = {0.f, 0.f, 0.f}, acc_cls[3] = {0.f, 0.f, 0.f};
     const float thr = g.iou_thresh;
     const float nf = (float)a.n_global;
     const float one = 1.0f;
-    // chunk walk of the gradient span: a thread's chunk index advances by kThreads (= 4*kThreads floats)
-    const int step_q = (4 * kThreads) / L, step_r = (4 * kThreads) - step_q * L;
 
     float cur[5];
     auto load_rec = [&](int tile, float (&dst)[5]) {
@@ -105,19 +93,33 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
     };
     load_rec(blockIdx.x, cur);
 
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+    int parity = 0;
+    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x, parity ^= 1) {
+        const DenseBuf& B = s.buf[parity];
         const long long rec0 = (long long)tile * tr;
         const int nrec = (int)min((long long)tr, a.total_rec - rec0);
         const int n_first = (int)(rec0 / g.rpi);
         const int n_last = (int)((rec0 + nrec - 1) / g.rpi);
         const int nslots = n_last - n_first + 1;          // 1 or 2
+        const int nfl = nrec * L;
 
-        // ---- tile setup ------------------------------------------------------------------------
+        // ---- zeros first: the whole span, 16 B per store, nothing waits for them ----------------------
+        if (with_grad) {
+            float4* gdst = reinterpret_cast<float4*>(a.grad + (size_t)rec0 * L);
+            const int nchunks = nfl >> 2;
+            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+            for (int c = tid; c < nchunks; c += kThreads) __stcs(gdst + c, z4);
+            // only the very last tile of the tensor can end off a 16-byte boundary
+            if (tid < (nfl & 3)) a.grad[(size_t)rec0 * L + (nchunks << 2) + tid] = 0.f;
+        }
+
+        // ---- tile setup (into this parity's buffers) ---------------------------------------------------
         // warp sl (< nslots): valid labels of image slot sl -> per-head boxes, order kept (:239-247);
         // warp 2: the owned entries that fall into this tile, order kept
         if (warp < nslots) {
             const int sl = warp;
-            float* gts = sl == 0 ? s.gt0 : s.gt1;
+            float* gts = B.gt[sl];
             const float* lab = a.targets + (size_t)(n_first + sl) * m * 5;
             int count = 0;
             for (int base = 0; base < m; base += 32) {
@@ -140,35 +142,36 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                 }
                 count += __popc(mask);
             }
-            if (lane == 0) s.gt_count[sl] = count;
+            if (lane == 0) B.meta[sl] = count;
         } else if (warp == 2) {
             int count = 0;
-            for (int sl = 0; sl < nslots; ++sl) {
-                const int n_img = n_first + sl;
-                const long long img_rec0 = (long long)n_img * g.rpi;
-                for (int base = 0; base < cap_entries; base += 32) {
-                    const int e = base + lane;
-                    int rec = -1;
-                    if (e < cap_entries) rec = a.own[(size_t)n_img * cap_entries + e].rec;
-                    const long long grec = img_rec0 + rec;
-                    const bool in = rec >= 0 && grec >= rec0 && grec < rec0 + nrec;
-                    const unsigned mask = __ballot_sync(0xffffffffu, in);
-                    const int pos = count + __popc(mask & ((1u << lane) - 1u));
-                    if (in) {
-                        s.list_rec[pos] = (int)(grec - rec0);
-                        s.list_idx[pos] = n_img * cap_entries + e;
-                        s.objflag[(int)(grec - rec0)] = 1;
+            if (!(a.debug & 4)) {
+                for (int sl = 0; sl < nslots; ++sl) {
+                    const int n_img = n_first + sl;
+                    const long long img_rec0 = (long long)n_img * g.rpi;
+                    for (int base = 0; base < cap_entries; base += 32) {
+                        const int e = base + lane;
+                        int rec = -1;
+                        if (e < cap_entries) rec = a.own[(size_t)n_img * cap_entries + e].rec;
+                        const long long grec = img_rec0 + rec;
+                        const bool in = rec >= 0 && grec >= rec0 && grec < rec0 + nrec;
+                        const unsigned mask = __ballot_sync(0xffffffffu, in);
+                        const int pos = count + __popc(mask & ((1u << lane) - 1u));
+                        if (in) {
+                            B.list_rec[pos] = (int)(grec - rec0);
+                            B.list_idx[pos] = n_img * cap_entries + e;
+                        }
+                        count += __popc(mask);
                     }
-                    count += __popc(mask);
                 }
             }
-            if (lane == 0) s.nlist[0] = count;
+            if (lane == 0) B.meta[2] = count;
         }
         // prefetch the next tile's logits while this one is processed
         float nxt[5];
         load_rec(tile + gridDim.x, nxt);
-        __syncthreads();                                                                   // (A)
-        const int nl = (a.debug & 4) ? 0 : s.nlist[0];
+        __syncthreads();          // the tile's one barrier: buffers ready, zero stores ordered before value stores
+        const int nl = B.meta[2];
 
         // ---- record phase: thread = record ---------------------------------------------------------
         if (tid < nrec) {
@@ -179,8 +182,8 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
             const BoxDec d = decode_box(g, p, cur[0], cur[1], cur[2], cur[3], cur[4]);
             const float parea = __fmul_rn(d.w, d.h);                                       // :267
             const int sl = n_img - n_first;
-            const int V = s.gt_count[sl];
-            const float* gt = (sl == 0 ? s.gt0 : s.gt1) + (size_t)p.h * m * 5;
+            const int V = B.meta[sl];
+            const float* gt = B.gt[sl] + (size_t)p.h * m * 5;
             float maxiou = -INFINITY;                                                      // reduce_max over V = 0
             for (int j = 0; j < V; ++j) {
                 GtBox t;
@@ -188,7 +191,8 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                 t.area = gt[j * 5 + 4];
                 maxiou = fmaxf(maxiou, iou_ref(d.x0, d.y0, d.x1, d.y1, parea, t, g.tiou));   // :294
             }
-            const bool is_obj = s.objflag[tid] != 0;
+            bool is_obj = false;                                                           // :328 scatter of owned anchors
+            for (int i = 0; i < nl; ++i) is_obj |= (B.list_rec[i] == tid);
             const float bg = ((maxiou < thr) ? one : 0.0f) * (one - (is_obj ? one : 0.0f));   // :331-332
             const float pc = d.conf;
             float l = -logf(one - pc);                                                     // :335
@@ -219,63 +223,27 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                 if (is_obj) {
                     // owner terms of every label assigned here, in label order (duplicates add, rule T3)
                     for (int i = 0; i < nl; ++i) {
-                        if (s.list_rec[i] != tid) continue;
-                        const OwnEntry* e = a.own + s.list_idx[i];
+                        if (B.list_rec[i] != tid) continue;
+                        const OwnEntry* e = a.own + B.list_idx[i];
 #pragma unroll
                         for (int c = 0; c < 5; ++c) gv[c] += e->g[c];
                     }
                 }
-                float* o = s.gv + tid * 5;
+                float* o = a.grad + (size_t)grec * L;
+                if (a.rect_active || is_obj) {
 #pragma unroll
-                for (int c = 0; c < 5; ++c) o[c] = gv[c];
-            }
-        }
-        __syncthreads();                                                                   // (B)
-        if (warp == 2) {
-            for (int i = lane; i < nl; i += 32) s.objflag[s.list_rec[i]] = 0;              // re-arm for the next tile
-        }
-
-        // ---- the tile's gradient span leaves as 128-bit streaming stores -----------------------------
-        if (with_grad && !(a.debug & 8)) {
-            const int nfl = nrec * L;
-            const int nchunks = nfl >> 2;
-            float4* gdst = reinterpret_cast<float4*>(a.grad + (size_t)rec0 * L);
-            int r = (4 * tid) / L;
-            int o = 4 * tid - r * L;
-            for (int c = tid; c < nchunks; c += kThreads) {
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (o < 5 || o + 3 >= L) {
-                    // the chunk touches the box/conf channels of record r and/or of record r + 1
-                    float e[4];
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        int pos = o + k, rr = r;
-                        if (pos >= L) { pos -= L; ++rr; }
-                        e[k] = pos < 5 ? s.gv[rr * 5 + pos] : 0.f;
-                    }
-                    v = make_float4(e[0], e[1], e[2], e[3]);
+                    for (int c = 0; c < 4; ++c) o[c] = gv[c];
                 }
-                __stcs(gdst + c, v);
-                r += step_q;
-                o += step_r;
-                if (o >= L) { o -= L; ++r; }
-            }
-            // only the very last tile of the tensor can end off a 16-byte boundary
-            const int tail = nfl & 3;
-            if (tid < tail) {
-                const int i = (nchunks << 2) + tid;
-                const int rr = i / L, pos = i - rr * L;
-                a.grad[(size_t)rec0 * L + i] = pos < 5 ? s.gv[rr * 5 + pos] : 0.f;
+                o[4] = gv[4];
             }
         }
 
         // ---- records that own a label: class term and its gradient (one warp per record) ------------
         if (nl > 0 && C > 0) {
-            __syncthreads();                                                               // (D) zeros are out
             for (int i = 0; i < nl; ++i) {
-                const int rt = s.list_rec[i];
+                const int rt = B.list_rec[i];
                 if ((rt & (kWarps - 1)) != warp) continue;      // same record -> same warp, label order
-                const OwnEntry* e = a.own + s.list_idx[i];
+                const OwnEntry* e = a.own + B.list_idx[i];
                 const int cls = e->cls;
                 if (cls < 0 || cls >= C) continue;               // zero one-hot row: no loss, no gradient
                 const long long grec = rec0 + rt;
@@ -291,10 +259,12 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                 const float qc = expf(__ldg(z + cls) - mx) * inv;                          // softmax :190
                 const float qcc = clip_ref(qc, g.lo, g.hi);                                // :191
                 if (lane == 0) acc_cls[h] += -logf(qcc);                                   // loss :363-364
-                if (with_grad && !(a.debug & 8)) {
+                if (with_grad) {
                     const float pass = (qc >= g.lo && qc <= g.hi) ? 1.0f : 0.f;
                     const float coef = a.kappa * g.lw[h][4] * (-1.0f / qcc) * pass * qc;
                     float* go = a.grad + (size_t)grec * L + 5;
+                    // on top of the zeros (ordered by the tile barrier); a second label on the same record
+                    // is handled by the same lanes of the same warp, later in this loop
                     for (int k = lane; k < C; k += 32) {
                         const float qk = expf(__ldg(z + k) - mx) * inv;
                         go[k] = __ldcg(go + k) + coef * ((k == cls ? 1.0f : 0.f) - qk);
@@ -302,7 +272,6 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                 }
                 __syncwarp();
             }
-            __syncthreads();                                                               // (E) list is free again
         }
 #pragma unroll
         for (int c = 0; c < 5; ++c) cur[c] = nxt[c];
@@ -368,7 +337,7 @@ cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStrea
     if (tr < 4) return cudaErrorInvalidValue;
     a.tr = (int)tr;
     a.num_tiles = (int)((a.total_rec + tr - 1) / tr);
-    const size_t smem = dense_smem_bytes(a.tr, a.m);
+    const size_t smem = dense_smem_bytes(a.m);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     cudaError_t err = cudaFuncSetAttribute(loss_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
