@@ -18,6 +18,9 @@ CASES = {
                                dict(iou_thresh=0.6, is_focal_loss=True, focal_alpha=0.7, focal_gamma=2.0,
                                     is_tiou_recall=True)),
     "tiny_32_c2": (32, 32, 2, SHIPPED_ANCHORS, dict(iou_thresh=0.3)),
+    # record lengths >= 12 floats take the whole-sector gradient path of the dense pass: even and odd L
+    "coco_96x64_c13": (96, 64, 13, coco_anchors(), dict(iou_thresh=0.5)),
+    "coco_64_c20": (64, 64, 20, coco_anchors(), dict(iou_thresh=0.4)),
     "coco_416_c80": (416, 416, 80, coco_anchors(), dict(iou_thresh=0.8)),
     "single_512_c0_focal": (512, 512, 0, three_anchor_shipped(),
                             dict(iou_thresh=0.8, is_focal_loss=True, focal_alpha=1.0, focal_gamma=2.0,

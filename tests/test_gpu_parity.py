@@ -25,7 +25,8 @@ from oracle import nms_c, ref_numpy as rn, ref_postprocess as rp, ref_torch as r
 
 pytestmark = pytest.mark.gpu
 
-SMALL = ["tiny_32_c2", "coco_64x96_c4", "coco_128_c3_focal_tiou", "shipped_384x480_c0", "single_160_c1_focal"]
+SMALL = ["tiny_32_c2", "coco_64x96_c4", "coco_128_c3_focal_tiou", "shipped_384x480_c0", "single_160_c1_focal",
+         "coco_96x64_c13", "coco_64_c20"]
 GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "postprocess_*.npz")))
 
 
@@ -215,15 +216,54 @@ def test_empty_images_and_duplicates(yv3):
     assert np.all(np.abs(g - grad64) <= 1e-5 * np.abs(grad64) + 1e-6 * np.abs(grad64).max())
 
 
-def test_unaligned_label_rows_take_the_scalar_path(yv3):
-    """M not a multiple of 4 => label rows are not 16-B multiples => no bulk copy; results unchanged."""
-    spec, p, t = _inputs("coco_64x96_c4", 3, 5)
+@pytest.mark.parametrize("name", ["coco_64x96_c4", "coco_64_c20"])
+def test_unaligned_tensors_take_the_scalar_path(yv3, name):
+    """predicts starting 4 bytes off a 16-byte boundary (a view into a larger buffer) and M not a multiple of 4:
+    the dense pass falls back to scalar loads/stores; results unchanged."""
+    spec, p, t = _inputs(name, 3, 5)
     yv3.backend.set_epsilon(spec.eps)
     loss = yv3.YOLOv3Loss(rectified_coord_num=-1, **product_loss_args(spec))
-    total, grad = loss.loss_and_grad(torch.from_numpy(t).cuda(), torch.from_numpy(p).cuda())
+    buf = torch.empty(p.size + 1, dtype=torch.float32, device="cuda")
+    pd = buf[1:].view(p.shape)
+    pd.copy_(torch.from_numpy(p))
+    assert pd.data_ptr() % 16 == 4
+    total, grad = loss.loss_and_grad(torch.from_numpy(t).cuda(), pd)
+    loss.check_status()
     total64, detail64, grad64 = rt.loss_and_grad(t, p, spec, dtype=torch.float64)
     np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), detail64, rtol=1e-5, atol=1e-6)
-    assert np.all(np.abs(grad.cpu().numpy() - grad64) <= 1e-5 * np.abs(grad64) + 1e-6 * np.abs(grad64).max())
+    g = grad.cpu().numpy()
+    assert np.all(np.abs(g - grad64) <= 1e-5 * np.abs(grad64) + 1e-6 * np.abs(grad64).max())
+    assert np.array_equal(g == 0, grad64 == 0)
+
+
+@pytest.mark.parametrize("rect", [False, True])
+def test_loss_at_the_benchmark_shape(yv3, rect):
+    """416x416, 80 classes (L = 85): the whole-sector gradient path at the shape bench.py times; duplicate
+    labels on one anchor and an empty image included."""
+    spec, p, t = _inputs("coco_416_c80", 3, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    t = t.reshape(3, 8, 5)
+    t[1] = -1.0
+    t[2, 1] = t[2, 0]
+    t = t.reshape(3, 40)
+    loss = yv3.YOLOv3Loss(rectified_coord_num=(0 if rect else -1), **product_loss_args(spec))
+    total, grad = loss.loss_and_grad(torch.from_numpy(t).cuda(), torch.from_numpy(p).cuda())
+    loss.check_status()
+    total64, detail64, grad64 = rt.loss_and_grad(t, p, spec, rectified_active=rect, dtype=torch.float64)
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), detail64, rtol=1e-5, atol=1e-6)
+    _, _, grad32 = rt.loss_and_grad(t, p, spec, rectified_active=rect, dtype=torch.float32)
+    g = grad.cpu().numpy()
+    gmax = np.abs(grad64).max()
+    # (s + c) - c at c up to 51 quantises the xy term to ulp(51) = 3.8e-6 (SURVEY F8): the fp32 reference itself
+    # is that far from fp64, so the element-wise bound carries 3e-6 * gmax and the kernel must be no further
+    # from fp64 than the fp32 oracle is (x4 slack)
+    assert np.all(np.abs(g - grad64) <= 1e-5 * np.abs(grad64) + 3e-6 * gmax)
+    assert np.abs(g - grad64).max() <= 4 * max(np.abs(grad32 - grad64).max(), 1e-7 * gmax)
+    assert np.array_equal(g == 0, grad64 == 0)
+    # repeated launches reuse the workspace counters (ticket, chunk counter): same bits every time
+    total2, grad2 = loss.loss_and_grad(torch.from_numpy(t).cuda(), torch.from_numpy(p).cuda())
+    if not rect:
+        assert torch.equal(grad, grad2) and total.item() == total2.item()
 
 
 # ---- post-process -------------------------------------------------------------------------------------

@@ -18,6 +18,7 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
     const int m = a.m;
     float* rho_s = sm;                 // [3][m]
     float* term_s = sm + 3 * m;        // [3 terms][3][m]
+    int* valid_s = (int*)(sm + 12 * m); // [m]
     const int n = blockIdx.x;
     const int tid = threadIdx.x;
     const bool active = tid < 3 * m;
@@ -55,7 +56,25 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
         }
     }
     if (active) rho_s[h * m + j] = inside ? rho : 0.0f;
+    if (active && h == 0) valid_s[j] = valid ? 1 : 0;
     __syncthreads();
+
+    // the image's valid labels in this head's grid units, label order kept (:239-247): the list every anchor of
+    // the image is compared with in the dense pass (:267-294)
+    if (active) {
+        int pos = 0, total = 0;
+        for (int q = 0; q < m; ++q) {
+            const int v = valid_s[q];
+            pos += (q < j) ? v : 0;
+            total += v;
+        }
+        if (valid) {
+            float4* o = reinterpret_cast<float4*>(a.gtab + (((size_t)n * 3 + h) * m + pos) * kGtFloats);
+            o[0] = make_float4(T.box.x0, T.box.y0, T.box.x1, T.box.y1);
+            o[1] = make_float4(T.box.area, 0.f, 0.f, 0.f);
+        }
+        if (tid == 0) a.vcount[n] = total;
+    }
 
     bool owned = false;
     if (inside) {
@@ -70,6 +89,10 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
     for (int c = 0; c < 5; ++c) e.g[c] = 0.f;
     if (owned) {
         e.rec = record_of(g, h, row, col, best);
+        {
+            const long long grec = (long long)n * g.rpi + e.rec;                 // object mask bit (:328)
+            atomicOr(a.objbits + (grec >> 5), 1u << (unsigned)(grec & 31));
+        }
         e.cls = (int)cf;                                                 // tf.cast(., int32) truncates (:362)
         const float one = 1.0f;
         float sc = __fsub_rn(2.0f, __fdiv_rn(__fmul_rn(T.tw, T.th), g.fHW[h]));          // :350
@@ -127,7 +150,7 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
 
 cudaError_t launch_assign(const Geo& g, const AssignArgs& a, cudaStream_t stream) {
     int threads = ((3 * a.m + 31) / 32) * 32;
-    size_t smem = sizeof(float) * 12 * (size_t)a.m;
+    size_t smem = sizeof(float) * 13 * (size_t)a.m;
     assign_kernel<<<a.n, threads, smem, stream>>>(g, a);
     return cudaGetLastError();
 }

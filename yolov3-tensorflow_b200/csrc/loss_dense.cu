@@ -6,194 +6,312 @@
 // :140-164, the batch mean :112 and the detail rows :115-138.  The backward is the closed form TF
 // autodiff yields for those operators; no gradient flows through IoU or masks.
 //
-// Shape of the kernel (B200), v2 -- profiles/r01_v1_ncu_summary.md says why v1 (two 87 KB tile images per
-// SM pushed out by TMA, one 8-warp CTA per SM) was latency-bound:
-//  * the packed tensor is a flat array of records of L floats; a tile = TR (<= 256) consecutive records,
-//    whose byte offset is a multiple of 16, so the gradient of a tile is one 16-B aligned span;
-//  * nothing of the gradient is staged: a tile's span is first covered with 128-bit streaming ZERO stores
-//    (fire-and-forget, issued before the arithmetic so they overlap it), and after the CTA barrier every
-//    thread overwrites the five box/conf floats of its own record with their values.  L-5 of a record's L
-//    gradient floats are zeros, so this is ~94 % of the bytes at ~3 instructions per 16 B;
-//  * a thread owns one record: it reads the record's 5 box/conf logits (class logits of non-responsible
-//    anchors are never read, their gradient is identically 0), decodes, takes the max IoU over the
-//    image's labels held in shared memory, accumulates the loss terms and stores 5 gradient values;
-//  * shared memory holds only the decoded labels of the <= 2 images a tile touches and the list of owned
-//    entries falling into the tile, double-buffered by tile parity => ONE barrier per tile and several
-//    CTAs per SM, so the 20-B logit gathers of one CTA overlap the arithmetic and stores of the others;
-//  * the few records that own a label get the owner terms added in label order by their thread, and
-//    their softmax-CE class gradient added on top of the zeros by a warp;
-//  * loss sums: registers -> warp shuffles -> one partial row per CTA -> the last CTA to finish adds
-//    the rows in index order (double) and writes the 18 detail values + their sum.  No float atomics.
+// Shape of the kernel (B200), v5.  profiles/r01_v3_ncu_summary.md and r01_v4_notes.md say why the earlier
+// shapes (CTA tiles staged in shared memory behind a barrier; zero-fill followed by partial-sector value
+// stores; logits through L1) were latency- and traffic-bound.
+//  * everything per-image is prepared by the assignment kernel (assign.cu): the valid labels in each
+//    head's grid units (gtab), their count, and the object mask as one bit per record (objbits).  The
+//    dense pass has NO shared-memory staging and NO CTA barrier in its loop;
+//  * the packed tensor is a flat array of records of L floats.  A WARP owns a chunk of 32 consecutive
+//    records (128*L bytes: a sector-aligned span), independent of every other warp; chunks are claimed
+//    grid-stride, the grid sized so that every warp gets the same number of them; the logits and object
+//    bits of a warp's next chunk are already in flight while it works on the current one;
+//  * a lane owns one record: it reads the two aligned 128-bit words holding the record's 5 box/conf
+//    logits with L2-only loads (an L1 miss would fetch the whole 128-byte line; class logits of
+//    non-responsible anchors are never read: their gradient is identically 0), decodes, takes the max IoU
+//    over the image's labels (L1-resident loads from gtab, four labels in flight, branch-free IoU),
+//    accumulates the loss terms and composes its gradient values;
+//  * gradient of a chunk: every 32-byte sector is written exactly once, whole.  L-5 of a record's L floats
+//    are zeros (the class logits of an anchor that owns no label): the lanes cover the sectors that hold no
+//    box/conf value with 128-bit streaming zero stores (fire-and-forget, issued before the arithmetic); the
+//    one or two sectors around a record's five values are written by the record's lane, values and zeros
+//    together.  No sector is first zeroed and then partially overwritten (that costs a DRAM read-modify-write
+//    once the zero sector has left L2) and nothing needs ordering;
+//  * the few lanes whose object bit is set add the owner terms of their labels in label order and write
+//    the softmax-CE class gradient of their record on top of the zeros (after a __syncwarp);
+//  * loss sums: registers -> warp shuffles -> one partial row per CTA -> the last CTA to finish folds
+//    the rows in a fixed order (double) and writes the 18 detail values + their sum.  No float atomics.
+#include "tile_ops.cuh"
 #include "yv3_kernels.cuh"
 
 namespace yv3 {
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-constexpr int kSlots = 2;             // images a tile may touch (TR <= records per image)
+constexpr int kSmallL = 8;            // records shorter than this are composed in shared memory
 
-struct DenseBuf {                     // one per tile parity
-    float* gt[kSlots];                // [3][m][5]  (x0, y0, x1, y1, area) of the valid labels, label order
-    int* list_rec;                    // [cap] tile-relative record of an owned entry
-    int* list_idx;                    // [cap] index into own[]
-    int* meta;                        // [0..1] valid-label count per slot, [2] entries in the list
-};
-struct DenseSmem {
-    DenseBuf buf[2];
-    float* red;                       // [kWarps][12]
-};
-
-__host__ __device__ inline size_t dense_smem_bytes(int m) {
-    const size_t cap = (size_t)kSlots * 3 * m;
-    size_t per = kSlots * align_up((size_t)3 * m * 5 * 4, 16) + 2 * align_up(cap * 4, 16) + 16;
-    return 2 * per + kWarps * 12 * 4 + 16;
+// value k (0..4) of a record whose first float sits at position `ph` (0..3) of the 8 floats in (a, b)
+__device__ __forceinline__ float pick(const float4& a, const float4& b, int ph, int k) {
+    const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    float v = f[k];
+    v = (ph == 1) ? f[k + 1] : v;
+    v = (ph == 2) ? f[k + 2] : v;
+    v = (ph == 3) ? f[k + 3] : v;
+    return v;
 }
 
-__device__ __forceinline__ DenseSmem carve(unsigned char* base, int m) {
-    DenseSmem s;
-    size_t o = (16 - ((size_t)smem_u32(base) & 15)) & 15;
-    auto take = [&](size_t bytes) {
-        unsigned char* p = base + o;
-        o += (bytes + 15) / 16 * 16;
-        return p;
-    };
-    const size_t cap = (size_t)kSlots * 3 * m;
+// The 12 floats starting at a 32-byte sector boundary that hold a record's five gradient values at float
+// position pos (0..7), zeros elsewhere: three conditional shifts (by 1, 2, 4), selects only.
+struct Win12 {
+    float4 a, b, c;
+};
+__device__ __forceinline__ Win12 compose(const float (&gv)[5], int pos) {
+    const bool s1 = pos & 1, s2 = pos & 2, s4 = pos & 4;
+    float x[6];
+    x[0] = s1 ? 0.f : gv[0];
 #pragma unroll
-    for (int b = 0; b < 2; ++b) {
-        s.buf[b].gt[0] = (float*)take((size_t)3 * m * 5 * 4);
-        s.buf[b].gt[1] = (float*)take((size_t)3 * m * 5 * 4);
-        s.buf[b].list_rec = (int*)take(cap * 4);
-        s.buf[b].list_idx = (int*)take(cap * 4);
-        s.buf[b].meta = (int*)take(16);
+    for (int i = 1; i < 5; ++i) x[i] = s1 ? gv[i - 1] : gv[i];
+    x[5] = s1 ? gv[4] : 0.f;
+    float y[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float lo = (i < 6) ? x[i] : 0.f;
+        const float hi = (i >= 2) ? x[i - 2] : 0.f;
+        y[i] = s2 ? hi : lo;
     }
-    s.red = (float*)take(kWarps * 12 * 4);
-    return s;
+    float z[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) {
+        const float lo = (i < 8) ? y[i] : 0.f;
+        const float hi = (i >= 4) ? y[i - 4] : 0.f;
+        z[i] = s4 ? hi : lo;
+    }
+    Win12 w;
+    w.a = make_float4(z[0], z[1], z[2], z[3]);
+    w.b = make_float4(z[4], z[5], z[6], z[7]);
+    w.c = make_float4(z[8], z[9], z[10], z[11]);
+    return w;
 }
 
-__global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_constant__ Geo g, const DenseArgs a) {
-    extern __shared__ unsigned char smem_raw[];
-    const bool with_grad = a.grad != nullptr && !(a.debug & 8);
-    const DenseSmem s = carve(smem_raw, a.m);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int L = g.L, C = g.C, m = a.m, tr = a.tr;
-    const int cap_entries = 3 * m;
+// The background test of yolov3_loss.py:294,331 for one (anchor, label) pair: is IoU < iou_thresh?  The IoU itself
+// is fl(inter / fl(fl(aP + aT) - inter)); the quotient is only needed when it lands within 2^-20 (relative) of the
+// threshold: inter < t*u*(1 - 2^-20) implies fl(inter/u) < t and inter > t*u*(1 + 2^-20) implies fl(inter/u) >= t
+// (each product is off by at most 2^-24 relative).  Everything else -- the band, NaNs, the TIoU variant -- takes the
+// exact expression of iou_ref, so the decision is the reference's bit for bit.
+__device__ __forceinline__ bool iou_below(float px0, float py0, float px1, float py1, float parea, const float4& t,
+                                          float tarea, float thr, int tiou) {
+    const float iw = fmaxf(__fsub_rn(fminf(px1, t.z), fmaxf(px0, t.x)), 0.0f);
+    const float ih = fmaxf(__fsub_rn(fminf(py1, t.w), fmaxf(py0, t.y)), 0.0f);
+    const float inter = __fmul_rn(iw, ih);
+    const float uni = __fsub_rn(__fadd_rn(parea, tarea), inter);
+    if (!tiou) {
+        const float tb = __fmul_rn(thr, uni);
+        if (inter < __fmul_rn(tb, 0.99999905f)) return true;
+        if (inter > __fmul_rn(tb, 1.00000095f)) return false;
+    }
+    GtBox g;
+    g.x0 = t.x; g.y0 = t.y; g.x1 = t.z; g.y1 = t.w; g.area = tarea;
+    return iou_ref(px0, py0, px1, py1, parea, g, tiou) < thr;
+}
 
-    float acc_noobj[3] = {0.f, 0.f, 0.f}, acc_rect[3] = {0.f, 0.f, 0.f}, acc_cls[3] = {0.f, 0.f, 0.f};
+struct Logits {
+    float4 a, b;      // VEC: the two aligned words around the record; scalar path: a = t0..t3, b.x = t4
+};
+template <int VEC>
+__device__ __forceinline__ Logits load_logits(const float* __restrict__ predicts, long long grec, int L, bool ok) {
+    Logits q;
+    q.a = make_float4(0.f, 0.f, 0.f, 0.f);
+    q.b = q.a;
+    if (ok) {
+        if (VEC) {
+            // L2-only loads: an L1 miss would pull the whole 128-byte line for 20 useful bytes
+            const float4* p = reinterpret_cast<const float4*>(predicts) + ((grec * L) >> 2);
+            q.a = __ldcg(p);
+            q.b = __ldcg(p + 1);
+        } else {
+            const float* p = predicts + grec * L;
+            q.a = make_float4(__ldcg(p), __ldcg(p + 1), __ldcg(p + 2), __ldcg(p + 3));
+            q.b.x = __ldcg(p + 4);
+        }
+    }
+    return q;
+}
+
+constexpr int kWideL = 12;            // from here on a 32-byte sector holds values of at most one record
+
+// The valid labels of the (at most two) images a warp's chunk touches, in the warp's own shared-memory slots
+// (slot = image & 1): [V, pad x3] then per head m label entries of 8 floats (x0, y0, x1, y1, area, pad x3), head
+// stride m*8 + 4 floats so that the three heads' entries fall into different banks.
+__host__ __device__ inline int gt_slot_floats(int m) { return 4 + 3 * (m * kGtFloats + 4); }
+
+__device__ __forceinline__ void gt_refill(float* slot, const DenseArgs& a, int n_img, int lane) {
+    const int m = a.m;
+    const int V = __ldg(a.vcount + n_img);
+    if (lane == 0) reinterpret_cast<int*>(slot)[0] = V;
+#pragma unroll
+    for (int h = 0; h < 3; ++h) {
+        const float4* src = reinterpret_cast<const float4*>(a.gtab + ((size_t)n_img * 3 + h) * m * kGtFloats);
+        float4* dst = reinterpret_cast<float4*>(slot + 4 + h * (m * kGtFloats + 4));
+        for (int i = lane; i < 2 * V; i += 32) dst[i] = __ldg(src + i);
+    }
+}
+
+template <int VEC, int SGT>
+__global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_constant__ Geo g,
+                                                                 const __grid_constant__ DenseArgs a) {
+    extern __shared__ __align__(16) float gt_s[];          // SGT: [kWarps][2][gt_slot_floats(m)]
+    __shared__ float red_s[kWarps][12];
+    __shared__ float stage_s[VEC ? 1 : kWarps * 32 * kSmallL];
+    const bool with_grad = a.grad != nullptr && !(a.debug & 8);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int L = g.L, C = g.C, m = a.m;
+    const int nw = gridDim.x * kWarps;
     const float thr = g.iou_thresh;
     const float nf = (float)a.n_global;
     const float one = 1.0f;
+    const bool wide = VEC && L >= kWideL;
 
-    float cur[5];
-    auto load_rec = [&](int tile, float (&dst)[5]) {
-        const long long grec = (long long)tile * tr + tid;
-        const bool ok = tile < a.num_tiles && tid < tr && grec < a.total_rec;
-        const float* p = a.predicts + (size_t)(ok ? grec : 0) * L;
-#pragma unroll
-        for (int c = 0; c < 5; ++c) dst[c] = ok ? __ldg(p + c) : 0.f;
-    };
-    load_rec(blockIdx.x, cur);
+    float an0 = 0.f, an1 = 0.f, an2 = 0.f;       // noobj sums per head
+    float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f;       // sum of squared raw box logits per head
+    float ac0 = 0.f, ac1 = 0.f, ac2 = 0.f;       // class sums per head
 
-    int parity = 0;
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x, parity ^= 1) {
-        const DenseBuf& B = s.buf[parity];
-        const long long rec0 = (long long)tile * tr;
-        const int nrec = (int)min((long long)tr, a.total_rec - rec0);
-        const int n_first = (int)(rec0 / g.rpi);
-        const int n_last = (int)((rec0 + nrec - 1) / g.rpi);
-        const int nslots = n_last - n_first + 1;          // 1 or 2
+    // zero-fill bookkeeping of the wide path: this lane's 128-bit words of a chunk are lane, lane + 32, ...;
+    // word c lies in sector c >> 1, which starts at float 8 * (c >> 1) of the chunk = position q of a record.
+    // The sector carries box/conf values iff q <= 4 (a record starts at or just before it) or q >= L - 7
+    // (the next record starts inside it); those sectors are written whole by the record's lane instead.
+    // A chunk starts on a record boundary, so the pattern is the same for every chunk.
+    // The pattern is one bit per loop trip, computed on the host (a.zlo / a.zhi); trips beyond 64 (L > 256) are
+    // tested on the fly.
+    const int dq = 128 % L;
+    const int trips = (8 * L + 31) >> 5;             // 128-bit words of a full chunk / 32 lanes
+    const unsigned zlo = a.zlo[lane], zhi = a.zhi[lane];
+    int q64 = 0;                                     // the position after 64 trips
+    if (trips > 64) {
+        int q = (8 * (lane >> 1)) % L;
+        for (int k = 0; k < 64; ++k) { q += dq; q -= (q >= L) ? L : 0; }
+        q64 = q;
+    }
+
+    // a warp owns a.cpw consecutive chunks (the launcher sizes the grid so that every warp gets the same number):
+    // it stays inside one or two images, whose labels it keeps in its shared-memory slots
+    int cur = (blockIdx.x * kWarps + warp) * a.cpw;
+    const int cend = min(cur + a.cpw, a.num_chunks);
+    int nxt = cur + 1;
+    float* slots = gt_s + (size_t)warp * 2 * gt_slot_floats(m);
+    int held0 = -1, held1 = -1;                      // image held by slot 0 / 1 (warp-uniform)
+    Logits qv = load_logits<VEC>(a.predicts, (long long)cur * 32 + lane, L,
+                                 cur < cend && (long long)cur * 32 + lane < a.total_rec);
+    unsigned objn = (cur < cend) ? __ldg(a.objbits + cur) : 0u;
+
+    while (cur < cend) {
+        const int chunk = cur;
+        const unsigned objw = objn;                        // rec0 is a multiple of 32: one word per chunk
+        const long long rec0 = (long long)chunk * 32;
+        const int nrec = (int)min(32LL, a.total_rec - rec0);
+        const long long grec = rec0 + lane;
+        const bool ok = lane < nrec;
+        const long long off = grec * L;                    // first float of the record
+        const int ph = VEC ? (int)(off & 3) : 0;
+        const float t0 = VEC ? pick(qv.a, qv.b, ph, 0) : qv.a.x, t1 = VEC ? pick(qv.a, qv.b, ph, 1) : qv.a.y;
+        const float t2 = VEC ? pick(qv.a, qv.b, ph, 2) : qv.a.z, t3 = VEC ? pick(qv.a, qv.b, ph, 3) : qv.a.w;
+        const float t4 = VEC ? pick(qv.a, qv.b, ph, 4) : qv.b.x;
+        // the tensor's last chunk may end off a sector boundary: it takes the generic path
+        const bool fast = wide && (chunk != a.num_chunks - 1);
+
+        // ---- zeros first: 16 B per store, nothing waits for them ---------------------------------------
         const int nfl = nrec * L;
-
-        // ---- zeros first: the whole span, 16 B per store, nothing waits for them ----------------------
-        if (with_grad) {
-            float4* gdst = reinterpret_cast<float4*>(a.grad + (size_t)rec0 * L);
-            const int nchunks = nfl >> 2;
-            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-            for (int c = tid; c < nchunks; c += kThreads) __stcs(gdst + c, z4);
-            // only the very last tile of the tensor can end off a 16-byte boundary
-            if (tid < (nfl & 3)) a.grad[(size_t)rec0 * L + (nchunks << 2) + tid] = 0.f;
-        }
-
-        // ---- tile setup (into this parity's buffers) ---------------------------------------------------
-        // warp sl (< nslots): valid labels of image slot sl -> per-head boxes, order kept (:239-247);
-        // warp 2: the owned entries that fall into this tile, order kept
-        if (warp < nslots) {
-            const int sl = warp;
-            float* gts = B.gt[sl];
-            const float* lab = a.targets + (size_t)(n_first + sl) * m * 5;
-            int count = 0;
-            for (int base = 0; base < m; base += 32) {
-                const int j = base + lane;
-                float xn = -1.f, yn = 0.f, wn = 0.f, hn = 0.f;
-                if (j < m) {
-                    const float* t = lab + j * 5;
-                    xn = __ldg(t); yn = __ldg(t + 1); wn = __ldg(t + 2); hn = __ldg(t + 3);
-                }
-                const bool valid = (j < m) && (__fmul_rn(xn, g.fW[0]) >= 0.0f);
-                const unsigned mask = __ballot_sync(0xffffffffu, valid);
-                const int pos = count + __popc(mask & ((1u << lane) - 1u));
-                if (valid) {
-#pragma unroll
-                    for (int h = 0; h < 3; ++h) {
-                        const GtDec T = decode_label(g, h, xn, yn, wn, hn);
-                        float* o = gts + ((size_t)h * m + pos) * 5;
-                        o[0] = T.box.x0; o[1] = T.box.y0; o[2] = T.box.x1; o[3] = T.box.y1; o[4] = T.box.area;
+        if (with_grad && L >= kSmallL) {
+            float* gspan = a.grad + (size_t)rec0 * L;
+            if (VEC) {
+                float4* gdst = reinterpret_cast<float4*>(gspan);
+                const int n16 = nfl >> 2;
+                const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (fast) {
+                    float4* gl = gdst + lane;
+                    unsigned mk = zlo;
+                    const int t32 = min(trips, 32);
+#pragma unroll 8
+                    for (int k = 0; k < t32; ++k) {
+                        if (mk & 1u) __stcs(gl + 32 * k, z4);
+                        mk >>= 1;
                     }
-                }
-                count += __popc(mask);
-            }
-            if (lane == 0) B.meta[sl] = count;
-        } else if (warp == 2) {
-            int count = 0;
-            if (!(a.debug & 4)) {
-                for (int sl = 0; sl < nslots; ++sl) {
-                    const int n_img = n_first + sl;
-                    const long long img_rec0 = (long long)n_img * g.rpi;
-                    for (int base = 0; base < cap_entries; base += 32) {
-                        const int e = base + lane;
-                        int rec = -1;
-                        if (e < cap_entries) rec = a.own[(size_t)n_img * cap_entries + e].rec;
-                        const long long grec = img_rec0 + rec;
-                        const bool in = rec >= 0 && grec >= rec0 && grec < rec0 + nrec;
-                        const unsigned mask = __ballot_sync(0xffffffffu, in);
-                        const int pos = count + __popc(mask & ((1u << lane) - 1u));
-                        if (in) {
-                            B.list_rec[pos] = (int)(grec - rec0);
-                            B.list_idx[pos] = n_img * cap_entries + e;
+                    if (trips > 32) {
+                        mk = zhi;
+                        const int t64 = min(trips, 64);
+                        for (int k = 32; k < t64; ++k) {
+                            if (mk & 1u) __stcs(gl + 32 * k, z4);
+                            mk >>= 1;
                         }
-                        count += __popc(mask);
+                        int q = q64;
+                        for (int k = 64; k < trips; ++k) {
+                            if (lane + 32 * k < n16 && q > 4 && q < L - 7) __stcs(gl + 32 * k, z4);
+                            q += dq;
+                            q -= (q >= L) ? L : 0;
+                        }
                     }
+                } else {
+#pragma unroll 4
+                    for (int c = lane; c < n16; c += 32) __stcs(gdst + c, z4);
+                    if (lane < (nfl & 3)) gspan[(n16 << 2) + lane] = 0.f;
+                }
+            } else {
+                for (int c = lane; c < nfl; c += 32) __stcs(gspan + c, 0.f);
+            }
+        }
+        // ---- the next chunk's logits go in flight; this chunk's object bits ------------------------------
+        qv = load_logits<VEC>(a.predicts, (long long)nxt * 32 + lane, L,
+                              nxt < cend && (long long)nxt * 32 + lane < a.total_rec);
+        objn = (nxt < cend) ? __ldg(a.objbits + nxt) : 0u;
+        const bool is_obj = ok && ((objw >> lane) & 1u);     // :328 scatter of owned anchors
+
+        // ---- record phase: lane = record -----------------------------------------------------------
+        float gv[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+        // one division per chunk (uniform), lanes step from there
+        const int n_first = (int)((unsigned)rec0 / (unsigned)g.rpi);
+        const int r_first = (int)((unsigned)rec0 - (unsigned)n_first * (unsigned)g.rpi);
+        if (SGT) {
+            // labels of the chunk's image(s) into the warp's slots (only when the warp crosses into a new image)
+            const int n_last = n_first + ((r_first + nrec - 1 >= g.rpi) ? 1 : 0);       // rpi >= 32 on this path
+            bool filled = false;
+            for (int ni = n_first; ni <= n_last; ++ni) {
+                const int held = (ni & 1) ? held1 : held0;
+                if (held != ni) {
+                    if (!filled) __syncwarp();           // earlier reads of the slot are done
+                    gt_refill(slots + (ni & 1) * gt_slot_floats(m), a, ni, lane);
+                    if (ni & 1) held1 = ni; else held0 = ni;
+                    filled = true;
                 }
             }
-            if (lane == 0) B.meta[2] = count;
+            if (filled) __syncwarp();
         }
-        // prefetch the next tile's logits while this one is processed
-        float nxt[5];
-        load_rec(tile + gridDim.x, nxt);
-        __syncthreads();          // the tile's one barrier: buffers ready, zero stores ordered before value stores
-        const int nl = B.meta[2];
-
-        // ---- record phase: thread = record ---------------------------------------------------------
-        if (tid < nrec) {
-            const long long grec = rec0 + tid;
-            const int n_img = (int)(grec / g.rpi);
-            const int r_img = (int)(grec - (long long)n_img * g.rpi);
+        int n_img = n_first, r_img = r_first + lane, head = 0;
+        if (ok) {
+            while (r_img >= g.rpi) { r_img -= g.rpi; ++n_img; }
             const RecLoc p = locate(g, r_img);
-            const BoxDec d = decode_box(g, p, cur[0], cur[1], cur[2], cur[3], cur[4]);
+            head = p.h;
+            const BoxDec d = decode_box(g, p, t0, t1, t2, t3, t4);
             const float parea = __fmul_rn(d.w, d.h);                                       // :267
-            const int sl = n_img - n_first;
-            const int V = B.meta[sl];
-            const float* gt = B.gt[sl] + (size_t)p.h * m * 5;
-            float maxiou = -INFINITY;                                                      // reduce_max over V = 0
-            for (int j = 0; j < V; ++j) {
-                GtBox t;
-                t.x0 = gt[j * 5 + 0]; t.y0 = gt[j * 5 + 1]; t.x1 = gt[j * 5 + 2]; t.y1 = gt[j * 5 + 3];
-                t.area = gt[j * 5 + 4];
-                maxiou = fmaxf(maxiou, iou_ref(d.x0, d.y0, d.x1, d.y1, parea, t, g.tiou));   // :294
+            int V;
+            const float4* gt;
+            if (SGT) {
+                const float* slot = slots + (n_img & 1) * gt_slot_floats(m);
+                V = reinterpret_cast<const int*>(slot)[0];
+                gt = reinterpret_cast<const float4*>(slot + 4 + p.h * (m * kGtFloats + 4));
+            } else {
+                V = __ldg(a.vcount + n_img);
+                gt = reinterpret_cast<const float4*>(a.gtab + ((size_t)n_img * 3 + p.h) * m * kGtFloats);
             }
-            bool is_obj = false;                                                           // :328 scatter of owned anchors
-            for (int i = 0; i < nl; ++i) is_obj |= (B.list_rec[i] == tid);
-            const float bg = ((maxiou < thr) ? one : 0.0f) * (one - (is_obj ? one : 0.0f));   // :331-332
+            bool none_ge = true;                    // max over the labels < thr  <=>  every IoU < thr (V = 0: -inf < thr)
+            for (int j = 0; j < V; j += 4) {
+                // four labels in flight; past the end the last one is repeated (the decision does not change)
+                float4 bx[4];
+                float ta[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int jj = min(j + u, V - 1);
+                    if (SGT) {
+                        bx[u] = gt[2 * jj];
+                        ta[u] = reinterpret_cast<const float*>(gt + 2 * jj + 1)[0];
+                    } else {
+                        bx[u] = __ldg(gt + 2 * jj);
+                        ta[u] = __ldg(reinterpret_cast<const float*>(gt + 2 * jj + 1));
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    none_ge = none_ge && iou_below(d.x0, d.y0, d.x1, d.y1, parea, bx[u], ta[u], thr, g.tiou);   // :294
+            }
+            const float bg = (none_ge ? one : 0.0f) * (one - (is_obj ? one : 0.0f));       // :331-332
             const float pc = d.conf;
             float l = -logf(one - pc);                                                     // :335
             float fprime;
@@ -205,90 +323,134 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                 fprime = one / (one - pc);
             }
             const float contrib = l * bg;                                                  // :338 (0 * inf = NaN kept)
-            const float sq = cur[0] * cur[0] + cur[1] * cur[1] + cur[2] * cur[2] + cur[3] * cur[3];   // :153-155
-            if (p.h == 0) { acc_noobj[0] += contrib; acc_rect[0] += sq; }
-            else if (p.h == 1) { acc_noobj[1] += contrib; acc_rect[1] += sq; }
-            else { acc_noobj[2] += contrib; acc_rect[2] += sq; }
+            const float sq = t0 * t0 + t1 * t1 + t2 * t2 + t3 * t3;                        // :153-155
+            an0 += (p.h == 0) ? contrib : 0.f; an1 += (p.h == 1) ? contrib : 0.f; an2 += (p.h == 2) ? contrib : 0.f;
+            ar0 += (p.h == 0) ? sq : 0.f; ar1 += (p.h == 1) ? sq : 0.f; ar2 += (p.h == 2) ? sq : 0.f;
             if (with_grad) {
                 const float pass = (d.sc >= g.lo && d.sc <= g.hi) ? one : 0.f;
-                float gv[5];
                 if (a.rect_active) {
                     const float rg = a.upstream * g.rw[p.h] * 2.0f;
-                    gv[0] = rg * cur[0] / nf; gv[1] = rg * cur[1] / nf;
-                    gv[2] = rg * cur[2] / nf; gv[3] = rg * cur[3] / nf;
-                } else {
-                    gv[0] = 0.f; gv[1] = 0.f; gv[2] = 0.f; gv[3] = 0.f;
+                    gv[0] = rg * t0 / nf; gv[1] = rg * t1 / nf;
+                    gv[2] = rg * t2 / nf; gv[3] = rg * t3 / nf;
                 }
                 gv[4] = a.kappa * bg * g.lw[p.h][2] * fprime * pass * d.sc * (one - d.sc);
-                if (is_obj) {
-                    // owner terms of every label assigned here, in label order (duplicates add, rule T3)
-                    for (int i = 0; i < nl; ++i) {
-                        if (B.list_rec[i] != tid) continue;
-                        const OwnEntry* e = a.own + B.list_idx[i];
-#pragma unroll
-                        for (int c = 0; c < 5; ++c) gv[c] += e->g[c];
-                    }
-                }
-                float* o = a.grad + (size_t)grec * L;
-                if (a.rect_active || is_obj) {
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) o[c] = gv[c];
-                }
-                o[4] = gv[4];
             }
         }
 
-        // ---- records that own a label: class term and its gradient (one warp per record) ------------
-        if (nl > 0 && C > 0) {
-            for (int i = 0; i < nl; ++i) {
-                const int rt = B.list_rec[i];
-                if ((rt & (kWarps - 1)) != warp) continue;      // same record -> same warp, label order
-                const OwnEntry* e = a.own + B.list_idx[i];
-                const int cls = e->cls;
-                if (cls < 0 || cls >= C) continue;               // zero one-hot row: no loss, no gradient
-                const long long grec = rec0 + rt;
-                const int h = locate(g, (int)(grec % g.rpi)).h;
-                const float* z = a.predicts + (size_t)grec * L + 5;
-                float mx = -INFINITY;
-                for (int k = lane; k < C; k += 32) mx = fmaxf(mx, __ldg(z + k));
-                mx = warp_max(mx);                                                         // decoder :189
-                float sum = 0.f;
-                for (int k = lane; k < C; k += 32) sum += expf(__ldg(z + k) - mx);
-                sum = warp_sum(sum);
-                const float inv = 1.0f / sum;
-                const float qc = expf(__ldg(z + cls) - mx) * inv;                          // softmax :190
-                const float qcc = clip_ref(qc, g.lo, g.hi);                                // :191
-                if (lane == 0) acc_cls[h] += -logf(qcc);                                   // loss :363-364
-                if (with_grad) {
-                    const float pass = (qc >= g.lo && qc <= g.hi) ? 1.0f : 0.f;
-                    const float coef = a.kappa * g.lw[h][4] * (-1.0f / qcc) * pass * qc;
-                    float* go = a.grad + (size_t)grec * L + 5;
-                    // on top of the zeros (ordered by the tile barrier); a second label on the same record
-                    // is handled by the same lanes of the same warp, later in this loop
-                    for (int k = lane; k < C; k += 32) {
-                        const float qk = expf(__ldg(z + k) - mx) * inv;
-                        go[k] = __ldcg(go + k) + coef * ((k == cls ? 1.0f : 0.f) - qk);
+        // ---- the record's five gradient values ---------------------------------------------------------
+        if (with_grad) {
+            if (fast) {
+                // whole sectors, disjoint from the zero fill: no ordering needed
+                if (ok) {
+                    const int pos = (int)(off & 7);
+                    const Win12 w = compose(gv, pos);
+                    float4* o = reinterpret_cast<float4*>(a.grad) + ((off >> 3) << 1);
+                    __stcs(o, w.a);
+                    __stcs(o + 1, w.b);
+                    if (pos >= 4) {
+                        __stcs(o + 2, w.c);
+                        __stcs(o + 3, make_float4(0.f, 0.f, 0.f, 0.f));
                     }
                 }
+            } else if (L >= kSmallL) {
+                __syncwarp();                 // every lane's zero stores are ordered before the values
+                if (ok) {
+                    float* o = a.grad + (size_t)off;
+#pragma unroll
+                    for (int c = 0; c < 5; ++c) o[c] = gv[c];
+                }
+            } else {
+                // short records (class_num < 3): every float of the span carries a value or sits next to one;
+                // compose the chunk in shared memory and write it out coalesced
+                float* st = stage_s + warp * 32 * kSmallL;
+                if (ok) {
+                    float* r = st + lane * L;
+                    r[0] = gv[0]; r[1] = gv[1]; r[2] = gv[2]; r[3] = gv[3]; r[4] = gv[4];
+                    for (int c = 5; c < L; ++c) r[c] = 0.f;
+                }
                 __syncwarp();
+                float* gspan = a.grad + (size_t)rec0 * L;
+                for (int c = lane; c < nfl; c += 32) gspan[c] = st[c];
             }
         }
-#pragma unroll
-        for (int c = 0; c < 5; ++c) cur[c] = nxt[c];
+
+        // ---- records that own a label (object bit set): the whole warp serves them one after the other ------
+        // owner-side box/conf terms of assign.cu added in label order (duplicates add, rule T3), then the class
+        // term (:361-364) and its softmax-CE gradient with the classes spread over the lanes
+        unsigned ob = __ballot_sync(0xffffffffu, is_obj);
+        if (ob && !(a.debug & 4)) {
+            if (with_grad) __syncwarp();      // the chunk's stores above are ordered before the read-modify-writes
+            while (ob) {
+                const int src = __ffs(ob) - 1;
+                ob &= ob - 1;
+                const int o_n = __shfl_sync(0xffffffffu, n_img, src);
+                const int o_r = __shfl_sync(0xffffffffu, r_img, src);
+                const int o_h = __shfl_sync(0xffffffffu, head, src);
+                const size_t o_off = (size_t)(rec0 + src) * L;
+                const OwnEntry* e0 = a.own + ((size_t)o_n * 3 + o_h) * m;
+                float mx = 0.f, inv = 0.f;
+                bool have = false, first = true;
+                float gacc = 0.f;                                   // lanes 0..4: channel `lane` of the record
+                if (with_grad && lane < 5) gacc = __ldcg(a.grad + o_off + lane);
+                bool touched = false;
+                for (int jb = 0; jb < m; jb += 32) {
+                    const int je = jb + lane;
+                    const bool hit = je < m && e0[je].rec == o_r;
+                    unsigned hits = __ballot_sync(0xffffffffu, hit);
+                    while (hits) {                                 // label order
+                        const int j = jb + __ffs(hits) - 1;
+                        hits &= hits - 1;
+                        if (with_grad && lane < 5) { gacc += e0[j].g[lane]; touched = true; }
+                        const int cls = e0[j].cls;
+                        if (C == 0 || cls < 0 || cls >= C) continue;     // zero one-hot row: no loss, no gradient
+                        const float* z = a.predicts + o_off + 5;
+                        if (!have) {                               // decoder :189-190
+                            float vmax = -INFINITY;
+                            for (int k = lane; k < C; k += 32) vmax = fmaxf(vmax, __ldg(z + k));
+                            mx = warp_max(vmax);
+                            float sum = 0.f;
+                            for (int k = lane; k < C; k += 32) sum += expf(__ldg(z + k) - mx);
+                            inv = 1.0f / warp_sum(sum);
+                            have = true;
+                        }
+                        const float qc = expf(__ldg(z + cls) - mx) * inv;
+                        const float qcc = clip_ref(qc, g.lo, g.hi);                                // :191
+                        if (lane == 0) {
+                            const float lv = -logf(qcc);                                           // loss :363-364
+                            ac0 += (o_h == 0) ? lv : 0.f; ac1 += (o_h == 1) ? lv : 0.f; ac2 += (o_h == 2) ? lv : 0.f;
+                        }
+                        if (with_grad) {
+                            const float pass = (qc >= g.lo && qc <= g.hi) ? 1.0f : 0.f;
+                            const float coef = a.kappa * g.lw[o_h][4] * (-1.0f / qcc) * pass * qc;
+                            float* go = a.grad + o_off + 5;
+                            // a second label on the same record: the same lane adds to what it wrote for the first
+                            for (int k = lane; k < C; k += 32) {
+                                const float qk = expf(__ldg(z + k) - mx) * inv;
+                                const float v = coef * ((k == cls ? 1.0f : 0.f) - qk);
+                                go[k] = first ? v : (__ldcg(go + k) + v);
+                            }
+                            first = false;
+                        }
+                    }
+                }
+                if (touched) a.grad[o_off + lane] = gacc;
+            }
+        }
+        cur = nxt;
+        nxt += 1;
     }
 
     // ---- reduction: thread -> warp -> CTA partial row -> last CTA --------------------------------
-    float v[9] = {acc_noobj[0], acc_noobj[1], acc_noobj[2], acc_cls[0], acc_cls[1], acc_cls[2],
-                  acc_rect[0], acc_rect[1], acc_rect[2]};
+    float v[9] = {an0, an1, an2, ac0, ac1, ac2, ar0, ar1, ar2};
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
         const float w = warp_sum(v[k]);
-        if (lane == 0) s.red[warp * 12 + k] = w;
+        if (lane == 0) red_s[warp][k] = w;
     }
     __syncthreads();
     if (tid < 9) {
         float acc = 0.f;
-        for (int w = 0; w < kWarps; ++w) acc += s.red[w * 12 + tid];
+        for (int w = 0; w < kWarps; ++w) acc += red_s[w][tid];
         a.partials[(size_t)blockIdx.x * kPartialFloats + tid] = acc;
     }
     __shared__ int is_last;
@@ -301,20 +463,42 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
     __syncthreads();
     if (!is_last) return;
     __threadfence();
+    // the last CTA: all 256 threads fold the partial rows (thread t takes rows t, t + 256, ... in index order,
+    // in double), lanes fold by shuffles, warps through shared memory: a fixed order => a deterministic sum
+    __shared__ double fold_s[kWarps][18];
+    double part[18];
+#pragma unroll
+    for (int k = 0; k < 18; ++k) part[k] = 0.0;
+    for (int b = tid; b < (int)gridDim.x; b += kThreads) {
+        const float4* row = reinterpret_cast<const float4*>(a.partials + (size_t)b * kPartialFloats);
+        const float4 r0 = __ldcg(row), r1 = __ldcg(row + 1), r2 = __ldcg(row + 2);
+        part[0] += (double)r0.x; part[1] += (double)r0.y; part[2] += (double)r0.z;      // noobj
+        part[3] += (double)r0.w; part[4] += (double)r1.x; part[5] += (double)r1.y;      // cls
+        part[6] += (double)r1.z; part[7] += (double)r1.w; part[8] += (double)r2.x;      // rect
+    }
+    for (int i = tid; i < a.n; i += kThreads) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) part[9 + k] += (double)__ldcg(a.img_terms + (size_t)i * 9 + k);   // xy, wh, obj
+    }
+#pragma unroll
+    for (int k = 0; k < 18; ++k) {
+        double x = part[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if (lane == 0) fold_s[warp][k] = x;
+    }
+    __syncthreads();
     __shared__ float fin[18];
     if (tid < 18) {
         const int row = tid / 3, h = tid - row * 3;       // rows: xy, wh, noobj, obj, cls, rect
+        // source column in part[]: noobj 0..2, cls 3..5, rect 6..8, xy 9..11, wh 12..14, obj 15..17
+        const int src = (row == 0) ? 9 + h : (row == 1) ? 12 + h : (row == 2) ? h : (row == 3) ? 15 + h
+                      : (row == 4) ? 3 + h : 6 + h;
         double acc = 0.0;
-        if (row == 0 || row == 1 || row == 3) {
-            const int term = (row == 0) ? 0 : ((row == 1) ? 1 : 2);
-            for (int i = 0; i < a.n; ++i) acc += (double)__ldcg(a.img_terms + (size_t)i * 9 + term * 3 + h);
-        } else {
-            const int col = (row == 2) ? h : ((row == 4) ? 3 + h : 6 + h);
-            for (int b = 0; b < (int)gridDim.x; ++b) acc += (double)__ldcg(a.partials + (size_t)b * kPartialFloats + col);
-            if (row == 2) acc *= (double)g.lw[h][2];
-            else if (row == 4) acc *= (double)g.lw[h][4];
-            else acc = a.rect_active ? acc * (double)g.rw[h] : 0.0;
-        }
+        for (int w = 0; w < kWarps; ++w) acc += fold_s[w][src];
+        if (row == 2) acc *= (double)g.lw[h][2];
+        else if (row == 4) acc *= (double)g.lw[h][4];
+        else if (row == 5) acc = a.rect_active ? acc * (double)g.rw[h] : 0.0;
         const float out = (float)(acc / (double)a.n_global);
         a.detail[tid] = out;
         fin[tid] = out;
@@ -330,24 +514,45 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
     }
 }
 
-cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream) {
-    // a tile = one record per thread, never more than an image holds (a tile touches <= 2 images)
-    long long tr = min((long long)kThreads, (long long)g.rpi);
-    tr &= ~3LL;
-    if (tr < 4) return cudaErrorInvalidValue;
-    a.tr = (int)tr;
-    a.num_tiles = (int)((a.total_rec + tr - 1) / tr);
-    const size_t smem = dense_smem_bytes(a.m);
-    if (smem > 200 * 1024) return cudaErrorInvalidValue;
-    cudaError_t err = cudaFuncSetAttribute(loss_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+template <int VEC, int SGT>
+static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, cudaStream_t stream) {
+    const size_t smem = SGT ? (size_t)kWarps * 2 * gt_slot_floats(a.m) * sizeof(float) : 0;
+    cudaError_t err = cudaFuncSetAttribute(loss_dense_kernel<VEC, SGT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     int per_sm = 1;
-    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_dense_kernel, kThreads, smem);
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_dense_kernel<VEC, SGT>, kThreads, smem);
     if (err != cudaSuccess) return err;
     if (per_sm < 1) per_sm = 1;
-    const int grid = (int)min((long long)min(sm_count * per_sm, kMaxGrid), (long long)a.num_tiles);
-    loss_dense_kernel<<<grid, kThreads, smem, stream>>>(g, a);
+    // every warp the same number of consecutive chunks: cpw at the largest resident grid, then just enough CTAs
+    const long long slots = (long long)min(sm_count * per_sm, kMaxGrid) * kWarps;
+    a.cpw = (int)max(1LL, ((long long)a.num_chunks + slots - 1) / slots);
+    const int grid = (int)max(1LL, ((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps));
+    loss_dense_kernel<VEC, SGT><<<grid, kThreads, smem, stream>>>(g, a);
     return cudaGetLastError();
+}
+
+cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream) {
+    a.num_chunks = (int)((a.total_rec + 31) / 32);
+    // zero-fill pattern of the whole-sector path (see the kernel): bit k of lane l <=> 128-bit word l + 32 k of a
+    // chunk lies in a sector without box/conf values
+    const int L = g.L;
+    for (int lane = 0; lane < 32; ++lane) {
+        unsigned lo = 0, hi = 0;
+        for (int k = 0; k < 64; ++k) {
+            const int c = lane + 32 * k;
+            if (c >= 8 * L) break;
+            const int q = (8 * (c >> 1)) % L;
+            const bool z = q > 4 && q < L - 7;
+            if (k < 32) lo |= z ? (1u << k) : 0u; else hi |= z ? (1u << (k - 32)) : 0u;
+        }
+        a.zlo[lane] = lo;
+        a.zhi[lane] = hi;
+    }
+    // labels in shared memory when they fit (2 slots per warp) and a chunk touches at most two images
+    const bool sgt = a.m <= 32 && g.rpi >= 32 && !(a.debug & 16);
+    const bool vec = a.vec_ok && g.L >= kSmallL;
+    if (vec) return sgt ? launch_variant<1, 1>(g, a, sm_count, stream) : launch_variant<1, 0>(g, a, sm_count, stream);
+    return sgt ? launch_variant<0, 1>(g, a, sm_count, stream) : launch_variant<0, 0>(g, a, sm_count, stream);
 }
 
 }  // namespace yv3

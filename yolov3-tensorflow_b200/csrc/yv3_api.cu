@@ -45,7 +45,8 @@ int check_shape(const yv3_config* c) {
     if (c->class_num < 0 || c->class_num > 16383) return YV3_ERR_SHAPE;
     long long rpi = (long long)c->grid_h[2] * c->grid_w[2] *
                     (16LL * c->box_num[0] + 4LL * c->box_num[1] + c->box_num[2]);
-    if (rpi > (1LL << 22)) return YV3_ERR_SHAPE;       // record ids are packed into 22-bit fields
+    if (rpi >= (1LL << 22)) return YV3_ERR_SHAPE;      // record ids are packed into 22-bit fields
+    if (c->grid_w[0] > 1024) return YV3_ERR_SHAPE;     // exact reciprocal division in locate()
     return YV3_OK;
 }
 
@@ -94,6 +95,9 @@ Geo make_geo(const yv3_config* c) {
     }
     g.rpr = base;
     g.rpi = g.rows32 * g.rpr;
+    auto magic = [](int d) { return d == 1 ? 0u : (unsigned)((1ULL << 32) / (unsigned long long)d + 1ULL); };
+    g.mg_rpr = magic(g.rpr);
+    for (int h = 0; h < 3; ++h) { g.mg_B[h] = magic(g.B[h]); g.mg_W[h] = magic(g.W[h]); }
     g.lo = (float)c->eps;                                 // python double -> fp32 constant
     g.hi = (float)(1.0 - c->eps);
     g.iou_thresh = c->iou_thresh;
@@ -153,7 +157,7 @@ int yv3_query_workspace(const yv3_config* cfg, int n, int m, size_t* bytes) {
     int rc = yv3_config_check(cfg);
     if (rc != YV3_OK) return rc;
     if (n < 1 || m < 1 || m > YV3_MAX_GT) return YV3_ERR_SHAPE;
-    *bytes = carve_workspace(nullptr, n, m).bytes;
+    *bytes = carve_workspace(nullptr, n, m, make_geo(cfg).rpi).bytes;
     return YV3_OK;
 }
 
@@ -170,7 +174,7 @@ int loss_common_checks(const yv3_config* cfg, const float* predicts, const float
     if (n < 1 || m < 1 || m > YV3_MAX_GT) return YV3_ERR_SHAPE;
     if (!workspace) return YV3_ERR_WORKSPACE;
     if (!aligned16(workspace)) return YV3_ERR_ALIGN;
-    if (workspace_bytes < carve_workspace(nullptr, n, m).bytes) return YV3_ERR_WORKSPACE;
+    if (workspace_bytes < carve_workspace(nullptr, n, m, make_geo(cfg).rpi).bytes) return YV3_ERR_WORKSPACE;
     if (!aligned4(predicts) || !aligned4(targets)) return YV3_ERR_ALIGN;
     return YV3_OK;
 }
@@ -185,12 +189,13 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
     if (rc != YV3_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     const Geo g = make_geo(cfg);
-    Workspace ws = carve_workspace(workspace, n, m);
-    if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
+    Workspace ws = carve_workspace(workspace, n, m, g.rpi);
+    if (!cuda_ok(cudaMemsetAsync(ws.status, 0, ws.zero_bytes, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
     AssignArgs a;
     a.predicts = predicts; a.targets = targets; a.n = n; a.m = m;
     a.kappa = 1.0f / (float)n;
     a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
+    a.objbits = ws.objbits; a.gtab = ws.gtab; a.vcount = ws.vcount;
     a.table = table; a.iou_out = iou;
     if (!cuda_ok(launch_assign(g, a, st), "launch_assign")) return YV3_ERR_CUDA;
     return YV3_OK;
@@ -203,18 +208,20 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
     if (rc != YV3_OK) return rc;
     if (!loss_out20) return YV3_ERR_NULL;
     if (n_global < n) return YV3_ERR_SHAPE;
+    if ((long long)n * yv3_records_per_image(cfg) >= (1LL << 31)) return YV3_ERR_CAPACITY;
     if (grad_predicts && !aligned16(grad_predicts)) return YV3_ERR_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
     const Geo g = make_geo(cfg);
-    Workspace ws = carve_workspace(workspace, n, m);
+    Workspace ws = carve_workspace(workspace, n, m, g.rpi);
     if ((phases & 3) == 0) return YV3_ERR_SHAPE;
     const float kappa = upstream / (float)n_global;
     if (phases & 1) {
-        if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
+        if (!cuda_ok(cudaMemsetAsync(ws.status, 0, ws.zero_bytes, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
         AssignArgs a;
         a.predicts = predicts; a.targets = targets; a.n = n; a.m = m;
         a.kappa = kappa;
         a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
+    a.objbits = ws.objbits; a.gtab = ws.gtab; a.vcount = ws.vcount;
         a.table = nullptr; a.iou_out = nullptr;
         if (!cuda_ok(launch_assign(g, a, st), "launch_assign")) return YV3_ERR_CUDA;
     }
@@ -222,19 +229,21 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
 
     DenseArgs d;
     memset(&d, 0, sizeof(d));
-    d.predicts = predicts; d.targets = targets; d.grad = grad_predicts;
+    d.predicts = predicts; d.grad = grad_predicts;
     d.own = ws.own; d.img_terms = ws.img_terms; d.partials = ws.partials; d.status = ws.status;
+    d.objbits = ws.objbits; d.gtab = ws.gtab; d.vcount = ws.vcount;
     d.detail = loss_out20;
     d.n = n; d.m = m; d.n_global = n_global;
     d.total_rec = (long long)n * g.rpi;
     d.kappa = kappa; d.upstream = upstream;
     d.rect_active = rectified_active ? 1 : 0;
-    // a label row is m*20 bytes: bulk copies need 16-B aligned source rows and sizes
-    d.tma_labels = (aligned16(targets) && (m % 4) == 0) ? 1 : 0;
+    // both tensors 16-byte aligned: the box logits of a record are read (and its gradient written) as two
+    // aligned 128-bit words; otherwise the scalar path
+    d.vec_ok = (aligned16(predicts) && (!grad_predicts || aligned16(grad_predicts))) ? 1 : 0;
     {
         const char* dbg = getenv("YV3_DEBUG");
         d.debug = dbg ? atoi(dbg) : 0;
-        if (d.debug & 1) d.tma_labels = 0;
+        if (d.debug & 1) d.vec_ok = 0;
     }
     if (!cuda_ok(launch_loss_dense(g, d, sm_count_cached(), st), "launch_loss_dense")) return YV3_ERR_CUDA;
     return YV3_OK;

@@ -36,7 +36,12 @@ struct Geo {
     int focal;
     float alpha, gamma;
     int tiou;
+    // ceil(2^32 / d) for the divisors of locate(): exact quotients for numerators < 2^22, d <= 2^10
+    unsigned mg_rpr, mg_B[3], mg_W[3];      // 0 for d = 1
 };
+
+// x / d for x < 2^22 with mg = floor(2^32 / d) + 1, d <= 2^10 (x * (mg * d - 2^32) < 2^32)
+__device__ __forceinline__ int fast_div(int x, unsigned mg) { return mg ? (int)__umulhi((unsigned)x, mg) : x; }
 
 struct RecLoc {
     int h, y, x, b;
@@ -45,16 +50,16 @@ struct RecLoc {
 // record index inside an image (packed order) -> head / cell / anchor   
 __device__ __forceinline__ RecLoc locate(const Geo& g, int r_img) {
     RecLoc o;
-    int row = r_img / g.rpr;
+    int row = fast_div(r_img, g.mg_rpr);
     int k = r_img - row * g.rpr;
     o.h = (k >= g.seg_base[2]) ? 2 : ((k >= g.seg_base[1]) ? 1 : 0);
     int kk = k - g.seg_base[o.h];
     int B = g.B[o.h];
-    int cell = kk / B;
+    int cell = fast_div(kk, g.mg_B[o.h]);
     o.b = kk - cell * B;
     int gidx = row * g.fold[o.h] + cell;
     int W = g.W[o.h];
-    o.y = gidx / W;
+    o.y = fast_div(gidx, g.mg_W[o.h]);
     o.x = gidx - o.y * W;
     return o;
 }
@@ -203,10 +208,15 @@ __device__ __forceinline__ float warp_max(float v) {
 }
 
 // ---- workspace layout of the loss path (device memory handed in by the caller) ----------------
-// [0]   int32 status[4]          : 0 error bits, 1 ticket counter of the final reduction
-// then  OwnEntry own[n][3][m]    : assignment result, consumed by the dense pass
-// then  float   img_terms[n][9]  : per image, per head weighted xy / wh / obj sums
-// then  float   partials[grid][8]: per CTA noobj[3], cls[3], rect... (see loss_dense.cu)
+// [0]   int32 status[8]            : 0 error bits, 1 ticket counter of the final reduction
+// then  uint32 objbits[ceil(n*rpi/32)] : bit r = record r (global index) is the anchor some owned label maps to
+//                                    (the object mask of yolov3_loss.py:328); zeroed together with status
+// then  OwnEntry own[n][3][m]      : assignment result, consumed by the dense pass
+// then  float   img_terms[n][9]    : per image, per head weighted xy / wh / obj sums
+// then  float   gtab[n][3][m][8]   : valid labels of an image in head-h grid units, label order kept:
+//                                    x0, y0, x1, y1, area, 3 pad  (label_decoder.py:53-59, yolov3_loss.py:239-247, :273)
+// then  int32   vcount[n]          : number of valid labels of an image
+// then  float   partials[grid][12] : per CTA noobj[3], cls[3], rect[3] (see loss_dense.cu)
 struct OwnEntry {
     int32_t rec;    // record index inside the image the label is assigned to in this head, or -1
     int32_t cls;    // int(label class); may lie outside [0, C)
@@ -219,28 +229,40 @@ constexpr int kStatusInts = 8;
 constexpr unsigned kStatusGtRange = 1u;
 constexpr unsigned kStatusNonFinite = 2u;
 constexpr unsigned kStatusCapacity = 4u;
+constexpr int kGtFloats = 8;
 
 struct Workspace {
     int32_t* status;
+    uint32_t* objbits;
+    size_t zero_bytes;      // status + objbits: one memset at the start of the assignment phase
     OwnEntry* own;
     float* img_terms;
+    float* gtab;
+    int32_t* vcount;
     float* partials;
     size_t bytes;
 };
-constexpr int kMaxGrid = 1024;          // upper bound on CTAs of the dense pass
+constexpr int kMaxGrid = 2048;          // upper bound on CTAs of the dense pass
 constexpr int kPartialFloats = 12;      // noobj[3], cls[3], rect[3], pad[3]
 
 __host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-inline Workspace carve_workspace(void* base, int n, int m) {
+inline Workspace carve_workspace(void* base, int n, int m, long long rpi) {
     Workspace w;
     size_t off = 0;
     char* p = (char*)base;
     w.status = (int32_t*)(p + off);
-    off = align_up(off + sizeof(int32_t) * kStatusInts, 256);
+    off = align_up(off + sizeof(int32_t) * kStatusInts, 32);
+    w.objbits = (uint32_t*)(p + off);
+    off = align_up(off + sizeof(uint32_t) * (size_t)(((long long)n * rpi + 31) / 32 + 1), 256);
+    w.zero_bytes = off;
     w.own = (OwnEntry*)(p + off);
     off = align_up(off + sizeof(OwnEntry) * (size_t)n * 3 * (size_t)m, 256);
     w.img_terms = (float*)(p + off);
     off = align_up(off + sizeof(float) * 9 * (size_t)n, 256);
+    w.gtab = (float*)(p + off);
+    off = align_up(off + sizeof(float) * kGtFloats * 3 * (size_t)m * (size_t)n, 256);
+    w.vcount = (int32_t*)(p + off);
+    off = align_up(off + sizeof(int32_t) * (size_t)n, 256);
     w.partials = (float*)(p + off);
     off = align_up(off + sizeof(float) * kPartialFloats * kMaxGrid, 256);
     w.bytes = off;

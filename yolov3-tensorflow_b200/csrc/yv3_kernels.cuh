@@ -13,6 +13,9 @@ struct AssignArgs {
     OwnEntry* own;        // [n][3][m]
     float* img_terms;     // [n][3][3]  weighted xy, wh, obj sums per head
     int32_t* status;
+    uint32_t* objbits;    // object mask bits by global record index (zeroed by the caller)
+    float* gtab;          // [n][3][m][8] valid labels per head (x0, y0, x1, y1, area), label order
+    int32_t* vcount;      // [n]
     int32_t* table;       // optional public output [n][m][3][4]
     float* iou_out;       // optional public output [n][m][3]
 };
@@ -21,22 +24,25 @@ cudaError_t launch_assign(const Geo& g, const AssignArgs& a, cudaStream_t stream
 // ---- loss_dense.cu -----------------------------------------------------------------------------
 struct DenseArgs {
     const float* predicts;
-    const float* targets;
     float* grad;                      // may be NULL: forward only
     const OwnEntry* own;
     const float* img_terms;
+    const uint32_t* objbits;
+    const float* gtab;
+    const int32_t* vcount;
     float* partials;
     int32_t* status;
     float* detail;                    // 20 floats: 18 detail values, their sum, pad
     int n, m, n_global;
-    int tr;                           // records per tile (multiple of 4, <= kThreads * RPT, <= rpi)
-    int num_tiles;
+    int num_chunks;                   // 32-record chunks (one per warp iteration)
+    int cpw;                          // consecutive chunks per warp
+    unsigned zlo[32], zhi[32];        // per lane: zero-fill pattern of a chunk (set by the launcher)
     long long total_rec;
     float kappa;                      // upstream / n_global
     float upstream;
     int rect_active;
-    int tma_labels;                   // label rows are 16-B aligned: stage them with a bulk copy
-    int debug;                        // developer switches (YV3_DEBUG): 2 plain stores, 4 skip fix-up, 8 skip store
+    int vec_ok;                       // predicts and grad are 16-byte aligned
+    int debug;                        // developer switches (YV3_DEBUG): 1 scalar path, 4 skip class terms, 8 skip the gradient stores, 16 labels from global memory
 };
 cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream);
 
