@@ -31,6 +31,8 @@
 //    the softmax-CE class gradient of their record on top of the zeros (after a __syncwarp);
 //  * loss sums: registers -> warp shuffles -> one partial row per CTA -> the last CTA to finish folds
 //    the rows in a fixed order (double) and writes the 18 detail values + their sum.  No float atomics.
+#include <stdlib.h>
+
 #include "tile_ops.cuh"
 #include "yv3_kernels.cuh"
 
@@ -149,7 +151,7 @@ __device__ __forceinline__ void gt_refill(float* slot, const DenseArgs& a, int n
 template <int VEC, int SGT>
 __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_constant__ Geo g,
                                                                  const __grid_constant__ DenseArgs a) {
-    extern __shared__ __align__(16) float gt_s[];          // SGT: [kWarps][2][gt_slot_floats(m)]
+    extern __shared__ __align__(16) float gt_s[];          // SGT: [kWarps][2][gt_slot_floats(m)], then the zero block
     __shared__ float red_s[kWarps][12];
     __shared__ float stage_s[VEC ? 1 : kWarps * 32 * kSmallL];
     const bool with_grad = a.grad != nullptr && !(a.debug & 8);
@@ -193,6 +195,24 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                                  cur < cend && (long long)cur * 32 + lane < a.total_rec);
     unsigned objn = (cur < cend) ? __ldg(a.objbits + cur) : 0u;
 
+    // bulk zero fill (a.bulk): a block of zeros in shared memory is the source of one asynchronous bulk (TMA)
+    // store per chunk, issued by lane 0 one chunk ahead; the record lanes later overwrite the sectors around
+    // their values whole.  The issuing warp never waits on the store queue.
+    const bool bulk = VEC && a.bulk && with_grad && wide;
+    float* zblk = gt_s + (SGT ? (size_t)kWarps * 2 * gt_slot_floats(m) : 0);
+    const unsigned chunk_bytes = 128u * (unsigned)L;
+    if (bulk) {
+        for (int i = tid; i < a.zero_bytes / 4; i += kThreads) zblk[i] = 0.f;
+        fence_async_smem();
+        __syncthreads();
+        if (lane == 0 && cur < cend && cur != a.num_chunks - 1) {
+            char* dst = reinterpret_cast<char*>(a.grad) + (size_t)cur * chunk_bytes;
+            for (unsigned o = 0; o < chunk_bytes; o += (unsigned)a.zero_bytes)
+                bulk_s2g(dst + o, zblk, min((unsigned)a.zero_bytes, chunk_bytes - o));
+            bulk_commit();
+        }
+    }
+
     while (cur < cend) {
         const int chunk = cur;
         const unsigned objw = objn;                        // rec0 is a multiple of 32: one word per chunk
@@ -216,7 +236,9 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                 float4* gdst = reinterpret_cast<float4*>(gspan);
                 const int n16 = nfl >> 2;
                 const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (fast) {
+                if (fast && bulk) {
+                    // zeros already on their way (issued one chunk ahead)
+                } else if (fast) {
                     float4* gl = gdst + lane;
                     unsigned mk = zlo;
                     const int t32 = min(trips, 32);
@@ -252,6 +274,13 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
         qv = load_logits<VEC>(a.predicts, (long long)nxt * 32 + lane, L,
                               nxt < cend && (long long)nxt * 32 + lane < a.total_rec);
         objn = (nxt < cend) ? __ldg(a.objbits + nxt) : 0u;
+        const bool ahead = bulk && nxt < cend && nxt != a.num_chunks - 1;
+        if (ahead && lane == 0) {
+            char* dst = reinterpret_cast<char*>(a.grad) + (size_t)nxt * chunk_bytes;
+            for (unsigned o = 0; o < chunk_bytes; o += (unsigned)a.zero_bytes)
+                bulk_s2g(dst + o, zblk, min((unsigned)a.zero_bytes, chunk_bytes - o));
+            bulk_commit();
+        }
         const bool is_obj = ok && ((objw >> lane) & 1u);     // :328 scatter of owned anchors
 
         // ---- record phase: lane = record -----------------------------------------------------------
@@ -340,7 +369,15 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
         // ---- the record's five gradient values ---------------------------------------------------------
         if (with_grad) {
             if (fast) {
-                // whole sectors, disjoint from the zero fill: no ordering needed
+                // whole sectors: disjoint from the lanes' zero fill; after the bulk zero fill of this chunk has
+                // completed (lane 0 waits for its bulk group, the warp barrier passes that on)
+                if (bulk) {
+                    if (lane == 0) {
+                        if (ahead) bulk_wait_all<1>(); else bulk_wait_all<0>();
+                        asm volatile("fence.proxy.async.global;" ::: "memory");
+                    }
+                    __syncwarp();
+                }
                 if (ok) {
                     const int pos = (int)(off & 7);
                     const Win12 w = compose(gv, pos);
@@ -516,7 +553,9 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
 
 template <int VEC, int SGT>
 static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, cudaStream_t stream) {
-    const size_t smem = SGT ? (size_t)kWarps * 2 * gt_slot_floats(a.m) * sizeof(float) : 0;
+    a.bulk = (VEC && g.L >= kWideL && !(a.debug & 64)) ? 1 : 0;
+    a.zero_bytes = a.bulk ? (int)min(128LL * g.L, 16384LL) : 0;
+    const size_t smem = (SGT ? (size_t)kWarps * 2 * gt_slot_floats(a.m) * sizeof(float) : 0) + (size_t)a.zero_bytes;
     cudaError_t err = cudaFuncSetAttribute(loss_dense_kernel<VEC, SGT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     int per_sm = 1;
@@ -526,6 +565,11 @@ static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, cuda
     // every warp the same number of consecutive chunks: cpw at the largest resident grid, then just enough CTAs
     const long long slots = (long long)min(sm_count * per_sm, kMaxGrid) * kWarps;
     a.cpw = (int)max(1LL, ((long long)a.num_chunks + slots - 1) / slots);
+    if (const char* e = getenv("YV3_CPW")) {                       // developer override
+        const int v = atoi(e);
+        const long long need = ((long long)a.num_chunks + (long long)v * kWarps - 1) / ((long long)v * kWarps);
+        if (v >= 1 && need <= kMaxGrid) a.cpw = v;
+    }
     const int grid = (int)max(1LL, ((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps));
     loss_dense_kernel<VEC, SGT><<<grid, kThreads, smem, stream>>>(g, a);
     return cudaGetLastError();

@@ -36,13 +36,15 @@ struct DenseArgs {
     int n, m, n_global;
     int num_chunks;                   // 32-record chunks (one per warp iteration)
     int cpw;                          // consecutive chunks per warp
+    int bulk;                         // zero fill by bulk (TMA) stores from a shared-memory block of zeros
+    int zero_bytes;                   // size of that block (multiple of 16)
     unsigned zlo[32], zhi[32];        // per lane: zero-fill pattern of a chunk (set by the launcher)
     long long total_rec;
     float kappa;                      // upstream / n_global
     float upstream;
     int rect_active;
     int vec_ok;                       // predicts and grad are 16-byte aligned
-    int debug;                        // developer switches (YV3_DEBUG): 1 scalar path, 4 skip class terms, 8 skip the gradient stores, 16 labels from global memory
+    int debug;                        // developer switches (YV3_DEBUG): 1 scalar path, 4 skip class terms, 8 skip the gradient stores, 16 labels from global memory, 64 zero fill by the lanes instead of bulk stores
 };
 cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream);
 
