@@ -562,9 +562,13 @@ static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, cuda
     err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_dense_kernel<VEC, SGT>, kThreads, smem);
     if (err != cudaSuccess) return err;
     if (per_sm < 1) per_sm = 1;
-    // every warp the same number of consecutive chunks: cpw at the largest resident grid, then just enough CTAs
-    const long long slots = (long long)min(sm_count * per_sm, kMaxGrid) * kWarps;
-    a.cpw = (int)max(1LL, ((long long)a.num_chunks + slots - 1) / slots);
+    // two consecutive chunks per warp (the second one's logits and zero fill are in flight while the first is
+    // worked on) and as many CTAs as that takes: the hardware scheduler balances them (measured best on B200,
+    // profiles/r01_dense_cpw_sweep.txt); one chunk per warp when there is less work than resident warps, more
+    // when the grid would exceed the partial-row table
+    const long long slots = (long long)sm_count * per_sm * kWarps;
+    a.cpw = a.num_chunks >= 2 * slots ? 2 : 1;
+    while (((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps) > kMaxGrid) ++a.cpw;
     if (const char* e = getenv("YV3_CPW")) {                       // developer override
         const int v = atoi(e);
         const long long need = ((long long)a.num_chunks + (long long)v * kWarps - 1) / ((long long)v * kWarps);

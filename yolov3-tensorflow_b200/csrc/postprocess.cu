@@ -7,11 +7,12 @@
 //           dropped iff an earlier KEPT box of the same class has IoU_f64 > thresh (strict).
 //
 // Kernels:
-//   score_packed_kernel   one sweep over the packed logits (HBM-bound, 4*A*L bytes/image): tile in shared
-//                         memory by bulk copy, one thread per record, (score, prob, class) written in
-//                         head-raster order (12 B/record).
-//   compact_kernel        one CTA per image: order-preserving compaction (block scan per head) of the
-//                         records that pass the threshold; survivors' boxes are re-decoded from 5 logits.
+//   score_tile_kernel     one sweep over the packed logits (HBM-bound, 4*A*L bytes/image): tile in shared
+//                         memory by bulk copy, one thread per record, approximate early-out, exact scores for
+//                         the few records near or above the threshold, survivors ranked inside the tile.
+//   gather_kernel         one CTA per image: prefix over the tiles' counts, candidate rows written in the
+//                         reference's order; survivors' boxes are decoded from 5 logits.
+//   score_decoded_kernel / compact_kernel   the same for already decoded heads of one image (filter_boxes' inputs).
 //   sort_kernel           one CTA per image: 64-bit keys (class | ~score | row) bitonic-sorted in shared
 //                         memory (global memory beyond 16 Ki candidates).
 //   nms_kernel            one CTA per (class, image) segment: 256-candidate chunks; each chunk is first
@@ -27,43 +28,214 @@ namespace yv3 {
 
 constexpr int kScoreThreads = 128;
 
-// ---- (score, prob, class) of every record -----------------------------------------------------------
-__global__ void __launch_bounds__(kScoreThreads) score_packed_kernel(const __grid_constant__ Geo g,
-                                                                     const float* __restrict__ predicts,
-                                                                     const TileLaunch q, float* __restrict__ score,
-                                                                     float* __restrict__ prob, int32_t* __restrict__ cls) {
+// ---- fused score + threshold over the packed logits ---------------------------------------------------------
+// One CTA per tile of <= 128 consecutive records (<= 2 images), one thread per record:
+//  1. the tile lands in shared memory (bulk copy);
+//  2. every thread bounds its record's score from above: score = fl(clip(max_c p_c) * conf) <= conf, and
+//     max_c p_c = 1 / sum_k exp(z_k - max z) where the sum is first taken with ex2.approx (4 instructions per
+//     class instead of ~16).  A record whose bound, widened by 1e-3, stays below the threshold cannot pass
+//     (:62 is strict) and is dropped; the others ("maybe", a few per tile) are queued;
+//  3. the queued records are scored exactly -- the same class_stats / class_best as the decode kernel, one record per
+//     thread of the FIRST warps, so the expensive path runs on dense lanes;
+//  4. survivors are ranked inside the tile per (image slot, head) with warp ballots and written to the tile's
+//     staging rows (score, prob, class, record-in-head); six counts per tile.
+// gather_kernel then turns counts into the reference's order (head /8,/16,/32, raster inside a head) per image and
+// writes the candidate rows, decoding each survivor's box from its five logits.
+struct ScoreTiles {
+    int tr;                 // records per tile (multiple of 4, <= kScoreThreads, <= records per image)
+    int num_tiles;
+    long long total_rec;
+    int tma;
+    int early;              // threshold large enough for the approximate early-out (thresh > 2 * eps)
+};
+
+__global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_constant__ Geo g,
+                                                                   const float* __restrict__ predicts, const ScoreTiles q,
+                                                                   float thresh, float4* __restrict__ stage,
+                                                                   int32_t* __restrict__ tcount) {
     extern __shared__ __align__(128) unsigned char ssm[];
     __shared__ uint64_t bar;
+    __shared__ int wcnt_s[kScoreThreads / 32][8];
     const int L = g.L, C = g.C, tr = q.tr;
     float* tile = (float*)ssm;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long rec0 = (long long)blockIdx.x * tr;
     const int nrec = (int)min((long long)tr, q.total_rec - rec0);
     tile_load<kScoreThreads>(tile, predicts + (size_t)rec0 * L, nrec * L, q.tma, &bar);
 
-    const int off1 = g.head_rec[0], off2 = g.head_rec[0] + g.head_rec[1];
-    // one thread per record: records are L floats apart in shared memory (bank-conflict free for odd L)
-    for (int ri = tid; ri < nrec; ri += kScoreThreads) {
-        const long long grec = rec0 + ri;
-        const int n_img = (int)(grec / g.rpi);
-        const RecLoc p = locate(g, (int)(grec - (long long)n_img * g.rpi));
-        const int rih = (p.y * g.W[p.h] + p.x) * g.B[p.h] + p.b;
-        const size_t o = (size_t)n_img * g.rpi + (p.h == 0 ? 0 : (p.h == 1 ? off1 : off2)) + rih;
-        const float* r = tile + (size_t)ri * L;
-        const float conf = clip_ref(sigmoid_ref(r[4]), g.lo, g.hi);
-        if (C > 0) {
-            const ClassStats cs = class_stats(r + 5, C);
-            float best;
-            int arg;
-            class_best(r + 5, C, cs, g.lo, g.hi, best, arg);
-            score[o] = __fmul_rn(best, conf);                           // :59
-            prob[o] = best;
-            cls[o] = arg;
-        } else {
-            score[o] = conf;                                            // :53-55 (prob 1, class 0)
-            prob[o] = 1.0f;
-            cls[o] = 0;
+    const bool have = tid < nrec;
+    const float* r = tile + (size_t)tid * L;
+    float conf = 0.f;
+    bool maybe = false;
+    if (have) {
+        conf = clip_ref(sigmoid_ref(r[4]), g.lo, g.hi);
+        if (C == 0) {
+            maybe = false;
+        } else if (!q.early) {
+            maybe = true;
+        } else if (conf > thresh) {                                  // fl(prob * conf) <= conf for prob <= 1
+            float mx = r[5];
+            for (int k = 1; k < C; ++k) mx = fmaxf(mx, r[5 + k]);
+            const float ml = mx * 1.4426950408889634f;
+            float s0 = 0.f, s1 = 0.f;
+            int k = 0;
+            for (; k + 2 <= C; k += 2) {
+                s0 += exp2f_approx(__fmaf_rn(r[5 + k], 1.4426950408889634f, -ml));
+                s1 += exp2f_approx(__fmaf_rn(r[6 + k], 1.4426950408889634f, -ml));
+            }
+            if (k < C) s0 += exp2f_approx(__fmaf_rn(r[5 + k], 1.4426950408889634f, -ml));
+            // true score <= conf / sum * (1 + 1e-5); keep a 1e-3 band around the threshold for the exact path
+            maybe = !(conf < thresh * (s0 + s1) * 0.999f);
         }
+    }
+    // ---- exact scores of the queued records: one record at a time, the classes spread over the warp's lanes ------
+    float4 mine = make_float4(conf, 1.0f, __int_as_float(0), (have && conf > thresh) ? 1.f : 0.f);   // :53-55 (C = 0)
+    if (C > 0) {
+        mine = make_float4(0.f, 0.f, 0.f, 0.f);
+        unsigned mb = __ballot_sync(0xffffffffu, maybe);
+        while (mb) {
+            const int src = __ffs(mb) - 1;
+            mb &= mb - 1;
+            const float* rr = tile + (size_t)(warp * 32 + src) * L;
+            const ClassStats cs = class_stats_warp(rr + 5, C, lane);
+            float best = clip_ref(cs.inv, g.lo, g.hi);
+            int arg = cs.arg;
+            if (cs.near > 1) {                                                       // rounding tie: the serial rule
+                if (lane == 0) class_best(rr + 5, C, cs, g.lo, g.hi, best, arg);
+                best = __shfl_sync(0xffffffffu, best, 0);
+                arg = __shfl_sync(0xffffffffu, arg, 0);
+            }
+            if (lane == src) {
+                const float sc = __fmul_rn(best, conf);                              // :59
+                mine = make_float4(sc, best, __int_as_float(arg), (sc > thresh) ? 1.f : 0.f);   // :62 strict, fp32
+            }
+        }
+    }
+    const bool pass = have && mine.w != 0.f;
+
+    // ---- rank inside the tile per (image slot, head) ---------------------------------------------------------
+    const long long grec = rec0 + tid;
+    const int n_first = (int)(rec0 / g.rpi);
+    int n_img = n_first, r_img = (int)(rec0 - (long long)n_first * g.rpi) + tid;
+    if (r_img >= g.rpi) { r_img -= g.rpi; ++n_img; }
+    RecLoc p = {0, 0, 0, 0};
+    if (have) p = locate(g, r_img);
+    const int grp = have ? (n_img - n_first) * 3 + p.h : 7;
+    int my_rank = 0;
+    (void)grec;
+#pragma unroll
+    for (int gi = 0; gi < 6; ++gi) {
+        const unsigned b = __ballot_sync(0xffffffffu, pass && grp == gi);
+        if (grp == gi) my_rank = __popc(b & ((1u << lane) - 1u));
+        if (lane == 0) wcnt_s[warp][gi] = __popc(b);
+    }
+    __syncthreads();
+    if (pass) {
+        int base = 0;
+        for (int gi = 0; gi < grp; ++gi)
+            for (int w = 0; w < kScoreThreads / 32; ++w) base += wcnt_s[w][gi];
+        for (int w = 0; w < warp; ++w) base += wcnt_s[w][grp];
+        const int rih = (p.y * g.W[p.h] + p.x) * g.B[p.h] + p.b;
+        stage[(size_t)blockIdx.x * tr + base + my_rank] = make_float4(mine.x, mine.y, mine.z, __int_as_float(rih));
+    }
+    if (tid < 6) {
+        int c = 0;
+        for (int w = 0; w < kScoreThreads / 32; ++w) c += wcnt_s[w][tid];
+        tcount[(size_t)blockIdx.x * 8 + tid] = c;
+    }
+}
+
+// One CTA per image: the tiles' counts go to shared memory, an exclusive prefix per head puts them in the reference's
+// order (head /8,/16,/32, raster inside a head: tiles in order, staged order inside a tile), then one THREAD per
+// candidate row finds its tile by binary search and writes the row (:65-75), decoding the box from its five logits.
+constexpr int kGatherThreads = 512;
+__global__ void __launch_bounds__(kGatherThreads) gather_kernel(const __grid_constant__ Geo g, const float* __restrict__ predicts,
+                                                                const ScoreTiles q, const float4* __restrict__ stage,
+                                                                const int32_t* __restrict__ tcount, float* __restrict__ cand,
+                                                                int capacity, int32_t* __restrict__ counts, int32_t* status) {
+    __shared__ int wsum_s[kGatherThreads / 32];
+    __shared__ int carry_s;
+    __shared__ int head_base_s[4];
+    extern __shared__ int gsm[];                   // tc_s [ntiles][8] counts of this image's tiles (slot resolved: 3 used),
+                                                   // then pre_s [3][ntiles] exclusive prefix inside a head
+    const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long img0 = (long long)n * g.rpi;
+    const int t0 = (int)(img0 / q.tr), t1 = (int)((img0 + g.rpi - 1) / q.tr);
+    const int ntiles = t1 - t0 + 1;
+    int* tc_s = gsm;
+    int* pre_s = gsm + 8 * ntiles;
+    for (int i = tid; i < ntiles * 8; i += kGatherThreads) {
+        const int ti = i >> 3, c = i & 7;
+        const int t = t0 + ti;
+        const int sl = n - (int)(((long long)t * q.tr) / g.rpi);                 // 0 or 1: this image's slot in the tile
+        // columns 0..2: this image's counts per head; 3..5: staged rows BEFORE this image's group of head c - 3
+        int v = 0;
+        const int32_t* tc = tcount + (size_t)t * 8;
+        if (c < 3) v = tc[sl * 3 + c];
+        else if (c < 6) { for (int gi = 0; gi < sl * 3 + (c - 3); ++gi) v += tc[gi]; }
+        tc_s[i] = v;
+    }
+    __syncthreads();
+    int total_all = 0;
+    for (int h = 0; h < 3; ++h) {
+        if (tid == 0) carry_s = 0;
+        __syncthreads();
+        for (int b = 0; b < ntiles; b += kGatherThreads) {
+            const int ti = b + tid;
+            const int c = (ti < ntiles) ? tc_s[ti * 8 + h] : 0;
+            int incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            if (lane == 31) wsum_s[warp] = incl;
+            __syncthreads();
+            int wbase = carry_s;
+            for (int w = 0; w < warp; ++w) wbase += wsum_s[w];
+            if (ti < ntiles) pre_s[h * ntiles + ti] = wbase + incl - c;
+            __syncthreads();
+            if (tid == kGatherThreads - 1) carry_s = wbase + incl;
+            __syncthreads();
+        }
+        if (tid == 0) { head_base_s[h] = total_all; counts[n * 3 + h] = carry_s; }
+        total_all += carry_s;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        head_base_s[3] = total_all;
+        if (total_all > capacity) atomicOr((unsigned*)status, kStatusCapacity);
+    }
+    __syncthreads();
+    float* out = cand + (size_t)n * capacity * YV3_CAND_COLS;
+    const int nrows = min(total_all, capacity);
+    for (int pos = tid; pos < nrows; pos += kGatherThreads) {
+        const int h = (pos >= head_base_s[2]) ? 2 : ((pos >= head_base_s[1]) ? 1 : 0);
+        const int rel = pos - head_base_s[h];
+        // last tile whose exclusive prefix is <= rel and that holds rows (prefix strictly increases past it)
+        const int* pre = pre_s + h * ntiles;
+        int lo = 0, hi = ntiles - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (pre[mid] <= rel) lo = mid; else hi = mid - 1;
+        }
+        // tiles with zero rows share the prefix of their successor: step back to the one that contains rel
+        while (rel - pre[lo] >= tc_s[lo * 8 + h]) --lo;
+        const int e = rel - pre[lo];
+        const float4 sv = stage[(size_t)(t0 + lo) * q.tr + tc_s[lo * 8 + 3 + h] + e];
+        const int rih = __float_as_int(sv.w);
+        RecLoc p;
+        p.h = h;
+        const int cell = rih / g.B[h];
+        p.b = rih - cell * g.B[h];
+        p.y = cell / g.W[h];
+        p.x = cell - p.y * g.W[h];
+        const float* r = predicts + ((size_t)n * g.rpi + record_of(g, h, p.y, p.x, p.b)) * g.L;
+        const BoxDec d = decode_box(g, p, __ldg(r), __ldg(r + 1), __ldg(r + 2), __ldg(r + 3), __ldg(r + 4));
+        float4* o = reinterpret_cast<float4*>(out + (size_t)pos * YV3_CAND_COLS);
+        o[0] = make_float4(__fdiv_rn(d.x0, g.fW[h]), __fdiv_rn(d.y0, g.fH[h]), __fdiv_rn(d.x1, g.fW[h]),
+                           __fdiv_rn(d.y1, g.fH[h]));                            // :65-68
+        o[1] = make_float4(d.conf, sv.y, (float)__float_as_int(sv.z), sv.x);
     }
 }
 
@@ -177,6 +349,31 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const __grid_c
     if (tid == 0 && base > capacity) atomicOr((unsigned*)status, kStatusCapacity);
 }
 
+// ---- fp64 IoU test of the NMS (shared by the fused small-segment pass and the chunked kernel) -------------
+struct BoxD {
+    double x0, y0, x1, y1, area;
+};
+__device__ __forceinline__ BoxD to_boxd(const float4 b) {
+    BoxD o;
+    o.x0 = (double)b.x; o.y0 = (double)b.y; o.x1 = (double)b.z; o.y1 = (double)b.w;
+    o.area = __dmul_rn(__dsub_rn(o.x1, o.x0), __dsub_rn(o.y1, o.y0));     // (x1 - x0) * (y1 - y0)
+    return o;
+}
+// _cal_iou(box, truth) > thresh  (:132-145, :124): w/h early-out, union = (area_a + area_b) - inter
+__device__ __forceinline__ bool suppresses(const BoxD& a, const BoxD& b, double thresh) {
+    const double w = __dsub_rn(fmin(a.x1, b.x1), fmax(a.x0, b.x0));
+    const double h = __dsub_rn(fmin(a.y1, b.y1), fmax(a.y0, b.y0));
+    if (w <= 0.0 || h <= 0.0) return 0.0 > thresh;
+    const double inter = __dmul_rn(w, h);
+    const double uni = __dsub_rn(__dadd_rn(a.area, b.area), inter);
+    // fl(inter / uni) > thresh is decided without the division unless the quotient lies within 2^-48 (relative)
+    // of the threshold: the products below are off by at most 2^-52 each
+    const double tu = __dmul_rn(thresh, uni);
+    if (inter > __dmul_rn(tu, 1.0000000000000036)) return true;          // 1 + 2^-48
+    if (inter < __dmul_rn(tu, 0.9999999999999964)) return false;         // 1 - 2^-48
+    return __ddiv_rn(inter, uni) > thresh;
+}
+
 // ---- sort: (class asc, score desc, row asc) -----------------------------------------------------------
 constexpr int kSortThreads = 1024;
 constexpr int kSortSmemKeys = 16384;
@@ -207,12 +404,22 @@ __device__ __forceinline__ void bitonic_sort(unsigned long long* keys, int n2, i
     }
 }
 
+constexpr int kFuseMaxK = 4096;         // lists up to this size get their short segments resolved inside the sort kernel
+constexpr int kFuseMaxSeg = 32;         // ... segments up to one warp wide
+
+// One CTA per image: sort keys (class asc, score desc, row asc) in shared memory, publish the sorted order, then --
+// for lists of at most kFuseMaxK candidates -- resolve every class segment of at most 32 candidates right here, one
+// warp per segment: lane j holds candidate j of the segment, the kept candidates are visited in order, each is
+// broadcast from shared memory and tested against the later lanes in fp64 (_apply_nms :117-128).  Longer segments
+// are left to nms_kernel.
 __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restrict__ cand, const int32_t* __restrict__ count,
-                                                            int count_cols, int capacity, int cap2,
+                                                            int count_cols, int capacity, int cap2, int n2s, double thresh,
                                                             unsigned long long* __restrict__ gkeys, float4* __restrict__ sbox,
-                                                            int32_t* __restrict__ sidx) {
+                                                            int32_t* __restrict__ sidx, unsigned char* __restrict__ keep,
+                                                            int2* __restrict__ wl, int32_t* __restrict__ wl_count) {
     extern __shared__ __align__(16) unsigned long long skeys[];
-    const int n = blockIdx.x, tid = threadIdx.x;
+    __shared__ int nseg_s;
+    const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int K = 0;
     for (int c = 0; c < count_cols; ++c) K += count[n * count_cols + c];
     K = max(0, min(K, capacity));
@@ -221,7 +428,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
     if (n2 < 2) n2 = 2;
     const float* rows = cand + (size_t)n * capacity * YV3_CAND_COLS;
     unsigned long long* gk = gkeys + (size_t)n * cap2;
-    unsigned long long* keys = (n2 <= kSortSmemKeys) ? skeys : gk;
+    unsigned long long* keys = (n2 <= n2s) ? skeys : gk;
     for (int i = tid; i < n2; i += kSortThreads) {
         unsigned long long key = kPadKey;
         if (i < K) {
@@ -230,14 +437,52 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
         }
         keys[i] = key;
     }
+    if (tid == 0) nseg_s = 0;
     __syncthreads();
     bitonic_sort(keys, n2, tid);
+    const bool fuse = K <= kFuseMaxK && keys == skeys;
+    float4* box_s = reinterpret_cast<float4*>(skeys + kFuseMaxK);            // [kFuseMaxK]   (fuse only: n2 <= kFuseMaxK)
+    int* seg_s = reinterpret_cast<int*>(box_s + kFuseMaxK);                  // [kFuseMaxK]
     for (int i = tid; i < K; i += kSortThreads) {
         const unsigned long long key = keys[i];
         const int row = (int)(key & 0x3ffffULL);
         if (keys != gk) gk[i] = key;
         sidx[(size_t)n * capacity + i] = row;
-        sbox[(size_t)n * capacity + i] = reinterpret_cast<const float4*>(rows + (size_t)row * YV3_CAND_COLS)[0];
+        const float4 b = reinterpret_cast<const float4*>(rows + (size_t)row * YV3_CAND_COLS)[0];
+        sbox[(size_t)n * capacity + i] = b;
+        const bool starts = i == 0 || (keys[i - 1] >> 50) != (key >> 50);
+        if (fuse) {
+            box_s[i] = b;
+            if (starts) seg_s[atomicAdd(&nseg_s, 1)] = i;
+        } else if (starts) {
+            wl[atomicAdd(wl_count, 1)] = make_int2(n, i);          // every segment of a long list goes to nms_kernel
+        }
+    }
+    if (!fuse) return;
+    __syncthreads();
+    const int nseg = nseg_s;
+    unsigned char* keep_n = keep + (size_t)n * capacity;
+    for (int sg = warp; sg < nseg; sg += kSortThreads / 32) {
+        const int s0 = seg_s[sg];
+        const unsigned long long c0 = keys[s0] >> 50;
+        const int p = s0 + lane;
+        const bool in = p < K && (keys[p] >> 50) == c0;
+        const unsigned members = __ballot_sync(0xffffffffu, in);
+        if (members == 0xffffffffu && s0 + 32 < K && (keys[s0 + 32] >> 50) == c0) {                // longer than a warp
+            if (lane == 0) wl[atomicAdd(wl_count, 1)] = make_int2(n, s0);
+            continue;
+        }
+        const int len = __popc(members);            // members are the low `len` lanes (the list is sorted by class)
+        BoxD mine = {};
+        if (in) mine = to_boxd(box_s[p]);
+        unsigned alive = members;
+        for (int i = 0; i < len - 1; ++i) {
+            if (!((alive >> i) & 1u)) continue;
+            const BoxD bi = to_boxd(box_s[s0 + i]);
+            const bool drop = lane > i && ((alive >> lane) & 1u) && suppresses(bi, mine, thresh);
+            alive &= ~__ballot_sync(0xffffffffu, drop);
+        }
+        if (in) keep_n[(int)(keys[p] & 0x3ffffULL)] = (unsigned char)((alive >> lane) & 1u);
     }
 }
 
@@ -246,30 +491,12 @@ constexpr int kNmsThreads = 256;
 constexpr int kNmsChunk = 256;
 constexpr int kKeptSmem = 2048;
 
-struct BoxD {
-    double x0, y0, x1, y1, area;
-};
-__device__ __forceinline__ BoxD to_boxd(const float4 b) {
-    BoxD o;
-    o.x0 = (double)b.x; o.y0 = (double)b.y; o.x1 = (double)b.z; o.y1 = (double)b.w;
-    o.area = __dmul_rn(__dsub_rn(o.x1, o.x0), __dsub_rn(o.y1, o.y0));     // (x1 - x0) * (y1 - y0)
-    return o;
-}
-// _cal_iou(box, truth) > thresh  (:132-145, :124): w/h early-out, union = (area_a + area_b) - inter
-__device__ __forceinline__ bool suppresses(const BoxD& a, const BoxD& b, double thresh) {
-    const double w = __dsub_rn(fmin(a.x1, b.x1), fmax(a.x0, b.x0));
-    const double h = __dsub_rn(fmin(a.y1, b.y1), fmax(a.y0, b.y0));
-    if (w <= 0.0 || h <= 0.0) return 0.0 > thresh;
-    const double inter = __dmul_rn(w, h);
-    const double uni = __dsub_rn(__dadd_rn(a.area, b.area), inter);
-    return __ddiv_rn(inter, uni) > thresh;
-}
-
 __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const unsigned long long* __restrict__ gkeys,
                                                           const int32_t* __restrict__ count, int count_cols,
                                                           int capacity, int cap2, double thresh,
                                                           const float4* __restrict__ sbox, const int32_t* __restrict__ sidx,
-                                                          float4* __restrict__ kspill, unsigned char* __restrict__ keep) {
+                                                          float4* __restrict__ kspill, unsigned char* __restrict__ keep,
+                                                          const int2* __restrict__ wl, const int32_t* __restrict__ wl_count) {
     __shared__ float4 kept_s[kKeptSmem];
     __shared__ float4 chunk_s[kNmsChunk];
     __shared__ unsigned long long mask_s[kNmsChunk][kNmsChunk / 64];
@@ -277,26 +504,31 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const unsigned long lo
     __shared__ unsigned char kept_flag_s[kNmsChunk];
     __shared__ int seg_s[2];
     __shared__ int nkept_s;
-    const int c = blockIdx.x, n = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nwork = *wl_count;
+  // segments queued by sort_kernel (the ones longer than a warp, and all segments of lists it did not resolve)
+  for (int wi = blockIdx.x; wi < nwork; wi += gridDim.x) {
+    __syncthreads();                                   // shared state of the previous segment is done with
+    const int2 job = wl[wi];
+    const int n = job.x;
     int K = 0;
     for (int q = 0; q < count_cols; ++q) K += count[n * count_cols + q];
     K = max(0, min(K, capacity));
-    if (K == 0) return;
     const unsigned long long* keys = gkeys + (size_t)n * cap2;
-    if (tid < 2) {
-        // first sorted position whose class field is >= c + tid
-        const unsigned long long want = (unsigned long long)(c + tid);
-        int lo = 0, hi = K;
+    if (tid == 0) {
+        // end of the segment: first sorted position whose class field exceeds this segment's
+        const unsigned long long want = (keys[job.y] >> 50) + 1ULL;
+        int lo = job.y, hi = K;
         while (lo < hi) {
             const int mid = (lo + hi) >> 1;
             if ((keys[mid] >> 50) < want) lo = mid + 1; else hi = mid;
         }
-        seg_s[tid] = lo;
+        seg_s[0] = job.y;
+        seg_s[1] = lo;
+        nkept_s = 0;
     }
-    if (tid == 0) nkept_s = 0;
     __syncthreads();
     const int s0 = seg_s[0], s1 = seg_s[1];
-    if (s0 >= s1) return;
     const float4* boxes = sbox + (size_t)n * capacity;
     float4* spill = kspill + (size_t)n * capacity + s0;
     const int32_t* rowof = sidx + (size_t)n * capacity;
@@ -366,40 +598,45 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const unsigned long lo
         if (tid < cnt) keep_n[rowof[c0 + tid]] = kept_flag_s[tid];
         __syncthreads();
     }
+  }
 }
 
 // ---- launchers ------------------------------------------------------------------------------------------
-static TileLaunch score_tiles(const Geo& g, const float* predicts, int n) {
-    TileLaunch q;
+static ScoreTiles score_tiles(const Geo& g, const float* predicts, int n, float thresh) {
+    ScoreTiles q;
     q.total_rec = (long long)n * g.rpi;
     long long tr = (long long)(45056 / ((size_t)g.L * 4));       // ~44 KB per CTA: five CTAs per SM
-    tr = min(tr, (long long)kScoreThreads * 4);
-    if (tr > kScoreThreads) tr = tr / kScoreThreads * kScoreThreads;
+    tr = min(tr, (long long)kScoreThreads);
+    tr = min(tr, (long long)g.rpi);                               // a tile touches at most two images
     tr &= ~3LL;
     if (tr < 4) tr = 4;
     q.tr = (int)tr;
     q.num_tiles = (int)((q.total_rec + tr - 1) / tr);
     q.tma = (((uintptr_t)predicts & 15u) == 0) ? 1 : 0;
+    q.early = (thresh > 2.0f * g.lo) ? 1 : 0;
     return q;
 }
 
+int score_num_tiles(const Geo& g, int n) { return score_tiles(g, nullptr, n, 0.f).num_tiles; }
+
 cudaError_t launch_filter_packed(const Geo& g, const float* predicts, int n, float thresh, float* cand,
-                                 int capacity, int32_t* counts, int32_t* status, float* score, float* prob,
-                                 int32_t* cls, int sm_count, cudaStream_t stream) {
+                                 int capacity, int32_t* counts, int32_t* status, float4* stage, int32_t* tcount,
+                                 int sm_count, cudaStream_t stream) {
     (void)sm_count;
-    const TileLaunch q = score_tiles(g, predicts, n);
+    const ScoreTiles q = score_tiles(g, predicts, n, thresh);
     const size_t smem = (size_t)q.tr * g.L * 4 + 128;
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
-    cudaError_t err = cudaFuncSetAttribute(score_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t err = cudaFuncSetAttribute(score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
-    score_packed_kernel<<<q.num_tiles, kScoreThreads, smem, stream>>>(g, predicts, q, score, prob, cls);
+    score_tile_kernel<<<q.num_tiles, kScoreThreads, smem, stream>>>(g, predicts, q, thresh, stage, tcount);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
-    CompactSrc s;
-    memset(&s, 0, sizeof(s));
-    s.predicts = predicts;
-    s.mode = 0;
-    compact_kernel<<<n, kCompactThreads, 0, stream>>>(g, s, thresh, score, prob, cls, cand, capacity, counts, status);
+    const int ntiles_img = (int)((g.rpi + q.tr - 1) / q.tr) + 2;
+    const size_t gsmem = (size_t)11 * ntiles_img * sizeof(int);
+    if (gsmem > 200 * 1024) return cudaErrorInvalidValue;
+    err = cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem);
+    if (err != cudaSuccess) return err;
+    gather_kernel<<<n, kGatherThreads, gsmem, stream>>>(g, predicts, q, stage, tcount, cand, capacity, counts, status);
     return cudaGetLastError();
 }
 
@@ -433,15 +670,23 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     const int cap2 = nms_cap2(capacity);
     cudaError_t err = cudaMemsetAsync(keep, 0, (size_t)n * capacity, stream);
     if (err != cudaSuccess) return err;
-    const size_t smem = (size_t)min(cap2, kSortSmemKeys) * 8;
+    const int n2s = min(cap2, kSortSmemKeys);
+    // keys, and for short lists (fused pass) the sorted boxes and the segment starts behind the first kFuseMaxK keys
+    const size_t fuse_bytes = (size_t)kFuseMaxK * (8 + 16 + 4);
+    const bool can_fuse = n2s >= 2;
+    const size_t smem = max((size_t)n2s * 8, can_fuse ? fuse_bytes : (size_t)0);
     err = cudaFuncSetAttribute(sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
-    sort_kernel<<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, ws.keys, ws.sbox, ws.sidx);
+    err = cudaMemsetAsync(ws.wl_count, 0, sizeof(int32_t), stream);
+    if (err != cudaSuccess) return err;
+    sort_kernel<<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, n2s, thresh, ws.keys, ws.sbox,
+                                                   ws.sidx, keep, ws.wl, ws.wl_count);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
-    dim3 grid((unsigned)max(num_classes, 1), (unsigned)n);
-    nms_kernel<<<grid, kNmsThreads, 0, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx,
-                                                 ws.kspill, keep);
+    // a fixed grid walks the queue of long segments; with nothing queued every CTA leaves after one load
+    (void)num_classes;
+    nms_kernel<<<296, kNmsThreads, 0, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx,
+                                                ws.kspill, keep, ws.wl, ws.wl_count);
     return cudaGetLastError();
 }
 

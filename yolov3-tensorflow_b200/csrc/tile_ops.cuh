@@ -81,6 +81,49 @@ __device__ __forceinline__ ClassStats class_stats(const float* __restrict__ z, i
     return s;
 }
 
+// The same statistics by a whole WARP (all lanes call it, all lanes get the result), bit for bit: class k lives on
+// lane k & 31 in slot k >> 5; the four interleaved partial sums of class_stats are rebuilt by lanes 0..3, lane r
+// adding the terms of classes r, r + 4, r + 8, ... in increasing order (a shuffle and an add per term); a class past
+// the end contributes +0.0, which leaves a positive sum unchanged.
+__device__ __forceinline__ ClassStats class_stats_warp(const float* __restrict__ z, int C, int lane) {
+    ClassStats s;
+    float mx = -INFINITY;
+    for (int k = lane; k < C; k += 32) mx = fmaxf(mx, z[k]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    int arg = 0x7fffffff, near = 0;
+    float part = 0.f;                                  // lanes 0..3: partial sum r = lane
+    for (int base = 0; base < C; base += 32) {
+        const int k = base + lane;
+        float e = 0.f;
+        if (k < C) {
+            const float v = z[k];
+            if (v == mx && arg == 0x7fffffff) arg = k;
+            const float d = __fsub_rn(v, mx);
+            near += (d >= -2.4e-7f) ? 1 : 0;
+            e = expf(d);
+        }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            const float v = __shfl_sync(0xffffffffu, e, (lane & 3) + 4 * t);
+            part += v;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        arg = min(arg, __shfl_xor_sync(0xffffffffu, arg, o));
+        near += __shfl_xor_sync(0xffffffffu, near, o);
+    }
+    const float s0 = __shfl_sync(0xffffffffu, part, 0), s1 = __shfl_sync(0xffffffffu, part, 1);
+    const float s2 = __shfl_sync(0xffffffffu, part, 2), s3 = __shfl_sync(0xffffffffu, part, 3);
+    const float sum = __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
+    s.mx = mx;
+    s.inv = __fdiv_rn(1.0f, sum);
+    s.arg = arg;
+    s.near = near;
+    return s;
+}
+
 // clip(exp(z - mx) * inv): one class probability
 __device__ __forceinline__ float class_prob(float z, const ClassStats& s, float lo, float hi) {
     return clip_ref(__fmul_rn(expf(__fsub_rn(z, s.mx)), s.inv), lo, hi);

@@ -267,7 +267,7 @@ int yv3_read_status(void* workspace, void* stream) {
 // ---- decode, labels, post-process ------------------------------------------------------------------
 namespace {
 
-PostWs carve_post(void* base, long long rpi, int n, int capacity) {
+PostWs carve_post(void* base, long long rpi, int n, int capacity, int num_tiles = 0) {
     PostWs w;
     size_t off = 0;
     char* p = (char*)base;
@@ -282,10 +282,14 @@ PostWs carve_post(void* base, long long rpi, int n, int capacity) {
     w.score = (float*)take(recs * 4);
     w.prob = (float*)take(recs * 4);
     w.cls = (int32_t*)take(recs * 4);
+    w.stage = (float4*)take((recs + 256) * 16);
+    w.tcount = (int32_t*)take(((size_t)num_tiles + 1) * 8 * 4);
     w.keys = (unsigned long long*)take((size_t)n * nms_cap2(capacity) * 8);
     w.sbox = (float4*)take(rows * 16);
     w.sidx = (int32_t*)take(rows * 4);
     w.kspill = (float4*)take(rows * 16);
+    w.wl = (int2*)take(rows * 8);
+    w.wl_count = (int32_t*)take(256);
     w.bytes = off;
     return w;
 }
@@ -337,7 +341,7 @@ int yv3_query_postprocess_workspace(const yv3_config* cfg, int n, int32_t capaci
         if (rc != YV3_OK) return rc;
         rpi = make_geo(cfg).rpi;
     }
-    *bytes = carve_post(nullptr, rpi, n, capacity).bytes;
+    *bytes = carve_post(nullptr, rpi, n, capacity, cfg ? score_num_tiles(make_geo(cfg), n) : 0).bytes;
     return YV3_OK;
 }
 
@@ -353,7 +357,7 @@ static int post_checks(const yv3_config* cfg, int n, int32_t capacity, void* wor
         if (rc != YV3_OK) return rc;
         rpi = make_geo(cfg).rpi;
     }
-    *ws = carve_post(workspace, rpi, n, capacity);
+    *ws = carve_post(workspace, rpi, n, capacity, cfg ? score_num_tiles(make_geo(cfg), n) : 0);
     if (workspace_bytes < ws->bytes) return YV3_ERR_WORKSPACE;
     return YV3_OK;
 }
@@ -368,8 +372,8 @@ int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float
     cudaStream_t st = (cudaStream_t)stream;
     if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
     const Geo g = make_geo(cfg);
-    if (!cuda_ok(launch_filter_packed(g, predicts, n, score_thresh, cand, capacity, counts, ws.status, ws.score, ws.prob,
-                             ws.cls, sm_count_cached(), st), "launch_filter_packed")) return YV3_ERR_CUDA;
+    if (!cuda_ok(launch_filter_packed(g, predicts, n, score_thresh, cand, capacity, counts, ws.status, ws.stage, ws.tcount,
+                             sm_count_cached(), st), "launch_filter_packed")) return YV3_ERR_CUDA;
     return YV3_OK;
 }
 

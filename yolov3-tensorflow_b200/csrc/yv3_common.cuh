@@ -196,6 +196,13 @@ __device__ __forceinline__ void bulk_wait_all() {
 // make generic-proxy smem writes visible to the async proxy (TMA) before a bulk store reads them
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// 2^x by the special-function unit alone (ex2.approx.ftz): relative error about 2^-22
+__device__ __forceinline__ float exp2f_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -66,16 +66,21 @@ struct PostWs {
     float* score;               // [n][rpi]  head-raster order (filter only)
     float* prob;                // [n][rpi]
     int32_t* cls;               // [n][rpi]
+    float4* stage;              // [num_tiles][tr] staged survivors of the fused filter (score, prob, class, record)
+    int32_t* tcount;            // [num_tiles][8] survivors per tile and (image slot, head)
     unsigned long long* keys;   // [n][cap2] sorted keys (class | ~score | row)
     float4* sbox;               // [n][capacity] boxes in sorted order
     int32_t* sidx;              // [n][capacity] original row of a sorted position
     float4* kspill;             // [n][capacity] kept boxes beyond the shared-memory list
+    int2* wl;                   // [n][capacity] queue of (image, first sorted position) of segments for nms_kernel
+    int32_t* wl_count;
     size_t bytes;
 };
 int nms_cap2(int capacity);
+int score_num_tiles(const Geo& g, int n);
 cudaError_t launch_filter_packed(const Geo& g, const float* predicts, int n, float thresh, float* cand,
-                                 int capacity, int32_t* counts, int32_t* status, float* score, float* prob,
-                                 int32_t* cls, int sm_count, cudaStream_t stream);
+                                 int capacity, int32_t* counts, int32_t* status, float4* stage, int32_t* tcount,
+                                 int sm_count, cudaStream_t stream);
 cudaError_t launch_filter_decoded(const Geo& g, const float* const decoded[3], const float* const boxes[3],
                                   float thresh, float* cand, int capacity, int32_t* counts, int32_t* status,
                                   float* score, float* prob, int32_t* cls, int sm_count, cudaStream_t stream);
