@@ -42,29 +42,54 @@ constexpr int kScoreThreads = 128;
 // gather_kernel then turns counts into the reference's order (head /8,/16,/32, raster inside a head) per image and
 // writes the candidate rows, decoding each survivor's box from its five logits.
 struct ScoreTiles {
-    int tr;                 // records per tile (multiple of 4, <= kScoreThreads, <= records per image)
+    int tr;                 // records per tile = per WARP (multiple of 4, <= 32, <= records per image)
+    int wpc;                // warps (tiles) per CTA
+    int tile_floats;        // shared-memory floats reserved per tile (tr * L rounded up to 16 bytes)
     int num_tiles;
     long long total_rec;
     int tma;
     int early;              // threshold large enough for the approximate early-out (thresh > 2 * eps)
 };
 
+// A tile is the <= 32 consecutive records of ONE WARP: the warp lands it in its own slice of shared memory with
+// its own bulk copy and mbarrier, scores, ranks and stages it without ever meeting the other warps of the CTA (the
+// CTA only bundles warps so that their buffers fill the SM's shared memory).
 __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_constant__ Geo g,
                                                                    const float* __restrict__ predicts, const ScoreTiles q,
                                                                    float thresh, float4* __restrict__ stage,
                                                                    int32_t* __restrict__ tcount) {
     extern __shared__ __align__(128) unsigned char ssm[];
-    __shared__ uint64_t bar;
-    __shared__ int wcnt_s[kScoreThreads / 32][8];
+    __shared__ uint64_t bar_s[kScoreThreads / 32];
     const int L = g.L, C = g.C, tr = q.tr;
-    float* tile = (float*)ssm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long rec0 = (long long)blockIdx.x * tr;
+    const int unit = blockIdx.x * q.wpc + warp;
+    if (warp >= q.wpc || unit >= q.num_tiles) return;
+    float* tile = (float*)ssm + (size_t)warp * q.tile_floats;
+    const long long rec0 = (long long)unit * tr;
     const int nrec = (int)min((long long)tr, q.total_rec - rec0);
-    tile_load<kScoreThreads>(tile, predicts + (size_t)rec0 * L, nrec * L, q.tma, &bar);
+    {
+        const float* src = predicts + (size_t)rec0 * L;
+        const int nfl = nrec * L;
+        const unsigned bulk = q.tma ? (unsigned)(((size_t)nfl * 4) & ~(size_t)15) : 0u;
+        if (bulk) {
+            uint64_t* bar = &bar_s[warp];
+            if (lane == 0) {
+                mbar_init(bar, 1);
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                mbar_expect_tx(bar, bulk);
+                bulk_g2s(tile, src, bulk, bar);
+            }
+            for (int i = (int)(bulk / 4) + lane; i < nfl; i += 32) tile[i] = __ldg(src + i);
+            __syncwarp();                              // barrier init visible to every lane
+            mbar_wait(bar, 0);
+        } else {
+            for (int i = lane; i < nfl; i += 32) tile[i] = __ldg(src + i);
+        }
+        __syncwarp();
+    }
 
-    const bool have = tid < nrec;
-    const float* r = tile + (size_t)tid * L;
+    const bool have = lane < nrec;
+    const float* r = tile + (size_t)lane * L;
     float conf = 0.f;
     bool maybe = false;
     if (have) {
@@ -96,7 +121,7 @@ __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_
         while (mb) {
             const int src = __ffs(mb) - 1;
             mb &= mb - 1;
-            const float* rr = tile + (size_t)(warp * 32 + src) * L;
+            const float* rr = tile + (size_t)src * L;
             const ClassStats cs = class_stats_warp(rr + 5, C, lane);
             float best = clip_ref(cs.inv, g.lo, g.hi);
             int arg = cs.arg;
@@ -113,36 +138,26 @@ __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_
     }
     const bool pass = have && mine.w != 0.f;
 
-    // ---- rank inside the tile per (image slot, head) ---------------------------------------------------------
-    const long long grec = rec0 + tid;
+    // ---- rank inside the tile per (image slot, head): ballots only -----------------------------------------
     const int n_first = (int)(rec0 / g.rpi);
-    int n_img = n_first, r_img = (int)(rec0 - (long long)n_first * g.rpi) + tid;
+    int n_img = n_first, r_img = (int)(rec0 - (long long)n_first * g.rpi) + lane;
     if (r_img >= g.rpi) { r_img -= g.rpi; ++n_img; }
     RecLoc p = {0, 0, 0, 0};
     if (have) p = locate(g, r_img);
     const int grp = have ? (n_img - n_first) * 3 + p.h : 7;
-    int my_rank = 0;
-    (void)grec;
+    int my_rank = 0, my_base = 0, run = 0, cnt_lane = 0;
 #pragma unroll
     for (int gi = 0; gi < 6; ++gi) {
         const unsigned b = __ballot_sync(0xffffffffu, pass && grp == gi);
-        if (grp == gi) my_rank = __popc(b & ((1u << lane) - 1u));
-        if (lane == 0) wcnt_s[warp][gi] = __popc(b);
+        if (grp == gi) { my_rank = __popc(b & ((1u << lane) - 1u)); my_base = run; }
+        if (lane == gi) cnt_lane = __popc(b);
+        run += __popc(b);
     }
-    __syncthreads();
     if (pass) {
-        int base = 0;
-        for (int gi = 0; gi < grp; ++gi)
-            for (int w = 0; w < kScoreThreads / 32; ++w) base += wcnt_s[w][gi];
-        for (int w = 0; w < warp; ++w) base += wcnt_s[w][grp];
         const int rih = (p.y * g.W[p.h] + p.x) * g.B[p.h] + p.b;
-        stage[(size_t)blockIdx.x * tr + base + my_rank] = make_float4(mine.x, mine.y, mine.z, __int_as_float(rih));
+        stage[(size_t)unit * tr + my_base + my_rank] = make_float4(mine.x, mine.y, mine.z, __int_as_float(rih));
     }
-    if (tid < 6) {
-        int c = 0;
-        for (int w = 0; w < kScoreThreads / 32; ++w) c += wcnt_s[w][tid];
-        tcount[(size_t)blockIdx.x * 8 + tid] = c;
-    }
+    if (lane < 6) tcount[(size_t)unit * 8 + lane] = cnt_lane;
 }
 
 // One CTA per image: the tiles' counts go to shared memory, an exclusive prefix per head puts them in the reference's
@@ -605,13 +620,15 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const unsigned long lo
 static ScoreTiles score_tiles(const Geo& g, const float* predicts, int n, float thresh) {
     ScoreTiles q;
     q.total_rec = (long long)n * g.rpi;
-    long long tr = (long long)(45056 / ((size_t)g.L * 4));       // ~44 KB per CTA: five CTAs per SM
-    tr = min(tr, (long long)kScoreThreads);
+    long long tr = 32;
+    tr = min(tr, (long long)(200 * 1024) / ((long long)g.L * 4));   // a very long record: fewer records per warp
     tr = min(tr, (long long)g.rpi);                               // a tile touches at most two images
     tr &= ~3LL;
-    if (tr < 4) tr = 4;
-    q.tr = (int)tr;
-    q.num_tiles = (int)((q.total_rec + tr - 1) / tr);
+    q.tr = (int)max(tr, 0LL);
+    q.tile_floats = (int)(align_up((size_t)max(q.tr, 1) * g.L * 4, 128) / 4);
+    // ~44 KB of tiles per CTA (five CTAs per SM), at most four warps
+    q.wpc = (int)max(1LL, min((long long)(kScoreThreads / 32), (long long)45056 / ((long long)q.tile_floats * 4)));
+    q.num_tiles = q.tr ? (int)((q.total_rec + q.tr - 1) / q.tr) : 0;
     q.tma = (((uintptr_t)predicts & 15u) == 0) ? 1 : 0;
     q.early = (thresh > 2.0f * g.lo) ? 1 : 0;
     return q;
@@ -624,11 +641,13 @@ cudaError_t launch_filter_packed(const Geo& g, const float* predicts, int n, flo
                                  int sm_count, cudaStream_t stream) {
     (void)sm_count;
     const ScoreTiles q = score_tiles(g, predicts, n, thresh);
-    const size_t smem = (size_t)q.tr * g.L * 4 + 128;
-    if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    if (q.tr < 4) return cudaErrorInvalidValue;
+    const size_t smem = (size_t)q.wpc * q.tile_floats * 4;
+    if (smem > 220 * 1024) return cudaErrorInvalidValue;
     cudaError_t err = cudaFuncSetAttribute(score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
-    score_tile_kernel<<<q.num_tiles, kScoreThreads, smem, stream>>>(g, predicts, q, thresh, stage, tcount);
+    const int grid = (q.num_tiles + q.wpc - 1) / q.wpc;
+    score_tile_kernel<<<grid, 32 * q.wpc, smem, stream>>>(g, predicts, q, thresh, stage, tcount);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
     const int ntiles_img = (int)((g.rpi + q.tr - 1) / q.tr) + 2;
