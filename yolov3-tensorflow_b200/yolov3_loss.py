@@ -60,6 +60,10 @@ class YOLOv3Loss(object):
         self.records_per_image = int(self._lib.yv3_records_per_image(ctypes.byref(self._cfg)))
         self.packed_floats_per_image = int(self._lib.yv3_packed_floats_per_image(ctypes.byref(self._cfg)))
         self.process_group = process_group
+        # False: the caller sums the 20 loss floats over the ranks itself with all_reduce_detail() (e.g. after replaying
+        # a CUDA graph that holds this rank's launches)
+        self.auto_all_reduce = True
+        self._last_out = None
         # host-visible state of the tf.cond at yolov3_loss.py:125 (a bare backend variable there, :69)
         self.current_num = 0
         self._ws = {}
@@ -129,8 +133,9 @@ class YOLOv3Loss(object):
             events[1].record()
         if rect_active:
             self.current_num += n_global                                       # update_add (:152)
-        if world > 1:
+        if world > 1 and self.auto_all_reduce:
             self._all_reduce(out)
+        self._last_out = out
         self._last_ws = ws
         detail = out[:18].view(6, 3)
         self.loss_detail = detail
@@ -154,6 +159,11 @@ class YOLOv3Loss(object):
         ``grad_out`` reuses a caller-owned gradient buffer; ``events`` = (start, stop) CUDA events recorded
         around the dense sweep alone."""
         return self._run(targets, predicts, want_grad=True, upstream=upstream, events=events, grad_out=grad_out)
+
+    def all_reduce_detail(self):
+        """Sum the last call's 20 loss floats over the ranks (only needed with ``auto_all_reduce = False``)."""
+        if self._last_out is not None and self._world() > 1:
+            self._all_reduce(self._last_out)
 
     def assign(self, targets, predicts):
         """The integer decisions of the loss: (table (N,M,3,4) int32 [row, col, best_anchor, owned] per
