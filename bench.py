@@ -181,6 +181,9 @@ def main():
     ap.add_argument("--workload", default="cfg2_416_c80_b64", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--overlap", type=int, default=1, help="1: loss and post-process halves of a step on two streams")
+    ap.add_argument("--graph-steps", type=int, default=1, help="steps captured per CUDA graph (N = 1)")
+    ap.add_argument("--force-graph", action="store_true", help="skip the eager-vs-graph trial")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA-graph replay")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -216,10 +219,23 @@ def main():
     counts = torch.empty((n, 3), dtype=torch.int32, device=dev)
     keep = torch.empty((n, post.capacity), dtype=torch.uint8, device=dev)
 
+    post_stream = torch.cuda.Stream() if args.overlap else None
+
     def step(events=None):
-        total, _ = loss.loss_and_grad(td, pd, events=events, grad_out=grad)
-        post.filter(pd, w["score_thresh"], out=(cand, counts))
-        post.nms(cand, counts, w["nms_thresh"], out=keep)
+        if post_stream is None or events is not None:
+            total, _ = loss.loss_and_grad(td, pd, events=events, grad_out=grad)
+            post.filter(pd, w["score_thresh"], out=(cand, counts))
+            post.nms(cand, counts, w["nms_thresh"], out=keep)
+            return total
+        # the training half (assignment, dense pass) and the inference half (filter, sort, NMS) of a step share only
+        # their input: two streams, so the latency-bound post-process kernels run in the shadow of the dense pass
+        cur = torch.cuda.current_stream()
+        post_stream.wait_stream(cur)
+        with torch.cuda.stream(post_stream):
+            post.filter(pd, w["score_thresh"], out=(cand, counts))
+            post.nms(cand, counts, w["nms_thresh"], out=keep)
+        total, _ = loss.loss_and_grad(td, pd, grad_out=grad)
+        cur.wait_stream(post_stream)
         return total
 
     def fence():
@@ -252,6 +268,8 @@ def main():
     # the timed region: the whole step (assignment, dense pass, all-reduce at N > 1, filter, NMS) captured once in a
     # CUDA graph and replayed K times -- the launch-bound host loop is out of the way, the device work is identical
     graph, mode = None, "eager"
+    # several steps per graph (no collective inside at N = 1): consecutive steps overlap like eager launches do
+    unroll = args.graph_steps if world == 1 else 1
     if not args.no_graph:
         try:
             loss.auto_all_reduce = False                           # the collective stays outside the graph
@@ -262,27 +280,63 @@ def main():
             torch.cuda.current_stream().wait_stream(side)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                step()
-            mode = "cuda-graph replay" + (" + eager NCCL all-reduce of the 20 loss floats" if world > 1 else "")
+                for _ in range(unroll):
+                    step()
+            mode = "cuda-graph replay, %d step(s) per graph" % unroll + (" + eager NCCL all-reduce of the 20 loss floats" if world > 1 else "")
         except Exception as e:
             graph, mode = None, "eager (graph capture failed: %s)" % type(e).__name__
             torch.cuda.synchronize()
     if graph is None:
         loss.auto_all_reduce = True
 
-    def run():
+    def run(count):
+        """exactly `count` steps"""
         if graph is None:
-            return step()
-        graph.replay()
-        loss.all_reduce_detail()
-    for _ in range(3):
-        run()
+            for _ in range(count):
+                step()
+            return
+        for _ in range(count // unroll):
+            graph.replay()
+            loss.all_reduce_detail()
+        rest = count % unroll
+        if rest:
+            loss.auto_all_reduce = True
+            for _ in range(rest):
+                step()
+            loss.auto_all_reduce = False
+    run(3 * unroll)
     fence()
+    if graph is not None and not args.force_graph:
+        # launch mode by trial: the host may launch eagerly fast enough for consecutive steps to overlap better than
+        # graph replays do; 20 steps each, the faster one is used for the timed region
+        def trial(fn):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            fence()
+            a.record()
+            fn()
+            b.record()
+            fence()
+            return a.elapsed_time(b)
+
+        def eager20():
+            loss.auto_all_reduce = True
+            for _ in range(20):
+                step()
+            loss.auto_all_reduce = False
+
+        t_graph = trial(lambda: run(20 - 20 % unroll))
+        t_eager = trial(eager20)
+        verdict = torch.tensor([t_graph, t_eager], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(verdict, op=dist.ReduceOp.MAX)
+        if float(verdict[1]) < float(verdict[0]):
+            graph, mode = None, "eager launches (faster than graph replay in a 20-step trial: %.1f vs %.1f us/step)" % (
+                1e3 * float(verdict[1]) / 20, 1e3 * float(verdict[0]) / (20 - 20 % unroll))
+            loss.auto_all_reduce = True
     start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.mark = "timed"
     start.record()
-    for k in range(args.steps):
-        run()
+    run(args.steps)
     stop.record()
     fence()
     sampler.mark = "after"
@@ -356,7 +410,7 @@ def main():
                        "l2": "inputs larger than L2: predicts %.0f MB + gradient %.0f MB per GPU vs 126 MB L2" % (
                            pd.numel() * 4 / 1e6, grad.numel() * 4 / 1e6),
                        "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image,
-                       "launch": mode},
+                       "launch": mode, "streams": 2 if args.overlap else 1},
             "stage_ms": {"loss_dense_kernel": dense_ms, "filter_plus_nms": post_ms,
                          "assign_and_gaps": total_ms / args.steps - dense_ms - post_ms,
                          "note": "stage times from eager launches with events; ms_per_step from the timed region"},

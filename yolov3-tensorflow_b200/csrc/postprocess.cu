@@ -419,6 +419,33 @@ __device__ __forceinline__ void bitonic_sort(unsigned long long* keys, int n2, i
     }
 }
 
+// Lists of at most kSortThreads keys: one key per thread in a register; compare-exchange partners closer than a warp
+// are reached by shuffles, the others through shared memory (15 of the 55 steps at 1024 keys).  `keys` must be shared
+// memory; on return keys[0..n2) is sorted.
+__device__ __forceinline__ void bitonic_sort_regs(unsigned long long* keys, int n2, int tid) {
+    unsigned long long mine = (tid < n2) ? keys[tid] : kPadKey;
+    for (int k = 2; k <= n2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            unsigned long long other;
+            if (j >= 32) {
+                __syncthreads();                      // partners have read the previous round's values
+                if (tid < n2) keys[tid] = mine;
+                __syncthreads();
+                other = (tid < n2) ? keys[tid ^ j] : kPadKey;
+            } else {
+                other = __shfl_xor_sync(0xffffffffu, mine, j);
+            }
+            const bool lower = (tid & j) == 0, up = (tid & k) == 0;
+            const bool take_min = lower == up;
+            const unsigned long long mn = mine < other ? mine : other, mx = mine < other ? other : mine;
+            mine = take_min ? mn : mx;
+        }
+    }
+    __syncthreads();
+    if (tid < n2) keys[tid] = mine;
+    __syncthreads();
+}
+
 constexpr int kFuseMaxK = 4096;         // lists up to this size get their short segments resolved inside the sort kernel
 constexpr int kFuseMaxSeg = 32;         // ... segments up to one warp wide
 
@@ -454,7 +481,8 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
     }
     if (tid == 0) nseg_s = 0;
     __syncthreads();
-    bitonic_sort(keys, n2, tid);
+    if (keys == skeys && n2 <= kSortThreads) bitonic_sort_regs(keys, n2, tid);
+    else bitonic_sort(keys, n2, tid);
     const bool fuse = K <= kFuseMaxK && keys == skeys;
     float4* box_s = reinterpret_cast<float4*>(skeys + kFuseMaxK);            // [kFuseMaxK]   (fuse only: n2 <= kFuseMaxK)
     int* seg_s = reinterpret_cast<int*>(box_s + kFuseMaxK);                  // [kFuseMaxK]
@@ -489,12 +517,17 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
         }
         const int len = __popc(members);            // members are the low `len` lanes (the list is sorted by class)
         BoxD mine = {};
-        if (in) mine = to_boxd(box_s[p]);
+        float4 mine_f = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (in) { mine_f = box_s[p]; mine = to_boxd(mine_f); }
         unsigned alive = members;
         for (int i = 0; i < len - 1; ++i) {
             if (!((alive >> i) & 1u)) continue;
-            const BoxD bi = to_boxd(box_s[s0 + i]);
-            const bool drop = lane > i && ((alive >> lane) & 1u) && suppresses(bi, mine, thresh);
+            const float4 fi = box_s[s0 + i];
+            // the coordinates are fp32 values: min/max and the comparison are exact, so boxes that do not overlap
+            // (width or height <= 0, :139-142) never reach the fp64 arithmetic
+            const bool overlap = fminf(fi.z, mine_f.z) > fmaxf(fi.x, mine_f.x) && fminf(fi.w, mine_f.w) > fmaxf(fi.y, mine_f.y);
+            bool drop = lane > i && ((alive >> lane) & 1u);
+            if (drop) drop = overlap ? suppresses(to_boxd(fi), mine, thresh) : (0.0 > thresh);
             alive &= ~__ballot_sync(0xffffffffu, drop);
         }
         if (in) keep_n[(int)(keys[p] & 0x3ffffULL)] = (unsigned char)((alive >> lane) & 1u);
