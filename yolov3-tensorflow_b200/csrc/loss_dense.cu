@@ -148,12 +148,16 @@ __device__ __forceinline__ void gt_refill(float* slot, const DenseArgs& a, int n
     }
 }
 
-template <int VEC, int SGT>
-__global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_constant__ Geo g,
-                                                                 const __grid_constant__ DenseArgs a) {
+// ZW: a ninth warp does nothing but the zero fill of the CTA's chunks (those without an owning record), so that the
+// eight computing warps never queue behind the store stream; the sectors it writes and the sectors the record lanes
+// write are disjoint, so the two never need to meet.
+template <int VEC, int SGT, int ZW>
+__global__ void __launch_bounds__(kThreads + 32 * ZW, 3) loss_dense_kernel(const __grid_constant__ Geo g,
+                                                                           const __grid_constant__ DenseArgs a) {
     extern __shared__ __align__(16) float gt_s[];          // SGT: [kWarps][2][gt_slot_floats(m)], then the zero block
-    __shared__ float red_s[kWarps][12];
+    __shared__ float red_s[kWarps + 1][12];
     __shared__ float stage_s[VEC ? 1 : kWarps * 32 * kSmallL];
+    const int nthreads = kThreads + 32 * ZW, nwarps = kWarps + ZW;
     const bool with_grad = a.grad != nullptr && !(a.debug & 8);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int L = g.L, C = g.C, m = a.m;
@@ -186,10 +190,11 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
 
     // a warp owns a.cpw consecutive chunks (the launcher sizes the grid so that every warp gets the same number):
     // it stays inside one or two images, whose labels it keeps in its shared-memory slots
-    int cur = (blockIdx.x * kWarps + warp) * a.cpw;
-    const int cend = min(cur + a.cpw, a.num_chunks);
+    const bool zero_warp = ZW && warp == kWarps;
+    int cur = zero_warp ? 0 : (blockIdx.x * kWarps + warp) * a.cpw;
+    const int cend = zero_warp ? 0 : min(cur + a.cpw, a.num_chunks);
     int nxt = cur + 1;
-    float* slots = gt_s + (size_t)warp * 2 * gt_slot_floats(m);
+    float* slots = gt_s + (size_t)(zero_warp ? 0 : warp) * 2 * gt_slot_floats(m);
     int held0 = -1, held1 = -1;                      // image held by slot 0 / 1 (warp-uniform)
     Logits qv = load_logits<VEC>(a.predicts, (long long)cur * 32 + lane, L,
                                  cur < cend && (long long)cur * 32 + lane < a.total_rec);
@@ -202,7 +207,7 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
     float* zblk = gt_s + (SGT ? (size_t)kWarps * 2 * gt_slot_floats(m) : 0);
     const unsigned chunk_bytes = 128u * (unsigned)L;
     if (bulk) {
-        for (int i = tid; i < a.zero_bytes / 4; i += kThreads) zblk[i] = 0.f;
+        for (int i = tid; i < a.zero_bytes / 4; i += nthreads) zblk[i] = 0.f;
         fence_async_smem();
         __syncthreads();
         if (lane == 0 && cur < cend && cur != a.num_chunks - 1) {
@@ -210,6 +215,38 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
             for (unsigned o = 0; o < chunk_bytes; o += (unsigned)a.zero_bytes)
                 bulk_s2g(dst + o, zblk, min((unsigned)a.zero_bytes, chunk_bytes - o));
             bulk_commit();
+        }
+    }
+
+    if (zero_warp && with_grad && wide && !(a.debug & 512)) {
+        const int c0 = blockIdx.x * kWarps * a.cpw, c1 = min(c0 + kWarps * a.cpw, a.num_chunks);
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int c = c0; c < c1; ++c) {
+            // chunks with an owning record (their class gradient is written on top of the zeros) and the tensor's
+            // last chunk stay with the computing warp
+            if (c == a.num_chunks - 1 || __ldg(a.objbits + c) != 0u) continue;
+            float4* gl = reinterpret_cast<float4*>(a.grad) + (size_t)c * 8 * L + lane;
+            unsigned mk = zlo;
+            const int t32 = min(trips, 32);
+#pragma unroll 8
+            for (int k = 0; k < t32; ++k) {
+                if (mk & 1u) __stcs(gl + 32 * k, z4);
+                mk >>= 1;
+            }
+            if (trips > 32) {
+                mk = zhi;
+                const int t64 = min(trips, 64);
+                for (int k = 32; k < t64; ++k) {
+                    if (mk & 1u) __stcs(gl + 32 * k, z4);
+                    mk >>= 1;
+                }
+                int q = q64;
+                for (int k = 64; k < trips; ++k) {
+                    if (lane + 32 * k < 8 * L && q > 4 && q < L - 7) __stcs(gl + 32 * k, z4);
+                    q += dq;
+                    q -= (q >= L) ? L : 0;
+                }
+            }
         }
     }
 
@@ -238,6 +275,8 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                 const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (fast && bulk) {
                     // zeros already on their way (issued one chunk ahead)
+                } else if (fast && ZW && objw == 0u) {
+                    // the CTA's zero warp covers this chunk
                 } else if (fast) {
                     float4* gl = gdst + lane;
                     unsigned mk = zlo;
@@ -378,7 +417,7 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
                     }
                     __syncwarp();
                 }
-                if (ok) {
+                if (ok && !(a.debug & 256)) {
                     const int pos = (int)(off & 7);
                     const Win12 w = compose(gv, pos);
                     float4* o = reinterpret_cast<float4*>(a.grad) + ((off >> 3) << 1);
@@ -487,7 +526,7 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
     __syncthreads();
     if (tid < 9) {
         float acc = 0.f;
-        for (int w = 0; w < kWarps; ++w) acc += red_s[w][tid];
+        for (int w = 0; w < nwarps; ++w) acc += red_s[w][tid];
         a.partials[(size_t)blockIdx.x * kPartialFloats + tid] = acc;
     }
     __shared__ int is_last;
@@ -502,18 +541,18 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
     __threadfence();
     // the last CTA: all 256 threads fold the partial rows (thread t takes rows t, t + 256, ... in index order,
     // in double), lanes fold by shuffles, warps through shared memory: a fixed order => a deterministic sum
-    __shared__ double fold_s[kWarps][18];
+    __shared__ double fold_s[kWarps + 1][18];
     double part[18];
 #pragma unroll
     for (int k = 0; k < 18; ++k) part[k] = 0.0;
-    for (int b = tid; b < (int)gridDim.x; b += kThreads) {
+    for (int b = tid; b < (int)gridDim.x; b += nthreads) {
         const float4* row = reinterpret_cast<const float4*>(a.partials + (size_t)b * kPartialFloats);
         const float4 r0 = __ldcg(row), r1 = __ldcg(row + 1), r2 = __ldcg(row + 2);
         part[0] += (double)r0.x; part[1] += (double)r0.y; part[2] += (double)r0.z;      // noobj
         part[3] += (double)r0.w; part[4] += (double)r1.x; part[5] += (double)r1.y;      // cls
         part[6] += (double)r1.z; part[7] += (double)r1.w; part[8] += (double)r2.x;      // rect
     }
-    for (int i = tid; i < a.n; i += kThreads) {
+    for (int i = tid; i < a.n; i += nthreads) {
 #pragma unroll
         for (int k = 0; k < 9; ++k) part[9 + k] += (double)__ldcg(a.img_terms + (size_t)i * 9 + k);   // xy, wh, obj
     }
@@ -532,7 +571,7 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
         const int src = (row == 0) ? 9 + h : (row == 1) ? 12 + h : (row == 2) ? h : (row == 3) ? 15 + h
                       : (row == 4) ? 3 + h : 6 + h;
         double acc = 0.0;
-        for (int w = 0; w < kWarps; ++w) acc += fold_s[w][src];
+        for (int w = 0; w < nwarps; ++w) acc += fold_s[w][src];
         if (row == 2) acc *= (double)g.lw[h][2];
         else if (row == 4) acc *= (double)g.lw[h][4];
         else if (row == 5) acc = a.rect_active ? acc * (double)g.rw[h] : 0.0;
@@ -551,15 +590,15 @@ __global__ void __launch_bounds__(kThreads, 3) loss_dense_kernel(const __grid_co
     }
 }
 
-template <int VEC, int SGT>
+template <int VEC, int SGT, int ZW>
 static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, cudaStream_t stream) {
-    a.bulk = (VEC && g.L >= kWideL && !(a.debug & 64)) ? 1 : 0;
+    a.bulk = (VEC && !ZW && g.L >= kWideL && !(a.debug & 64)) ? 1 : 0;
     a.zero_bytes = a.bulk ? (int)min(128LL * g.L, 16384LL) : 0;
     const size_t smem = (SGT ? (size_t)kWarps * 2 * gt_slot_floats(a.m) * sizeof(float) : 0) + (size_t)a.zero_bytes;
-    cudaError_t err = cudaFuncSetAttribute(loss_dense_kernel<VEC, SGT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t err = cudaFuncSetAttribute(loss_dense_kernel<VEC, SGT, ZW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     int per_sm = 1;
-    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_dense_kernel<VEC, SGT>, kThreads, smem);
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_dense_kernel<VEC, SGT, ZW>, kThreads + 32 * ZW, smem);
     if (err != cudaSuccess) return err;
     if (per_sm < 1) per_sm = 1;
     // two consecutive chunks per warp (the second one's logits and zero fill are in flight while the first is
@@ -575,7 +614,7 @@ static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, cuda
         if (v >= 1 && need <= kMaxGrid) a.cpw = v;
     }
     const int grid = (int)max(1LL, ((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps));
-    loss_dense_kernel<VEC, SGT><<<grid, kThreads, smem, stream>>>(g, a);
+    loss_dense_kernel<VEC, SGT, ZW><<<grid, kThreads + 32 * ZW, smem, stream>>>(g, a);
     return cudaGetLastError();
 }
 
@@ -599,8 +638,12 @@ cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStrea
     // labels in shared memory when they fit (2 slots per warp) and a chunk touches at most two images
     const bool sgt = a.m <= 32 && g.rpi >= 32 && !(a.debug & 16);
     const bool vec = a.vec_ok && g.L >= kSmallL;
-    if (vec) return sgt ? launch_variant<1, 1>(g, a, sm_count, stream) : launch_variant<1, 0>(g, a, sm_count, stream);
-    return sgt ? launch_variant<0, 1>(g, a, sm_count, stream) : launch_variant<0, 0>(g, a, sm_count, stream);
+    // measured on B200 (profiles/r01_dense_variants.txt): the zero warp does not pay (88 vs 83 us at cfg2); kept as a
+    // developer switch (YV3_DEBUG bit 128)
+    const bool zw = vec && g.L >= kWideL && a.grad != nullptr && (a.debug & 128);
+    if (vec && zw) return sgt ? launch_variant<1, 1, 1>(g, a, sm_count, stream) : launch_variant<1, 0, 1>(g, a, sm_count, stream);
+    if (vec) return sgt ? launch_variant<1, 1, 0>(g, a, sm_count, stream) : launch_variant<1, 0, 0>(g, a, sm_count, stream);
+    return sgt ? launch_variant<0, 1, 0>(g, a, sm_count, stream) : launch_variant<0, 0, 0>(g, a, sm_count, stream);
 }
 
 }  // namespace yv3

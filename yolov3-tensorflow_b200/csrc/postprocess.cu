@@ -15,7 +15,7 @@
 //   score_decoded_kernel / compact_kernel   the same for already decoded heads of one image (filter_boxes' inputs).
 //   sort_kernel           one CTA per image: 64-bit keys (class | ~score | row) bitonic-sorted in shared
 //                         memory (global memory beyond 16 Ki candidates).
-//   nms_kernel            one CTA per (class, image) segment: 256-candidate chunks; each chunk is first
+//   nms_kernel<T>         persistent CTAs over the queued long segments, T-candidate chunks; each chunk is first
 //                         tested against the boxes kept so far, then resolved internally with a
 //                         shared-memory IoU bit matrix and a warp sweep.  IoU is fp64, uncontracted, in the
 //                         reference's operation order.
@@ -446,6 +446,8 @@ __device__ __forceinline__ void bitonic_sort_regs(unsigned long long* keys, int 
     __syncthreads();
 }
 
+constexpr int kNmsMedium = 256;         // threads = chunk size of the NMS kernel for segments of 33..256 candidates
+constexpr int kNmsLarge = 1024;         // ... and for longer ones
 constexpr int kFuseMaxK = 4096;         // lists up to this size get their short segments resolved inside the sort kernel
 constexpr int kFuseMaxSeg = 32;         // ... segments up to one warp wide
 
@@ -458,7 +460,8 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
                                                             int count_cols, int capacity, int cap2, int n2s, double thresh,
                                                             unsigned long long* __restrict__ gkeys, float4* __restrict__ sbox,
                                                             int32_t* __restrict__ sidx, unsigned char* __restrict__ keep,
-                                                            int2* __restrict__ wl, int32_t* __restrict__ wl_count) {
+                                                            int2* __restrict__ wl, int2* __restrict__ wl_large,
+                                                            int32_t* __restrict__ wl_count) {
     extern __shared__ __align__(16) unsigned long long skeys[];
     __shared__ int nseg_s;
     const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -498,7 +501,10 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
             box_s[i] = b;
             if (starts) seg_s[atomicAdd(&nseg_s, 1)] = i;
         } else if (starts) {
-            wl[atomicAdd(wl_count, 1)] = make_int2(n, i);          // every segment of a long list goes to nms_kernel
+            // every segment of a long list goes to nms_kernel: the wide kernel when it exceeds 256 candidates
+            const bool large = i + kNmsMedium < K && (keys[i + kNmsMedium] >> 50) == (key >> 50);
+            if (large) wl_large[atomicAdd(wl_count + 1, 1)] = make_int2(n, i);
+            else wl[atomicAdd(wl_count, 1)] = make_int2(n, i);
         }
     }
     if (!fuse) return;
@@ -512,7 +518,11 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
         const bool in = p < K && (keys[p] >> 50) == c0;
         const unsigned members = __ballot_sync(0xffffffffu, in);
         if (members == 0xffffffffu && s0 + 32 < K && (keys[s0 + 32] >> 50) == c0) {                // longer than a warp
-            if (lane == 0) wl[atomicAdd(wl_count, 1)] = make_int2(n, s0);
+            if (lane == 0) {
+                const bool large = s0 + kNmsMedium < K && (keys[s0 + kNmsMedium] >> 50) == c0;
+                if (large) wl_large[atomicAdd(wl_count + 1, 1)] = make_int2(n, s0);
+                else wl[atomicAdd(wl_count, 1)] = make_int2(n, s0);
+            }
             continue;
         }
         const int len = __popc(members);            // members are the low `len` lanes (the list is sorted by class)
@@ -535,26 +545,40 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
 }
 
 // ---- greedy NMS per (class, image) segment ---------------------------------------------------------------
-constexpr int kNmsThreads = 256;
-constexpr int kNmsChunk = 256;
 constexpr int kKeptSmem = 2048;
 
-__global__ void __launch_bounds__(kNmsThreads) nms_kernel(const unsigned long long* __restrict__ gkeys,
-                                                          const int32_t* __restrict__ count, int count_cols,
-                                                          int capacity, int cap2, double thresh,
-                                                          const float4* __restrict__ sbox, const int32_t* __restrict__ sidx,
-                                                          float4* __restrict__ kspill, unsigned char* __restrict__ keep,
-                                                          const int2* __restrict__ wl, const int32_t* __restrict__ wl_count) {
-    __shared__ float4 kept_s[kKeptSmem];
-    __shared__ float4 chunk_s[kNmsChunk];
-    __shared__ unsigned long long mask_s[kNmsChunk][kNmsChunk / 64];
-    __shared__ unsigned char alive_s[kNmsChunk];
-    __shared__ unsigned char kept_flag_s[kNmsChunk];
+__host__ __device__ inline size_t nms_smem_bytes(int T) {
+    return (size_t)kKeptSmem * 16 + (size_t)T * 16 + (size_t)T * (T / 64) * 8 + (size_t)T * 2;
+}
+
+// exact test on the fp32 coordinates: do the boxes overlap at all (:139-142)?  (min/max/compare are exact)
+__device__ __forceinline__ bool overlaps_f32(const float4& a, const float4& b) {
+    return fminf(a.z, b.z) > fmaxf(a.x, b.x) && fminf(a.w, b.w) > fmaxf(a.y, b.y);
+}
+
+// Greedy NMS of the queued segments, one CTA per segment at a time, T threads = T candidates per chunk: each chunk is
+// first tested against the boxes kept so far (all T candidates in parallel), then resolved internally with a T x T
+// suppression bit matrix in shared memory and a sweep by one warp.  Pairs that do not overlap are settled in fp32;
+// the fp64 IoU runs for the others.
+template <int T>
+__global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __restrict__ gkeys,
+                                                const int32_t* __restrict__ count, int count_cols,
+                                                int capacity, int cap2, double thresh,
+                                                const float4* __restrict__ sbox, const int32_t* __restrict__ sidx,
+                                                float4* __restrict__ kspill, unsigned char* __restrict__ keep,
+                                                const int2* __restrict__ wl, const int32_t* __restrict__ wl_count) {
+    constexpr int W = T / 64;                         // 64-bit words per row of the bit matrix
+    extern __shared__ __align__(16) unsigned char nsm[];
+    float4* kept_s = reinterpret_cast<float4*>(nsm);                          // [kKeptSmem]
+    float4* chunk_s = kept_s + kKeptSmem;                                     // [T]
+    unsigned long long* mask_s = reinterpret_cast<unsigned long long*>(chunk_s + T);   // [T][W]
+    unsigned char* alive_s = reinterpret_cast<unsigned char*>(mask_s + (size_t)T * W); // [T]
+    unsigned char* kept_flag_s = alive_s + T;                                 // [T]
     __shared__ int seg_s[2];
     __shared__ int nkept_s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nwork = *wl_count;
-  // segments queued by sort_kernel (the ones longer than a warp, and all segments of lists it did not resolve)
+    const bool none_overlap_drops = 0.0 > thresh;      // a negative threshold suppresses even disjoint boxes (:124)
   for (int wi = blockIdx.x; wi < nwork; wi += gridDim.x) {
     __syncthreads();                                   // shared state of the previous segment is done with
     const int2 job = wl[wi];
@@ -582,8 +606,8 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const unsigned long lo
     const int32_t* rowof = sidx + (size_t)n * capacity;
     unsigned char* keep_n = keep + (size_t)n * capacity;
 
-    for (int c0 = s0; c0 < s1; c0 += kNmsChunk) {
-        const int cnt = min(kNmsChunk, s1 - c0);
+    for (int c0 = s0; c0 < s1; c0 += T) {
+        const int cnt = min(T, s1 - c0);
         const int nk = nkept_s;
         // phase 1: this thread's candidate against every box kept so far
         bool alive = tid < cnt;
@@ -597,33 +621,39 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const unsigned long lo
         for (int q = 0; q < nk; ++q) {
             if (!__any_sync(0xffffffffu, alive)) break;
             const float4 kb = (q < kKeptSmem) ? kept_s[q] : spill[q];
-            if (alive && suppresses(to_boxd(kb), mine, thresh)) alive = false;
+            if (alive) {
+                const bool drop = overlaps_f32(kb, mine_f) ? suppresses(to_boxd(kb), mine, thresh) : none_overlap_drops;
+                if (drop) alive = false;
+            }
         }
         alive_s[tid] = alive ? 1 : 0;
         __syncthreads();
         // phase 2: bit matrix inside the chunk: row i, bit j (j > i) <=> i suppresses j
         {
-            unsigned long long w0 = 0, w1 = 0, w2 = 0, w3 = 0;
-            if (alive) {
-                for (int j = tid + 1; j < cnt; ++j) {
-                    if (!alive_s[j]) continue;
-                    if (suppresses(mine, to_boxd(chunk_s[j]), thresh)) {
-                        const unsigned long long bit = 1ULL << (j & 63);
-                        const int w = j >> 6;
-                        if (w == 0) w0 |= bit; else if (w == 1) w1 |= bit; else if (w == 2) w2 |= bit; else w3 |= bit;
+            unsigned long long* row = mask_s + (size_t)tid * W;
+            const int wfirst = (tid + 1) >> 6, wend = (cnt + 63) >> 6;
+            for (int w = 0; w < W; ++w) {
+                unsigned long long bits = 0;
+                if (alive && w >= wfirst && w < wend) {
+                    const int jb = max(tid + 1, w << 6), je = min(cnt, (w + 1) << 6);
+                    for (int j = jb; j < je; ++j) {
+                        if (!alive_s[j]) continue;
+                        const float4 oj = chunk_s[j];
+                        const bool drop = overlaps_f32(mine_f, oj) ? suppresses(mine, to_boxd(oj), thresh) : none_overlap_drops;
+                        if (drop) bits |= 1ULL << (j & 63);
                     }
                 }
+                row[w] = bits;
             }
-            mask_s[tid][0] = w0; mask_s[tid][1] = w1; mask_s[tid][2] = w2; mask_s[tid][3] = w3;
         }
         __syncthreads();
-        // sweep: warp 0 walks the chunk in order; lane w (< 4) carries word w of the removed set
+        // sweep: warp 0 walks the chunk in order; lane w (< W) carries word w of the removed set
         if (warp == 0) {
             unsigned long long removed = 0;
             for (int i = 0; i < cnt; ++i) {
                 const unsigned long long word = __shfl_sync(0xffffffffu, removed, i >> 6);
                 const bool k = alive_s[i] && !((word >> (i & 63)) & 1ULL);
-                if (k && lane < 4) removed |= mask_s[i][lane];
+                if (k && lane < W) removed |= mask_s[(size_t)i * W + lane];
                 if (lane == 0) kept_flag_s[i] = k ? 1 : 0;
             }
         }
@@ -729,16 +759,25 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     const size_t smem = max((size_t)n2s * 8, can_fuse ? fuse_bytes : (size_t)0);
     err = cudaFuncSetAttribute(sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
-    err = cudaMemsetAsync(ws.wl_count, 0, sizeof(int32_t), stream);
+    err = cudaMemsetAsync(ws.wl_count, 0, 2 * sizeof(int32_t), stream);
     if (err != cudaSuccess) return err;
+    int2* wl_large = ws.wl + (size_t)n * capacity;
     sort_kernel<<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, n2s, thresh, ws.keys, ws.sbox,
-                                                   ws.sidx, keep, ws.wl, ws.wl_count);
+                                                   ws.sidx, keep, ws.wl, wl_large, ws.wl_count);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
-    // a fixed grid walks the queue of long segments; with nothing queued every CTA leaves after one load
+    // fixed grids walk the two queues of long segments; with nothing queued every CTA leaves after one load
     (void)num_classes;
-    nms_kernel<<<296, kNmsThreads, 0, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx,
-                                                ws.kspill, keep, ws.wl, ws.wl_count);
+    err = cudaFuncSetAttribute(nms_kernel<kNmsMedium>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)nms_smem_bytes(kNmsMedium));
+    if (err != cudaSuccess) return err;
+    err = cudaFuncSetAttribute(nms_kernel<kNmsLarge>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)nms_smem_bytes(kNmsLarge));
+    if (err != cudaSuccess) return err;
+    nms_kernel<kNmsMedium><<<592, kNmsMedium, nms_smem_bytes(kNmsMedium), stream>>>(
+        ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx, ws.kspill, keep, ws.wl, ws.wl_count);
+    err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
+    nms_kernel<kNmsLarge><<<148, kNmsLarge, nms_smem_bytes(kNmsLarge), stream>>>(
+        ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx, ws.kspill, keep, wl_large, ws.wl_count + 1);
     return cudaGetLastError();
 }
 

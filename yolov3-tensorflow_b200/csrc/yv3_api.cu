@@ -288,7 +288,7 @@ PostWs carve_post(void* base, long long rpi, int n, int capacity, int num_tiles 
     w.sbox = (float4*)take(rows * 16);
     w.sidx = (int32_t*)take(rows * 4);
     w.kspill = (float4*)take(rows * 16);
-    w.wl = (int2*)take(rows * 8);
+    w.wl = (int2*)take((rows + rows / 256 + 16) * 8);      // medium-segment queue [rows], then the large-segment queue
     w.wl_count = (int32_t*)take(256);
     w.bytes = off;
     return w;
