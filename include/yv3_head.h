@@ -91,6 +91,21 @@ int yv3_decode(const yv3_config* cfg, const float* predicts, int n, float* const
 int yv3_label_decode(const yv3_config* cfg, const float* targets, int n, int m, float* const out[6],
                      void* stream);
 
+/* Label ingestion, the step that produces `targets`: the letter-box label transform of
+ * FileUtil._parse_image_with_label (dataset/file_util.py:47-52) and the -1 padded batch of
+ * FileUtil.get_dataset (dataset/file_util.py:97), for n images at once.
+ *   labels       device, the images' label rows back to back, 5 floats each [x, y, w, h, cls] normalised to
+ *                the SOURCE image (the numbers of a label.txt line, file_util.py:22-32)
+ *   row_offsets  device int32[n + 1]: image i owns rows row_offsets[i] .. row_offsets[i + 1]
+ *   image_hw     device int32[n][2]: source image height, width in pixels (tf.shape(image)[0:2])
+ *   target_h/w   the network input size (configs.py:36)
+ *   targets      device (n, m * 5) fp32: transformed rows, then -1 up to m slots.  An image with more than m
+ *                rows is an error (YV3_ERR_SHAPE is returned by the host check of the caller-supplied maximum).
+ * fp32 arithmetic in the reference's order: r = (w_src / W, h_src / H) reversed and divided by its max;
+ * xy' = xy * r + (1 - r) / 2;  wh' = wh * r. */
+int yv3_label_batch(const float* labels, const int32_t* row_offsets, const int32_t* image_hw, int n, int m,
+                    int target_h, int target_w, float* targets, void* stream);
+
 /* Ground-truth -> cell / anchor / head assignment: YOLOv3Loss._get_valid_target, _calc_iou (response
  * part) and the cross-head ownership test (yolov3/yolov3_loss.py:225-252, :269-302, :203-208).
  * table[n][j][h] = {row, col, best_anchor, owned} (int32; all -1/-1/-1/0 for a padding slot),

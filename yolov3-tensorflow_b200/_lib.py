@@ -60,6 +60,7 @@ _SIGNATURES = {
     "yv3_query_workspace": (ctypes.c_int, [_P, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_size_t)]),
     "yv3_decode": (ctypes.c_int, [_P, _P, ctypes.c_int, ctypes.POINTER(_P), _P]),
     "yv3_label_decode": (ctypes.c_int, [_P, _P, ctypes.c_int, ctypes.c_int, ctypes.POINTER(_P), _P]),
+    "yv3_label_batch": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, _P, _P]),
     "yv3_assign": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, _P, _P, _P, ctypes.c_size_t, _P]),
     "yv3_loss_fwd_bwd": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                         ctypes.c_float, _P, _P, _P, ctypes.c_size_t, ctypes.c_int, _P]),

@@ -129,4 +129,39 @@ cudaError_t launch_label_decode(const Geo& g, const float* targets, int n, int m
     return cudaGetLastError();
 }
 
+// ---- label ingestion (dataset/file_util.py:47-52, :97) ----------------------------------------------------
+__global__ void label_batch_kernel(const float* __restrict__ labels, const int32_t* __restrict__ row_offsets,
+                                   const int32_t* __restrict__ image_hw, int n, int m, float fh, float fw,
+                                   float* __restrict__ targets) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)n * m) return;
+    const int img = (int)(i / m), slot = (int)(i - (long long)img * m);
+    float* o = targets + i * 5;
+    const int r0 = row_offsets[img], r1 = row_offsets[img + 1];
+    if (slot >= r1 - r0) {                                            // padded_batch(padding_values=-1.)
+        o[0] = -1.f; o[1] = -1.f; o[2] = -1.f; o[3] = -1.f; o[4] = -1.f;
+        return;
+    }
+    // src_size_hw = shape[0:2] / image_size;  resize_wh_ratio = src_size_hw[::-1] / reduce_max(src_size_hw)
+    const float sh = __fdiv_rn((float)image_hw[2 * img], fh), sw = __fdiv_rn((float)image_hw[2 * img + 1], fw);
+    const float mx = fmaxf(sh, sw);
+    const float rw = __fdiv_rn(sw, mx), rh = __fdiv_rn(sh, mx);
+    const float* t = labels + (size_t)(r0 + slot) * 5;
+    // label_xy * ratio + (1 - ratio) / 2.0 ;  label_wh * ratio ;  class unchanged
+    o[0] = __fadd_rn(__fmul_rn(__ldg(t + 0), rw), __fmul_rn(__fsub_rn(1.0f, rw), 0.5f));
+    o[1] = __fadd_rn(__fmul_rn(__ldg(t + 1), rh), __fmul_rn(__fsub_rn(1.0f, rh), 0.5f));
+    o[2] = __fmul_rn(__ldg(t + 2), rw);
+    o[3] = __fmul_rn(__ldg(t + 3), rh);
+    o[4] = __ldg(t + 4);
+}
+
+cudaError_t launch_label_batch(const float* labels, const int32_t* row_offsets, const int32_t* image_hw, int n, int m,
+                               int target_h, int target_w, float* targets, cudaStream_t stream) {
+    const long long slots = (long long)n * m;
+    const int threads = 128;
+    label_batch_kernel<<<(int)((slots + threads - 1) / threads), threads, 0, stream>>>(
+        labels, row_offsets, image_hw, n, m, (float)target_h, (float)target_w, targets);
+    return cudaGetLastError();
+}
+
 }  // namespace yv3

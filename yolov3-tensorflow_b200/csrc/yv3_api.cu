@@ -332,6 +332,15 @@ int yv3_label_decode(const yv3_config* cfg, const float* targets, int n, int m, 
     return YV3_OK;
 }
 
+int yv3_label_batch(const float* labels, const int32_t* row_offsets, const int32_t* image_hw, int n, int m,
+                    int target_h, int target_w, float* targets, void* stream) {
+    if (!row_offsets || !image_hw || !targets) return YV3_ERR_NULL;       // labels may be NULL when no image has rows
+    if (n < 1 || m < 1 || m > YV3_MAX_GT || target_h < 1 || target_w < 1) return YV3_ERR_SHAPE;
+    if (!cuda_ok(launch_label_batch(labels, row_offsets, image_hw, n, m, target_h, target_w, targets,
+                                    (cudaStream_t)stream), "launch_label_batch")) return YV3_ERR_CUDA;
+    return YV3_OK;
+}
+
 int yv3_query_postprocess_workspace(const yv3_config* cfg, int n, int32_t capacity, size_t* bytes) {
     if (!bytes) return YV3_ERR_NULL;
     if (n < 1 || capacity < 1 || capacity > (1 << 18)) return YV3_ERR_CAPACITY;

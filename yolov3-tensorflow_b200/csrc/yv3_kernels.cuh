@@ -60,6 +60,9 @@ cudaError_t launch_decode(const Geo& g, const DecodeArgs& a, int sm_count, cudaS
 cudaError_t launch_label_decode(const Geo& g, const float* targets, int n, int m, float* const out[6],
                                 cudaStream_t stream);
 
+cudaError_t launch_label_batch(const float* labels, const int32_t* row_offsets, const int32_t* image_hw, int n, int m,
+                               int target_h, int target_w, float* targets, cudaStream_t stream);
+
 // ---- postprocess.cu ----------------------------------------------------------------------------
 struct PostWs {
     int32_t* status;            // [kStatusInts]
