@@ -182,7 +182,11 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--overlap", type=int, default=1, help="1: loss and post-process halves of a step on two streams")
-    ap.add_argument("--graph-steps", type=int, default=1, help="steps captured per CUDA graph (N = 1)")
+    ap.add_argument("--priority", default="post", choices=["none", "post", "loss"],
+                    help="which half of a step runs on a high-priority stream (two-stream mode)")
+    ap.add_argument("--graph-steps", type=int, default=8, help="steps captured per CUDA graph (N = 1)")
+    ap.add_argument("--pipeline", type=int, default=1,
+                    help="1: the two streams are joined once per graph / timed region, 0: after every step")
     ap.add_argument("--force-graph", action="store_true", help="skip the eager-vs-graph trial")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA-graph replay")
     args = ap.parse_args()
@@ -219,24 +223,47 @@ def main():
     counts = torch.empty((n, 3), dtype=torch.int32, device=dev)
     keep = torch.empty((n, post.capacity), dtype=torch.uint8, device=dev)
 
-    post_stream = torch.cuda.Stream() if args.overlap else None
+    post_stream = None
+    if args.overlap:
+        # the block scheduler serves the high-priority stream first whenever an SM slot frees up
+        post_stream = torch.cuda.Stream(priority=-1 if args.priority == "post" else 0)
+        if args.priority == "loss":
+            torch.cuda.set_stream(torch.cuda.Stream(priority=-1))
 
-    def step(events=None):
+    def half_loss(events=None):
+        total, _ = loss.loss_and_grad(td, pd, events=events, grad_out=grad)
+        return total
+
+    def half_post():
+        post.filter(pd, w["score_thresh"], out=(cand, counts))
+        post.nms(cand, counts, w["nms_thresh"], out=keep)
+
+    def steps(count, events=None):
+        """`count` complete steps.  The training half (assignment, dense pass) and the inference half (filter, sort,
+        NMS) of a step share only their input, so they run on two streams.  --pipeline 1: the streams are joined once
+        per call (consecutive steps of either half queue behind each other, the latency-bound tail of one step's
+        post-process runs under the next step's sweeps); --pipeline 0: joined after every step."""
         if post_stream is None or events is not None:
-            total, _ = loss.loss_and_grad(td, pd, events=events, grad_out=grad)
-            post.filter(pd, w["score_thresh"], out=(cand, counts))
-            post.nms(cand, counts, w["nms_thresh"], out=keep)
+            for k in range(count):
+                total = half_loss(events)
+                half_post()
             return total
-        # the training half (assignment, dense pass) and the inference half (filter, sort, NMS) of a step share only
-        # their input: two streams, so the latency-bound post-process kernels run in the shadow of the dense pass
         cur = torch.cuda.current_stream()
         post_stream.wait_stream(cur)
-        with torch.cuda.stream(post_stream):
-            post.filter(pd, w["score_thresh"], out=(cand, counts))
-            post.nms(cand, counts, w["nms_thresh"], out=keep)
-        total, _ = loss.loss_and_grad(td, pd, grad_out=grad)
-        cur.wait_stream(post_stream)
+        for k in range(count):
+            with torch.cuda.stream(post_stream):
+                half_post()
+            total = half_loss()
+            if not args.pipeline:
+                cur.wait_stream(post_stream)
+                if k + 1 < count:
+                    post_stream.wait_stream(cur)
+        if args.pipeline:
+            cur.wait_stream(post_stream)
         return total
+
+    def step(events=None):
+        return steps(1, events)
 
     def fence():
         if world > 1:
@@ -280,8 +307,7 @@ def main():
             torch.cuda.current_stream().wait_stream(side)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                for _ in range(unroll):
-                    step()
+                steps(unroll)
             mode = "cuda-graph replay, %d step(s) per graph" % unroll + (" + eager NCCL all-reduce of the 20 loss floats" if world > 1 else "")
         except Exception as e:
             graph, mode = None, "eager (graph capture failed: %s)" % type(e).__name__
@@ -292,8 +318,7 @@ def main():
     def run(count):
         """exactly `count` steps"""
         if graph is None:
-            for _ in range(count):
-                step()
+            steps(count)
             return
         for _ in range(count // unroll):
             graph.replay()
@@ -301,8 +326,7 @@ def main():
         rest = count % unroll
         if rest:
             loss.auto_all_reduce = True
-            for _ in range(rest):
-                step()
+            steps(rest)
             loss.auto_all_reduce = False
     run(3 * unroll)
     fence()
@@ -320,8 +344,7 @@ def main():
 
         def eager20():
             loss.auto_all_reduce = True
-            for _ in range(20):
-                step()
+            steps(20)
             loss.auto_all_reduce = False
 
         t_graph = trial(lambda: run(20 - 20 % unroll))
@@ -410,7 +433,10 @@ def main():
                        "l2": "inputs larger than L2: predicts %.0f MB + gradient %.0f MB per GPU vs 126 MB L2" % (
                            pd.numel() * 4 / 1e6, grad.numel() * 4 / 1e6),
                        "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image,
-                       "launch": mode, "streams": 2 if args.overlap else 1},
+                       "launch": mode, "streams": 2 if args.overlap else 1,
+                       "high_priority_stream": args.priority if args.overlap else None,
+                       "stream_join": ("once per %d-step graph" % unroll if graph is not None else "once per timed region")
+                       if (args.overlap and args.pipeline) else "every step"},
             "stage_ms": {"loss_dense_kernel": dense_ms, "filter_plus_nms": post_ms,
                          "assign_and_gaps": total_ms / args.steps - dense_ms - post_ms,
                          "note": "stage times from eager launches with events; ms_per_step from the timed region"},
@@ -422,7 +448,7 @@ def main():
                     "h2d_bytes_per_step": int(p_host.numel() * 4 + t_host.numel() * 4),
                     "d2h_bytes_per_step": int(19 * 4 + counts_host.numel() * 4 + keep_host.numel()),
                     "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
-            "gpu_launches": 6 * args.steps,
+            "gpu_launches": 7 * args.steps,      # assign, dense, score, gather, sort, nms x2
             "clocks": sampler.summary(),
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define YV3_ABI_VERSION 1
+#define YV3_ABI_VERSION 2
 #define YV3_MAX_BOX 8      /* anchors per head (reference ships 3 / 2 / 3, configs.py:37-41) */
 #define YV3_MAX_GT 256     /* label slots per image (M) */
 
@@ -126,10 +126,12 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
  *                      images / n_global).  [18] = their sum = this rank's share of the scalar
  *                      loss (:137).  [19] = 0.  Summing (all-reducing) the 20 floats over the
  *                      ranks of a batch-sharded job gives the global values.
- *   phases             3 = the whole loss.  The path is two launches -- 1: the per-label assignment
- *                      kernel (centre-cell IoU, ownership, owner-side terms; latency-bound, tiny),
- *                      2: the fused dense sweep (HBM-bound) -- and a caller that wants to time them
- *                      separately may issue them as two calls with the same arguments (1 then 2).
+ *   phases             bit mask, 7 = the whole loss.  The path is three launches -- 1: the per-label
+ *                      assignment kernel (centre-cell IoU, ownership, owner-side terms; latency-bound,
+ *                      tiny), 2: the fused dense sweep (HBM-bound; leaves one row of partial sums per
+ *                      CTA in the workspace), 4: the fold of those rows into loss_out20 (one CTA) --
+ *                      and a caller that wants to time them separately may issue them as separate
+ *                      calls with the same arguments, in that order.
  *   grad_predicts      device, packed layout, n images; must be 16-byte aligned; may be NULL
  *                      (forward only).  Every element is written. */
 int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,

@@ -343,6 +343,42 @@ def test_filter_rows_close_to_oracle_decode(yv3):
         np.testing.assert_allclose(rows, ref_rows, rtol=1e-5, atol=1e-6)
 
 
+def test_filter_early_out_is_safe_on_extreme_class_logits(yv3):
+    """The score sweep drops records on an approximate upper bound of the score (one pass, exponents relative to the
+    first class logit).  Offsets, peaks, overflowing and underflowing exponent sums must all end in the exact path or
+    be dropped rightly: the result equals filter_boxes on the materialised decode (the exact kernel) row for row."""
+    spec, p, _ = _inputs("coco_64_c20", 3, 4, seed=77)
+    C, L = spec.class_num, spec.box_len
+    rec = p.reshape(3, -1, L).copy()
+    kind = np.arange(rec.shape[1]) % 8
+    rec[:, kind == 1, 5:] += 3.0e4                           # large common offset: cancels in softmax
+    rec[:, kind == 2, 5 + 7] += 100.0                        # one dominant class: prob = 1
+    rec[:, kind == 3, 5] = -200.0                            # first logit far below: every relative exponent overflows
+    rec[:, kind == 4, 5] = 200.0                             # first logit far above: every other term underflows
+    rec[:, kind == 5, 5] = -87.0                             # eight equal classes 125.5 binary orders above the first:
+    rec[:, kind == 5, 6:14] = 0.0                            # each term is finite, their sum is not; true sum = 8 + tail
+    rec[:, kind == 5, 14:] = -30.0
+    rec[:, kind == 6, 5:] = -1.0e4 + rec[:, kind == 6, 5:] * 50.0     # wide spread around a large negative offset
+    rec[:, :, 4] += 1.5                                      # more records above the confidence gate
+    p = rec.reshape(p.shape).astype(np.float32)
+    pd = torch.from_numpy(p).cuda()
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    dec = yv3.YOLOv3Decoder(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes).decode(pd)
+    for thr in (0.05, 0.3, 0.9):
+        cand, counts = post.filter(pd, thr)
+        post.check_status()
+        for i in range(3):
+            args = []
+            for h in range(3):
+                args += [dec[h][1][i], dec[h][2][i]]
+            filt = yv3.YOLOv3PostProcessor.filter_boxes(*args, thr)
+            c = counts[i].cpu().numpy()
+            assert [len(f) for f in filt] == c.tolist()
+            assert c.sum() > 0
+            rows = cand[i, :int(c.sum())].cpu().numpy()
+            assert np.array_equal(np.concatenate([f.reshape(-1, 8) for f in filt], 0).astype(np.float32), rows)
+
+
 def test_capacity_overflow_is_reported(yv3):
     spec, p, _ = _inputs("coco_64x96_c4", 1, 4)
     post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes, capacity=16)

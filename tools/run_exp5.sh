@@ -1,0 +1,10 @@
+# developer experiment: CTA size of the dense pass with the fold in its own kernel
+for v in "256 16384" "128 16384" "64 4096" "32 2048" "32 4096"; do
+  set -- $v
+  export YV3_EXTRA_NVCC="-DYV3_DENSE_THREADS=$1 -DYV3_DENSE_ZBLK=$2"
+  timeout 600 python -c "import __graft_entry__ as g; g.build()" 2>&1 | tail -1
+  grep -A2 "loss_dense_kernelILi1ELi1ELi0" yolov3-tensorflow_b200/lib/build.log | grep -E "Used" | head -1
+  for c in 1 2 3; do
+    echo "threads $1 zblk $2 cpw $c"; YV3_CPW=$c timeout 120 python tools/dense_bench.py cfg2_416_c80_b64 100 2>&1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['loss_dense'], d['loss_all']['median_us'], d['loss_fwd_only']['median_us'])"
+  done
+done

@@ -99,7 +99,7 @@ def lib():
         fn = getattr(handle, name)             # AttributeError = header and library disagree
         fn.restype = res
         fn.argtypes = args
-    if handle.yv3_abi_version() != 1:
+    if handle.yv3_abi_version() != 2:
         raise RuntimeError("libyv3head.so ABI version mismatch")
     _LIB = handle
     return _LIB

@@ -21,7 +21,7 @@ HEADERS = ["yv3_common.cuh", "yv3_kernels.cuh", "tile_ops.cuh", os.path.join("..
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v",
-]
+] + os.environ.get("YV3_EXTRA_NVCC", "").split()        # developer experiments (-D switches); part of the fingerprint
 
 
 def _nvcc():

@@ -6,31 +6,28 @@
 // :140-164, the batch mean :112 and the detail rows :115-138.  The backward is the closed form TF
 // autodiff yields for those operators; no gradient flows through IoU or masks.
 //
-// Shape of the kernel (B200), v5.  profiles/r01_v3_ncu_summary.md and r01_v4_notes.md say why the earlier
-// shapes (CTA tiles staged in shared memory behind a barrier; zero-fill followed by partial-sector value
-// stores; logits through L1) were latency- and traffic-bound.
-//  * everything per-image is prepared by the assignment kernel (assign.cu): the valid labels in each
-//    head's grid units (gtab), their count, and the object mask as one bit per record (objbits).  The
-//    dense pass has NO shared-memory staging and NO CTA barrier in its loop;
-//  * the packed tensor is a flat array of records of L floats.  A WARP owns a chunk of 32 consecutive
-//    records (128*L bytes: a sector-aligned span), independent of every other warp; chunks are claimed
-//    grid-stride, the grid sized so that every warp gets the same number of them; the logits and object
-//    bits of a warp's next chunk are already in flight while it works on the current one;
-//  * a lane owns one record: it reads the two aligned 128-bit words holding the record's 5 box/conf
-//    logits with L2-only loads (an L1 miss would fetch the whole 128-byte line; class logits of
-//    non-responsible anchors are never read: their gradient is identically 0), decodes, takes the max IoU
-//    over the image's labels (L1-resident loads from gtab, four labels in flight, branch-free IoU),
-//    accumulates the loss terms and composes its gradient values;
-//  * gradient of a chunk: every 32-byte sector is written exactly once, whole.  L-5 of a record's L floats
-//    are zeros (the class logits of an anchor that owns no label): the lanes cover the sectors that hold no
-//    box/conf value with 128-bit streaming zero stores (fire-and-forget, issued before the arithmetic); the
-//    one or two sectors around a record's five values are written by the record's lane, values and zeros
-//    together.  No sector is first zeroed and then partially overwritten (that costs a DRAM read-modify-write
-//    once the zero sector has left L2) and nothing needs ordering;
-//  * the few lanes whose object bit is set add the owner terms of their labels in label order and write
-//    the softmax-CE class gradient of their record on top of the zeros (after a __syncwarp);
-//  * loss sums: registers -> warp shuffles -> one partial row per CTA -> the last CTA to finish folds
-//    the rows in a fixed order (double) and writes the 18 detail values + their sum.  No float atomics.
+// Shape of the kernel (B200).  profiles/r01_dense_variants.txt lists the shapes tried before this one and what each
+// cost (CTA tiles staged behind a barrier; zero-fill followed by partial-sector value stores; logits through L1;
+// per-lane owner path; a dedicated zero-fill warp; 64-register / 32-warp build; smaller CTAs).
+//  * everything per-image is prepared by the assignment kernel (assign.cu): the valid labels in each head's grid
+//    units (gtab), their count, and the object mask as one bit per record (objbits);
+//  * the packed tensor is a flat array of records of L floats.  A WARP owns `cpw` consecutive chunks of 32
+//    consecutive records (a chunk is 128*L bytes: a sector-aligned span), independent of every other warp -- no CTA
+//    barrier in the loop; the logits and object bits of the warp's next chunk are in flight while it works on the
+//    current one.  The labels of the (at most two) images its chunks touch sit in the warp's own shared-memory slots;
+//  * a lane owns one record: it reads the two aligned 128-bit words holding the record's 5 box/conf logits with
+//    L2-only loads (class logits of non-responsible anchors are never read: their gradient is identically 0),
+//    decodes, and decides "IoU < iou_thresh for every label" four labels at a time with a division-free test that is
+//    exact outside a 2^-19 band below the threshold (the band and everything above it take the reference expression);
+//  * gradient of a chunk: L-5 of a record's L floats are zeros.  One asynchronous bulk (TMA) store per chunk, issued
+//    by lane 0 one chunk ahead from a block of zeros in shared memory, covers the whole span; the record's lane then
+//    writes the one or two 32-byte sectors around its five values WHOLE (values and zeros together), so no sector is
+//    ever partially written.  Without the bulk path (unaligned tensors, short records) lanes write the zeros with
+//    128-bit streaming stores under a host-computed mask that skips the value sectors;
+//  * the few lanes whose object bit is set are served by the whole warp one after the other: owner terms of their
+//    labels added in label order by lanes 0..4, the softmax-CE class gradient with the classes spread over the lanes;
+//  * loss sums: registers -> warp shuffles -> one partial row per CTA -> the last CTA to finish folds the rows in a
+//    fixed order (double) and writes the 18 detail values + their sum.  No float atomics.
 #include <stdlib.h>
 
 #include "tile_ops.cuh"
@@ -38,8 +35,19 @@
 
 namespace yv3 {
 
-constexpr int kThreads = 256;
+#ifndef YV3_DENSE_THREADS
+#define YV3_DENSE_THREADS 256
+#endif
+constexpr int kThreads = YV3_DENSE_THREADS;
 constexpr int kWarps = kThreads / 32;
+#ifndef YV3_DENSE_ZBLK
+#define YV3_DENSE_ZBLK 16384          // bytes of the shared-memory zero block one bulk store reads (multiple of 16)
+#endif
+#ifndef YV3_DENSE_MINB
+// resident CTAs per SM the register budget is set for: 24 warps, 80 registers (32 warps = 64 registers spills and
+// measured slower, 98 vs 82 us)
+#define YV3_DENSE_MINB (768 / YV3_DENSE_THREADS)
+#endif
 constexpr int kSmallL = 8;            // records shorter than this are composed in shared memory
 
 // value k (0..4) of a record whose first float sits at position `ph` (0..3) of the 8 floats in (a, b)
@@ -86,21 +94,21 @@ __device__ __forceinline__ Win12 compose(const float (&gv)[5], int pos) {
 }
 
 // The background test of yolov3_loss.py:294,331 for one (anchor, label) pair: is IoU < iou_thresh?  The IoU itself
-// is fl(inter / fl(fl(aP + aT) - inter)); the quotient is only needed when it lands within 2^-20 (relative) of the
-// threshold: inter < t*u*(1 - 2^-20) implies fl(inter/u) < t and inter > t*u*(1 + 2^-20) implies fl(inter/u) >= t
-// (each product is off by at most 2^-24 relative).  Everything else -- the band, NaNs, the TIoU variant -- takes the
-// exact expression of iou_ref, so the decision is the reference's bit for bit.
-__device__ __forceinline__ bool iou_below(float px0, float py0, float px1, float py1, float parea, const float4& t,
-                                          float tarea, float thr, int tiou) {
+// is fl(inter / fl(fl(aP + aT) - inter)); the quotient is only needed when it lands close to the threshold.  With
+// thr_lo = fl(thr * (1 - 2^-19)):   inter < fl(thr_lo * uni)   implies   inter / uni < thr * (1 - 2^-20)   (two
+// roundings of at most 2^-24 each), hence fl(inter / uni) < thr.  `surely_below` is that one-multiply test; whatever
+// it does not settle -- the band below the threshold, everything above it, NaNs, uni <= 0, thr <= 0, the TIoU variant
+// -- takes the exact expression of iou_ref (`iou_below_exact`), so the decision is the reference's bit for bit.
+__device__ __forceinline__ bool surely_below(float px0, float py0, float px1, float py1, float parea, const float4& t,
+                                             float tarea, float thr_lo) {
     const float iw = fmaxf(__fsub_rn(fminf(px1, t.z), fmaxf(px0, t.x)), 0.0f);
     const float ih = fmaxf(__fsub_rn(fminf(py1, t.w), fmaxf(py0, t.y)), 0.0f);
     const float inter = __fmul_rn(iw, ih);
     const float uni = __fsub_rn(__fadd_rn(parea, tarea), inter);
-    if (!tiou) {
-        const float tb = __fmul_rn(thr, uni);
-        if (inter < __fmul_rn(tb, 0.99999905f)) return true;
-        if (inter > __fmul_rn(tb, 1.00000095f)) return false;
-    }
+    return inter < __fmul_rn(thr_lo, uni);
+}
+__device__ __forceinline__ bool iou_below_exact(float px0, float py0, float px1, float py1, float parea, const float4& t,
+                                                float tarea, float thr, int tiou) {
     GtBox g;
     g.x0 = t.x; g.y0 = t.y; g.x1 = t.z; g.y1 = t.w; g.area = tarea;
     return iou_ref(px0, py0, px1, py1, parea, g, tiou) < thr;
@@ -132,19 +140,23 @@ __device__ __forceinline__ Logits load_logits(const float* __restrict__ predicts
 constexpr int kWideL = 12;            // from here on a 32-byte sector holds values of at most one record
 
 // The valid labels of the (at most two) images a warp's chunk touches, in the warp's own shared-memory slots
-// (slot = image & 1): [V, pad x3] then per head m label entries of 8 floats (x0, y0, x1, y1, area, pad x3), head
-// stride m*8 + 4 floats so that the three heads' entries fall into different banks.
-__host__ __device__ inline int gt_slot_floats(int m) { return 4 + 3 * (m * kGtFloats + 4); }
+// (slot = image & 1): [V, pad x3] then per head label entries of 8 floats (x0, y0, x1, y1, area, pad x3), head
+// stride m4*8 + 4 floats (m4 = m rounded up to 4) so that the three heads' entries fall into different banks.  The
+// entries V .. round_up(V, 4) - 1 repeat label V - 1: the background test walks the labels four at a time with
+// constant offsets and no index clamping, and a repeated label does not change an "all below" decision.
+__host__ __device__ inline int gt_head_stride(int m) { return ((m + 3) & ~3) * kGtFloats + 4; }
+__host__ __device__ inline int gt_slot_floats(int m) { return 4 + 3 * gt_head_stride(m); }
 
 __device__ __forceinline__ void gt_refill(float* slot, const DenseArgs& a, int n_img, int lane) {
     const int m = a.m;
     const int V = __ldg(a.vcount + n_img);
     if (lane == 0) reinterpret_cast<int*>(slot)[0] = V;
+    const int V4 = (V + 3) & ~3;
 #pragma unroll
     for (int h = 0; h < 3; ++h) {
         const float4* src = reinterpret_cast<const float4*>(a.gtab + ((size_t)n_img * 3 + h) * m * kGtFloats);
-        float4* dst = reinterpret_cast<float4*>(slot + 4 + h * (m * kGtFloats + 4));
-        for (int i = lane; i < 2 * V; i += 32) dst[i] = __ldg(src + i);
+        float4* dst = reinterpret_cast<float4*>(slot + 4 + h * gt_head_stride(m));
+        for (int i = lane; i < 2 * V4; i += 32) dst[i] = __ldg(src + 2 * min(i >> 1, V - 1) + (i & 1));
     }
 }
 
@@ -152,7 +164,7 @@ __device__ __forceinline__ void gt_refill(float* slot, const DenseArgs& a, int n
 // eight computing warps never queue behind the store stream; the sectors it writes and the sectors the record lanes
 // write are disjoint, so the two never need to meet.
 template <int VEC, int SGT, int ZW>
-__global__ void __launch_bounds__(kThreads + 32 * ZW, 3) loss_dense_kernel(const __grid_constant__ Geo g,
+__global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense_kernel(const __grid_constant__ Geo g,
                                                                            const __grid_constant__ DenseArgs a) {
     extern __shared__ __align__(16) float gt_s[];          // SGT: [kWarps][2][gt_slot_floats(m)], then the zero block
     __shared__ float red_s[kWarps + 1][12];
@@ -163,6 +175,7 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, 3) loss_dense_kernel(const
     const int L = g.L, C = g.C, m = a.m;
     const int nw = gridDim.x * kWarps;
     const float thr = g.iou_thresh;
+    const float thr_lo = __fmul_rn(thr, 0.99999809265136719f);      // thr * (1 - 2^-19), see surely_below
     const float nf = (float)a.n_global;
     const float one = 1.0f;
     const bool wide = VEC && L >= kWideL;
@@ -354,7 +367,7 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, 3) loss_dense_kernel(const
             if (SGT) {
                 const float* slot = slots + (n_img & 1) * gt_slot_floats(m);
                 V = reinterpret_cast<const int*>(slot)[0];
-                gt = reinterpret_cast<const float4*>(slot + 4 + p.h * (m * kGtFloats + 4));
+                gt = reinterpret_cast<const float4*>(slot + 4 + p.h * gt_head_stride(m));
             } else {
                 V = __ldg(a.vcount + n_img);
                 gt = reinterpret_cast<const float4*>(a.gtab + ((size_t)n_img * 3 + p.h) * m * kGtFloats);
@@ -366,18 +379,23 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, 3) loss_dense_kernel(const
                 float ta[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    const int jj = min(j + u, V - 1);
                     if (SGT) {
-                        bx[u] = gt[2 * jj];
-                        ta[u] = reinterpret_cast<const float*>(gt + 2 * jj + 1)[0];
+                        bx[u] = gt[2 * (j + u)];                                   // slots are padded to four (gt_refill)
+                        ta[u] = reinterpret_cast<const float*>(gt + 2 * (j + u) + 1)[0];
                     } else {
+                        const int jj = min(j + u, V - 1);
                         bx[u] = __ldg(gt + 2 * jj);
                         ta[u] = __ldg(reinterpret_cast<const float*>(gt + 2 * jj + 1));
                     }
                 }
+                bool sure = !g.tiou;
 #pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    none_ge = none_ge && iou_below(d.x0, d.y0, d.x1, d.y1, parea, bx[u], ta[u], thr, g.tiou);   // :294
+                for (int u = 0; u < 4; ++u) sure = sure & surely_below(d.x0, d.y0, d.x1, d.y1, parea, bx[u], ta[u], thr_lo);
+                if (!sure) {                                                       // rare: some IoU near or above thr
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        none_ge = none_ge && iou_below_exact(d.x0, d.y0, d.x1, d.y1, parea, bx[u], ta[u], thr, g.tiou);   // :294
+                }
             }
             const float bg = (none_ge ? one : 0.0f) * (one - (is_obj ? one : 0.0f));       // :331-332
             const float pc = d.conf;
@@ -516,7 +534,7 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, 3) loss_dense_kernel(const
         nxt += 1;
     }
 
-    // ---- reduction: thread -> warp -> CTA partial row -> last CTA --------------------------------
+    // ---- reduction: thread -> warp -> CTA partial row (loss_fold_kernel folds the rows) ----------------
     float v[9] = {an0, an1, an2, ac0, ac1, ac2, ar0, ar1, ar2};
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
@@ -529,30 +547,29 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, 3) loss_dense_kernel(const
         for (int w = 0; w < nwarps; ++w) acc += red_s[w][tid];
         a.partials[(size_t)blockIdx.x * kPartialFloats + tid] = acc;
     }
-    __shared__ int is_last;
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-        const int ticket = atomicAdd(&a.status[1], 1);
-        is_last = (ticket == (int)gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    // the last CTA: all 256 threads fold the partial rows (thread t takes rows t, t + 256, ... in index order,
-    // in double), lanes fold by shuffles, warps through shared memory: a fixed order => a deterministic sum
-    __shared__ double fold_s[kWarps + 1][18];
+}
+
+// The fold of the per-CTA partial rows (the launch boundary orders it after every row is written): thread t takes
+// rows t, t + T, ... in index order, in double; lanes fold by shuffles, warps through shared memory -- a fixed order,
+// hence a deterministic sum -- then the 18 detail values (:115-138) and their sum (:137).
+constexpr int kFoldThreads = 256;
+__global__ void __launch_bounds__(kFoldThreads) loss_fold_kernel(const __grid_constant__ Geo g,
+                                                                 const __grid_constant__ DenseArgs a, int nrows) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int nwarps = kFoldThreads / 32;
+    __shared__ double fold_s[nwarps][18];
     double part[18];
 #pragma unroll
     for (int k = 0; k < 18; ++k) part[k] = 0.0;
-    for (int b = tid; b < (int)gridDim.x; b += nthreads) {
+#pragma unroll 4
+    for (int b = tid; b < nrows; b += kFoldThreads) {
         const float4* row = reinterpret_cast<const float4*>(a.partials + (size_t)b * kPartialFloats);
         const float4 r0 = __ldcg(row), r1 = __ldcg(row + 1), r2 = __ldcg(row + 2);
         part[0] += (double)r0.x; part[1] += (double)r0.y; part[2] += (double)r0.z;      // noobj
         part[3] += (double)r0.w; part[4] += (double)r1.x; part[5] += (double)r1.y;      // cls
         part[6] += (double)r1.z; part[7] += (double)r1.w; part[8] += (double)r2.x;      // rect
     }
-    for (int i = tid; i < a.n; i += nthreads) {
+    for (int i = tid; i < a.n; i += kFoldThreads) {
 #pragma unroll
         for (int k = 0; k < 9; ++k) part[9 + k] += (double)__ldcg(a.img_terms + (size_t)i * 9 + k);   // xy, wh, obj
     }
@@ -586,14 +603,13 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, 3) loss_dense_kernel(const
         for (int i = 0; i < 18; ++i) total += fin[i];
         a.detail[18] = total;
         a.detail[19] = 0.f;
-        a.status[1] = 0;                                  // re-arm the ticket for the next launch
     }
 }
 
 template <int VEC, int SGT, int ZW>
-static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, cudaStream_t stream) {
+static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, bool sweep, bool fold, cudaStream_t stream) {
     a.bulk = (VEC && !ZW && g.L >= kWideL && !(a.debug & 64)) ? 1 : 0;
-    a.zero_bytes = a.bulk ? (int)min(128LL * g.L, 16384LL) : 0;
+    a.zero_bytes = a.bulk ? (int)min(128LL * g.L, (long long)YV3_DENSE_ZBLK) : 0;
     const size_t smem = (SGT ? (size_t)kWarps * 2 * gt_slot_floats(a.m) * sizeof(float) : 0) + (size_t)a.zero_bytes;
     cudaError_t err = cudaFuncSetAttribute(loss_dense_kernel<VEC, SGT, ZW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
@@ -601,12 +617,12 @@ static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, cuda
     err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_dense_kernel<VEC, SGT, ZW>, kThreads + 32 * ZW, smem);
     if (err != cudaSuccess) return err;
     if (per_sm < 1) per_sm = 1;
-    // two consecutive chunks per warp (the second one's logits and zero fill are in flight while the first is
-    // worked on) and as many CTAs as that takes: the hardware scheduler balances them (measured best on B200,
-    // profiles/r01_dense_cpw_sweep.txt); one chunk per warp when there is less work than resident warps, more
-    // when the grid would exceed the partial-row table
-    const long long slots = (long long)sm_count * per_sm * kWarps;
-    a.cpw = a.num_chunks >= 2 * slots ? 2 : 1;
+    // one chunk per warp and as many CTAs as that takes: short-lived CTAs give their slot back as soon as their slowest
+    // warp is done, and the hardware scheduler balances the rest (measured best on B200 once the final fold left the
+    // kernel: 68 / 70 / 75 us at 1 / 2 / 3 chunks per warp, profiles/r01_dense_variants.txt); more chunks per warp
+    // only when the grid would exceed the partial-row table
+    (void)sm_count; (void)per_sm;
+    a.cpw = 1;
     while (((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps) > kMaxGrid) ++a.cpw;
     if (const char* e = getenv("YV3_CPW")) {                       // developer override
         const int v = atoi(e);
@@ -614,11 +630,16 @@ static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, cuda
         if (v >= 1 && need <= kMaxGrid) a.cpw = v;
     }
     const int grid = (int)max(1LL, ((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps));
-    loss_dense_kernel<VEC, SGT, ZW><<<grid, kThreads + 32 * ZW, smem, stream>>>(g, a);
+    if (sweep) {
+        loss_dense_kernel<VEC, SGT, ZW><<<grid, kThreads + 32 * ZW, smem, stream>>>(g, a);
+        err = cudaGetLastError();
+        if (err != cudaSuccess) return err;
+    }
+    if (fold) loss_fold_kernel<<<1, kFoldThreads, 0, stream>>>(g, a, grid);      // the grid is a function of the arguments
     return cudaGetLastError();
 }
 
-cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream) {
+cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool sweep, bool fold, cudaStream_t stream) {
     a.num_chunks = (int)((a.total_rec + 31) / 32);
     // zero-fill pattern of the whole-sector path (see the kernel): bit k of lane l <=> 128-bit word l + 32 k of a
     // chunk lies in a sector without box/conf values
@@ -641,9 +662,9 @@ cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStrea
     // measured on B200 (profiles/r01_dense_variants.txt): the zero warp does not pay (88 vs 83 us at cfg2); kept as a
     // developer switch (YV3_DEBUG bit 128)
     const bool zw = vec && g.L >= kWideL && a.grad != nullptr && (a.debug & 128);
-    if (vec && zw) return sgt ? launch_variant<1, 1, 1>(g, a, sm_count, stream) : launch_variant<1, 0, 1>(g, a, sm_count, stream);
-    if (vec) return sgt ? launch_variant<1, 1, 0>(g, a, sm_count, stream) : launch_variant<1, 0, 0>(g, a, sm_count, stream);
-    return sgt ? launch_variant<0, 1, 0>(g, a, sm_count, stream) : launch_variant<0, 0, 0>(g, a, sm_count, stream);
+    if (vec && zw) return sgt ? launch_variant<1, 1, 1>(g, a, sm_count, sweep, fold, stream) : launch_variant<1, 0, 1>(g, a, sm_count, sweep, fold, stream);
+    if (vec) return sgt ? launch_variant<1, 1, 0>(g, a, sm_count, sweep, fold, stream) : launch_variant<1, 0, 0>(g, a, sm_count, sweep, fold, stream);
+    return sgt ? launch_variant<0, 1, 0>(g, a, sm_count, sweep, fold, stream) : launch_variant<0, 0, 0>(g, a, sm_count, sweep, fold, stream);
 }
 
 }  // namespace yv3

@@ -19,6 +19,7 @@
 //                         tested against the boxes kept so far, then resolved internally with a
 //                         shared-memory IoU bit matrix and a warp sweep.  IoU is fp64, uncontracted, in the
 //                         reference's operation order.
+#include <stdlib.h>
 #include <string.h>
 
 #include "tile_ops.cuh"
@@ -99,18 +100,35 @@ __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_
         } else if (!q.early) {
             maybe = true;
         } else if (conf > thresh) {                                  // fl(prob * conf) <= conf for prob <= 1
-            float mx = r[5];
-            for (int k = 1; k < C; ++k) mx = fmaxf(mx, r[5 + k]);
-            const float ml = mx * 1.4426950408889634f;
-            float s0 = 0.f, s1 = 0.f;
-            int k = 0;
-            for (; k + 2 <= C; k += 2) {
-                s0 += exp2f_approx(__fmaf_rn(r[5 + k], 1.4426950408889634f, -ml));
-                s1 += exp2f_approx(__fmaf_rn(r[6 + k], 1.4426950408889634f, -ml));
+            // ONE pass over the class logits: the sum is taken relative to the first logit c (S = sum 2^((z_k - c) log2e))
+            // while the maximum M is tracked, then sum_k exp(z_k - M) = S * 2^(-(M - c) log2e).  The product of c
+            // and log2e is the same rounded constant in every term, so it cancels; what is left is the rounding of
+            // each exponent (|.| < 128, else a term is inf or 0 and the record goes to the exact path below).
+            const float l2e = 1.4426950408889634f;
+            const float z0 = r[5];
+            const float cl = __fmul_rn(z0, l2e);
+            float mx = z0;
+            float s0 = 1.0f, s1 = 0.f, s2 = 0.f, s3 = 0.f;              // the first logit's own term is 2^0
+            int k = 1;
+            for (; k + 4 <= C; k += 4) {
+                const float a0 = r[5 + k], a1 = r[6 + k], a2 = r[7 + k], a3 = r[8 + k];
+                mx = fmaxf(fmaxf(mx, a0), a1);                         // FMNMX3
+                mx = fmaxf(fmaxf(mx, a2), a3);
+                s0 += exp2f_approx(__fmaf_rn(a0, l2e, -cl));
+                s1 += exp2f_approx(__fmaf_rn(a1, l2e, -cl));
+                s2 += exp2f_approx(__fmaf_rn(a2, l2e, -cl));
+                s3 += exp2f_approx(__fmaf_rn(a3, l2e, -cl));
             }
-            if (k < C) s0 += exp2f_approx(__fmaf_rn(r[5 + k], 1.4426950408889634f, -ml));
-            // true score <= conf / sum * (1 + 1e-5); keep a 1e-3 band around the threshold for the exact path
-            maybe = !(conf < thresh * (s0 + s1) * 0.999f);
+            for (; k < C; ++k) {
+                const float a0 = r[5 + k];
+                mx = fmaxf(mx, a0);
+                s0 += exp2f_approx(__fmaf_rn(a0, l2e, -cl));
+            }
+            const float S = (s0 + s1) + (s2 + s3);
+            const float E = exp2f_approx(__fmaf_rn(-mx, l2e, cl));
+            // true score <= conf / (S * E) * (1 + 1e-5); keep a 1e-3 band around the threshold for the exact path.
+            // A sum that overflowed (or a NaN) proves nothing: both comparisons are written so that they fail then.
+            maybe = !(conf < thresh * (S * E) * 0.999f) || !(S <= 3.0e38f);
         }
     }
     // ---- exact scores of the queued records: one record at a time, the classes spread over the warp's lanes ------
@@ -689,8 +707,15 @@ static ScoreTiles score_tiles(const Geo& g, const float* predicts, int n, float 
     tr &= ~3LL;
     q.tr = (int)max(tr, 0LL);
     q.tile_floats = (int)(align_up((size_t)max(q.tr, 1) * g.L * 4, 128) / 4);
-    // ~44 KB of tiles per CTA (five CTAs per SM), at most four warps
-    q.wpc = (int)max(1LL, min((long long)(kScoreThreads / 32), (long long)45056 / ((long long)q.tile_floats * 4)));
+    // one warp (one tile) per CTA: the tile buffers fill the SM's shared memory either way (~19 per SM at L = 85), but
+    // a finished warp's buffer goes back to the block scheduler at once instead of waiting for three siblings
+    // (measured at cfg2 on B200: 52.7 us with four warps per CTA, 46.6 us with one; profiles/r01_score_variants.txt)
+    q.wpc = 1;
+    if (const char* e = getenv("YV3_SCORE_WPC")) {                 // developer override
+        const long long fit = max(1LL, min((long long)(kScoreThreads / 32), (long long)45056 / ((long long)q.tile_floats * 4)));
+        const int v = atoi(e);
+        if (v >= 1 && v <= fit) q.wpc = v;
+    }
     q.num_tiles = q.tr ? (int)((q.total_rec + q.tr - 1) / q.tr) : 0;
     q.tma = (((uintptr_t)predicts & 15u) == 0) ? 1 : 0;
     q.early = (thresh > 2.0f * g.lo) ? 1 : 0;

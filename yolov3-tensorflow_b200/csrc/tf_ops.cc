@@ -120,7 +120,7 @@ class Yolov3HeadLossOp : public tf::OpKernel {
         void* st = StreamOf(ctx);
         const int rc = yv3_loss_fwd_bwd(&cfg_, p.flat<float>().data(), t.flat<float>().data(), n, m, /*n_global=*/n,
                                         active, 1.0f, out20.flat<float>().data(), grad->flat<float>().data(),
-                                        ws.flat<tf::uint8>().data(), bytes, 3, st);
+                                        ws.flat<tf::uint8>().data(), bytes, 7, st);
         OP_REQUIRES(ctx, rc == YV3_OK, tf::errors::Internal(yv3_strerror(rc)));
         cudaMemcpyAsync(detail->flat<float>().data(), out20.flat<float>().data(), 18 * sizeof(float),
                         cudaMemcpyDeviceToDevice, (cudaStream_t)st);

@@ -213,7 +213,7 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
     cudaStream_t st = (cudaStream_t)stream;
     const Geo g = make_geo(cfg);
     Workspace ws = carve_workspace(workspace, n, m, g.rpi);
-    if ((phases & 3) == 0) return YV3_ERR_SHAPE;
+    if ((phases & 7) == 0) return YV3_ERR_SHAPE;
     const float kappa = upstream / (float)n_global;
     if (phases & 1) {
         if (!cuda_ok(cudaMemsetAsync(ws.status, 0, ws.zero_bytes, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
@@ -225,7 +225,7 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
         a.table = nullptr; a.iou_out = nullptr;
         if (!cuda_ok(launch_assign(g, a, st), "launch_assign")) return YV3_ERR_CUDA;
     }
-    if (!(phases & 2)) return YV3_OK;
+    if (!(phases & 6)) return YV3_OK;
 
     DenseArgs d;
     memset(&d, 0, sizeof(d));
@@ -245,7 +245,8 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
         d.debug = dbg ? atoi(dbg) : 0;
         if (d.debug & 1) d.vec_ok = 0;
     }
-    if (!cuda_ok(launch_loss_dense(g, d, sm_count_cached(), st), "launch_loss_dense")) return YV3_ERR_CUDA;
+    if (!cuda_ok(launch_loss_dense(g, d, sm_count_cached(), (phases & 2) != 0, (phases & 4) != 0, st), "launch_loss_dense"))
+        return YV3_ERR_CUDA;
     return YV3_OK;
 }
 

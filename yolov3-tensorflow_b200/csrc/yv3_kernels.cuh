@@ -46,7 +46,7 @@ struct DenseArgs {
     int vec_ok;                       // predicts and grad are 16-byte aligned
     int debug;                        // developer switches (YV3_DEBUG): 1 scalar path, 4 skip class terms, 8 skip the gradient stores, 16 labels from global memory, 64 zero fill by the lanes instead of bulk stores, 128 zero-fill warp per CTA, 256 skip value stores, 512 skip the zero warp's stores
 };
-cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, cudaStream_t stream);
+cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool sweep, bool fold, cudaStream_t stream);
 
 // ---- decode.cu ---------------------------------------------------------------------------------
 struct DecodeArgs {

@@ -124,13 +124,14 @@ class YOLOv3Loss(object):
                 float(upstream), _lib.ptr(out), _lib.ptr(grad), _lib.ptr(ws), ws.numel())
         stream = _lib.current_stream_ptr(p.device)
         if events is None:
-            _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 3, stream), "yv3_loss_fwd_bwd")
+            _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 7, stream), "yv3_loss_fwd_bwd")
         else:
             # (start, stop) torch.cuda.Event pair bracketing the dense sweep alone (bench.py's roofline)
             _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 1, stream), "yv3_loss_fwd_bwd[assign]")
             events[0].record()
             _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 2, stream), "yv3_loss_fwd_bwd[dense]")
             events[1].record()
+            _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 4, stream), "yv3_loss_fwd_bwd[fold]")
         if rect_active:
             self.current_num += n_global                                       # update_add (:152)
         if world > 1 and self.auto_all_reduce:
