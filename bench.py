@@ -438,8 +438,10 @@ def main():
                        "stream_join": ("once per %d-step graph" % unroll if graph is not None else "once per timed region")
                        if (args.overlap and args.pipeline) else "every step"},
             "stage_ms": {"loss_dense_kernel": dense_ms, "filter_plus_nms": post_ms,
-                         "assign_and_gaps": total_ms / args.steps - dense_ms - post_ms,
-                         "note": "stage times from eager launches with events; ms_per_step from the timed region"},
+                         "step_minus_stages": total_ms / args.steps - dense_ms - post_ms,
+                         "note": "stage times from eager single-stream launches with events; ms_per_step from the timed "
+                                 "region (step_minus_stages < 0: the two halves overlap on two streams; it also holds "
+                                 "the assignment and fold kernels)"},
             "roofline": {"kernel": "loss_dense_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_per_image * n, "avg_launch_ms": dense_ms,
@@ -448,7 +450,7 @@ def main():
                     "h2d_bytes_per_step": int(p_host.numel() * 4 + t_host.numel() * 4),
                     "d2h_bytes_per_step": int(19 * 4 + counts_host.numel() * 4 + keep_host.numel()),
                     "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
-            "gpu_launches": 7 * args.steps,      # assign, dense, score, gather, sort, nms x2
+            "gpu_launches": 8 * args.steps,      # assign, dense sweep, fold, score, gather, sort, nms x2
             "clocks": sampler.summary(),
         }
         if world == 1 and not args.no_cpu_baseline:

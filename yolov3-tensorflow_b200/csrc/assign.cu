@@ -69,10 +69,20 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
             total += v;
         }
         if (valid) {
-            float4* o = reinterpret_cast<float4*>(a.gtab + (((size_t)n * 3 + h) * m + pos) * kGtFloats);
-            o[0] = make_float4(T.box.x0, T.box.y0, T.box.x1, T.box.y1);
-            o[1] = make_float4(T.box.area, 0.f, 0.f, 0.f);
+            float* slot = a.gtab + (size_t)n * gt_slot_floats(m);
+            float4* o = reinterpret_cast<float4*>(slot + 4 + h * gt_head_stride(m)) + 2 * pos;
+            const float4 bx = make_float4(T.box.x0, T.box.y0, T.box.x1, T.box.y1);
+            const float4 ar = make_float4(T.box.area, 0.f, 0.f, 0.f);
+            o[0] = bx;
+            o[1] = ar;
+            if (pos == total - 1) {                       // the last valid label pads the list to a multiple of four
+                for (int e = total; e < ((total + 3) & ~3); ++e) {
+                    o[2 * (e - pos)] = bx;
+                    o[2 * (e - pos) + 1] = ar;
+                }
+            }
         }
+        if (tid == 0) reinterpret_cast<int32_t*>(a.gtab + (size_t)n * gt_slot_floats(m))[0] = total;
         if (tid == 0) a.vcount[n] = total;
     }
 

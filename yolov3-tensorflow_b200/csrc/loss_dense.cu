@@ -139,34 +139,13 @@ __device__ __forceinline__ Logits load_logits(const float* __restrict__ predicts
 
 constexpr int kWideL = 12;            // from here on a 32-byte sector holds values of at most one record
 
-// The valid labels of the (at most two) images a warp's chunk touches, in the warp's own shared-memory slots
-// (slot = image & 1): [V, pad x3] then per head label entries of 8 floats (x0, y0, x1, y1, area, pad x3), head
-// stride m4*8 + 4 floats (m4 = m rounded up to 4) so that the three heads' entries fall into different banks.  The
-// entries V .. round_up(V, 4) - 1 repeat label V - 1: the background test walks the labels four at a time with
-// constant offsets and no index clamping, and a repeated label does not change an "all below" decision.
-__host__ __device__ inline int gt_head_stride(int m) { return ((m + 3) & ~3) * kGtFloats + 4; }
-__host__ __device__ inline int gt_slot_floats(int m) { return 4 + 3 * gt_head_stride(m); }
-
-__device__ __forceinline__ void gt_refill(float* slot, const DenseArgs& a, int n_img, int lane) {
-    const int m = a.m;
-    const int V = __ldg(a.vcount + n_img);
-    if (lane == 0) reinterpret_cast<int*>(slot)[0] = V;
-    const int V4 = (V + 3) & ~3;
-#pragma unroll
-    for (int h = 0; h < 3; ++h) {
-        const float4* src = reinterpret_cast<const float4*>(a.gtab + ((size_t)n_img * 3 + h) * m * kGtFloats);
-        float4* dst = reinterpret_cast<float4*>(slot + 4 + h * gt_head_stride(m));
-        for (int i = lane; i < 2 * V4; i += 32) dst[i] = __ldg(src + 2 * min(i >> 1, V - 1) + (i & 1));
-    }
-}
-
 // ZW: a ninth warp does nothing but the zero fill of the CTA's chunks (those without an owning record), so that the
 // eight computing warps never queue behind the store stream; the sectors it writes and the sectors the record lanes
 // write are disjoint, so the two never need to meet.
 template <int VEC, int SGT, int ZW>
 __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense_kernel(const __grid_constant__ Geo g,
                                                                            const __grid_constant__ DenseArgs a) {
-    extern __shared__ __align__(16) float gt_s[];          // SGT: [kWarps][2][gt_slot_floats(m)], then the zero block
+    extern __shared__ __align__(16) float gt_s[];          // SGT: [2][gt_slot_floats(m)] (slot = image & 1), then the zero block
     __shared__ float red_s[kWarps + 1][12];
     __shared__ float stage_s[VEC ? 1 : kWarps * 32 * kSmallL];
     const int nthreads = kThreads + 32 * ZW, nwarps = kWarps + ZW;
@@ -207,8 +186,7 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
     int cur = zero_warp ? 0 : (blockIdx.x * kWarps + warp) * a.cpw;
     const int cend = zero_warp ? 0 : min(cur + a.cpw, a.num_chunks);
     int nxt = cur + 1;
-    float* slots = gt_s + (size_t)(zero_warp ? 0 : warp) * 2 * gt_slot_floats(m);
-    int held0 = -1, held1 = -1;                      // image held by slot 0 / 1 (warp-uniform)
+    float* slots = gt_s;
     Logits qv = load_logits<VEC>(a.predicts, (long long)cur * 32 + lane, L,
                                  cur < cend && (long long)cur * 32 + lane < a.total_rec);
     unsigned objn = (cur < cend) ? __ldg(a.objbits + cur) : 0u;
@@ -217,12 +195,30 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
     // store per chunk, issued by lane 0 one chunk ahead; the record lanes later overwrite the sectors around
     // their values whole.  The issuing warp never waits on the store queue.
     const bool bulk = VEC && a.bulk && with_grad && wide;
-    float* zblk = gt_s + (SGT ? (size_t)kWarps * 2 * gt_slot_floats(m) : 0);
+    float* zblk = gt_s + (SGT ? (size_t)2 * gt_slot_floats(m) : 0);
     const unsigned chunk_bytes = 128u * (unsigned)L;
+    if (SGT) {
+        // the label slots of the (at most two) images the CTA's records lie in, copied as they are (the assignment
+        // kernel wrote them in this layout, count and padding included): one 128-bit load per thread, all in flight
+        // together with the logits above
+        const int slot_f4 = gt_slot_floats(m) >> 2;
+        const long long crec0 = (long long)blockIdx.x * kWarps * a.cpw * 32;
+        const long long crec1 = min(crec0 + (long long)kWarps * a.cpw * 32, a.total_rec) - 1;
+        const int ia = (int)(crec0 / g.rpi), ib = (int)(crec1 / g.rpi);
+        const float4* src = reinterpret_cast<const float4*>(a.gtab);
+        float4* dst = reinterpret_cast<float4*>(gt_s);
+        for (int i = tid; i < 2 * slot_f4; i += nthreads) {
+            const int second = i >= slot_f4 ? 1 : 0;
+            const int img = ia + second;
+            if (img <= ib) dst[(size_t)(img & 1) * slot_f4 + (i - second * slot_f4)] = __ldg(src + (size_t)img * slot_f4 + (i - second * slot_f4));
+        }
+    }
     if (bulk) {
         for (int i = tid; i < a.zero_bytes / 4; i += nthreads) zblk[i] = 0.f;
         fence_async_smem();
-        __syncthreads();
+    }
+    if (SGT || bulk) __syncthreads();
+    if (bulk) {
         if (lane == 0 && cur < cend && cur != a.num_chunks - 1) {
             char* dst = reinterpret_cast<char*>(a.grad) + (size_t)cur * chunk_bytes;
             for (unsigned o = 0; o < chunk_bytes; o += (unsigned)a.zero_bytes)
@@ -340,21 +336,6 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
         // one division per chunk (uniform), lanes step from there
         const int n_first = (int)((unsigned)rec0 / (unsigned)g.rpi);
         const int r_first = (int)((unsigned)rec0 - (unsigned)n_first * (unsigned)g.rpi);
-        if (SGT) {
-            // labels of the chunk's image(s) into the warp's slots (only when the warp crosses into a new image)
-            const int n_last = n_first + ((r_first + nrec - 1 >= g.rpi) ? 1 : 0);       // rpi >= 32 on this path
-            bool filled = false;
-            for (int ni = n_first; ni <= n_last; ++ni) {
-                const int held = (ni & 1) ? held1 : held0;
-                if (held != ni) {
-                    if (!filled) __syncwarp();           // earlier reads of the slot are done
-                    gt_refill(slots + (ni & 1) * gt_slot_floats(m), a, ni, lane);
-                    if (ni & 1) held1 = ni; else held0 = ni;
-                    filled = true;
-                }
-            }
-            if (filled) __syncwarp();
-        }
         int n_img = n_first, r_img = r_first + lane, head = 0;
         if (ok) {
             while (r_img >= g.rpi) { r_img -= g.rpi; ++n_img; }
@@ -369,8 +350,9 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
                 V = reinterpret_cast<const int*>(slot)[0];
                 gt = reinterpret_cast<const float4*>(slot + 4 + p.h * gt_head_stride(m));
             } else {
-                V = __ldg(a.vcount + n_img);
-                gt = reinterpret_cast<const float4*>(a.gtab + ((size_t)n_img * 3 + p.h) * m * kGtFloats);
+                const float* slot = a.gtab + (size_t)n_img * gt_slot_floats(m);
+                V = __ldg(reinterpret_cast<const int*>(slot));
+                gt = reinterpret_cast<const float4*>(slot + 4 + p.h * gt_head_stride(m));
             }
             bool none_ge = true;                    // max over the labels < thr  <=>  every IoU < thr (V = 0: -inf < thr)
             for (int j = 0; j < V; j += 4) {
@@ -380,12 +362,11 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     if (SGT) {
-                        bx[u] = gt[2 * (j + u)];                                   // slots are padded to four (gt_refill)
+                        bx[u] = gt[2 * (j + u)];                                   // slots are padded to four (assign.cu)
                         ta[u] = reinterpret_cast<const float*>(gt + 2 * (j + u) + 1)[0];
                     } else {
-                        const int jj = min(j + u, V - 1);
-                        bx[u] = __ldg(gt + 2 * jj);
-                        ta[u] = __ldg(reinterpret_cast<const float*>(gt + 2 * jj + 1));
+                        bx[u] = __ldg(gt + 2 * (j + u));
+                        ta[u] = __ldg(reinterpret_cast<const float*>(gt + 2 * (j + u) + 1));
                     }
                 }
                 bool sure = !g.tiou;
@@ -610,25 +591,10 @@ template <int VEC, int SGT, int ZW>
 static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, bool sweep, bool fold, cudaStream_t stream) {
     a.bulk = (VEC && !ZW && g.L >= kWideL && !(a.debug & 64)) ? 1 : 0;
     a.zero_bytes = a.bulk ? (int)min(128LL * g.L, (long long)YV3_DENSE_ZBLK) : 0;
-    const size_t smem = (SGT ? (size_t)kWarps * 2 * gt_slot_floats(a.m) * sizeof(float) : 0) + (size_t)a.zero_bytes;
+    const size_t smem = (SGT ? (size_t)2 * gt_slot_floats(a.m) * sizeof(float) : 0) + (size_t)a.zero_bytes;
     cudaError_t err = cudaFuncSetAttribute(loss_dense_kernel<VEC, SGT, ZW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
-    int per_sm = 1;
-    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, loss_dense_kernel<VEC, SGT, ZW>, kThreads + 32 * ZW, smem);
-    if (err != cudaSuccess) return err;
-    if (per_sm < 1) per_sm = 1;
-    // one chunk per warp and as many CTAs as that takes: short-lived CTAs give their slot back as soon as their slowest
-    // warp is done, and the hardware scheduler balances the rest (measured best on B200 once the final fold left the
-    // kernel: 68 / 70 / 75 us at 1 / 2 / 3 chunks per warp, profiles/r01_dense_variants.txt); more chunks per warp
-    // only when the grid would exceed the partial-row table
-    (void)sm_count; (void)per_sm;
-    a.cpw = 1;
-    while (((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps) > kMaxGrid) ++a.cpw;
-    if (const char* e = getenv("YV3_CPW")) {                       // developer override
-        const int v = atoi(e);
-        const long long need = ((long long)a.num_chunks + (long long)v * kWarps - 1) / ((long long)v * kWarps);
-        if (v >= 1 && need <= kMaxGrid) a.cpw = v;
-    }
+    (void)sm_count;
     const int grid = (int)max(1LL, ((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps));
     if (sweep) {
         loss_dense_kernel<VEC, SGT, ZW><<<grid, kThreads + 32 * ZW, smem, stream>>>(g, a);
@@ -656,8 +622,19 @@ cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool swee
         a.zlo[lane] = lo;
         a.zhi[lane] = hi;
     }
-    // labels in shared memory when they fit (2 slots per warp) and a chunk touches at most two images
-    const bool sgt = a.m <= 32 && g.rpi >= 32 && !(a.debug & 16);
+    // one chunk per warp and as many CTAs as that takes: short-lived CTAs give their slot back as soon as their slowest
+    // warp is done, and the hardware scheduler balances the rest (measured best on B200 once the final fold left the
+    // kernel: 68 / 70 / 75 us at 1 / 2 / 3 chunks per warp, profiles/r01_dense_variants.txt); more chunks per warp
+    // only when the grid would exceed the partial-row table
+    a.cpw = 1;
+    while (((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps) > kMaxGrid) ++a.cpw;
+    if (const char* e = getenv("YV3_CPW")) {                       // developer override
+        const int v = atoi(e);
+        const long long need = ((long long)a.num_chunks + (long long)v * kWarps - 1) / ((long long)v * kWarps);
+        if (v >= 1 && need <= kMaxGrid) a.cpw = v;
+    }
+    // labels in shared memory when they fit and the records of a CTA lie in at most two images (two slots per CTA)
+    const bool sgt = a.m <= 32 && g.rpi >= (long long)kWarps * a.cpw * 32 && !(a.debug & 16);
     const bool vec = a.vec_ok && g.L >= kSmallL;
     // measured on B200 (profiles/r01_dense_variants.txt): the zero warp does not pay (88 vs 83 us at cfg2); kept as a
     // developer switch (YV3_DEBUG bit 128)

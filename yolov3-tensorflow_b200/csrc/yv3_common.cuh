@@ -220,8 +220,9 @@ __device__ __forceinline__ float warp_max(float v) {
 //                                    (the object mask of yolov3_loss.py:328); zeroed together with status
 // then  OwnEntry own[n][3][m]      : assignment result, consumed by the dense pass
 // then  float   img_terms[n][9]    : per image, per head weighted xy / wh / obj sums
-// then  float   gtab[n][3][m][8]   : valid labels of an image in head-h grid units, label order kept:
-//                                    x0, y0, x1, y1, area, 3 pad  (label_decoder.py:53-59, yolov3_loss.py:239-247, :273)
+// then  float   gtab[n][gt_slot_floats(m)] : per image [V, 3 pad], then per head the valid labels in head-h grid units,
+//                                    label order kept: x0, y0, x1, y1, area, 3 pad  (label_decoder.py:53-59,
+//                                    yolov3_loss.py:239-247, :273); see gt_slot_floats below
 // then  int32   vcount[n]          : number of valid labels of an image
 // then  float   partials[grid][12] : per CTA noobj[3], cls[3], rect[3] (see loss_dense.cu)
 struct OwnEntry {
@@ -237,6 +238,13 @@ constexpr unsigned kStatusGtRange = 1u;
 constexpr unsigned kStatusNonFinite = 2u;
 constexpr unsigned kStatusCapacity = 4u;
 constexpr int kGtFloats = 8;
+// One image's label slot, the unit the dense pass copies to shared memory as it is: [V, pad x3], then per head label
+// entries of 8 floats (x0, y0, x1, y1, area, pad x3), head stride m4*8 + 4 floats (m4 = m rounded up to 4) so that the
+// three heads' entries fall into different banks.  Entries V .. round_up(V, 4) - 1 repeat label V - 1 (written by
+// the assignment kernel): the background test walks the labels four at a time with constant offsets and no index
+// clamping, and a repeated label does not change an "all below" decision.
+__host__ __device__ inline int gt_head_stride(int m) { return ((m + 3) & ~3) * kGtFloats + 4; }
+__host__ __device__ inline int gt_slot_floats(int m) { return 4 + 3 * gt_head_stride(m); }
 
 struct Workspace {
     int32_t* status;
@@ -267,7 +275,7 @@ inline Workspace carve_workspace(void* base, int n, int m, long long rpi) {
     w.img_terms = (float*)(p + off);
     off = align_up(off + sizeof(float) * 9 * (size_t)n, 256);
     w.gtab = (float*)(p + off);
-    off = align_up(off + sizeof(float) * kGtFloats * 3 * (size_t)m * (size_t)n, 256);
+    off = align_up(off + sizeof(float) * (size_t)gt_slot_floats(m) * (size_t)n, 256);
     w.vcount = (int32_t*)(p + off);
     off = align_up(off + sizeof(int32_t) * (size_t)n, 256);
     w.partials = (float*)(p + off);
