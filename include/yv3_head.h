@@ -138,6 +138,19 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
                      int n_global, int rectified_active, float upstream, float* loss_out20,
                      float* grad_predicts, void* workspace, size_t workspace_bytes, int phases, void* stream);
 
+/* The same loss on the three head tensors BEFORE they are packed: head_predicts[h] is the output of head h's
+ * last convolution, (n, H_h, W_h, B_h * (5 + C)) fp32 contiguous, h = /8, /16, /32.  Replaces the Reshape + concatenate
+ * of yolov3/yolov3_detector.py:80-85 on the way in (a full read + write of the tensor the packed form needs first)
+ * and the matching split of the gradient on the way out: head_grads[h] has the shape of head_predicts[h] and every
+ * element is written (may be NULL as a whole: forward only).  A head tensor alone is the packed layout of a geometry
+ * that has only that head (the Reshape is a reinterpretation), so the same kernels run once per tensor; results
+ * per record are bit-identical to the packed call, the loss sums are folded in a different (still fixed) order.
+ * All other arguments as in yv3_loss_fwd_bwd.  SURVEY 8(f) rank 2; the inference path still takes the packed form. */
+int yv3_loss_fwd_bwd_heads(const yv3_config* cfg, const float* const head_predicts[3], const float* targets, int n,
+                           int m, int n_global, int rectified_active, float upstream, float* loss_out20,
+                           float* const head_grads[3], void* workspace, size_t workspace_bytes, int phases,
+                           void* stream);
+
 /* Deferred status of the last yv3_assign / yv3_loss_fwd_bwd that used `workspace`: synchronises the
  * stream and returns YV3_OK, YV3_ERR_GT_RANGE or YV3_ERR_NONFINITE (the errors TF would raise /
  * the NaNs it would silently propagate). */

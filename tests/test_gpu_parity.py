@@ -168,6 +168,61 @@ def test_loss_and_gradient_match_oracle(yv3, name, rect):
     np.testing.assert_allclose(loss.rectified_coord_loss.cpu().numpy(), detail64[5], rtol=1e-5, atol=1e-6)
 
 
+@pytest.mark.parametrize("rect", [False, True])
+@pytest.mark.parametrize("name", SMALL)
+def test_loss_on_unpacked_head_tensors(yv3, name, rect):
+    """the three head tensors before yolov3_detector.py:80-85 packs them.  Per record the arithmetic
+    is the packed call's, so gradients are bit-identical to the packed gradient split the same way; the loss sums are
+    folded in another fixed order (fp32 noise); both agree with the oracle."""
+    spec, p, t = _inputs(name, 3, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    n = p.shape[0]
+    heads = [np.ascontiguousarray(h.reshape(n, h.shape[1], h.shape[2], -1)) for h in rn.unpack(p, spec)]
+    td = torch.from_numpy(t).cuda()
+    packed = yv3.YOLOv3Loss(rectified_coord_num=(0 if rect else -1), **product_loss_args(spec))
+    total_p, grad_p = packed.loss_and_grad(td, torch.from_numpy(p).cuda())
+    detail_p = packed.loss_detail.cpu().numpy()
+    loss = yv3.YOLOv3Loss(rectified_coord_num=(0 if rect else -1), **product_loss_args(spec))
+    total, grads = loss.loss_and_grad_heads(td, [torch.from_numpy(h).cuda() for h in heads])
+    loss.check_status()
+    assert loss.current_num == packed.current_num
+    ref_split = rn.unpack(grad_p.cpu().numpy(), spec)
+    for h in range(3):
+        assert grads[h].shape == heads[h].shape
+        assert np.array_equal(grads[h].cpu().numpy().reshape(ref_split[h].shape), ref_split[h])
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), detail_p, rtol=2e-6, atol=1e-7)
+    np.testing.assert_allclose(total.item(), total_p.item(), rtol=2e-6)
+    _, detail64, _ = rt.loss_and_grad(t, p, spec, rectified_active=rect, dtype=torch.float64)
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), detail64, rtol=1e-5, atol=1e-6)
+    # forward only, and a 5-d view of the same memory
+    total_f, none = loss.loss_and_grad_heads(td, [torch.from_numpy(h).cuda().view(n, h.shape[1], h.shape[2], spec.box_num[i], spec.box_len)
+                                                  for i, h in enumerate(heads)], want_grad=False)
+    assert none is None
+    if not rect:
+        assert total_f.item() == total.item()
+
+
+def test_unpacked_head_tensors_at_the_benchmark_shape(yv3):
+    import bench
+    w = bench.WORKLOADS["cfg2_416_c80_b64"]
+    spec = bench.build_spec(w)
+    yv3.backend.set_epsilon(spec.eps)
+    n, m = 8, w["m"]
+    p, t = bench.synth(spec, n, m, 0)
+    p, t = p[:n], t[:n]
+    heads = [np.ascontiguousarray(h.reshape(n, h.shape[1], h.shape[2], -1)) for h in rn.unpack(p, spec)]
+    td = torch.from_numpy(t).cuda()
+    packed = yv3.YOLOv3Loss(rectified_coord_num=-1, **product_loss_args(spec))
+    _, grad_p = packed.loss_and_grad(td, torch.from_numpy(p).cuda())
+    loss = yv3.YOLOv3Loss(rectified_coord_num=-1, **product_loss_args(spec))
+    _, grads = loss.loss_and_grad_heads(td, [torch.from_numpy(h).cuda() for h in heads])
+    loss.check_status()
+    ref_split = rn.unpack(grad_p.cpu().numpy(), spec)
+    for h in range(3):
+        assert np.array_equal(grads[h].cpu().numpy().reshape(ref_split[h].shape), ref_split[h])
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), packed.loss_detail.cpu().numpy(), rtol=2e-6, atol=1e-7)
+
+
 def test_loss_autograd_and_forward_only(yv3):
     spec, p, t = _inputs("coco_64x96_c4", 2, 6)
     yv3.backend.set_epsilon(spec.eps)

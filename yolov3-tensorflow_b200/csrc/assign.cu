@@ -13,6 +13,14 @@
 namespace yv3 {
 
 
+// (head, row, col, anchor) -> record index inside an image of the tensor that holds head h
+__device__ __forceinline__ int rec_in_layout(const Geo& g, const HeadLayout& lay, int h, int y, int x, int b) {
+    const int gidx = y * g.W[h] + x;
+    const int row = gidx / g.fold[h];
+    const int cell = gidx - row * g.fold[h];
+    return row * lay.rpr[h] + lay.seg[h] + cell * g.B[h] + b;
+}
+
 __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a) {
     extern __shared__ float sm[];
     const int m = a.m;
@@ -42,8 +50,8 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
     BoxDec bd = {};
     if (inside) {
         RecLoc p; p.h = h; p.y = row; p.x = col; p.b = 0;
-        int rec0 = record_of(g, h, row, col, 0);
-        const float* base = a.predicts + ((size_t)n * g.rpi + rec0) * g.L;
+        const int rec0 = rec_in_layout(g, a.lay, h, row, col, 0);
+        const float* base = a.lay.pred[h] + ((size_t)n * a.lay.rpi[h] + rec0) * g.L;
         rho = -INFINITY;
         for (int b = 0; b < g.B[h]; ++b) {
             const float* r = base + (size_t)b * g.L;
@@ -98,10 +106,10 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
 #pragma unroll
     for (int c = 0; c < 5; ++c) e.g[c] = 0.f;
     if (owned) {
-        e.rec = record_of(g, h, row, col, best);
+        e.rec = rec_in_layout(g, a.lay, h, row, col, best);
         {
-            const long long grec = (long long)n * g.rpi + e.rec;                 // object mask bit (:328)
-            atomicOr(a.objbits + (grec >> 5), 1u << (unsigned)(grec & 31));
+            const long long grec = (long long)n * a.lay.rpi[h] + e.rec;          // object mask bit (:328)
+            atomicOr(a.lay.objbits[h] + (grec >> 5), 1u << (unsigned)(grec & 31));
         }
         e.cls = (int)cf;                                                 // tf.cast(., int32) truncates (:362)
         const float one = 1.0f;
@@ -158,7 +166,15 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
     }
 }
 
-cudaError_t launch_assign(const Geo& g, const AssignArgs& a, cudaStream_t stream) {
+cudaError_t launch_assign(const Geo& g, const AssignArgs& a_in, cudaStream_t stream) {
+    AssignArgs a = a_in;
+    if (!a.lay.pred[0]) {                                   // packed form: one tensor, one bit array
+        for (int h = 0; h < 3; ++h) {
+            a.lay.pred[h] = a.predicts;
+            a.lay.rpi[h] = g.rpi; a.lay.rpr[h] = g.rpr; a.lay.seg[h] = g.seg_base[h];
+            a.lay.objbits[h] = a.objbits;
+        }
+    }
     int threads = ((3 * a.m + 31) / 32) * 32;
     size_t smem = sizeof(float) * 13 * (size_t)a.m;
     assign_kernel<<<a.n, threads, smem, stream>>>(g, a);

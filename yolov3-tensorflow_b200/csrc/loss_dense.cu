@@ -526,7 +526,7 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
     if (tid < 9) {
         float acc = 0.f;
         for (int w = 0; w < nwarps; ++w) acc += red_s[w][tid];
-        a.partials[(size_t)blockIdx.x * kPartialFloats + tid] = acc;
+        a.partials[((size_t)a.row_base + blockIdx.x) * kPartialFloats + tid] = acc;
     }
 }
 
@@ -588,7 +588,7 @@ __global__ void __launch_bounds__(kFoldThreads) loss_fold_kernel(const __grid_co
 }
 
 template <int VEC, int SGT, int ZW>
-static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, bool sweep, bool fold, cudaStream_t stream) {
+static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, bool sweep, bool fold, cudaStream_t stream, int* grid_out) {
     a.bulk = (VEC && !ZW && g.L >= kWideL && !(a.debug & 64)) ? 1 : 0;
     a.zero_bytes = a.bulk ? (int)min(128LL * g.L, (long long)YV3_DENSE_ZBLK) : 0;
     const size_t smem = (SGT ? (size_t)2 * gt_slot_floats(a.m) * sizeof(float) : 0) + (size_t)a.zero_bytes;
@@ -601,11 +601,18 @@ static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, bool
         err = cudaGetLastError();
         if (err != cudaSuccess) return err;
     }
-    if (fold) loss_fold_kernel<<<1, kFoldThreads, 0, stream>>>(g, a, grid);      // the grid is a function of the arguments
+    if (grid_out) *grid_out = grid;
+    if (fold) loss_fold_kernel<<<1, kFoldThreads, 0, stream>>>(g, a, a.row_base + grid);      // the grid is a function of the arguments
     return cudaGetLastError();
 }
 
-cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool sweep, bool fold, cudaStream_t stream) {
+cudaError_t launch_loss_fold(const Geo& g, const DenseArgs& a, int nrows, cudaStream_t stream) {
+    loss_fold_kernel<<<1, kFoldThreads, 0, stream>>>(g, a, nrows);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool sweep, bool fold, cudaStream_t stream, int* grid_out) {
+    const int max_grid = a.max_grid > 0 ? a.max_grid : kMaxGrid;
     a.num_chunks = (int)((a.total_rec + 31) / 32);
     // zero-fill pattern of the whole-sector path (see the kernel): bit k of lane l <=> 128-bit word l + 32 k of a
     // chunk lies in a sector without box/conf values
@@ -627,11 +634,11 @@ cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool swee
     // kernel: 68 / 70 / 75 us at 1 / 2 / 3 chunks per warp, profiles/r01_dense_variants.txt); more chunks per warp
     // only when the grid would exceed the partial-row table
     a.cpw = 1;
-    while (((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps) > kMaxGrid) ++a.cpw;
+    while (((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps) > max_grid) ++a.cpw;
     if (const char* e = getenv("YV3_CPW")) {                       // developer override
         const int v = atoi(e);
         const long long need = ((long long)a.num_chunks + (long long)v * kWarps - 1) / ((long long)v * kWarps);
-        if (v >= 1 && need <= kMaxGrid) a.cpw = v;
+        if (v >= 1 && need <= max_grid) a.cpw = v;
     }
     // labels in shared memory when they fit and the records of a CTA lie in at most two images (two slots per CTA)
     const bool sgt = a.m <= 32 && g.rpi >= (long long)kWarps * a.cpw * 32 && !(a.debug & 16);
@@ -639,9 +646,9 @@ cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool swee
     // measured on B200 (profiles/r01_dense_variants.txt): the zero warp does not pay (88 vs 83 us at cfg2); kept as a
     // developer switch (YV3_DEBUG bit 128)
     const bool zw = vec && g.L >= kWideL && a.grad != nullptr && (a.debug & 128);
-    if (vec && zw) return sgt ? launch_variant<1, 1, 1>(g, a, sm_count, sweep, fold, stream) : launch_variant<1, 0, 1>(g, a, sm_count, sweep, fold, stream);
-    if (vec) return sgt ? launch_variant<1, 1, 0>(g, a, sm_count, sweep, fold, stream) : launch_variant<1, 0, 0>(g, a, sm_count, sweep, fold, stream);
-    return sgt ? launch_variant<0, 1, 0>(g, a, sm_count, sweep, fold, stream) : launch_variant<0, 0, 0>(g, a, sm_count, sweep, fold, stream);
+    if (vec && zw) return sgt ? launch_variant<1, 1, 1>(g, a, sm_count, sweep, fold, stream, grid_out) : launch_variant<1, 0, 1>(g, a, sm_count, sweep, fold, stream, grid_out);
+    if (vec) return sgt ? launch_variant<1, 1, 0>(g, a, sm_count, sweep, fold, stream, grid_out) : launch_variant<1, 0, 0>(g, a, sm_count, sweep, fold, stream, grid_out);
+    return sgt ? launch_variant<0, 1, 0>(g, a, sm_count, sweep, fold, stream, grid_out) : launch_variant<0, 0, 0>(g, a, sm_count, sweep, fold, stream, grid_out);
 }
 
 }  // namespace yv3

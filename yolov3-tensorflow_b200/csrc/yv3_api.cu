@@ -192,6 +192,7 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
     Workspace ws = carve_workspace(workspace, n, m, g.rpi);
     if (!cuda_ok(cudaMemsetAsync(ws.status, 0, ws.zero_bytes, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
     AssignArgs a;
+    memset(&a, 0, sizeof(a));
     a.predicts = predicts; a.targets = targets; a.n = n; a.m = m;
     a.kappa = 1.0f / (float)n;
     a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
@@ -201,53 +202,118 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
     return YV3_OK;
 }
 
-int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
-                     int n_global, int rectified_active, float upstream, float* loss_out20,
-                     float* grad_predicts, void* workspace, size_t workspace_bytes, int phases, void* stream) {
-    int rc = loss_common_checks(cfg, predicts, targets, n, m, workspace, workspace_bytes);
+// The geometry of ONE head tensor (N, H, W, B*L) seen as a packed tensor that has only that head: the /32 row of
+// yolov3_detector.py:80-85 holds fold*B records of it, starting at 0 (the Reshape alone, without the concatenate).
+static Geo head_geo(const Geo& g, int h) {
+    Geo q = g;
+    q.rpr = g.fold[h] * g.B[h];
+    q.rpi = g.rows32 * q.rpr;
+    const int far = 1 << 30;
+    q.seg_base[0] = 0;
+    q.seg_base[1] = (h >= 1) ? 0 : far;          // locate(): k >= seg_base[2] ? 2 : k >= seg_base[1] ? 1 : 0
+    q.seg_base[2] = (h == 2) ? 0 : far;
+    q.mg_rpr = q.rpr == 1 ? 0u : (unsigned)((1ULL << 32) / (unsigned long long)q.rpr + 1ULL);
+    return q;
+}
+
+static int loss_impl(const yv3_config* cfg, const float* const pred[3], bool unpacked, const float* targets, int n,
+                     int m, int n_global, int rectified_active, float upstream, float* loss_out20,
+                     float* const grad[3], void* workspace, size_t workspace_bytes, int phases, void* stream) {
+    int rc = loss_common_checks(cfg, pred[0], targets, n, m, workspace, workspace_bytes);
     if (rc != YV3_OK) return rc;
     if (!loss_out20) return YV3_ERR_NULL;
     if (n_global < n) return YV3_ERR_SHAPE;
     if ((long long)n * yv3_records_per_image(cfg) >= (1LL << 31)) return YV3_ERR_CAPACITY;
-    if (grad_predicts && !aligned16(grad_predicts)) return YV3_ERR_ALIGN;
+    const int tensors = unpacked ? 3 : 1;
+    const bool want_grad = grad[0] != nullptr;
+    for (int h = 0; h < tensors; ++h) {
+        if (!pred[h]) return YV3_ERR_NULL;
+        if (!aligned4(pred[h])) return YV3_ERR_ALIGN;
+        if (want_grad && (!grad[h] || !aligned16(grad[h]))) return grad[h] ? YV3_ERR_ALIGN : YV3_ERR_NULL;
+    }
     cudaStream_t st = (cudaStream_t)stream;
     const Geo g = make_geo(cfg);
     Workspace ws = carve_workspace(workspace, n, m, g.rpi);
     if ((phases & 7) == 0) return YV3_ERR_SHAPE;
     const float kappa = upstream / (float)n_global;
+    // one object-bit region per tensor
+    Geo gh[3];
+    uint32_t* bits[3];
+    {
+        size_t word = 0;
+        for (int h = 0; h < 3; ++h) {
+            gh[h] = unpacked ? head_geo(g, h) : g;
+            bits[h] = ws.objbits + (unpacked ? word : 0);
+            word += (size_t)(((long long)n * gh[h].rpi + 31) / 32 + 1);
+        }
+    }
     if (phases & 1) {
         if (!cuda_ok(cudaMemsetAsync(ws.status, 0, ws.zero_bytes, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
         AssignArgs a;
-        a.predicts = predicts; a.targets = targets; a.n = n; a.m = m;
+        memset(&a, 0, sizeof(a));
+        a.predicts = pred[0]; a.targets = targets; a.n = n; a.m = m;
         a.kappa = kappa;
         a.own = ws.own; a.img_terms = ws.img_terms; a.status = ws.status;
-    a.objbits = ws.objbits; a.gtab = ws.gtab; a.vcount = ws.vcount;
-        a.table = nullptr; a.iou_out = nullptr;
+        a.objbits = ws.objbits; a.gtab = ws.gtab; a.vcount = ws.vcount;
+        if (unpacked) {
+            for (int h = 0; h < 3; ++h) {
+                a.lay.pred[h] = pred[h];
+                a.lay.rpi[h] = gh[h].rpi; a.lay.rpr[h] = gh[h].rpr; a.lay.seg[h] = 0;
+                a.lay.objbits[h] = bits[h];
+            }
+        }
         if (!cuda_ok(launch_assign(g, a, st), "launch_assign")) return YV3_ERR_CUDA;
     }
     if (!(phases & 6)) return YV3_OK;
 
     DenseArgs d;
     memset(&d, 0, sizeof(d));
-    d.predicts = predicts; d.grad = grad_predicts;
     d.own = ws.own; d.img_terms = ws.img_terms; d.partials = ws.partials; d.status = ws.status;
-    d.objbits = ws.objbits; d.gtab = ws.gtab; d.vcount = ws.vcount;
+    d.gtab = ws.gtab; d.vcount = ws.vcount;
     d.detail = loss_out20;
     d.n = n; d.m = m; d.n_global = n_global;
-    d.total_rec = (long long)n * g.rpi;
     d.kappa = kappa; d.upstream = upstream;
     d.rect_active = rectified_active ? 1 : 0;
-    // both tensors 16-byte aligned: the box logits of a record are read (and its gradient written) as two
-    // aligned 128-bit words; otherwise the scalar path
-    d.vec_ok = (aligned16(predicts) && (!grad_predicts || aligned16(grad_predicts))) ? 1 : 0;
-    {
-        const char* dbg = getenv("YV3_DEBUG");
-        d.debug = dbg ? atoi(dbg) : 0;
-        if (d.debug & 1) d.vec_ok = 0;
+    const char* dbg = getenv("YV3_DEBUG");
+    d.debug = dbg ? atoi(dbg) : 0;
+    int rows = 0;
+    for (int h = 0; h < tensors; ++h) {
+        d.predicts = pred[h]; d.grad = grad[h];
+        d.objbits = bits[h];
+        d.total_rec = (long long)n * gh[h].rpi;
+        d.row_base = rows;
+        d.max_grid = unpacked ? kMaxGrid / 4 : kMaxGrid;
+        // both tensors 16-byte aligned: the box logits of a record are read (and its gradient written) as two
+        // aligned 128-bit words; otherwise the scalar path
+        d.vec_ok = (aligned16(pred[h]) && (!grad[h] || aligned16(grad[h])) && !(d.debug & 1)) ? 1 : 0;
+        int grid = 0;
+        if (!cuda_ok(launch_loss_dense(gh[h], d, sm_count_cached(), (phases & 2) != 0, false, st, &grid), "launch_loss_dense"))
+            return YV3_ERR_CUDA;
+        rows += grid;
     }
-    if (!cuda_ok(launch_loss_dense(g, d, sm_count_cached(), (phases & 2) != 0, (phases & 4) != 0, st), "launch_loss_dense"))
-        return YV3_ERR_CUDA;
+    if (phases & 4) {
+        if (!cuda_ok(launch_loss_fold(g, d, rows, st), "launch_loss_fold")) return YV3_ERR_CUDA;
+    }
     return YV3_OK;
+}
+
+int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
+                     int n_global, int rectified_active, float upstream, float* loss_out20,
+                     float* grad_predicts, void* workspace, size_t workspace_bytes, int phases, void* stream) {
+    const float* pred[3] = {predicts, nullptr, nullptr};
+    float* grad[3] = {grad_predicts, nullptr, nullptr};
+    return loss_impl(cfg, pred, false, targets, n, m, n_global, rectified_active, upstream, loss_out20, grad, workspace,
+                     workspace_bytes, phases, stream);
+}
+
+int yv3_loss_fwd_bwd_heads(const yv3_config* cfg, const float* const head_predicts[3], const float* targets, int n,
+                           int m, int n_global, int rectified_active, float upstream, float* loss_out20,
+                           float* const head_grads[3], void* workspace, size_t workspace_bytes, int phases,
+                           void* stream) {
+    if (!head_predicts) return YV3_ERR_NULL;
+    float* none[3] = {nullptr, nullptr, nullptr};
+    return loss_impl(cfg, head_predicts, true, targets, n, m, n_global, rectified_active, upstream, loss_out20,
+                     head_grads ? head_grads : none, workspace, workspace_bytes, phases, stream);
 }
 
 int yv3_read_status(void* workspace, void* stream) {

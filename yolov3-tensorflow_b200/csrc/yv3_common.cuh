@@ -268,7 +268,7 @@ inline Workspace carve_workspace(void* base, int n, int m, long long rpi) {
     w.status = (int32_t*)(p + off);
     off = align_up(off + sizeof(int32_t) * kStatusInts, 32);
     w.objbits = (uint32_t*)(p + off);
-    off = align_up(off + sizeof(uint32_t) * (size_t)(((long long)n * rpi + 31) / 32 + 1), 256);
+    off = align_up(off + sizeof(uint32_t) * (size_t)(((long long)n * rpi + 31) / 32 + 8), 256);   // + slack: one region per head tensor in the un-packed form
     w.zero_bytes = off;
     w.own = (OwnEntry*)(p + off);
     off = align_up(off + sizeof(OwnEntry) * (size_t)n * 3 * (size_t)m, 256);

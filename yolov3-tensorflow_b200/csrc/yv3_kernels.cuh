@@ -5,8 +5,18 @@
 namespace yv3 {
 
 // ---- assign.cu ---------------------------------------------------------------------------------
+// Where the records of head h live: the packed tensor (one base, the head's segment inside every /32 row), or one
+// tensor per head (N, H, W, B*L) -- which is the packed layout of a geometry that has only that head (a /32 row of
+// it holds fold*B records starting at 0).  record = row32 * rpr + seg + cell * B + b inside an image of rpi records.
+struct HeadLayout {
+    const float* pred[3];
+    int rpi[3], rpr[3], seg[3];
+    uint32_t* objbits[3];      // object mask bits by record index in that tensor (zeroed by the caller)
+};
+
 struct AssignArgs {
-    const float* predicts;
+    const float* predicts;    // packed form (lay is filled from it by launch_assign when lay.pred[0] is NULL)
+    HeadLayout lay;
     const float* targets;
     int n, m;
     float kappa;          // upstream / n_global
@@ -44,9 +54,12 @@ struct DenseArgs {
     float upstream;
     int rect_active;
     int vec_ok;                       // predicts and grad are 16-byte aligned
+    int row_base;                     // first partial row of this launch (un-packed form: one launch per head tensor)
+    int max_grid;                     // CTAs this launch may use (rows of the partial table it owns)
     int debug;                        // developer switches (YV3_DEBUG): 1 scalar path, 4 skip class terms, 8 skip the gradient stores, 16 labels from global memory, 64 zero fill by the lanes instead of bulk stores, 128 zero-fill warp per CTA, 256 skip value stores, 512 skip the zero warp's stores
 };
-cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool sweep, bool fold, cudaStream_t stream);
+cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool sweep, bool fold, cudaStream_t stream, int* grid_out = nullptr);
+cudaError_t launch_loss_fold(const Geo& g, const DenseArgs& a, int nrows, cudaStream_t stream);
 
 // ---- decode.cu ---------------------------------------------------------------------------------
 struct DecodeArgs {

@@ -53,6 +53,7 @@ class YOLOv3Loss(object):
         self.focal_gamma = focal_gamma
         self.is_tiou_recall = is_tiou_recall
         self.rectified_coord_num = int(rectified_coord_num)
+        self._box_num = [len(a) for a in anchor_boxes]
         self._cfg = _lib.make_config(self.head_grid_sizes, self.class_num, anchor_boxes, iou_thresh,
                                      loss_weights, rectified_loss_weight, is_focal_loss, focal_alpha,
                                      focal_gamma, is_tiou_recall)
@@ -160,6 +161,53 @@ class YOLOv3Loss(object):
         ``grad_out`` reuses a caller-owned gradient buffer; ``events`` = (start, stop) CUDA events recorded
         around the dense sweep alone."""
         return self._run(targets, predicts, want_grad=True, upstream=upstream, events=events, grad_out=grad_out)
+
+    def loss_and_grad_heads(self, targets, head_predicts, upstream=1.0, want_grad=True, grads_out=None):
+        """The same loss on the three head tensors BEFORE yolov3_detector.py:80-85 packs them: ``head_predicts`` =
+        [/8, /16, /32] conv outputs, each (N, H_h, W_h, B_h * (5 + C)) (or (..., B_h, 5 + C)) fp32 contiguous.
+        Returns (total loss, [gradient per head tensor, same shapes] or None).  Saves the Reshape + concatenate copy
+        on the way in and the split of the gradient on the way out."""
+        if len(head_predicts) != 3:
+            raise ValueError("head_predicts must hold the /8, /16 and /32 head tensors")
+        heads = [_lib.to_device_f32(p) for p in head_predicts]
+        t = _lib.to_device_f32(targets, heads[0].device)
+        n = heads[0].shape[0]
+        for h, p in enumerate(heads):
+            gh, gw = self.head_grid_sizes[h]
+            if p.shape[0] != n or tuple(p.shape[1:3]) != (gh, gw) or p[0].numel() != gh * gw * self._box_num[h] * self.box_len:
+                raise ValueError("head %d must be (N, %d, %d, %d), got %s" % (
+                    h, gh, gw, self._box_num[h] * self.box_len, tuple(p.shape)))
+        if t.dim() != 2 or t.shape[0] != n or t.shape[1] % 5 != 0 or t.shape[1] == 0:
+            raise ValueError("targets must be (N, M*5) with the same N as the head tensors")
+        m = t.shape[1] // 5
+        world = self._world()
+        n_global = n * world
+        rect_active = self.current_num <= self.rectified_coord_num            # :125 (read before the add)
+        ws = self._workspace(n, m, heads[0].device)
+        out = torch.empty(20, dtype=torch.float32, device=heads[0].device)
+        grads = None
+        if want_grad:
+            grads = [torch.empty_like(p) for p in heads] if grads_out is None else list(grads_out)
+            for g, p in zip(grads, heads):
+                if g.shape != p.shape or g.dtype != torch.float32 or not g.is_contiguous() or g.device != p.device:
+                    raise ValueError("grads_out must be contiguous fp32 tensors shaped like the head tensors")
+        pp = (ctypes.c_void_p * 3)(*[_lib.ptr(p) for p in heads])
+        gp = (ctypes.c_void_p * 3)(*[_lib.ptr(g) for g in grads]) if grads is not None else None
+        rc = self._lib.yv3_loss_fwd_bwd_heads(ctypes.byref(self._cfg), pp, _lib.ptr(t), n, m, n_global,
+                                              1 if rect_active else 0, float(upstream), _lib.ptr(out), gp, _lib.ptr(ws),
+                                              ws.numel(), 7, _lib.current_stream_ptr(heads[0].device))
+        _lib.check(rc, "yv3_loss_fwd_bwd_heads")
+        if rect_active:
+            self.current_num += n_global                                       # update_add (:152)
+        if world > 1 and self.auto_all_reduce:
+            self._all_reduce(out)
+        self._last_out = out
+        self._last_ws = ws
+        detail = out[:18].view(6, 3)
+        self.loss_detail = detail
+        for i, name in enumerate(_DETAIL_NAMES):
+            setattr(self, name, detail[i])
+        return out[18], grads
 
     def all_reduce_detail(self):
         """Sum the last call's 20 loss floats over the ranks (only needed with ``auto_all_reduce = False``)."""
