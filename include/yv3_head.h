@@ -145,7 +145,7 @@ int yv3_loss_fwd_bwd(const yv3_config* cfg, const float* predicts, const float* 
  * element is written (may be NULL as a whole: forward only).  A head tensor alone is the packed layout of a geometry
  * that has only that head (the Reshape is a reinterpretation), so the same kernels run once per tensor; results
  * per record are bit-identical to the packed call, the loss sums are folded in a different (still fixed) order.
- * All other arguments as in yv3_loss_fwd_bwd.  SURVEY 8(f) rank 2; the inference path still takes the packed form. */
+ * All other arguments as in yv3_loss_fwd_bwd.  SURVEY 8(f) rank 2; yv3_filter_heads is the inference-side twin. */
 int yv3_loss_fwd_bwd_heads(const yv3_config* cfg, const float* const head_predicts[3], const float* targets, int n,
                            int m, int n_global, int rectified_active, float upstream, float* loss_out20,
                            float* const head_grads[3], void* workspace, size_t workspace_bytes, int phases,
@@ -186,6 +186,12 @@ int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], con
 int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float score_thresh,
                       float* cand, int32_t capacity, int32_t* counts, void* workspace,
                       size_t workspace_bytes, void* stream);
+
+/* yv3_filter_packed on the three head tensors before they are packed (head_predicts[h]: (n, H_h, W_h, B_h * (5 + C))
+ * fp32 contiguous, h = /8, /16, /32; see yv3_loss_fwd_bwd_heads): same rows, same order, same counts.  Every head must
+ * have at least 4 records per image (YV3_ERR_SHAPE otherwise: a 32x32 input with fewer than 4 anchors at /32). */
+int yv3_filter_heads(const yv3_config* cfg, const float* const head_predicts[3], int n, float score_thresh, float* cand,
+                     int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Class-aware greedy NMS, YOLOv3PostProcessor._apply_nms (yolov3/yolov3_post_process.py:108-159), for
  * n independent candidate lists.  cand is (n, capacity, 8) fp32; list i holds

@@ -381,6 +381,31 @@ def test_fused_filter_nms_from_packed_logits(yv3, name, thr):
             assert np.array_equal(np.asarray(got_lists[h]).reshape(-1, 9), np.asarray(ref_lists[h]).reshape(-1, 9))
 
 
+@pytest.mark.parametrize("name", SMALL)
+@pytest.mark.parametrize("thr", [0.3, 0.001])
+def test_filter_on_unpacked_head_tensors(yv3, name, thr):
+    """SURVEY 8f rank 2, inference side: the candidate rows and counts from the three head tensors equal the packed
+    call's bit for bit."""
+    spec, p, _ = _inputs(name, 3, 4)
+    yv3.backend.set_epsilon(spec.eps)
+    n = p.shape[0]
+    heads = [torch.from_numpy(np.ascontiguousarray(h.reshape(n, h.shape[1], h.shape[2], -1))).cuda() for h in rn.unpack(p, spec)]
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    cand_p, counts_p = post.filter(torch.from_numpy(p).cuda(), thr)
+    cand_p, counts_p = cand_p.cpu().numpy(), counts_p.cpu().numpy()
+    if min(hh * ww * b for (hh, ww), b in zip(spec.head_grid_sizes, spec.box_num)) < 4:
+        from yolov3_tensorflow_b200._lib import Yv3Error
+        with pytest.raises(Yv3Error):                      # documented limit: >= 4 records per image in every head
+            post.filter_heads(heads, thr)
+        return
+    cand_h, counts_h = post.filter_heads(heads, thr)
+    post.check_status()
+    assert np.array_equal(counts_h.cpu().numpy(), counts_p)
+    for i in range(n):
+        k = int(counts_p[i].sum())
+        assert np.array_equal(cand_h[i, :k].cpu().numpy(), cand_p[i, :k])
+
+
 def test_filter_rows_close_to_oracle_decode(yv3):
     """From logits, rows agree with the NumPy oracle to fp32 noise and the kept counts are equal away from
     the threshold."""

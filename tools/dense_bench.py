@@ -71,6 +71,11 @@ def main():
     out["loss_dense"] = {"median_us": 1e3 * t[len(t) // 2], "p10_us": 1e3 * t[len(t) // 10]}
     out["loss_all"] = timed(lambda: loss.loss_and_grad(td, pd, grad_out=grad), steps)
     out["loss_fwd_only"] = timed(lambda: loss.loss(td, pd), steps)
+    from oracle import ref_numpy as rn
+    heads = [torch.from_numpy(np.ascontiguousarray(h.reshape(n, h.shape[1], h.shape[2], -1))).cuda() for h in rn.unpack(p_np, spec)]
+    hgrads = [torch.empty_like(h) for h in heads]
+    out["loss_all_unpacked_heads"] = timed(lambda: loss.loss_and_grad_heads(td, heads, grads_out=hgrads), steps)
+    out["pack_copy_for_context"] = timed(lambda: torch.cat([h.reshape(n, spec.head_grid_sizes[2][0], spec.head_grid_sizes[2][1], -1) for h in heads], dim=-1), steps)
     out["filter"] = timed(lambda: post.filter(pd, w["score_thresh"], out=(cand, counts)), steps)
     out["nms"] = timed(lambda: post.nms(cand, counts, w["nms_thresh"], out=keep), steps)
     out["memset_grad"] = timed(lambda: grad.zero_(), steps)

@@ -74,6 +74,8 @@ _SIGNATURES = {
                                           ctypes.c_int32, _P, _P, ctypes.c_size_t, _P]),
     "yv3_filter_packed": (ctypes.c_int, [_P, _P, ctypes.c_int, ctypes.c_float, _P, ctypes.c_int32, _P, _P,
                                          ctypes.c_size_t, _P]),
+    "yv3_filter_heads": (ctypes.c_int, [_P, ctypes.POINTER(_P), ctypes.c_int, ctypes.c_float, _P, ctypes.c_int32, _P,
+                                        _P, ctypes.c_size_t, _P]),
     "yv3_nms": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int32, ctypes.c_int,
                                ctypes.c_double, _P, _P, ctypes.c_size_t, _P]),
 }

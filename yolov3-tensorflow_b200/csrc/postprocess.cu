@@ -178,44 +178,62 @@ __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_
     if (lane < 6) tcount[(size_t)unit * 8 + lane] = cnt_lane;
 }
 
-// One CTA per image: the tiles' counts go to shared memory, an exclusive prefix per head puts them in the reference's
-// order (head /8,/16,/32, raster inside a head: tiles in order, staged order inside a tile), then one THREAD per
-// candidate row finds its tile by binary search and writes the row (:65-75), decoding the box from its five logits.
+// One CTA per image: per head, the counts of the tiles that hold the image's records of that head go to shared memory
+// and an exclusive prefix puts them in the reference's order (head /8,/16,/32, raster inside a head: tiles in order,
+// staged order inside a tile); then one THREAD per candidate row finds its tile by binary search and writes the row
+// (:65-75), decoding the box from its five logits.  `src` says where head h's records and tiles live: the packed tensor
+// (all three heads share one tile range) or one tensor per head.
+struct GatherSrc {
+    const float* pred[3];
+    int rpi[3], rpr[3], seg[3];     // records per image / per 32-row / first record of the head in a row, in that tensor
+    int tbase[3];                   // first tile of that tensor in stage / tcount
+};
 constexpr int kGatherThreads = 512;
-__global__ void __launch_bounds__(kGatherThreads) gather_kernel(const __grid_constant__ Geo g, const float* __restrict__ predicts,
-                                                                const ScoreTiles q, const float4* __restrict__ stage,
+__global__ void __launch_bounds__(kGatherThreads) gather_kernel(const __grid_constant__ Geo g, const __grid_constant__ GatherSrc src,
+                                                                int tr, const float4* __restrict__ stage,
                                                                 const int32_t* __restrict__ tcount, float* __restrict__ cand,
                                                                 int capacity, int32_t* __restrict__ counts, int32_t* status) {
     __shared__ int wsum_s[kGatherThreads / 32];
     __shared__ int carry_s;
     __shared__ int head_base_s[4];
-    extern __shared__ int gsm[];                   // tc_s [ntiles][8] counts of this image's tiles (slot resolved: 3 used),
-                                                   // then pre_s [3][ntiles] exclusive prefix inside a head
+    __shared__ int t0_s[3], nt_s[3], off_s[3];
+    extern __shared__ int gsm[];                   // per head list: cnt_s[nt], before_s[nt], pre_s[nt] (concatenated)
     const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long img0 = (long long)n * g.rpi;
-    const int t0 = (int)(img0 / q.tr), t1 = (int)((img0 + g.rpi - 1) / q.tr);
-    const int ntiles = t1 - t0 + 1;
-    int* tc_s = gsm;
-    int* pre_s = gsm + 8 * ntiles;
-    for (int i = tid; i < ntiles * 8; i += kGatherThreads) {
-        const int ti = i >> 3, c = i & 7;
-        const int t = t0 + ti;
-        const int sl = n - (int)(((long long)t * q.tr) / g.rpi);                 // 0 or 1: this image's slot in the tile
-        // columns 0..2: this image's counts per head; 3..5: staged rows BEFORE this image's group of head c - 3
-        int v = 0;
-        const int32_t* tc = tcount + (size_t)t * 8;
-        if (c < 3) v = tc[sl * 3 + c];
-        else if (c < 6) { for (int gi = 0; gi < sl * 3 + (c - 3); ++gi) v += tc[gi]; }
-        tc_s[i] = v;
+    if (tid == 0) {
+        int off = 0;
+        for (int h = 0; h < 3; ++h) {
+            const long long img0 = (long long)n * src.rpi[h];
+            const int t0 = (int)(img0 / tr), t1 = (int)((img0 + src.rpi[h] - 1) / tr);
+            t0_s[h] = t0; nt_s[h] = t1 - t0 + 1; off_s[h] = off;
+            off += 3 * (t1 - t0 + 1);
+        }
+    }
+    __syncthreads();
+    for (int h = 0; h < 3; ++h) {
+        const int nt = nt_s[h];
+        int* cnt_s = gsm + off_s[h];
+        int* before_s = cnt_s + nt;
+        for (int ti = tid; ti < nt; ti += kGatherThreads) {
+            const int tl = t0_s[h] + ti;                                               // tile inside its tensor
+            const int sl = n - (int)(((long long)tl * tr) / src.rpi[h]);              // 0 or 1: this image's slot in the tile
+            const int32_t* tc = tcount + (size_t)(src.tbase[h] + tl) * 8;
+            int before = 0;
+            for (int gi = 0; gi < sl * 3 + h; ++gi) before += tc[gi];                  // staged rows ahead of this group
+            cnt_s[ti] = tc[sl * 3 + h];
+            before_s[ti] = before;
+        }
     }
     __syncthreads();
     int total_all = 0;
     for (int h = 0; h < 3; ++h) {
+        const int nt = nt_s[h];
+        const int* cnt_s = gsm + off_s[h];
+        int* pre_s = gsm + off_s[h] + 2 * nt;
         if (tid == 0) carry_s = 0;
         __syncthreads();
-        for (int b = 0; b < ntiles; b += kGatherThreads) {
+        for (int b = 0; b < nt; b += kGatherThreads) {
             const int ti = b + tid;
-            const int c = (ti < ntiles) ? tc_s[ti * 8 + h] : 0;
+            const int c = (ti < nt) ? cnt_s[ti] : 0;
             int incl = c;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -226,7 +244,7 @@ __global__ void __launch_bounds__(kGatherThreads) gather_kernel(const __grid_con
             __syncthreads();
             int wbase = carry_s;
             for (int w = 0; w < warp; ++w) wbase += wsum_s[w];
-            if (ti < ntiles) pre_s[h * ntiles + ti] = wbase + incl - c;
+            if (ti < nt) pre_s[ti] = wbase + incl - c;
             __syncthreads();
             if (tid == kGatherThreads - 1) carry_s = wbase + incl;
             __syncthreads();
@@ -245,17 +263,20 @@ __global__ void __launch_bounds__(kGatherThreads) gather_kernel(const __grid_con
     for (int pos = tid; pos < nrows; pos += kGatherThreads) {
         const int h = (pos >= head_base_s[2]) ? 2 : ((pos >= head_base_s[1]) ? 1 : 0);
         const int rel = pos - head_base_s[h];
+        const int nt = nt_s[h];
+        const int* cnt_s = gsm + off_s[h];
+        const int* before_s = cnt_s + nt;
+        const int* pre = cnt_s + 2 * nt;
         // last tile whose exclusive prefix is <= rel and that holds rows (prefix strictly increases past it)
-        const int* pre = pre_s + h * ntiles;
-        int lo = 0, hi = ntiles - 1;
+        int lo = 0, hi = nt - 1;
         while (lo < hi) {
             const int mid = (lo + hi + 1) >> 1;
             if (pre[mid] <= rel) lo = mid; else hi = mid - 1;
         }
         // tiles with zero rows share the prefix of their successor: step back to the one that contains rel
-        while (rel - pre[lo] >= tc_s[lo * 8 + h]) --lo;
+        while (rel - pre[lo] >= cnt_s[lo]) --lo;
         const int e = rel - pre[lo];
-        const float4 sv = stage[(size_t)(t0 + lo) * q.tr + tc_s[lo * 8 + 3 + h] + e];
+        const float4 sv = stage[(size_t)(src.tbase[h] + t0_s[h] + lo) * tr + before_s[lo] + e];
         const int rih = __float_as_int(sv.w);
         RecLoc p;
         p.h = h;
@@ -263,7 +284,9 @@ __global__ void __launch_bounds__(kGatherThreads) gather_kernel(const __grid_con
         p.b = rih - cell * g.B[h];
         p.y = cell / g.W[h];
         p.x = cell - p.y * g.W[h];
-        const float* r = predicts + ((size_t)n * g.rpi + record_of(g, h, p.y, p.x, p.b)) * g.L;
+        const int row32 = cell / g.fold[h];
+        const int rec = row32 * src.rpr[h] + src.seg[h] + (cell - row32 * g.fold[h]) * g.B[h] + p.b;
+        const float* r = src.pred[h] + ((size_t)n * src.rpi[h] + rec) * g.L;
         const BoxDec d = decode_box(g, p, __ldg(r), __ldg(r + 1), __ldg(r + 2), __ldg(r + 3), __ldg(r + 4));
         float4* o = reinterpret_cast<float4*>(out + (size_t)pos * YV3_CAND_COLS);
         o[0] = make_float4(__fdiv_rn(d.x0, g.fW[h]), __fdiv_rn(d.y0, g.fH[h]), __fdiv_rn(d.x1, g.fW[h]),
@@ -698,14 +721,14 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
 }
 
 // ---- launchers ------------------------------------------------------------------------------------------
-static ScoreTiles score_tiles(const Geo& g, const float* predicts, int n, float thresh) {
+static ScoreTiles score_tiles(const Geo& g, const float* predicts, int n, float thresh, int tr_force = 0) {
     ScoreTiles q;
     q.total_rec = (long long)n * g.rpi;
     long long tr = 32;
     tr = min(tr, (long long)(200 * 1024) / ((long long)g.L * 4));   // a very long record: fewer records per warp
     tr = min(tr, (long long)g.rpi);                               // a tile touches at most two images
     tr &= ~3LL;
-    q.tr = (int)max(tr, 0LL);
+    q.tr = tr_force ? tr_force : (int)max(tr, 0LL);
     q.tile_floats = (int)(align_up((size_t)max(q.tr, 1) * g.L * 4, 128) / 4);
     // one warp (one tile) per CTA: the tile buffers fill the SM's shared memory either way (~19 per SM at L = 85), but
     // a finished warp's buffer goes back to the block scheduler at once instead of waiting for three siblings
@@ -722,28 +745,56 @@ static ScoreTiles score_tiles(const Geo& g, const float* predicts, int n, float 
     return q;
 }
 
-int score_num_tiles(const Geo& g, int n) { return score_tiles(g, nullptr, n, 0.f).num_tiles; }
+// records per tile when every head tensor is swept on its own: the smallest of the three (a tile touches two images at most)
+int heads_tr(const Geo& g, int n) {
+    int tr = 32;
+    for (int h = 0; h < 3; ++h) tr = min(tr, score_tiles(head_geo(g, h), nullptr, n, 0.f).tr);
+    return tr;
+}
 
-cudaError_t launch_filter_packed(const Geo& g, const float* predicts, int n, float thresh, float* cand,
+// tiles the workspace must hold: the packed sweep or the three per-head sweeps, whichever is more
+int score_num_tiles(const Geo& g, int n) {
+    const int packed = score_tiles(g, nullptr, n, 0.f).num_tiles;
+    const int tr = heads_tr(g, n);
+    int heads = 0;
+    if (tr >= 4) for (int h = 0; h < 3; ++h) heads += score_tiles(head_geo(g, h), nullptr, n, 0.f, tr).num_tiles;
+    return max(packed, heads) + 4;
+}
+
+// pred[0] alone: the packed tensor; unpacked: one tensor per head (N, H, W, B*L), each swept under its single-head geometry
+cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool unpacked, int n, float thresh, float* cand,
                                  int capacity, int32_t* counts, int32_t* status, float4* stage, int32_t* tcount,
                                  int sm_count, cudaStream_t stream) {
     (void)sm_count;
-    const ScoreTiles q = score_tiles(g, predicts, n, thresh);
-    if (q.tr < 4) return cudaErrorInvalidValue;
-    const size_t smem = (size_t)q.wpc * q.tile_floats * 4;
-    if (smem > 220 * 1024) return cudaErrorInvalidValue;
-    cudaError_t err = cudaFuncSetAttribute(score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (err != cudaSuccess) return err;
-    const int grid = (q.num_tiles + q.wpc - 1) / q.wpc;
-    score_tile_kernel<<<grid, 32 * q.wpc, smem, stream>>>(g, predicts, q, thresh, stage, tcount);
-    err = cudaGetLastError();
-    if (err != cudaSuccess) return err;
-    const int ntiles_img = (int)((g.rpi + q.tr - 1) / q.tr) + 2;
-    const size_t gsmem = (size_t)11 * ntiles_img * sizeof(int);
+    GatherSrc src;
+    memset(&src, 0, sizeof(src));
+    const int tr = unpacked ? heads_tr(g, n) : score_tiles(g, pred[0], n, thresh).tr;
+    if (tr < 4) return cudaErrorInvalidValue;
+    int tbase = 0, gtiles = 0;
+    for (int h = 0; h < (unpacked ? 3 : 1); ++h) {
+        const Geo gh = unpacked ? head_geo(g, h) : g;
+        const ScoreTiles q = score_tiles(gh, pred[h], n, thresh, tr);
+        const size_t smem = (size_t)q.wpc * q.tile_floats * 4;
+        if (smem > 220 * 1024) return cudaErrorInvalidValue;
+        cudaError_t err = cudaFuncSetAttribute(score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err != cudaSuccess) return err;
+        const int grid = (q.num_tiles + q.wpc - 1) / q.wpc;
+        score_tile_kernel<<<grid, 32 * q.wpc, smem, stream>>>(gh, pred[h], q, thresh, stage + (size_t)tbase * tr, tcount + (size_t)tbase * 8);
+        err = cudaGetLastError();
+        if (err != cudaSuccess) return err;
+        for (int k = (unpacked ? h : 0); k < (unpacked ? h + 1 : 3); ++k) {
+            src.pred[k] = pred[h];
+            src.rpi[k] = gh.rpi; src.rpr[k] = gh.rpr; src.seg[k] = unpacked ? 0 : g.seg_base[k];
+            src.tbase[k] = tbase;
+            gtiles += (int)((gh.rpi + tr - 1) / tr) + 2;
+        }
+        tbase += q.num_tiles;
+    }
+    const size_t gsmem = (size_t)3 * gtiles * sizeof(int);
     if (gsmem > 200 * 1024) return cudaErrorInvalidValue;
-    err = cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem);
+    cudaError_t err = cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem);
     if (err != cudaSuccess) return err;
-    gather_kernel<<<n, kGatherThreads, gsmem, stream>>>(g, predicts, q, stage, tcount, cand, capacity, counts, status);
+    gather_kernel<<<n, kGatherThreads, gsmem, stream>>>(g, src, tr, stage, tcount, cand, capacity, counts, status);
     return cudaGetLastError();
 }
 

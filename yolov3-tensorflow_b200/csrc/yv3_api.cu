@@ -202,20 +202,6 @@ int yv3_assign(const yv3_config* cfg, const float* predicts, const float* target
     return YV3_OK;
 }
 
-// The geometry of ONE head tensor (N, H, W, B*L) seen as a packed tensor that has only that head: the /32 row of
-// yolov3_detector.py:80-85 holds fold*B records of it, starting at 0 (the Reshape alone, without the concatenate).
-static Geo head_geo(const Geo& g, int h) {
-    Geo q = g;
-    q.rpr = g.fold[h] * g.B[h];
-    q.rpi = g.rows32 * q.rpr;
-    const int far = 1 << 30;
-    q.seg_base[0] = 0;
-    q.seg_base[1] = (h >= 1) ? 0 : far;          // locate(): k >= seg_base[2] ? 2 : k >= seg_base[1] ? 1 : 0
-    q.seg_base[2] = (h == 2) ? 0 : far;
-    q.mg_rpr = q.rpr == 1 ? 0u : (unsigned)((1ULL << 32) / (unsigned long long)q.rpr + 1ULL);
-    return q;
-}
-
 static int loss_impl(const yv3_config* cfg, const float* const pred[3], bool unpacked, const float* targets, int n,
                      int m, int n_global, int rectified_active, float upstream, float* loss_out20,
                      float* const grad[3], void* workspace, size_t workspace_bytes, int phases, void* stream) {
@@ -438,19 +424,37 @@ static int post_checks(const yv3_config* cfg, int n, int32_t capacity, void* wor
     return YV3_OK;
 }
 
-int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float score_thresh, float* cand,
-                      int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, void* stream) {
-    if (!cfg || !predicts || !cand || !counts) return YV3_ERR_NULL;
+static int filter_impl(const yv3_config* cfg, const float* const pred[3], bool unpacked, int n, float score_thresh,
+                       float* cand, int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes,
+                       void* stream) {
+    if (!cfg || !cand || !counts) return YV3_ERR_NULL;
+    for (int h = 0; h < (unpacked ? 3 : 1); ++h) {
+        if (!pred[h]) return YV3_ERR_NULL;
+        if (!aligned4(pred[h])) return YV3_ERR_ALIGN;
+    }
     PostWs ws;
     int rc = post_checks(cfg, n, capacity, workspace, workspace_bytes, &ws);
     if (rc != YV3_OK) return rc;
-    if (!aligned4(predicts) || !aligned16(cand)) return YV3_ERR_ALIGN;
+    if (!aligned16(cand)) return YV3_ERR_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
     if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
     const Geo g = make_geo(cfg);
-    if (!cuda_ok(launch_filter_packed(g, predicts, n, score_thresh, cand, capacity, counts, ws.status, ws.stage, ws.tcount,
-                             sm_count_cached(), st), "launch_filter_packed")) return YV3_ERR_CUDA;
+    if (unpacked && heads_tr(g, n) < 4) return YV3_ERR_SHAPE;      // a head with fewer than 4 records per image
+    if (!cuda_ok(launch_filter_packed(g, pred, unpacked, n, score_thresh, cand, capacity, counts, ws.status, ws.stage,
+                                      ws.tcount, sm_count_cached(), st), "launch_filter_packed")) return YV3_ERR_CUDA;
     return YV3_OK;
+}
+
+int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float score_thresh, float* cand,
+                      int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, void* stream) {
+    const float* pred[3] = {predicts, nullptr, nullptr};
+    return filter_impl(cfg, pred, false, n, score_thresh, cand, capacity, counts, workspace, workspace_bytes, stream);
+}
+
+int yv3_filter_heads(const yv3_config* cfg, const float* const head_predicts[3], int n, float score_thresh, float* cand,
+                     int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!head_predicts) return YV3_ERR_NULL;
+    return filter_impl(cfg, head_predicts, true, n, score_thresh, cand, capacity, counts, workspace, workspace_bytes, stream);
 }
 
 int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], const float* const boxes[3],

@@ -40,6 +40,20 @@ struct Geo {
     unsigned mg_rpr, mg_B[3], mg_W[3];      // 0 for d = 1
 };
 
+// The geometry of ONE head tensor (N, H, W, B*L) seen as a packed tensor that has only that head: the /32 row of
+// yolov3_detector.py:80-85 holds fold*B records of it, starting at 0 (the Reshape alone, without the concatenate).
+inline Geo head_geo(const Geo& g, int h) {
+    Geo q = g;
+    q.rpr = g.fold[h] * g.B[h];
+    q.rpi = g.rows32 * q.rpr;
+    const int far = 1 << 30;
+    q.seg_base[0] = 0;
+    q.seg_base[1] = (h >= 1) ? 0 : far;          // locate(): k >= seg_base[2] ? 2 : k >= seg_base[1] ? 1 : 0
+    q.seg_base[2] = (h == 2) ? 0 : far;
+    q.mg_rpr = q.rpr == 1 ? 0u : (unsigned)((1ULL << 32) / (unsigned long long)q.rpr + 1ULL);
+    return q;
+}
+
 // x / d for x < 2^22 with mg = floor(2^32 / d) + 1, d <= 2^10 (x * (mg * d - 2^32) < 2^32)
 __device__ __forceinline__ int fast_div(int x, unsigned mg) { return mg ? (int)__umulhi((unsigned)x, mg) : x; }
 

@@ -94,7 +94,8 @@ struct PostWs {
 };
 int nms_cap2(int capacity);
 int score_num_tiles(const Geo& g, int n);
-cudaError_t launch_filter_packed(const Geo& g, const float* predicts, int n, float thresh, float* cand,
+int heads_tr(const Geo& g, int n);      // records per tile of the per-head sweeps; < 4: a head has fewer than 4 records per image
+cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool unpacked, int n, float thresh, float* cand,
                                  int capacity, int32_t* counts, int32_t* status, float4* stage, int32_t* tcount,
                                  int sm_count, cudaStream_t stream);
 cudaError_t launch_filter_decoded(const Geo& g, const float* const decoded[3], const float* const boxes[3],

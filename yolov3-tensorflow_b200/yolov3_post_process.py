@@ -215,6 +215,32 @@ class HeadPostProcessor(object):
         self._last_ws = ws
         return cand, counts
 
+    def filter_heads(self, head_predicts, score_thresh, out=None):
+        """``filter`` on the three head tensors before yolov3_detector.py:80-85 packs them ([/8, /16, /32], each
+        (N, H_h, W_h, B_h * (5 + C)) fp32 contiguous): same rows, order and counts, without the concatenate copy."""
+        if len(head_predicts) != 3:
+            raise ValueError("head_predicts must hold the /8, /16 and /32 head tensors")
+        heads = [_lib.to_device_f32(p) for p in head_predicts]
+        n = heads[0].shape[0]
+        for h, p in enumerate(heads):
+            gh, gw = self.head_grid_sizes[h]
+            if p.shape[0] != n or tuple(p.shape[1:3]) != (gh, gw) or p[0].numel() * 1 != gh * gw * int(self._cfg.box_num[h]) * (5 + self.class_num):
+                raise ValueError("head %d has shape %s, expected (N, %d, %d, %d)" % (
+                    h, tuple(p.shape), gh, gw, int(self._cfg.box_num[h]) * (5 + self.class_num)))
+        ws = self._workspace(n, heads[0].device)
+        if out is None:
+            cand = torch.empty((n, self.capacity, 8), dtype=torch.float32, device=heads[0].device)
+            counts = torch.empty((n, 3), dtype=torch.int32, device=heads[0].device)
+        else:
+            cand, counts = out
+        pp = (ctypes.c_void_p * 3)(*[_lib.ptr(p) for p in heads])
+        rc = self._lib.yv3_filter_heads(ctypes.byref(self._cfg), pp, n, float(np.float32(score_thresh)), _lib.ptr(cand),
+                                        self.capacity, _lib.ptr(counts), _lib.ptr(ws), ws.numel(),
+                                        _lib.current_stream_ptr(heads[0].device))
+        _lib.check(rc, "yv3_filter_heads")
+        self._last_ws = ws
+        return cand, counts
+
     def nms(self, cand, counts, nms_thresh, out=None):
         n = cand.shape[0]
         ws = self._workspace(n, cand.device)
