@@ -184,6 +184,9 @@ def main():
     ap.add_argument("--overlap", type=int, default=1, help="1: loss and post-process halves of a step on two streams")
     ap.add_argument("--priority", default="post", choices=["none", "post", "loss"],
                     help="which half of a step runs on a high-priority stream (two-stream mode)")
+    ap.add_argument("--layout", default="packed", choices=["packed", "heads"],
+                    help="packed: the reference's concatenated head tensor; heads: the three head tensors before "
+                         "yolov3_detector.py:80-85 packs them (yv3_loss_fwd_bwd_heads / yv3_filter_heads)")
     ap.add_argument("--graph-steps", type=int, default=8, help="steps captured per CUDA graph (N = 1)")
     ap.add_argument("--pipeline", type=int, default=1,
                     help="1: the two streams are joined once per graph / timed region, 0: after every step")
@@ -230,12 +233,28 @@ def main():
         if args.priority == "loss":
             torch.cuda.set_stream(torch.cuda.Stream(priority=-1))
 
+    heads = hgrads = None
+    if args.layout == "heads":
+        # the same logits as three contiguous head tensors (N, H, W, B*L): what the head convolutions emit
+        heads = []
+        for h in range(3):
+            gh, gw = spec.head_grid_sizes[h]
+            s0, s1 = spec.chan_base[h], spec.chan_base[h] + spec.head_channels[h]
+            heads.append(pd[..., s0:s1].reshape(n, gh, gw, -1).contiguous())
+        hgrads = [torch.empty_like(x) for x in heads]
+
     def half_loss(events=None):
+        if heads is not None and events is None:
+            total, _ = loss.loss_and_grad_heads(td, heads, grads_out=hgrads)
+            return total
         total, _ = loss.loss_and_grad(td, pd, events=events, grad_out=grad)
         return total
 
     def half_post():
-        post.filter(pd, w["score_thresh"], out=(cand, counts))
+        if heads is not None:
+            post.filter_heads(heads, w["score_thresh"], out=(cand, counts))
+        else:
+            post.filter(pd, w["score_thresh"], out=(cand, counts))
         post.nms(cand, counts, w["nms_thresh"], out=keep)
 
     def steps(count, events=None):
@@ -433,7 +452,7 @@ def main():
                        "l2": "inputs larger than L2: predicts %.0f MB + gradient %.0f MB per GPU vs 126 MB L2" % (
                            pd.numel() * 4 / 1e6, grad.numel() * 4 / 1e6),
                        "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image,
-                       "launch": mode, "streams": 2 if args.overlap else 1,
+                       "layout": args.layout, "launch": mode, "streams": 2 if args.overlap else 1,
                        "high_priority_stream": args.priority if args.overlap else None,
                        "stream_join": ("once per %d-step graph" % unroll if graph is not None else "once per timed region")
                        if (args.overlap and args.pipeline) else "every step"},
@@ -450,7 +469,8 @@ def main():
                     "h2d_bytes_per_step": int(p_host.numel() * 4 + t_host.numel() * 4),
                     "d2h_bytes_per_step": int(19 * 4 + counts_host.numel() * 4 + keep_host.numel()),
                     "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
-            "gpu_launches": 8 * args.steps,      # assign, dense sweep, fold, score, gather, sort, nms x2
+            # assign, dense sweep, fold, score, gather, sort, nms x2 (the sweeps run once per head tensor in the heads layout)
+            "gpu_launches": (12 if args.layout == "heads" else 8) * args.steps,
             "clocks": sampler.summary(),
         }
         if world == 1 and not args.no_cpu_baseline:
