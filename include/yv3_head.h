@@ -205,6 +205,19 @@ int yv3_nms(const yv3_config* cfg, const float* cand, const int32_t* counts, int
             int32_t capacity, int num_classes, double nms_thresh, uint8_t* keep, void* workspace,
             size_t workspace_bytes, void* stream);
 
+/* The rows run.py gets from apply_nms + resize_boxes (yolov3_post_process.py:94-104, :162-172), on the device: per
+ * image and per head (/8, /16, /32) the returned rows in local-id order,
+ *   [x0 * target_w, y0 * target_h, x1 * target_w, y1 * target_h, conf, prob, class, score, id]   float64
+ * (the reference's rows are float64 and an fp32 coordinate times an integer size is exact there).  cand / counts as
+ * written by yv3_filter_*, keep as written by yv3_nms.  bug_compat != 0 reproduces the shipped id collision of :81-104
+ * (a row is returned iff its local id equals the local id of a greedy survivor of ANY head); 0 returns the survivors.
+ *   rows_out    device, n * capacity * 9 doubles; image i's rows start at i * capacity * 9, heads back to back
+ *   counts_out  device, n * 3 int32: rows returned per head
+ * SURVEY 8(f) rank 3 (the mAP accumulation named there is an open TODO in the reference, run.py:78-79: nothing to match). */
+int yv3_collect_kept(const float* cand, const int32_t* counts, const uint8_t* keep, int n, int32_t capacity,
+                     double target_w, double target_h, int bug_compat, double* rows_out, int32_t* counts_out,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

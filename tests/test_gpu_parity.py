@@ -345,6 +345,22 @@ def test_postprocess_matches_reference_outputs(yv3, path):
     res = yv3.YOLOv3PostProcessor.resize_boxes(nms, np.array([w8 * 8, h8 * 8] * 2))
     for h in range(3):
         assert np.array_equal(np.asarray(res[h]).reshape(-1, 9), z["resized%d" % h])
+    # the same rows from the device-side collect (yv3_collect_kept) on the reference's own filtered rows
+    lens = [len(f) for f in filt]
+    if sum(lens):
+        from yolov3_tensorflow_b200 import _lib
+        cap = sum(lens)
+        cand = torch.from_numpy(np.concatenate([f.reshape(-1, 8) for f in filt], 0).astype(np.float32)).cuda().reshape(1, cap, 8)
+        counts = torch.tensor([lens], dtype=torch.int32, device="cuda")
+        keep = torch.from_numpy(mask.astype(np.uint8)).cuda().reshape(1, cap)
+        rows = torch.empty((1, cap, 9), dtype=torch.float64, device="cuda")
+        oc = torch.empty((1, 3), dtype=torch.int32, device="cuda")
+        _lib.check(_lib.lib().yv3_collect_kept(_lib.ptr(cand), _lib.ptr(counts), _lib.ptr(keep), 1, cap, float(w8 * 8),
+                                               float(h8 * 8), 1, _lib.ptr(rows), _lib.ptr(oc), None), "yv3_collect_kept")
+        oc = oc.cpu().numpy()[0]
+        assert oc.tolist() == [len(z["resized%d" % h]) for h in range(3)]
+        got = rows.cpu().numpy()[0, :oc.sum()]
+        assert np.array_equal(got, np.concatenate([z["resized%d" % h].reshape(-1, 9) for h in range(3)], 0))
 
 
 @pytest.mark.parametrize("name", SMALL)
@@ -404,6 +420,27 @@ def test_filter_on_unpacked_head_tensors(yv3, name, thr):
     for i in range(n):
         k = int(counts_p[i].sum())
         assert np.array_equal(cand_h[i, :k].cpu().numpy(), cand_p[i, :k])
+
+
+@pytest.mark.parametrize("bug_compat", [True, False])
+@pytest.mark.parametrize("name", ["coco_64x96_c4", "shipped_384x480_c0", "coco_64_c20"])
+def test_collect_kept_rows_resized(yv3, name, bug_compat):
+    """apply_nms' returned rows + resize_boxes on the device equal the host path (which the golden
+    vectors pin to the reference) row for row, float64."""
+    spec, p, _ = _inputs(name, 3, 4)
+    yv3.backend.set_epsilon(spec.eps)
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    res = post.run(torch.from_numpy(p).cuda(), 0.05, 0.45)
+    gh, gw = spec.head_grid_sizes[0]
+    size = (gw * 8, gh * 8)
+    rows, counts = post.collect(res, size, bug_compat=bug_compat)
+    rows, counts = rows.cpu().numpy(), counts.cpu().numpy()
+    for i in range(3):
+        ref = yv3.YOLOv3PostProcessor.resize_boxes(post.to_reference(res, i, bug_compat=bug_compat), np.array(size * 2))
+        assert counts[i].tolist() == [len(r) for r in ref]
+        flat = [np.asarray(r).reshape(-1, 9) for r in ref]
+        assert np.array_equal(rows[i, :counts[i].sum()], np.concatenate(flat, 0).astype(np.float64))
+    assert counts.sum() > 0
 
 
 def test_filter_rows_close_to_oracle_decode(yv3):

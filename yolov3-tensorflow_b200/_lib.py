@@ -67,6 +67,8 @@ _SIGNATURES = {
     "yv3_loss_fwd_bwd_heads": (ctypes.c_int, [_P, ctypes.POINTER(_P), _P, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                               ctypes.c_int, ctypes.c_float, _P, ctypes.POINTER(_P), _P, ctypes.c_size_t,
                                               ctypes.c_int, _P]),
+    "yv3_collect_kept": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int32, ctypes.c_double, ctypes.c_double,
+                                        ctypes.c_int, _P, _P, _P]),
     "yv3_read_status": (ctypes.c_int, [_P, _P]),
     "yv3_query_postprocess_workspace": (ctypes.c_int, [_P, ctypes.c_int, ctypes.c_int32,
                                                        ctypes.POINTER(ctypes.c_size_t)]),

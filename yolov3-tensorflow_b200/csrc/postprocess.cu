@@ -720,6 +720,77 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
   }
 }
 
+// ---- kept rows, resized (yolov3_post_process.py:94-104, :162-172) -------------------------------------------
+// One CTA per image: the rows apply_nms returns, per head in local-id order, with box[:4] * target_size and the id
+// column, as float64 (the reference's rows are float64; an fp32 coordinate times an integer size is exact there).
+// bug_compat: a row of head h is returned iff its LOCAL id is the local id of a greedy survivor of ANY head (:81-104,
+// start_index never advances); otherwise exactly the survivors.
+constexpr int kCollectThreads = 256;
+__global__ void __launch_bounds__(kCollectThreads) collect_kernel(const float* __restrict__ cand, const int32_t* __restrict__ counts,
+                                                                  const unsigned char* __restrict__ keep, int capacity,
+                                                                  double tw, double th, int bug_compat,
+                                                                  double* __restrict__ rows_out, int32_t* __restrict__ counts_out) {
+    __shared__ int wsum_s[kCollectThreads / 32];
+    __shared__ int carry_s;
+    const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int c[3], off[4];
+    off[0] = 0;
+    for (int h = 0; h < 3; ++h) {
+        c[h] = max(0, min(counts[n * 3 + h], capacity - off[h]));
+        off[h + 1] = off[h] + c[h];
+    }
+    const float* rows = cand + (size_t)n * capacity * YV3_CAND_COLS;
+    const unsigned char* kp = keep + (size_t)n * capacity;
+    double* out = rows_out + (size_t)n * capacity * 9;
+    if (tid == 0) carry_s = 0;
+    __syncthreads();
+    for (int h = 0; h < 3; ++h) {
+        const int start = carry_s;
+        __syncthreads();
+        for (int b = 0; b < c[h]; b += kCollectThreads) {
+            const int i = b + tid;
+            bool sel = false;
+            if (i < c[h]) {
+                if (bug_compat) {
+                    for (int k = 0; k < 3; ++k) sel = sel || (i < c[k] && kp[off[k] + i] != 0);
+                } else {
+                    sel = kp[off[h] + i] != 0;
+                }
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, sel);
+            if (lane == 0) wsum_s[warp] = __popc(bal);
+            __syncthreads();
+            int base = carry_s;
+            for (int w = 0; w < warp; ++w) base += wsum_s[w];
+            if (sel) {
+                const int pos = base + __popc(bal & ((1u << lane) - 1u));
+                const float4 r0 = *reinterpret_cast<const float4*>(rows + (size_t)(off[h] + i) * YV3_CAND_COLS);
+                const float4 r1 = *reinterpret_cast<const float4*>(rows + (size_t)(off[h] + i) * YV3_CAND_COLS + 4);
+                double* o = out + (size_t)pos * 9;
+                o[0] = __dmul_rn((double)r0.x, tw); o[1] = __dmul_rn((double)r0.y, th);
+                o[2] = __dmul_rn((double)r0.z, tw); o[3] = __dmul_rn((double)r0.w, th);
+                o[4] = (double)r1.x; o[5] = (double)r1.y; o[6] = (double)r1.z; o[7] = (double)r1.w;
+                o[8] = (double)i;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                int tot = 0;
+                for (int w = 0; w < kCollectThreads / 32; ++w) tot += wsum_s[w];
+                carry_s += tot;
+            }
+            __syncthreads();
+        }
+        if (tid == 0) counts_out[n * 3 + h] = carry_s - start;
+        __syncthreads();
+    }
+}
+
+cudaError_t launch_collect(const float* cand, const int32_t* counts, const unsigned char* keep, int n, int capacity,
+                           double tw, double th, int bug_compat, double* rows_out, int32_t* counts_out, cudaStream_t stream) {
+    collect_kernel<<<n, kCollectThreads, 0, stream>>>(cand, counts, keep, capacity, tw, th, bug_compat, rows_out, counts_out);
+    return cudaGetLastError();
+}
+
 // ---- launchers ------------------------------------------------------------------------------------------
 static ScoreTiles score_tiles(const Geo& g, const float* predicts, int n, float thresh, int tr_force = 0) {
     ScoreTiles q;

@@ -477,6 +477,17 @@ int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], con
     return YV3_OK;
 }
 
+int yv3_collect_kept(const float* cand, const int32_t* counts, const uint8_t* keep, int n, int32_t capacity,
+                     double target_w, double target_h, int bug_compat, double* rows_out, int32_t* counts_out,
+                     void* stream) {
+    if (!cand || !counts || !keep || !rows_out || !counts_out) return YV3_ERR_NULL;
+    if (n < 1 || capacity < 1 || capacity > YV3_MAX_CANDIDATES) return YV3_ERR_SHAPE;
+    if (!aligned16(cand) || ((uintptr_t)rows_out & 7u)) return YV3_ERR_ALIGN;
+    if (!cuda_ok(launch_collect(cand, counts, keep, n, capacity, target_w, target_h, bug_compat ? 1 : 0, rows_out, counts_out,
+                                (cudaStream_t)stream), "launch_collect")) return YV3_ERR_CUDA;
+    return YV3_OK;
+}
+
 int yv3_nms(const yv3_config* cfg, const float* cand, const int32_t* counts, int count_cols, int n,
             int32_t capacity, int num_classes, double nms_thresh, uint8_t* keep, void* workspace,
             size_t workspace_bytes, void* stream) {

@@ -94,6 +94,8 @@ struct PostWs {
 };
 int nms_cap2(int capacity);
 int score_num_tiles(const Geo& g, int n);
+cudaError_t launch_collect(const float* cand, const int32_t* counts, const unsigned char* keep, int n, int capacity,
+                           double tw, double th, int bug_compat, double* rows_out, int32_t* counts_out, cudaStream_t stream);
 int heads_tr(const Geo& g, int n);      // records per tile of the per-head sweeps; < 4: a head has fewer than 4 records per image
 cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool unpacked, int n, float thresh, float* cand,
                                  int capacity, int32_t* counts, int32_t* status, float4* stage, int32_t* tcount,

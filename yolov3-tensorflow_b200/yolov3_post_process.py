@@ -262,6 +262,20 @@ class HeadPostProcessor(object):
         rc = self._lib.yv3_read_status(_lib.ptr(self._last_ws), _lib.current_stream_ptr(self._last_ws.device))
         _lib.check(rc, "post-process")
 
+    def collect(self, result, target_size, bug_compat=True):
+        """apply_nms' returned rows + resize_boxes (yolov3_post_process.py:94-104, :162-172) on the device:
+        (rows (N, capacity, 9) float64 [x0*w, y0*h, x1*w, y1*h, conf, prob, class, score, id], counts (N, 3) int32 rows
+        per head).  ``target_size`` = (w, h) of the network input, as run.py passes it."""
+        cand, counts, keep = result["cand"], result["counts"], result["keep"]
+        n = cand.shape[0]
+        rows = torch.empty((n, self.capacity, 9), dtype=torch.float64, device=cand.device)
+        out_counts = torch.empty((n, 3), dtype=torch.int32, device=cand.device)
+        rc = self._lib.yv3_collect_kept(_lib.ptr(cand), _lib.ptr(counts), _lib.ptr(keep), n, self.capacity,
+                                        float(target_size[0]), float(target_size[1]), 1 if bug_compat else 0,
+                                        _lib.ptr(rows), _lib.ptr(out_counts), _lib.current_stream_ptr(cand.device))
+        _lib.check(rc, "yv3_collect_kept")
+        return rows, out_counts
+
     def to_reference(self, result, image, bug_compat=True):
         """run.py's per-image structure after filter_boxes + apply_nms: 3 entries, (0,9) array or list of
         (9,) float64 rows (fp32 rows for class_num == 0 are promoted by the id column exactly as in the
