@@ -16,8 +16,10 @@ from . import backend  # noqa: F401
 from ._lib import to_device_f32 as to_device  # noqa: F401
 from .label_decoder import LabelDecoder  # noqa: F401
 from .label_ingest import LabelBatcher, parse_label_line, read_label_file  # noqa: F401
+from .loss_detail_log import detail_log_values, detail_scalars, format_detail  # noqa: F401
 from .yolov3_decoder import YOLOv3Decoder  # noqa: F401
 from .yolov3_loss import YOLOv3Loss  # noqa: F401
 from .yolov3_post_process import HeadPostProcessor, YOLOv3PostProcessor  # noqa: F401
 
-__all__ = ["YOLOv3Decoder", "LabelDecoder", "LabelBatcher", "parse_label_line", "read_label_file", "YOLOv3Loss", "YOLOv3PostProcessor", "HeadPostProcessor", "backend", "to_device"]
+__all__ = ["YOLOv3Decoder", "LabelDecoder", "LabelBatcher", "parse_label_line", "read_label_file", "YOLOv3Loss", "YOLOv3PostProcessor", "HeadPostProcessor", "backend", "to_device",
+           "detail_log_values", "detail_scalars", "format_detail"]
