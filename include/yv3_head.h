@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define YV3_ABI_VERSION 2
+#define YV3_ABI_VERSION 3
 #define YV3_MAX_BOX 8      /* anchors per head (reference ships 3 / 2 / 3, configs.py:37-41) */
 #define YV3_MAX_GT 256     /* label slots per image (M) */
 
@@ -182,16 +182,19 @@ int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], con
 /* Fused decode + score + threshold straight from the packed logits of n images (the inference path
  * run.py:59-69 takes, without materialising the decoded tensors).  cand is (n, capacity, 8) fp32,
  * counts (n, 3) int32.  Per image the order is the reference's; results are identical to
- * yv3_decode followed by yv3_filter_decoded. */
+ * yv3_decode followed by yv3_filter_decoded.  phases: bit mask, 3 = the whole call.  It is two launches -- 1: the
+ * score sweep over the logits (HBM-bound; stages the survivors per 32-record tile in the workspace), 2: the gather
+ * that turns the staged survivors into cand / counts (tiny) -- and a scheduler may issue them as two calls with the
+ * same arguments, e.g. to start another HBM-bound kernel between them. */
 int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float score_thresh,
-                      float* cand, int32_t capacity, int32_t* counts, void* workspace,
-                      size_t workspace_bytes, void* stream);
+                      float* cand, int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes,
+                      int phases, void* stream);
 
 /* yv3_filter_packed on the three head tensors before they are packed (head_predicts[h]: (n, H_h, W_h, B_h * (5 + C))
  * fp32 contiguous, h = /8, /16, /32; see yv3_loss_fwd_bwd_heads): same rows, same order, same counts.  Every head must
  * have at least 4 records per image (YV3_ERR_SHAPE otherwise: a 32x32 input with fewer than 4 anchors at /32). */
 int yv3_filter_heads(const yv3_config* cfg, const float* const head_predicts[3], int n, float score_thresh, float* cand,
-                     int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, void* stream);
+                     int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, int phases, void* stream);
 
 /* Class-aware greedy NMS, YOLOv3PostProcessor._apply_nms (yolov3/yolov3_post_process.py:108-159), for
  * n independent candidate lists.  cand is (n, capacity, 8) fp32; list i holds

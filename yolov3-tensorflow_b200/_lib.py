@@ -75,9 +75,9 @@ _SIGNATURES = {
     "yv3_filter_decoded": (ctypes.c_int, [_P, ctypes.POINTER(_P), ctypes.POINTER(_P), ctypes.c_float, _P,
                                           ctypes.c_int32, _P, _P, ctypes.c_size_t, _P]),
     "yv3_filter_packed": (ctypes.c_int, [_P, _P, ctypes.c_int, ctypes.c_float, _P, ctypes.c_int32, _P, _P,
-                                         ctypes.c_size_t, _P]),
+                                         ctypes.c_size_t, ctypes.c_int, _P]),
     "yv3_filter_heads": (ctypes.c_int, [_P, ctypes.POINTER(_P), ctypes.c_int, ctypes.c_float, _P, ctypes.c_int32, _P,
-                                        _P, ctypes.c_size_t, _P]),
+                                        _P, ctypes.c_size_t, ctypes.c_int, _P]),
     "yv3_nms": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int32, ctypes.c_int,
                                ctypes.c_double, _P, _P, ctypes.c_size_t, _P]),
 }
@@ -106,7 +106,7 @@ def lib():
         fn = getattr(handle, name)             # AttributeError = header and library disagree
         fn.restype = res
         fn.argtypes = args
-    if handle.yv3_abi_version() != 2:
+    if handle.yv3_abi_version() != 3:
         raise RuntimeError("libyv3head.so ABI version mismatch")
     _LIB = handle
     return _LIB

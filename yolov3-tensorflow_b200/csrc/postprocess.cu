@@ -835,8 +835,7 @@ int score_num_tiles(const Geo& g, int n) {
 // pred[0] alone: the packed tensor; unpacked: one tensor per head (N, H, W, B*L), each swept under its single-head geometry
 cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool unpacked, int n, float thresh, float* cand,
                                  int capacity, int32_t* counts, int32_t* status, float4* stage, int32_t* tcount,
-                                 int sm_count, cudaStream_t stream) {
-    (void)sm_count;
+                                 bool sweep, bool gather, cudaStream_t stream) {
     GatherSrc src;
     memset(&src, 0, sizeof(src));
     const int tr = unpacked ? heads_tr(g, n) : score_tiles(g, pred[0], n, thresh).tr;
@@ -850,9 +849,11 @@ cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool 
         cudaError_t err = cudaFuncSetAttribute(score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;
         const int grid = (q.num_tiles + q.wpc - 1) / q.wpc;
-        score_tile_kernel<<<grid, 32 * q.wpc, smem, stream>>>(gh, pred[h], q, thresh, stage + (size_t)tbase * tr, tcount + (size_t)tbase * 8);
-        err = cudaGetLastError();
-        if (err != cudaSuccess) return err;
+        if (sweep) {
+            score_tile_kernel<<<grid, 32 * q.wpc, smem, stream>>>(gh, pred[h], q, thresh, stage + (size_t)tbase * tr, tcount + (size_t)tbase * 8);
+            err = cudaGetLastError();
+            if (err != cudaSuccess) return err;
+        }
         for (int k = (unpacked ? h : 0); k < (unpacked ? h + 1 : 3); ++k) {
             src.pred[k] = pred[h];
             src.rpi[k] = gh.rpi; src.rpr[k] = gh.rpr; src.seg[k] = unpacked ? 0 : g.seg_base[k];
@@ -861,6 +862,7 @@ cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool 
         }
         tbase += q.num_tiles;
     }
+    if (!gather) return cudaSuccess;
     const size_t gsmem = (size_t)3 * gtiles * sizeof(int);
     if (gsmem > 200 * 1024) return cudaErrorInvalidValue;
     cudaError_t err = cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem);

@@ -195,7 +195,7 @@ class Yolov3FilterNmsOp : public tf::OpKernel {
         OP_REQUIRES_OK(ctx, ctx->allocate_temp(tf::DT_UINT8, tf::TensorShape({(tf::int64)bytes}), &ws));
         void* st = StreamOf(ctx);
         int rc = yv3_filter_packed(&cfg_, p.flat<float>().data(), n, score_, cand->flat<float>().data(), cap_,
-                                   counts->flat<tf::int32>().data(), ws.flat<tf::uint8>().data(), bytes, st);
+                                   counts->flat<tf::int32>().data(), ws.flat<tf::uint8>().data(), bytes, 3, st);
         OP_REQUIRES(ctx, rc == YV3_OK, tf::errors::Internal(yv3_strerror(rc)));
         rc = yv3_nms(&cfg_, cand->flat<float>().data(), counts->flat<tf::int32>().data(), 3, n, cap_,
                      cfg_.class_num > 0 ? cfg_.class_num : 1, (double)nms_, keep->flat<tf::uint8>().data(),

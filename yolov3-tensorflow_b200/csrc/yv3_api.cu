@@ -426,7 +426,8 @@ static int post_checks(const yv3_config* cfg, int n, int32_t capacity, void* wor
 
 static int filter_impl(const yv3_config* cfg, const float* const pred[3], bool unpacked, int n, float score_thresh,
                        float* cand, int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes,
-                       void* stream) {
+                       int phases, void* stream) {
+    if ((phases & 3) == 0) return YV3_ERR_SHAPE;
     if (!cfg || !cand || !counts) return YV3_ERR_NULL;
     for (int h = 0; h < (unpacked ? 3 : 1); ++h) {
         if (!pred[h]) return YV3_ERR_NULL;
@@ -437,24 +438,29 @@ static int filter_impl(const yv3_config* cfg, const float* const pred[3], bool u
     if (rc != YV3_OK) return rc;
     if (!aligned16(cand)) return YV3_ERR_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
-    if (!cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
+    if ((phases & 1) && !cuda_ok(cudaMemsetAsync(ws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync"))
+        return YV3_ERR_CUDA;
     const Geo g = make_geo(cfg);
     if (unpacked && heads_tr(g, n) < 4) return YV3_ERR_SHAPE;      // a head with fewer than 4 records per image
     if (!cuda_ok(launch_filter_packed(g, pred, unpacked, n, score_thresh, cand, capacity, counts, ws.status, ws.stage,
-                                      ws.tcount, sm_count_cached(), st), "launch_filter_packed")) return YV3_ERR_CUDA;
+                                      ws.tcount, (phases & 1) != 0, (phases & 2) != 0, st), "launch_filter_packed"))
+        return YV3_ERR_CUDA;
     return YV3_OK;
 }
 
 int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float score_thresh, float* cand,
-                      int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, void* stream) {
+                      int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, int phases,
+                      void* stream) {
     const float* pred[3] = {predicts, nullptr, nullptr};
-    return filter_impl(cfg, pred, false, n, score_thresh, cand, capacity, counts, workspace, workspace_bytes, stream);
+    return filter_impl(cfg, pred, false, n, score_thresh, cand, capacity, counts, workspace, workspace_bytes, phases, stream);
 }
 
 int yv3_filter_heads(const yv3_config* cfg, const float* const head_predicts[3], int n, float score_thresh, float* cand,
-                     int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, void* stream) {
+                     int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, int phases,
+                     void* stream) {
     if (!head_predicts) return YV3_ERR_NULL;
-    return filter_impl(cfg, head_predicts, true, n, score_thresh, cand, capacity, counts, workspace, workspace_bytes, stream);
+    return filter_impl(cfg, head_predicts, true, n, score_thresh, cand, capacity, counts, workspace, workspace_bytes, phases,
+                       stream);
 }
 
 int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], const float* const boxes[3],

@@ -99,7 +99,7 @@ cudaError_t launch_collect(const float* cand, const int32_t* counts, const unsig
 int heads_tr(const Geo& g, int n);      // records per tile of the per-head sweeps; < 4: a head has fewer than 4 records per image
 cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool unpacked, int n, float thresh, float* cand,
                                  int capacity, int32_t* counts, int32_t* status, float4* stage, int32_t* tcount,
-                                 int sm_count, cudaStream_t stream);
+                                 bool sweep, bool gather, cudaStream_t stream);
 cudaError_t launch_filter_decoded(const Geo& g, const float* const decoded[3], const float* const boxes[3],
                                   float thresh, float* cand, int capacity, int32_t* counts, int32_t* status,
                                   float* score, float* prob, int32_t* cls, int sm_count, cudaStream_t stream);

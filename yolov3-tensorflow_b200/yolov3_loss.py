@@ -108,7 +108,8 @@ class YOLOv3Loss(object):
             raise ValueError("targets must be (N, M*5) with the same N as predicts")
         return t, p
 
-    def _run(self, targets, predicts, want_grad, upstream=1.0, events=None, grad_out=None):
+    def _run(self, targets, predicts, want_grad, upstream=1.0, events=None, grad_out=None, sweep_after=None,
+             sweep_done=None):
         t, p = self._prepare(targets, predicts)
         n, m = p.shape[0], t.shape[1] // 5
         world = self._world()
@@ -124,7 +125,18 @@ class YOLOv3Loss(object):
         args = (ctypes.byref(self._cfg), _lib.ptr(p), _lib.ptr(t), n, m, n_global, 1 if rect_active else 0,
                 float(upstream), _lib.ptr(out), _lib.ptr(grad), _lib.ptr(ws), ws.numel())
         stream = _lib.current_stream_ptr(p.device)
-        if events is None:
+        if sweep_after is not None or sweep_done is not None:
+            # a scheduler's hooks around the HBM-bound sweep: it starts after `sweep_after` (an event of another
+            # stream) and `sweep_done` is recorded right behind it; the small assignment and fold kernels are free
+            cur = torch.cuda.current_stream(p.device)
+            _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 1, stream), "yv3_loss_fwd_bwd[assign]")
+            if sweep_after is not None:
+                cur.wait_event(sweep_after)
+            _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 2, stream), "yv3_loss_fwd_bwd[dense]")
+            if sweep_done is not None:
+                sweep_done.record(cur)
+            _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 4, stream), "yv3_loss_fwd_bwd[fold]")
+        elif events is None:
             _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 7, stream), "yv3_loss_fwd_bwd")
         else:
             # (start, stop) torch.cuda.Event pair bracketing the dense sweep alone (bench.py's roofline)
@@ -156,11 +168,13 @@ class YOLOv3Loss(object):
 
     __call__ = loss
 
-    def loss_and_grad(self, targets, predicts, upstream=1.0, events=None, grad_out=None):
+    def loss_and_grad(self, targets, predicts, upstream=1.0, events=None, grad_out=None, sweep_after=None,
+                      sweep_done=None):
         """(total loss, d(upstream * loss)/d predicts in the packed layout) from one fused pass.
         ``grad_out`` reuses a caller-owned gradient buffer; ``events`` = (start, stop) CUDA events recorded
         around the dense sweep alone."""
-        return self._run(targets, predicts, want_grad=True, upstream=upstream, events=events, grad_out=grad_out)
+        return self._run(targets, predicts, want_grad=True, upstream=upstream, events=events, grad_out=grad_out,
+                         sweep_after=sweep_after, sweep_done=sweep_done)
 
     def loss_and_grad_heads(self, targets, head_predicts, upstream=1.0, want_grad=True, grads_out=None):
         """The same loss on the three head tensors BEFORE yolov3_detector.py:80-85 packs them: ``head_predicts`` =

@@ -196,7 +196,9 @@ class HeadPostProcessor(object):
             self._ws[key] = ws
         return ws
 
-    def filter(self, predicts, score_thresh, out=None):
+    def filter(self, predicts, score_thresh, out=None, sweep_done=None):
+        """cand (N, capacity, 8), counts (N, 3) from the packed logits.  ``sweep_done``: an event recorded between the
+        HBM-bound score sweep and the small gather kernel (a scheduler's hook, see bench.py --serialize-sweeps)."""
         p = _lib.to_device_f32(predicts)
         if p.dim() != 4 or p[0].numel() != self.packed_floats_per_image:
             raise ValueError("predicts does not have the packed head layout of this configuration")
@@ -207,11 +209,14 @@ class HeadPostProcessor(object):
             counts = torch.empty((n, 3), dtype=torch.int32, device=p.device)
         else:
             cand, counts = out
-        rc = self._lib.yv3_filter_packed(ctypes.byref(self._cfg), _lib.ptr(p), n,
-                                         float(np.float32(score_thresh)), _lib.ptr(cand), self.capacity,
-                                         _lib.ptr(counts), _lib.ptr(ws), ws.numel(),
-                                         _lib.current_stream_ptr(p.device))
-        _lib.check(rc, "yv3_filter_packed")
+        for phases in ((3,) if sweep_done is None else (1, 2)):
+            rc = self._lib.yv3_filter_packed(ctypes.byref(self._cfg), _lib.ptr(p), n,
+                                             float(np.float32(score_thresh)), _lib.ptr(cand), self.capacity,
+                                             _lib.ptr(counts), _lib.ptr(ws), ws.numel(), phases,
+                                             _lib.current_stream_ptr(p.device))
+            _lib.check(rc, "yv3_filter_packed")
+            if sweep_done is not None and phases == 1:
+                sweep_done.record(torch.cuda.current_stream(p.device))
         self._last_ws = ws
         return cand, counts
 
@@ -235,7 +240,7 @@ class HeadPostProcessor(object):
             cand, counts = out
         pp = (ctypes.c_void_p * 3)(*[_lib.ptr(p) for p in heads])
         rc = self._lib.yv3_filter_heads(ctypes.byref(self._cfg), pp, n, float(np.float32(score_thresh)), _lib.ptr(cand),
-                                        self.capacity, _lib.ptr(counts), _lib.ptr(ws), ws.numel(),
+                                        self.capacity, _lib.ptr(counts), _lib.ptr(ws), ws.numel(), 3,
                                         _lib.current_stream_ptr(heads[0].device))
         _lib.check(rc, "yv3_filter_heads")
         self._last_ws = ws
