@@ -28,6 +28,7 @@
 namespace yv3 {
 
 constexpr int kScoreThreads = 128;
+constexpr int kSerialExactFrom = 6;     // exact scores: warp-cooperative per record up to this many per tile, per lane beyond
 
 // ---- fused score + threshold over the packed logits ---------------------------------------------------------
 // One CTA per tile of <= 128 consecutive records (<= 2 images), one thread per record:
@@ -136,6 +137,20 @@ __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_
     if (C > 0) {
         mine = make_float4(0.f, 0.f, 0.f, 0.f);
         unsigned mb = __ballot_sync(0xffffffffu, maybe);
+        if (__popc(mb) > kSerialExactFrom) {
+            // many records of the tile need the exact score (a low threshold: nearly all of them): one record per lane,
+            // the thread-serial class_stats -- bit-identical to the warp version by construction (tile_ops.cuh) -- costs
+            // about six warp-cooperative records, whatever the count
+            if (maybe) {
+                const ClassStats cs = class_stats(r + 5, C);
+                float best;
+                int arg;
+                class_best(r + 5, C, cs, g.lo, g.hi, best, arg);
+                const float sc = __fmul_rn(best, conf);                                  // :59
+                mine = make_float4(sc, best, __int_as_float(arg), (sc > thresh) ? 1.f : 0.f);   // :62 strict, fp32
+            }
+            mb = 0u;
+        }
         while (mb) {
             const int src = __ffs(mb) - 1;
             mb &= mb - 1;
@@ -628,7 +643,14 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
     for (int q = 0; q < count_cols; ++q) K += count[n * count_cols + q];
     K = max(0, min(K, capacity));
     const unsigned long long* keys = gkeys + (size_t)n * cap2;
-    if (tid == 0) {
+    if (T == kNmsMedium) {
+        // a queued medium segment is at most T long: every thread probes one position, the first class change wins
+        if (tid == 0) { seg_s[0] = job.y; seg_s[1] = min(K, job.y + T); nkept_s = 0; }
+        __syncthreads();
+        const unsigned long long c0 = keys[job.y] >> 50;
+        const int p = job.y + 1 + tid;
+        if (p < K && (keys[p] >> 50) != c0) atomicMin(&seg_s[1], p);
+    } else if (tid == 0) {
         // end of the segment: first sorted position whose class field exceeds this segment's
         const unsigned long long want = (keys[job.y] >> 50) + 1ULL;
         int lo = job.y, hi = K;
@@ -669,33 +691,55 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
         }
         alive_s[tid] = alive ? 1 : 0;
         __syncthreads();
-        // phase 2: bit matrix inside the chunk: row i, bit j (j > i) <=> i suppresses j
+        // phase 2: bit matrix inside the chunk: row i, bit j (j > i) <=> i suppresses j.  The triangle is cut into tasks
+        // of (row, 32 columns) dealt round-robin to the threads, so the thread of row 0 does not test cnt - 1 pairs
+        // alone while the last rows idle; a task writes its own 32-bit half word, no atomics.
         {
-            unsigned long long* row = mask_s + (size_t)tid * W;
-            const int wfirst = (tid + 1) >> 6, wend = (cnt + 63) >> 6;
-            for (int w = 0; w < W; ++w) {
-                unsigned long long bits = 0;
-                if (alive && w >= wfirst && w < wend) {
-                    const int jb = max(tid + 1, w << 6), je = min(cnt, (w + 1) << 6);
+            unsigned* mask32 = reinterpret_cast<unsigned*>(mask_s);
+            const int hw_n = (cnt + 31) >> 5;                       // half words that hold columns < cnt
+            for (int i = tid; i < cnt * 2 * W; i += T) {            // rows' unused half words: zero
+                const int hw = i % (2 * W);
+                if (hw >= hw_n) mask32[i] = 0u;
+            }
+            for (int task = tid; task < cnt * hw_n; task += T) {
+                const int i = task / hw_n, hw = task - i * hw_n;
+                unsigned bits = 0u;
+                const int jb = max(i + 1, hw << 5), je = min(cnt, (hw + 1) << 5);
+                if (jb < je && alive_s[i]) {
+                    const float4 oi = chunk_s[i];
+                    const BoxD bi = to_boxd(oi);
                     for (int j = jb; j < je; ++j) {
                         if (!alive_s[j]) continue;
                         const float4 oj = chunk_s[j];
-                        const bool drop = overlaps_f32(mine_f, oj) ? suppresses(mine, to_boxd(oj), thresh) : none_overlap_drops;
-                        if (drop) bits |= 1ULL << (j & 63);
+                        const bool drop = overlaps_f32(oi, oj) ? suppresses(bi, to_boxd(oj), thresh) : none_overlap_drops;
+                        if (drop) bits |= 1u << (j & 31);
                     }
                 }
-                row[w] = bits;
+                mask32[(size_t)i * 2 * W + hw] = bits;
             }
         }
         __syncthreads();
-        // sweep: warp 0 walks the chunk in order; lane w (< W) carries word w of the removed set
+        // sweep: warp 0 walks the chunk in order, 64 rows (one word of the removed set) at a time.  Inside a block the
+        // decisions depend only on that word, which every lane carries redundantly (rblk) next to its own word
+        // (lane w < W: word w); the rows' words are loaded ahead, independent of the decisions, so the serial chain
+        // per row is a bit test and two ORs instead of a shuffle and a dependent shared-memory load.
         if (warp == 0) {
             unsigned long long removed = 0;
-            for (int i = 0; i < cnt; ++i) {
-                const unsigned long long word = __shfl_sync(0xffffffffu, removed, i >> 6);
-                const bool k = alive_s[i] && !((word >> (i & 63)) & 1ULL);
-                if (k && lane < W) removed |= mask_s[(size_t)i * W + lane];
-                if (lane == 0) kept_flag_s[i] = k ? 1 : 0;
+            for (int i0 = 0; i0 < cnt; i0 += 64) {
+                const int blk = i0 >> 6;
+                unsigned long long rblk = __shfl_sync(0xffffffffu, removed, blk);
+                unsigned long long kb = 0;
+#pragma unroll 8
+                for (int b = 0; b < 64; ++b) {
+                    const int i = i0 + b;                                        // < T: the rows exist, stale ones are masked
+                    const bool a = i < cnt && alive_s[i];
+                    const unsigned long long diag = mask_s[(size_t)i * W + blk];
+                    const unsigned long long own = (lane < W) ? mask_s[(size_t)i * W + lane] : 0ULL;
+                    const bool k = a && !((rblk >> b) & 1ULL);
+                    if (k) { rblk |= diag; removed |= own; kb |= 1ULL << b; }
+                }
+                kept_flag_s[i0 + lane] = (unsigned char)((kb >> lane) & 1ULL);
+                kept_flag_s[i0 + 32 + lane] = (unsigned char)((kb >> (lane + 32)) & 1ULL);
             }
         }
         __syncthreads();
