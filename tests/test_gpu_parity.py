@@ -443,6 +443,53 @@ def test_collect_kept_rows_resized(yv3, name, bug_compat):
     assert counts.sum() > 0
 
 
+@pytest.mark.parametrize("thr", [0.45, 0.2])
+def test_nms_segment_length_boundaries(yv3, thr):
+    """Class segments at the lengths where the NMS changes path or block: the warp path (<= 32), the 256-candidate
+    chunk kernel and its 64-row sweep blocks, the 1024-candidate kernel and its chunk boundary; two images with the
+    segments in opposite order.  Survivors equal the C oracle's greedy NMS (the reference's _apply_nms) index for index."""
+    import bench
+    spec = bench.build_spec(bench.WORKLOADS["cfg2_416_c80_b64"])
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    lengths = [1, 2, 31, 32, 33, 63, 64, 65, 127, 128, 129, 191, 193, 255, 256, 257, 300, 513, 1023, 1024, 1025, 1100, 2100]
+    rng = np.random.default_rng(5)
+    n = 2
+    cand = np.zeros((n, post.capacity, 8), dtype=np.float32)
+    counts = np.zeros((n, 3), dtype=np.int32)
+    for i in range(n):
+        order = lengths if i == 0 else lengths[::-1]
+        rows = []
+        for cls, ln in enumerate(order):
+            # boxes of one class crowd one region so that many pairs overlap around the threshold
+            cx = rng.uniform(0.3, 0.7, size=ln) + rng.normal(0, 0.05, size=ln)
+            cy = rng.uniform(0.3, 0.7, size=ln) + rng.normal(0, 0.05, size=ln)
+            w = rng.uniform(0.05, 0.3, size=ln)
+            h = rng.uniform(0.05, 0.3, size=ln)
+            r = np.zeros((ln, 8), dtype=np.float32)
+            r[:, 0], r[:, 1], r[:, 2], r[:, 3] = cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2
+            r[:, 4] = rng.uniform(0.2, 1.0, size=ln)
+            r[:, 5] = rng.uniform(0.2, 1.0, size=ln)
+            r[:, 6] = cls
+            r[:, 7] = r[:, 4] * r[:, 5]
+            rows.append(r)
+        rows = np.concatenate(rows, 0)
+        rows[::7, 7] = rows[3::7, 7][:len(rows[::7])] if len(rows[3::7]) >= len(rows[::7]) else rows[::7, 7]   # equal scores
+        rows = rows[rng.permutation(len(rows))]                  # candidate order is raster order, not class order
+        k = len(rows)
+        assert k <= post.capacity
+        cand[i, :k] = rows
+        counts[i] = [k // 2, k // 4, k - k // 2 - k // 4]
+    cd, ct = torch.from_numpy(cand).cuda(), torch.from_numpy(counts).cuda()
+    keep = post.nms(cd, ct, thr).cpu().numpy()
+    post.check_status()
+    for i in range(n):
+        k = int(counts[i].sum())
+        got = np.nonzero(keep[i, :k])[0]
+        want = np.sort(nms_c.greedy_nms(cand[i, :k].astype(np.float64), thr))
+        assert np.array_equal(got, want)
+        assert 0 < len(got) < k
+
+
 def test_filter_rows_close_to_oracle_decode(yv3):
     """From logits, rows agree with the NumPy oracle to fp32 noise and the kept counts are equal away from
     the threshold."""
