@@ -42,7 +42,16 @@ WORKLOADS = {
 }
 
 
+def product_spec(w):
+    """The workload's switches for the product arm: nothing under oracle/ or tests/ is imported on this path."""
+    from yolov3_tensorflow_b200 import synth as ps
+    anchors = ps.coco_anchors() if w["anchors"] == "coco" else ps.three_anchor_shipped()
+    return ps.ProductSpec(w["size"][0], w["size"][1], w["class_num"], anchors, iou_thresh=w["iou_thresh"],
+                          is_focal_loss=w["focal"], focal_alpha=1.0, focal_gamma=2.0, eps=1e-8)
+
+
 def build_spec(w):
+    """The same workload as the oracle's HeadSpec: CPU legs (cpu_baseline, --impl reference) and tests only."""
     from helpers import three_anchor_shipped
     from oracle.head_spec import SHIPPED_LOSS_WEIGHTS, HeadSpec, coco_anchors
     anchors = coco_anchors() if w["anchors"] == "coco" else three_anchor_shipped()
@@ -53,8 +62,10 @@ def build_spec(w):
 
 def synth(spec, n, m, rank):
     """logits iid N(0,1) clipped to [-8,8], seed 1234+rank; labels V~U{1..M}, seed 4321+rank."""
-    from helpers import make_predicts, make_targets
-    return make_predicts(spec, n, seed=1234 + rank), make_targets(spec, n, m, seed=4321 + rank, min_valid=1)
+    from yolov3_tensorflow_b200 import synth as ps
+    h32, w32 = spec.head_grid_sizes[2]
+    return (ps.make_predicts(n, h32 * 32, w32 * 32, spec.box_num, spec.class_num, seed=1234 + rank),
+            ps.make_targets(n, spec.class_num, m, seed=4321 + rank, min_valid=1))
 
 
 class ClockSampler(threading.Thread):
@@ -199,7 +210,7 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     w = WORKLOADS[args.workload]
-    spec = build_spec(w)
+    spec = build_spec(w) if args.impl == "reference" else product_spec(w)
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -211,7 +222,6 @@ def main():
     import torch
     import torch.distributed as dist
     import yolov3_tensorflow_b200 as yv3
-    from helpers import product_loss_args
 
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU path in the product)"
     torch.cuda.set_device(local_rank)
@@ -225,7 +235,7 @@ def main():
     p_host = torch.from_numpy(p_np).pin_memory()
     t_host = torch.from_numpy(t_np).pin_memory()
     pd, td = p_host.to(dev), t_host.to(dev)
-    loss = yv3.YOLOv3Loss(rectified_coord_num=w["rect"], **product_loss_args(spec))
+    loss = yv3.YOLOv3Loss(rectified_coord_num=w["rect"], **spec.loss_args)
     post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
     grad = torch.empty_like(pd)
     cand = torch.empty((n, post.capacity, 8), dtype=torch.float32, device=dev)
@@ -518,7 +528,7 @@ def main():
             "clocks": sampler.summary(),
         }
         if world == 1 and not args.no_cpu_baseline:
-            v, s, cores = time_cpu_port(spec, p_np, t_np, w, args.cpu_budget)
+            v, s, cores = time_cpu_port(build_spec(w), p_np, t_np, w, args.cpu_budget)       # the oracle enters here only
             line["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
                                     "sample": "%d of %d images, one pass (oracle port: torch-CPU fp32 loss + autograd, "
                                               "NumPy decode/filter, Python NMS as run.py runs it)" % (s, n)}

@@ -47,9 +47,8 @@ def packed_channels(box_num, class_num):
 def make_predicts(n, height, width, box_num, class_num, seed=1234, clip=8.0):
     rng = np.random.default_rng(seed)
     shape = (n, height // 32, width // 32, packed_channels(box_num, class_num))
-    p = rng.standard_normal(shape, dtype=np.float32)
-    np.clip(p, -clip, clip, out=p)
-    return p
+    p = rng.standard_normal(shape).astype(np.float32)
+    return np.clip(p, -clip, clip).astype(np.float32)
 
 
 def make_targets(n, class_num, m=16, seed=4321, min_valid=1, max_valid=None):
@@ -67,3 +66,29 @@ def make_targets(n, class_num, m=16, seed=4321, min_valid=1, max_valid=None):
         cls = rng.integers(0, max(class_num, 1), size=(v, 1))
         t[i, :v] = np.concatenate([xy, wh, cls], axis=1).astype(np.float32)
     return t.reshape(n, m * 5)
+
+
+# configs.py:52 (xy, wh, noobj, obj, cls per head)
+SHIPPED_LOSS_WEIGHTS = [(5, 5, 0.05, 3, 1), (8, 8, 0.05, 2, 1), (10, 10, 0.05, 2, 1)]
+
+
+class ProductSpec(object):
+    """The switches and derived sizes the product classes and bench.py need for one workload."""
+
+    def __init__(self, height, width, class_num, anchor_boxes, iou_thresh, loss_weights=None, rectified_loss_weight=(1.0, 1.0, 1.0),
+                 is_focal_loss=False, focal_alpha=1.0, focal_gamma=2.0, is_tiou_recall=False, eps=1e-8):
+        self.head_grid_sizes = head_grid_sizes(height, width)
+        self.class_num = int(class_num)
+        self.anchor_boxes = anchor_boxes
+        self.box_num = [len(a) for a in anchor_boxes]
+        self.box_len = 5 + self.class_num
+        fold = (16, 4, 1)
+        self.head_channels = [fold[h] * self.box_num[h] * self.box_len for h in range(3)]
+        self.chan_base = [0, self.head_channels[0], self.head_channels[0] + self.head_channels[1]]
+        self.ctot = sum(self.head_channels)
+        self.anchors_per_image = sum(gh * gw * b for (gh, gw), b in zip(self.head_grid_sizes, self.box_num))
+        self.eps = eps
+        self.loss_args = dict(head_grid_sizes=self.head_grid_sizes, class_num=self.class_num, anchor_boxes=anchor_boxes,
+                              iou_thresh=iou_thresh, loss_weights=loss_weights or SHIPPED_LOSS_WEIGHTS,
+                              rectified_loss_weight=list(rectified_loss_weight), is_focal_loss=is_focal_loss,
+                              focal_alpha=focal_alpha, focal_gamma=focal_gamma, is_tiou_recall=is_tiou_recall)
