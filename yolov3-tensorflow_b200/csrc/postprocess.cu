@@ -19,6 +19,7 @@
 //                         tested against the boxes kept so far, then resolved internally with a
 //                         shared-memory IoU bit matrix and a warp sweep.  IoU is fp64, uncontracted, in the
 //                         reference's operation order.
+#include <cooperative_groups.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -445,6 +446,25 @@ __device__ __forceinline__ bool suppresses(const BoxD& a, const BoxD& b, double 
     return __ddiv_rn(inter, uni) > thresh;
 }
 
+// The same decision for two boxes that are known to overlap (overlaps_f32, defined below, is the complement of the
+// reference's w <= 0 or h <= 0 early-out :139-142), from their fp32 rows: the coordinates are fp32 values, so min / max
+// can be taken in fp32 and converted -- (double)fminf(a, b) == fmin((double)a, (double)b) -- which replaces four
+// double min/max (a compare and two selects each) by conversions of results the overlap test has already computed.
+__device__ __forceinline__ double box_area_d(const float4& b) {
+    return __dmul_rn(__dsub_rn((double)b.z, (double)b.x), __dsub_rn((double)b.w, (double)b.y));    // (x1 - x0) * (y1 - y0)
+}
+__device__ __forceinline__ bool suppresses_overlapping(const float4& a, double area_a, const float4& b, double area_b,
+                                                       double thresh) {
+    const double w = __dsub_rn((double)fminf(a.z, b.z), (double)fmaxf(a.x, b.x));
+    const double h = __dsub_rn((double)fminf(a.w, b.w), (double)fmaxf(a.y, b.y));
+    const double inter = __dmul_rn(w, h);
+    const double uni = __dsub_rn(__dadd_rn(area_a, area_b), inter);
+    const double tu = __dmul_rn(thresh, uni);
+    if (inter > __dmul_rn(tu, 1.0000000000000036)) return true;          // 1 + 2^-48
+    if (inter < __dmul_rn(tu, 0.9999999999999964)) return false;         // 1 - 2^-48
+    return __ddiv_rn(inter, uni) > thresh;
+}
+
 // ---- sort: (class asc, score desc, row asc) -----------------------------------------------------------
 constexpr int kSortThreads = 1024;
 constexpr int kSortSmemKeys = 16384;
@@ -593,7 +613,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
             // (width or height <= 0, :139-142) never reach the fp64 arithmetic
             const bool overlap = fminf(fi.z, mine_f.z) > fmaxf(fi.x, mine_f.x) && fminf(fi.w, mine_f.w) > fmaxf(fi.y, mine_f.y);
             bool drop = lane > i && ((alive >> lane) & 1u);
-            if (drop) drop = overlap ? suppresses(to_boxd(fi), mine, thresh) : (0.0 > thresh);
+            if (drop) drop = overlap ? suppresses_overlapping(fi, box_area_d(fi), mine_f, mine.area, thresh) : (0.0 > thresh);
             alive &= ~__ballot_sync(0xffffffffu, drop);
         }
         if (in) keep_n[(int)(keys[p] & 0x3ffffULL)] = (unsigned char)((alive >> lane) & 1u);
@@ -685,7 +705,8 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
             if (!__any_sync(0xffffffffu, alive)) break;
             const float4 kb = (q < kKeptSmem) ? kept_s[q] : spill[q];
             if (alive) {
-                const bool drop = overlaps_f32(kb, mine_f) ? suppresses(to_boxd(kb), mine, thresh) : none_overlap_drops;
+                const bool drop = overlaps_f32(kb, mine_f) ? suppresses_overlapping(kb, box_area_d(kb), mine_f, mine.area, thresh)
+                                                           : none_overlap_drops;
                 if (drop) alive = false;
             }
         }
@@ -707,11 +728,12 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
                 const int jb = max(i + 1, hw << 5), je = min(cnt, (hw + 1) << 5);
                 if (jb < je && alive_s[i]) {
                     const float4 oi = chunk_s[i];
-                    const BoxD bi = to_boxd(oi);
+                    const double ai = box_area_d(oi);
                     for (int j = jb; j < je; ++j) {
                         if (!alive_s[j]) continue;
                         const float4 oj = chunk_s[j];
-                        const bool drop = overlaps_f32(oi, oj) ? suppresses(bi, to_boxd(oj), thresh) : none_overlap_drops;
+                        const bool drop = overlaps_f32(oi, oj) ? suppresses_overlapping(oi, ai, oj, box_area_d(oj), thresh)
+                                                               : none_overlap_drops;
                         if (drop) bits |= 1u << (j & 31);
                     }
                 }
@@ -762,6 +784,175 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
         __syncthreads();
     }
   }
+}
+
+// ---- long segments: one thread-block CLUSTER per segment ------------------------------------------------------
+// A segment of thousands of candidates (a single-class head with a low threshold) is a serial chain of 1024-candidate
+// chunks, and inside a chunk the work is (candidates x boxes kept so far) + (chunk x chunk) pair tests: one CTA took
+// milliseconds per image.  Here the 8 CTAs of a cluster share it: every CTA holds the chunk; the kept list (global
+// memory, L2-resident) is dealt round-robin, so each CTA tests all candidates against an eighth of it and the verdicts
+// are AND-ed through distributed shared memory; the rows of the chunk's bit matrix are dealt round-robin too and
+// written straight into the leader's shared memory; the leader sweeps, appends the survivors to the kept list and
+// publishes the count.  Four cluster barriers per chunk; the greedy order -- hence the result -- is unchanged.
+constexpr int kClu = 8;                 // CTAs per cluster (the portable maximum)
+constexpr int kCluT = 1024;             // threads per CTA = candidates per chunk
+__host__ __device__ inline size_t nms_cluster_smem_bytes() {
+    return (size_t)kCluT * 16 + (size_t)kCluT * (kCluT / 64) * 8 + (size_t)kCluT * 3;
+}
+
+__global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned long long* __restrict__ gkeys,
+                                                               const int32_t* __restrict__ count, int count_cols,
+                                                               int capacity, int cap2, double thresh,
+                                                               const float4* __restrict__ sbox, const int32_t* __restrict__ sidx,
+                                                               float4* __restrict__ kspill, unsigned char* __restrict__ keep,
+                                                               const int2* __restrict__ wl, const int32_t* __restrict__ wl_count) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    constexpr int T = kCluT, W = T / 64;
+    extern __shared__ __align__(16) unsigned char csm[];
+    float4* chunk_s = reinterpret_cast<float4*>(csm);                                         // [T]
+    unsigned long long* mask_s = reinterpret_cast<unsigned long long*>(chunk_s + T);         // [T][W]  (used in the leader)
+    unsigned char* alive_s = reinterpret_cast<unsigned char*>(mask_s + (size_t)T * W);       // [T] after the AND
+    unsigned char* verdict_s = alive_s + T;                                                  // [T] this CTA's share
+    unsigned char* kept_flag_s = verdict_s + T;                                              // [T]
+    __shared__ int seg_s[2];
+    __shared__ int nkept_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int r = (int)cluster.block_rank();
+    const int cid = blockIdx.x / kClu, ncl = gridDim.x / kClu;
+    unsigned* leader_mask32 = cluster.map_shared_rank(reinterpret_cast<unsigned*>(mask_s), 0);
+    const int* leader_nkept = cluster.map_shared_rank(&nkept_s, 0);
+    const int nwork = *wl_count;
+    const bool none_overlap_drops = 0.0 > thresh;
+    for (int wi = cid; wi < nwork; wi += ncl) {
+        const int2 job = wl[wi];
+        const int n = job.x;
+        int K = 0;
+        for (int q = 0; q < count_cols; ++q) K += count[n * count_cols + q];
+        K = max(0, min(K, capacity));
+        const unsigned long long* keys = gkeys + (size_t)n * cap2;
+        if (tid == 0) {
+            // end of the segment: first sorted position whose class field exceeds this segment's (every CTA finds it itself)
+            const unsigned long long want = (keys[job.y] >> 50) + 1ULL;
+            int lo = job.y, hi = K;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if ((keys[mid] >> 50) < want) lo = mid + 1; else hi = mid;
+            }
+            seg_s[0] = job.y;
+            seg_s[1] = lo;
+            nkept_s = 0;
+        }
+        __syncthreads();
+        const int s0 = seg_s[0], s1 = seg_s[1];
+        const float4* boxes = sbox + (size_t)n * capacity;
+        float4* spill = kspill + (size_t)n * capacity + s0;          // the kept list of this segment, in order
+        const int32_t* rowof = sidx + (size_t)n * capacity;
+        unsigned char* keep_n = keep + (size_t)n * capacity;
+        int nk = 0;
+        for (int c0 = s0; c0 < s1; c0 += T) {
+            const int cnt = min(T, s1 - c0);
+            // phase 1: this thread's candidate against this CTA's share of the boxes kept so far
+            bool alive = tid < cnt;
+            float4 mine_f = make_float4(0.f, 0.f, 0.f, 0.f);
+            BoxD mine = {};
+            if (alive) {
+                mine_f = boxes[c0 + tid];
+                mine = to_boxd(mine_f);
+                chunk_s[tid] = mine_f;
+            }
+            for (int q = r; q < nk; q += 4 * kClu) {
+                // four kept boxes in flight (the address does not depend on the verdicts)
+                float4 kb[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) kb[u] = __ldcg(spill + min(q + u * kClu, nk - 1));
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (q + u * kClu < nk && alive) {
+                        const bool drop = overlaps_f32(kb[u], mine_f)
+                                              ? suppresses_overlapping(kb[u], box_area_d(kb[u]), mine_f, mine.area, thresh)
+                                              : none_overlap_drops;
+                        if (drop) alive = false;
+                    }
+                }
+            }
+            verdict_s[tid] = alive ? 1 : 0;
+            cluster.sync();                                          // (A) every CTA's verdicts are in place
+            {
+                bool all = tid < cnt;
+#pragma unroll
+                for (int k = 0; k < kClu; ++k) {
+                    const unsigned char* rem = cluster.map_shared_rank(verdict_s, k);
+                    all = all && (rem[tid] != 0);
+                }
+                alive_s[tid] = all ? 1 : 0;
+            }
+            __syncthreads();
+            // phase 2: the rows i = r, r + 8, ... of the chunk's bit matrix (row i, bit j > i <=> i suppresses j), cut
+            // into (row, 32 columns) tasks; every half word of a row is written, straight into the leader's matrix
+            {
+                const int rows_mine = cnt > r ? (cnt - r + kClu - 1) / kClu : 0;
+                for (int task = tid; task < rows_mine * 2 * W; task += T) {
+                    const int li = task / (2 * W), hw = task - li * (2 * W);
+                    const int i = li * kClu + r;
+                    unsigned bits = 0u;
+                    const int jb = max(i + 1, hw << 5), je = min(cnt, (hw + 1) << 5);
+                    if (jb < je && alive_s[i]) {
+                        const float4 oi = chunk_s[i];
+                        const double ai = box_area_d(oi);
+                        for (int j = jb; j < je; ++j) {
+                            if (!alive_s[j]) continue;
+                            const float4 oj = chunk_s[j];
+                            const bool drop = overlaps_f32(oi, oj) ? suppresses_overlapping(oi, ai, oj, box_area_d(oj), thresh)
+                                                                   : none_overlap_drops;
+                            if (drop) bits |= 1u << (j & 31);
+                        }
+                    }
+                    leader_mask32[(size_t)i * 2 * W + hw] = bits;
+                }
+            }
+            cluster.sync();                                          // (B) the leader's matrix is complete
+            if (r == 0) {
+                if (warp == 0) {
+                    unsigned long long removed = 0;
+                    for (int i0 = 0; i0 < cnt; i0 += 64) {
+                        const int blk = i0 >> 6;
+                        unsigned long long rblk = __shfl_sync(0xffffffffu, removed, blk);
+                        unsigned long long kb = 0;
+#pragma unroll 8
+                        for (int b = 0; b < 64; ++b) {
+                            const int i = i0 + b;
+                            const bool a = i < cnt && alive_s[i];
+                            const unsigned long long diag = mask_s[(size_t)i * W + blk];
+                            const unsigned long long own = (lane < W) ? mask_s[(size_t)i * W + lane] : 0ULL;
+                            const bool k = a && !((rblk >> b) & 1ULL);
+                            if (k) { rblk |= diag; removed |= own; kb |= 1ULL << b; }
+                        }
+                        kept_flag_s[i0 + lane] = (unsigned char)((kb >> lane) & 1ULL);
+                        kept_flag_s[i0 + 32 + lane] = (unsigned char)((kb >> (lane + 32)) & 1ULL);
+                    }
+                    __syncwarp();
+                    // append the chunk's survivors to the kept list (order kept)
+                    int total = nk;
+                    for (int b = 0; b < cnt; b += 32) {
+                        const int i = b + lane;
+                        const bool k = i < cnt && kept_flag_s[i];
+                        const unsigned m = __ballot_sync(0xffffffffu, k);
+                        if (k) spill[total + __popc(m & ((1u << lane) - 1u))] = chunk_s[i];
+                        total += __popc(m);
+                    }
+                    if (lane == 0) nkept_s = total;
+                }
+                __syncthreads();
+                if (tid < cnt) keep_n[rowof[c0 + tid]] = kept_flag_s[tid];
+                __threadfence();                                     // the kept list is visible before the barrier below
+            }
+            cluster.sync();                                          // (C) kept list and count published
+            nk = *leader_nkept;
+        }
+        __syncthreads();
+    }
+    cluster.sync();                                                  // nobody leaves while its shared memory may be read
 }
 
 // ---- kept rows, resized (yolov3_post_process.py:94-104, :162-172) -------------------------------------------
@@ -969,6 +1160,44 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
         ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx, ws.kspill, keep, ws.wl, ws.wl_count);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
+    // segments longer than 256 candidates: one cluster of 8 CTAs per segment (falls back to one CTA per segment where
+    // such a cluster cannot be scheduled)
+    static int clusters = -1;
+    if (clusters < 0) {
+        clusters = 0;
+        if (cudaFuncSetAttribute(nms_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)nms_cluster_smem_bytes()) == cudaSuccess) {
+            cudaLaunchConfig_t q = {};
+            q.gridDim = dim3(kClu);
+            q.blockDim = dim3(kCluT);
+            q.dynamicSmemBytes = nms_cluster_smem_bytes();
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = kClu; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            q.attrs = at;
+            q.numAttrs = 1;
+            int nc = 0;
+            if (cudaOccupancyMaxActiveClusters(&nc, nms_cluster_kernel, &q) == cudaSuccess) clusters = nc;
+        }
+        (void)cudaGetLastError();
+        if (getenv("YV3_NO_CLUSTER")) clusters = 0;                  // developer switch
+    }
+    if (clusters >= 1) {
+        cudaLaunchConfig_t q = {};
+        q.gridDim = dim3(kClu * min(clusters, 16));
+        q.blockDim = dim3(kCluT);
+        q.dynamicSmemBytes = nms_cluster_smem_bytes();
+        q.stream = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = kClu; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        q.attrs = at;
+        q.numAttrs = 1;
+        const unsigned long long* a0 = ws.keys;
+        const int2* a10 = wl_large;
+        const int32_t* a11 = ws.wl_count + 1;
+        return cudaLaunchKernelEx(&q, nms_cluster_kernel, a0, count, count_cols, capacity, cap2, thresh,
+                                  (const float4*)ws.sbox, (const int32_t*)ws.sidx, ws.kspill, keep, a10, a11);
+    }
     nms_kernel<kNmsLarge><<<148, kNmsLarge, nms_smem_bytes(kNmsLarge), stream>>>(
         ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx, ws.kspill, keep, wl_large, ws.wl_count + 1);
     return cudaGetLastError();
