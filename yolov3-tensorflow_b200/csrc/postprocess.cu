@@ -431,23 +431,11 @@ __device__ __forceinline__ BoxD to_boxd(const float4 b) {
     o.area = __dmul_rn(__dsub_rn(o.x1, o.x0), __dsub_rn(o.y1, o.y0));     // (x1 - x0) * (y1 - y0)
     return o;
 }
-// _cal_iou(box, truth) > thresh  (:132-145, :124): w/h early-out, union = (area_a + area_b) - inter
-__device__ __forceinline__ bool suppresses(const BoxD& a, const BoxD& b, double thresh) {
-    const double w = __dsub_rn(fmin(a.x1, b.x1), fmax(a.x0, b.x0));
-    const double h = __dsub_rn(fmin(a.y1, b.y1), fmax(a.y0, b.y0));
-    if (w <= 0.0 || h <= 0.0) return 0.0 > thresh;
-    const double inter = __dmul_rn(w, h);
-    const double uni = __dsub_rn(__dadd_rn(a.area, b.area), inter);
-    // fl(inter / uni) > thresh is decided without the division unless the quotient lies within 2^-48 (relative)
-    // of the threshold: the products below are off by at most 2^-52 each
-    const double tu = __dmul_rn(thresh, uni);
-    if (inter > __dmul_rn(tu, 1.0000000000000036)) return true;          // 1 + 2^-48
-    if (inter < __dmul_rn(tu, 0.9999999999999964)) return false;         // 1 - 2^-48
-    return __ddiv_rn(inter, uni) > thresh;
-}
-
-// The same decision for two boxes that are known to overlap (overlaps_f32, defined below, is the complement of the
-// reference's w <= 0 or h <= 0 early-out :139-142), from their fp32 rows: the coordinates are fp32 values, so min / max
+// _cal_iou(box, truth) > thresh  (:132-145, :124) for two boxes that are known to overlap: union = (area_a + area_b) -
+// inter; fl(inter / uni) > thresh is decided without the division unless the quotient lies within 2^-48 (relative)
+// of the threshold (the products are off by at most 2^-52 each), then by the division itself.
+// "Known to overlap": overlaps_f32, defined below, is the complement of the reference's w <= 0 or h <= 0 early-out
+// (:139-142).  The decision is taken from the fp32 rows: the coordinates are fp32 values, so min / max
 // can be taken in fp32 and converted -- (double)fminf(a, b) == fmin((double)a, (double)b) -- which replaces four
 // double min/max (a compare and two selects each) by conversions of results the overlap test has already computed.
 __device__ __forceinline__ double box_area_d(const float4& b) {
