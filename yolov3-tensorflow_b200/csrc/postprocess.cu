@@ -782,7 +782,10 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
 // are AND-ed through distributed shared memory; the rows of the chunk's bit matrix are dealt round-robin too and
 // written straight into the leader's shared memory; the leader sweeps, appends the survivors to the kept list and
 // publishes the count.  Four cluster barriers per chunk; the greedy order -- hence the result -- is unchanged.
-constexpr int kClu = 8;                 // CTAs per cluster (the portable maximum)
+#ifndef YV3_NMS_CLUSTER
+#define YV3_NMS_CLUSTER 8
+#endif
+constexpr int kClu = YV3_NMS_CLUSTER;   // CTAs per cluster (8 is the portable maximum)
 constexpr int kCluT = 1024;             // threads per CTA = candidates per chunk
 __host__ __device__ inline size_t nms_cluster_smem_bytes() {
     return (size_t)kCluT * 16 + (size_t)kCluT * (kCluT / 64) * 8 + (size_t)kCluT * 3;
@@ -1171,7 +1174,7 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     }
     if (clusters >= 1) {
         cudaLaunchConfig_t q = {};
-        q.gridDim = dim3(kClu * min(clusters, 16));
+        q.gridDim = dim3(kClu * min(clusters, 32));
         q.blockDim = dim3(kCluT);
         q.dynamicSmemBytes = nms_cluster_smem_bytes();
         q.stream = stream;
