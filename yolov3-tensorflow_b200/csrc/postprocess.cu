@@ -777,15 +777,17 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
 // ---- long segments: one thread-block CLUSTER per segment ------------------------------------------------------
 // A segment of thousands of candidates (a single-class head with a low threshold) is a serial chain of 1024-candidate
 // chunks, and inside a chunk the work is (candidates x boxes kept so far) + (chunk x chunk) pair tests: one CTA took
-// milliseconds per image.  Here the 8 CTAs of a cluster share it: every CTA holds the chunk; the kept list (global
-// memory, L2-resident) is dealt round-robin, so each CTA tests all candidates against an eighth of it and the verdicts
+// milliseconds per image.  Here the CTAs of a cluster share it: every CTA holds the chunk; the kept list (global
+// memory, L2-resident) is dealt round-robin, so each CTA tests all candidates against its share of it and the verdicts
 // are AND-ed through distributed shared memory; the rows of the chunk's bit matrix are dealt round-robin too and
 // written straight into the leader's shared memory; the leader sweeps, appends the survivors to the kept list and
 // publishes the count.  Four cluster barriers per chunk; the greedy order -- hence the result -- is unchanged.
+// CTAs per cluster.  Measured on B200 at cfg5 (16 single-class segments of 8 053 candidates): 8 -> 2.17 ms (15 clusters
+// fit: two rounds), 7 -> 2.56, 6 -> 1.44 (one round), 4 -> 1.86 ms per step; 8 is the portable maximum.
 #ifndef YV3_NMS_CLUSTER
-#define YV3_NMS_CLUSTER 8
+#define YV3_NMS_CLUSTER 6
 #endif
-constexpr int kClu = YV3_NMS_CLUSTER;   // CTAs per cluster (8 is the portable maximum)
+constexpr int kClu = YV3_NMS_CLUSTER;
 constexpr int kCluT = 1024;             // threads per CTA = candidates per chunk
 __host__ __device__ inline size_t nms_cluster_smem_bytes() {
     return (size_t)kCluT * 16 + (size_t)kCluT * (kCluT / 64) * 8 + (size_t)kCluT * 3;
