@@ -200,7 +200,7 @@ def main():
                          "yolov3_detector.py:80-85 packs them (yv3_loss_fwd_bwd_heads / yv3_filter_heads)")
     ap.add_argument("--serialize-sweeps", type=int, default=-1,
                     help="1: the two HBM-bound sweeps (dense pass, score pass) never run at the same time; the small "
-                         "kernels of either half run under the other half's sweep (default: on at N = 1 with the "
+                         "kernels of either half run under the other half's sweep (default: on with the "
                          "packed layout, where several steps share a graph; measured 142 -> 140.5 us/step)")
     ap.add_argument("--graph-steps", type=int, default=8, help="steps captured per CUDA graph (N = 1)")
     ap.add_argument("--pipeline", type=int, default=1,
@@ -215,7 +215,7 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.serialize_sweeps < 0:
-        args.serialize_sweeps = 1 if (world == 1 and args.layout == "packed" and args.overlap and args.pipeline) else 0
+        args.serialize_sweeps = 1 if (args.layout == "packed" and args.overlap and args.pipeline) else 0
     if args.impl == "reference":
         return run_reference(args, w, spec, rank, world)
 
@@ -259,14 +259,14 @@ def main():
             heads.append(pd[..., s0:s1].reshape(n, gh, gw, -1).contiguous())
         hgrads = [torch.empty_like(x) for x in heads]
 
-    def half_loss(events=None, sweep_after=None, sweep_done=None):
+    def half_loss(events=None, sweep_after=None, sweep_done=None, out=None):
         if sweep_after is not None or sweep_done is not None:
-            total, _ = loss.loss_and_grad(td, pd, grad_out=grad, sweep_after=sweep_after, sweep_done=sweep_done)
+            total, _ = loss.loss_and_grad(td, pd, grad_out=grad, sweep_after=sweep_after, sweep_done=sweep_done, out=out)
             return total
         if heads is not None and events is None:
             total, _ = loss.loss_and_grad_heads(td, heads, grads_out=hgrads)
             return total
-        total, _ = loss.loss_and_grad(td, pd, events=events, grad_out=grad)
+        total, _ = loss.loss_and_grad(td, pd, events=events, grad_out=grad, out=out)
         return total
 
     def half_post():
@@ -276,7 +276,7 @@ def main():
             post.filter(pd, w["score_thresh"], out=(cand, counts))
         post.nms(cand, counts, w["nms_thresh"], out=keep)
 
-    def steps(count, events=None):
+    def steps(count, events=None, outs=None):
         """`count` complete steps.  The training half (assignment, dense pass) and the inference half (filter, sort,
         NMS) of a step share only their input, so they run on two streams.  --pipeline 1: the streams are joined once
         per call (consecutive steps of either half queue behind each other, the latency-bound tail of one step's
@@ -298,11 +298,12 @@ def main():
                     post.filter(pd, w["score_thresh"], out=(cand, counts), sweep_done=filt_done)   # recorded after the sweep
                     post.nms(cand, counts, w["nms_thresh"], out=keep)
                 dense_done = torch.cuda.Event()
-                total = half_loss(sweep_after=filt_done, sweep_done=dense_done)   # the dense sweep waits for the score sweep
+                total = half_loss(sweep_after=filt_done, sweep_done=dense_done,      # the dense sweep waits for the score sweep
+                                  out=None if outs is None else outs[k])
                 continue
             with torch.cuda.stream(post_stream):
                 half_post()
-            total = half_loss()
+            total = half_loss(out=None if (outs is None or heads is not None) else outs[k])
             if not args.pipeline:
                 cur.wait_stream(post_stream)
                 if k + 1 < count:
@@ -345,7 +346,10 @@ def main():
     # CUDA graph and replayed K times -- the launch-bound host loop is out of the way, the device work is identical
     graph, mode = None, "eager"
     # several steps per graph (no collective inside at N = 1): consecutive steps overlap like eager launches do
-    unroll = args.graph_steps if world == 1 else 1
+    # N > 1: the NCCL call stays outside the graph (a collective inside the capture hung in round 1); the steps of a
+    # graph write their 20 loss floats into the rows of one buffer, which is all-reduced once after the replay
+    unroll = args.graph_steps if (world == 1 or args.layout == "packed") else 1
+    loss_rows = torch.zeros((unroll, 20), dtype=torch.float32, device=dev) if world > 1 else None
     if not args.no_graph:
         try:
             loss.auto_all_reduce = False                           # the collective stays outside the graph
@@ -356,8 +360,9 @@ def main():
             torch.cuda.current_stream().wait_stream(side)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                steps(unroll)
-            mode = "cuda-graph replay, %d step(s) per graph" % unroll + (" + eager NCCL all-reduce of the 20 loss floats" if world > 1 else "")
+                steps(unroll, outs=loss_rows)
+            mode = "cuda-graph replay, %d step(s) per graph" % unroll + (
+                " + one eager NCCL all-reduce of the graph's %d x 20 loss floats" % unroll if world > 1 else "")
         except Exception as e:
             graph, mode = None, "eager (graph capture failed: %s)" % type(e).__name__
             torch.cuda.synchronize()
@@ -371,7 +376,8 @@ def main():
             return
         for _ in range(count // unroll):
             graph.replay()
-            loss.all_reduce_detail()
+            if world > 1:
+                dist.all_reduce(loss_rows)
         rest = count % unroll
         if rest:
             loss.auto_all_reduce = True
@@ -500,7 +506,8 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "desc": w["desc"], "per_gpu_batch": n, "global_batch": n * world,
                        "label_slots": m, "score_thresh": w["score_thresh"], "nms_thresh": w["nms_thresh"],
-                       "parallelism": "batch-sharded dp%d, one 20-float NCCL all-reduce per step" % world,
+                       "parallelism": "batch-sharded dp%d, the 20 loss floats of every step all-reduced over NCCL "
+                                      "(one call per graph replay / per eager step)" % world,
                        "l2": "inputs larger than L2: predicts %.0f MB + gradient %.0f MB per GPU vs 126 MB L2" % (
                            pd.numel() * 4 / 1e6, grad.numel() * 4 / 1e6),
                        "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image,

@@ -109,14 +109,17 @@ class YOLOv3Loss(object):
         return t, p
 
     def _run(self, targets, predicts, want_grad, upstream=1.0, events=None, grad_out=None, sweep_after=None,
-             sweep_done=None):
+             sweep_done=None, out=None):
         t, p = self._prepare(targets, predicts)
         n, m = p.shape[0], t.shape[1] // 5
         world = self._world()
         n_global = n * world
         rect_active = self.current_num <= self.rectified_coord_num            # :125 (read before the add)
         ws = self._workspace(n, m, p.device)
-        out = torch.empty(20, dtype=torch.float32, device=p.device)
+        if out is None:
+            out = torch.empty(20, dtype=torch.float32, device=p.device)
+        elif out.shape != (20,) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != p.device:
+            raise ValueError("out must be a contiguous fp32 tensor of 20 elements on the device of predicts")
         grad = None
         if want_grad:
             grad = torch.empty_like(p) if grad_out is None else grad_out
@@ -169,12 +172,13 @@ class YOLOv3Loss(object):
     __call__ = loss
 
     def loss_and_grad(self, targets, predicts, upstream=1.0, events=None, grad_out=None, sweep_after=None,
-                      sweep_done=None):
+                      sweep_done=None, out=None):
         """(total loss, d(upstream * loss)/d predicts in the packed layout) from one fused pass.
         ``grad_out`` reuses a caller-owned gradient buffer; ``events`` = (start, stop) CUDA events recorded
-        around the dense sweep alone."""
+        around the dense sweep alone; ``out`` = a caller-owned 20-float slot for [18 detail values, their sum, 0] (e.g.
+        row k of a (steps, 20) buffer that is all-reduced once for several steps)."""
         return self._run(targets, predicts, want_grad=True, upstream=upstream, events=events, grad_out=grad_out,
-                         sweep_after=sweep_after, sweep_done=sweep_done)
+                         sweep_after=sweep_after, sweep_done=sweep_done, out=out)
 
     def loss_and_grad_heads(self, targets, head_predicts, upstream=1.0, want_grad=True, grads_out=None):
         """The same loss on the three head tensors BEFORE yolov3_detector.py:80-85 packs them: ``head_predicts`` =
