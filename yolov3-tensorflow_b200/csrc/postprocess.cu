@@ -1153,7 +1153,7 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
         ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx, ws.kspill, keep, ws.wl, ws.wl_count);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
-    // segments longer than 256 candidates: one cluster of 8 CTAs per segment (falls back to one CTA per segment where
+    // segments longer than 256 candidates: one cluster of CTAs per segment (falls back to one CTA per segment where
     // such a cluster cannot be scheduled)
     static int clusters = -1;
     if (clusters < 0) {
