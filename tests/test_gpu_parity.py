@@ -543,6 +543,35 @@ def test_filter_early_out_is_safe_on_extreme_class_logits(yv3):
             assert np.array_equal(np.concatenate([f.reshape(-1, 8) for f in filt], 0).astype(np.float32), rows)
 
 
+def test_unpacked_entry_points_reject_bad_arguments(yv3):
+    import ctypes
+    from yolov3_tensorflow_b200 import _lib
+    spec, p, t = _inputs("coco_64x96_c4", 2, 4)
+    n = p.shape[0]
+    heads = [torch.from_numpy(np.ascontiguousarray(h.reshape(n, h.shape[1], h.shape[2], -1))).cuda() for h in rn.unpack(p, spec)]
+    loss = yv3.YOLOv3Loss(**product_loss_args(spec))
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    td = torch.from_numpy(t).cuda()
+    with pytest.raises(ValueError):
+        loss.loss_and_grad_heads(td, heads[:2])
+    with pytest.raises(ValueError):
+        loss.loss_and_grad_heads(td, [heads[1], heads[0], heads[2]])          # /16 tensor in the /8 slot
+    with pytest.raises(ValueError):
+        post.filter_heads([heads[0], heads[1], heads[2][:1]], 0.3)            # batch mismatch
+    # through the C ABI: a NULL head pointer and a phase mask without a phase
+    ws = loss._workspace(n, 4, td.device)
+    out = torch.empty(20, device="cuda")
+    pp = (ctypes.c_void_p * 3)(_lib.ptr(heads[0]), None, _lib.ptr(heads[2]))
+    rc = _lib.lib().yv3_loss_fwd_bwd_heads(ctypes.byref(loss._cfg), pp, _lib.ptr(td), n, 4, n, 0, 1.0, _lib.ptr(out), None,
+                                           _lib.ptr(ws), ws.numel(), 7, None)
+    assert rc == _lib.YV3_ERR_NULL
+    ok = (ctypes.c_void_p * 3)(*[_lib.ptr(h) for h in heads])
+    rc = _lib.lib().yv3_loss_fwd_bwd_heads(ctypes.byref(loss._cfg), ok, _lib.ptr(td), n, 4, n, 0, 1.0, _lib.ptr(out), None,
+                                           _lib.ptr(ws), ws.numel(), 0, None)
+    assert rc == _lib.YV3_ERR_SHAPE
+    torch.cuda.synchronize()
+
+
 def test_capacity_overflow_is_reported(yv3):
     spec, p, _ = _inputs("coco_64x96_c4", 1, 4)
     post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes, capacity=16)
