@@ -514,6 +514,8 @@ constexpr int kNmsMedium = 256;         // threads = chunk size of the NMS kerne
 constexpr int kNmsLarge = 1024;         // ... and for longer ones
 constexpr int kFuseMaxK = 4096;         // lists up to this size get their short segments resolved inside the sort kernel
 constexpr int kFuseMaxSeg = 32;         // ... segments up to one warp wide
+constexpr int kBucketMaxK = 4096;       // bucket path of the sort kernel: lists up to this size ...
+constexpr int kBucketClasses = 1024;    // ... with class ids below this (= kSortThreads: thread c owns class c) and <= 32 per class
 
 // One CTA per image: sort keys (class asc, score desc, row asc) in shared memory, publish the sorted order, then --
 // for lists of at most kFuseMaxK candidates -- resolve every class segment of at most 32 candidates right here, one
@@ -548,6 +550,98 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
     }
     if (tid == 0) nseg_s = 0;
     __syncthreads();
+    // ---- bucket path: every class of this image has at most 32 candidates (the usual case at a sensible score
+    // threshold: ~6 per class at cfg2).  Sorting by (class, score desc, row) is then a counting sort by class -- a
+    // shared-memory histogram, a prefix over the classes, a scatter -- followed by a rank sort inside each bucket by
+    // one warp, which goes straight on to the greedy NMS of that bucket with the candidates in its lanes.  No global
+    // bitonic sort, no sorted key / box / row tables in global memory (only the queued long segments need those).
+    if (K <= kBucketMaxK && n2s >= 2) {          // n2s >= 2: the launch reserved the fuse area (112 KB), 36 KB are used here
+        unsigned long long* bkey = skeys;                                             // [kBucketMaxK] keys, bucketed
+        int* hist_s = reinterpret_cast<int*>(skeys + kBucketMaxK);                    // [kBucketClasses] counts -> offsets
+        __shared__ int wtot_s[kSortThreads / 32];
+        hist_s[tid] = 0;                                                              // kBucketClasses == kSortThreads
+        __syncthreads();
+        unsigned long long mykey[kBucketMaxK / kSortThreads];
+        int mypos[kBucketMaxK / kSortThreads];
+        bool bad = false;
+#pragma unroll
+        for (int u = 0; u < kBucketMaxK / kSortThreads; ++u) {
+            const int i = tid + u * kSortThreads;
+            mypos[u] = -1;
+            mykey[u] = 0;
+            if (i < K) {
+                const float4 t = reinterpret_cast<const float4*>(rows + (size_t)i * YV3_CAND_COLS)[1];
+                mykey[u] = make_key(t.z, t.w, i);
+                const int c = (int)(mykey[u] >> 50);
+                if (c >= kBucketClasses) bad = true;
+                else mypos[u] = atomicAdd(&hist_s[c], 1);
+            }
+        }
+        __syncthreads();
+        const int mycount = hist_s[tid];
+        if (!__syncthreads_or((bad || mycount > kFuseMaxSeg) ? 1 : 0)) {
+            // exclusive prefix over the classes: thread c owns class c
+            int incl = mycount;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            if (lane == 31) wtot_s[warp] = incl;
+            __syncthreads();
+            int base = 0;
+            for (int w = 0; w < warp; ++w) base += wtot_s[w];
+            const int myoff = base + incl - mycount;
+            __syncthreads();                                  // every count has been read
+            hist_s[tid] = myoff;
+            __syncthreads();
+#pragma unroll
+            for (int u = 0; u < kBucketMaxK / kSortThreads; ++u)
+                if (mypos[u] >= 0) bkey[hist_s[(int)(mykey[u] >> 50)] + mypos[u]] = mykey[u];
+            __syncthreads();
+            unsigned char* keep_b = keep + (size_t)n * capacity;
+            // warp w serves the classes w, w + 32, ...; count(c) = offset(c + 1) - offset(c)
+            for (int c = warp; c < kBucketClasses; c += kSortThreads / 32) {
+                const int o0 = hist_s[c];
+                const int o1 = (c + 1 < kBucketClasses) ? hist_s[c + 1] : K;
+                const int len = o1 - o0;
+                if (len <= 0) continue;
+                const bool in = lane < len;
+                unsigned long long key = in ? bkey[o0 + lane] : kPadKey;
+                // rank sort: keys are unique (the row is part of the key)
+                int rank = 0;
+                for (int j = 0; j < len; ++j) {
+                    const unsigned long long other = __shfl_sync(0xffffffffu, key, j);
+                    rank += (other < key) ? 1 : 0;
+                }
+                __syncwarp();
+                if (in) bkey[o0 + rank] = key;
+                __syncwarp();
+                if (in) key = bkey[o0 + lane];
+                const int row = (int)(key & 0x3ffffULL);
+                float4 mine_f = make_float4(0.f, 0.f, 0.f, 0.f);
+                double mine_area = 0.0;
+                if (in) {
+                    mine_f = reinterpret_cast<const float4*>(rows + (size_t)row * YV3_CAND_COLS)[0];
+                    mine_area = box_area_d(mine_f);
+                }
+                unsigned alive = __ballot_sync(0xffffffffu, in);
+                for (int i = 0; i < len - 1; ++i) {
+                    if (!((alive >> i) & 1u)) continue;                                  // warp-uniform
+                    float4 fi;
+                    fi.x = __shfl_sync(0xffffffffu, mine_f.x, i); fi.y = __shfl_sync(0xffffffffu, mine_f.y, i);
+                    fi.z = __shfl_sync(0xffffffffu, mine_f.z, i); fi.w = __shfl_sync(0xffffffffu, mine_f.w, i);
+                    const bool overlap = fminf(fi.z, mine_f.z) > fmaxf(fi.x, mine_f.x) && fminf(fi.w, mine_f.w) > fmaxf(fi.y, mine_f.y);
+                    bool drop = lane > i && ((alive >> lane) & 1u);
+                    if (drop) drop = overlap ? suppresses_overlapping(fi, box_area_d(fi), mine_f, mine_area, thresh) : (0.0 > thresh);
+                    alive &= ~__ballot_sync(0xffffffffu, drop);
+                }
+                if (in) keep_b[row] = (unsigned char)((alive >> lane) & 1u);
+            }
+            return;
+        }
+        __syncthreads();                                      // the attempt is abandoned: the general path rebuilds everything
+    }
     if (keys == skeys && n2 <= kSortThreads) bitonic_sort_regs(keys, n2, tid);
     else bitonic_sort(keys, n2, tid);
     const bool fuse = K <= kFuseMaxK && keys == skeys;
