@@ -202,6 +202,9 @@ def main():
                     help="1: the two HBM-bound sweeps (dense pass, score pass) never run at the same time; the small "
                          "kernels of either half run under the other half's sweep (default: on with the "
                          "packed layout, where several steps share a graph; measured 142 -> 140.5 us/step)")
+    ap.add_argument("--fused", type=int, default=1,
+                    help="1 (packed layout): loss fwd+bwd and the post-process filter of a step in one call that reads the "
+                         "head tensor once (yv3_loss_filter_fused); 0: the two sweeps as separate calls")
     ap.add_argument("--graph-steps", type=int, default=8, help="steps captured per CUDA graph (N = 1)")
     ap.add_argument("--pipeline", type=int, default=1,
                     help="1: the two streams are joined once per graph / timed region, 0: after every step")
@@ -214,6 +217,10 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.layout != "packed":
+        args.fused = 0
+    if args.fused:
+        args.serialize_sweeps = 0
     if args.serialize_sweeps < 0:
         args.serialize_sweeps = 1 if (args.layout == "packed" and args.overlap and args.pipeline) else 0
     if args.impl == "reference":
@@ -237,6 +244,16 @@ def main():
     pd, td = p_host.to(dev), t_host.to(dev)
     loss = yv3.YOLOv3Loss(rectified_coord_num=w["rect"], **spec.loss_args)
     post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    # a second workspace pair for the fused schedule (steps alternate; the C ABI is re-entrant per workspace)
+    pairs = [(loss, post)]
+    if args.fused:
+        pairs.append((yv3.YOLOv3Loss(rectified_coord_num=w["rect"], **spec.loss_args),
+                      yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)))
+
+    def set_auto(v):
+        for lo, _ in pairs:
+            lo.auto_all_reduce = v
+
     grad = torch.empty_like(pd)
     cand = torch.empty((n, post.capacity, 8), dtype=torch.float32, device=dev)
     counts = torch.empty((n, 3), dtype=torch.int32, device=dev)
@@ -276,11 +293,57 @@ def main():
             post.filter(pd, w["score_thresh"], out=(cand, counts))
         post.nms(cand, counts, w["nms_thresh"], out=keep)
 
+    def fused_steps(count, events=None, outs=None):
+        """`count` complete steps with the one-sweep call.  Two streams, two (loss, post-process) workspace pairs
+        alternating by step: the HBM-bound sweeps run back to back on the current stream; everything small -- the
+        assignment of step k + 1, then fold + gather + sort + NMS of step k -- runs on the high-priority stream under
+        sweep k + 1 / k.  Order on the small stream: assign(k + 1), wait sweep(k), tail(k); so assign(k + 2), which
+        rewrites the workspace of step k, comes after tail(k), and sweep(k) only has to wait for assign(k)."""
+        thr = w["score_thresh"]
+        cur = torch.cuda.current_stream()
+        if post_stream is None or events is not None:
+            for k in range(count):
+                total, _, _, _ = loss.loss_grad_and_filter(td, pd, post, thr, grad_out=grad,
+                                                           out=None if outs is None else outs[k],
+                                                           filter_out=(cand, counts), events=events)
+                post.nms(cand, counts, w["nms_thresh"], out=keep)
+            return total
+
+        def part(k, phases):
+            lo, po = pairs[k & 1]
+            return lo.loss_grad_and_filter(td, pd, po, thr, grad_out=grad, out=None if outs is None else outs[k],
+                                           filter_out=(cand, counts), phases=phases)[0]
+
+        def assign(k):
+            with torch.cuda.stream(post_stream):
+                part(k, 1)
+                e = torch.cuda.Event()
+                e.record(post_stream)
+            return e
+
+        post_stream.wait_stream(cur)
+        a_done = assign(0)
+        for k in range(count):
+            a_next = assign(k + 1) if k + 1 < count else None
+            cur.wait_event(a_done)
+            part(k, 2)
+            swept = torch.cuda.Event()
+            swept.record(cur)
+            with torch.cuda.stream(post_stream):
+                post_stream.wait_event(swept)
+                total = part(k, 4)
+                pairs[k & 1][1].nms(cand, counts, w["nms_thresh"], out=keep)
+            a_done = a_next
+        cur.wait_stream(post_stream)
+        return total
+
     def steps(count, events=None, outs=None):
         """`count` complete steps.  The training half (assignment, dense pass) and the inference half (filter, sort,
         NMS) of a step share only their input, so they run on two streams.  --pipeline 1: the streams are joined once
         per call (consecutive steps of either half queue behind each other, the latency-bound tail of one step's
         post-process runs under the next step's sweeps); --pipeline 0: joined after every step."""
+        if args.fused:
+            return fused_steps(count, events, outs)
         if post_stream is None or events is not None:
             for k in range(count):
                 total = half_loss(events)
@@ -352,7 +415,7 @@ def main():
     loss_rows = torch.zeros((unroll, 20), dtype=torch.float32, device=dev) if world > 1 else None
     if not args.no_graph:
         try:
-            loss.auto_all_reduce = False                           # the collective stays outside the graph
+            set_auto(False)                           # the collective stays outside the graph
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
@@ -367,7 +430,7 @@ def main():
             graph, mode = None, "eager (graph capture failed: %s)" % type(e).__name__
             torch.cuda.synchronize()
     if graph is None:
-        loss.auto_all_reduce = True
+        set_auto(True)
 
     def run(count):
         """exactly `count` steps"""
@@ -380,9 +443,9 @@ def main():
                 dist.all_reduce(loss_rows)
         rest = count % unroll
         if rest:
-            loss.auto_all_reduce = True
+            set_auto(True)
             steps(rest)
-            loss.auto_all_reduce = False
+            set_auto(False)
     run(3 * unroll)
     fence()
     if graph is not None and not args.force_graph:
@@ -398,9 +461,9 @@ def main():
             return a.elapsed_time(b)
 
         def eager20():
-            loss.auto_all_reduce = True
+            set_auto(True)
             steps(20)
-            loss.auto_all_reduce = False
+            set_auto(False)
 
         t_graph = trial(lambda: run(20 - 20 % unroll))
         t_eager = trial(eager20)
@@ -410,7 +473,7 @@ def main():
         if float(verdict[1]) < float(verdict[0]):
             graph, mode = None, "eager launches (faster than graph replay in a 20-step trial: %.1f vs %.1f us/step)" % (
                 1e3 * float(verdict[1]) / 20, 1e3 * float(verdict[0]) / (20 - 20 % unroll))
-            loss.auto_all_reduce = True
+            set_auto(True)
     start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.mark = "timed"
     start.record()
@@ -419,14 +482,15 @@ def main():
     fence()
     sampler.mark = "after"
     total_ms = start.elapsed_time(stop)
-    loss.check_status()
-    post.check_status()
+    for lo, po in pairs:
+        lo.check_status()
+        po.check_status()
     cand_per_image = float(counts.sum().item()) / n
     kept_per_image = float(sum(int(keep[i, :int(counts[i].sum())].sum()) for i in range(min(n, 8)))) / min(n, 8)
 
     # ---- end to end through the public API with host buffers -------------------------------------------
 
-    loss.auto_all_reduce = True
+    set_auto(True)
 
     # Double-buffered: the host->device copy of step k + 1 (copy stream) runs while step k computes; the caller reads
     # step k - 1's loss and detections from pinned host memory once that step's device->host copies have landed.
@@ -452,8 +516,12 @@ def main():
                 ready = torch.cuda.Event()
                 ready.record(copy_stream)
             main.wait_event(ready)
-            total, _ = loss.loss_and_grad(tbuf[b], pbuf[b], grad_out=grad)
-            post.filter(pbuf[b], w["score_thresh"], out=(cand, counts))
+            if args.fused:
+                total, _, _, _ = loss.loss_grad_and_filter(tbuf[b], pbuf[b], post, w["score_thresh"], grad_out=grad,
+                                                           filter_out=(cand, counts))
+            else:
+                total, _ = loss.loss_and_grad(tbuf[b], pbuf[b], grad_out=grad)
+                post.filter(pbuf[b], w["score_thresh"], out=(cand, counts))
             post.nms(cand, counts, w["nms_thresh"], out=keep)
             out_hosts[b][:18].copy_(loss.loss_detail.reshape(-1), non_blocking=True)
             out_hosts[b][18:19].copy_(total.reshape(1), non_blocking=True)
@@ -489,6 +557,14 @@ def main():
     if rank == 0:
         A, L, C = spec.anchors_per_image, spec.box_len, spec.class_num
         alg_per_image = 4 * A * 5 + 4 * A * L + 4 * (owned / n) * C + 4 * m * 5
+        kernel_name = "loss_dense_kernel"
+        if args.fused:
+            # the fused sweep does the loss sweep's AND the score sweep's work: SURVEY 8(d)'s figures for the two added
+            # up with the tensor read counted once -- 4 A L in (every class logit feeds max / arg-max), 4 A L out
+            # (the dense gradient), the labels; the survivors' staging rows are noise
+            alg_per_image = 4 * A * L + 4 * A * L + 4 * m * 5
+            kernel_name = "fused_sweep_kernel"
+            assert loss.last_fused, "the fused call fell back to the two sweeps"
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(peaks_path):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
@@ -498,7 +574,7 @@ def main():
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(args.workload, {}).get("loss_dense_kernel_dram_bytes_per_launch")
+            traffic = json.load(open(tp)).get(args.workload, {}).get(kernel_name + "_dram_bytes_per_launch")
         line = {
             "metric": "head loss fwd+bwd + decode+filter+NMS throughput",
             "value": world * n * args.steps / (total_ms * 1e-3), "unit": "images/s",
@@ -511,16 +587,18 @@ def main():
                        "l2": "inputs larger than L2: predicts %.0f MB + gradient %.0f MB per GPU vs 126 MB L2" % (
                            pd.numel() * 4 / 1e6, grad.numel() * 4 / 1e6),
                        "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image,
-                       "layout": args.layout, "serialize_sweeps": bool(args.serialize_sweeps), "launch": mode, "streams": 2 if args.overlap else 1,
+                       "layout": args.layout, "fused_sweep": bool(args.fused), "serialize_sweeps": bool(args.serialize_sweeps), "launch": mode, "streams": 2 if args.overlap else 1,
                        "high_priority_stream": args.priority if args.overlap else None,
+                       "fused_schedule": "sweeps back to back on one stream; assignment of step k+1 and fold/gather/sort/NMS of step k on "
+                                         "the high-priority stream, two workspaces alternating" if (args.fused and args.overlap) else None,
                        "stream_join": ("once per %d-step graph" % unroll if graph is not None else "once per timed region")
                        if (args.overlap and args.pipeline) else "every step"},
-            "stage_ms": {"loss_dense_kernel": dense_ms, "filter_plus_nms": post_ms,
+            "stage_ms": {kernel_name: dense_ms, ("fold_gather_sort_nms" if args.fused else "filter_plus_nms"): post_ms,
                          "step_minus_stages": total_ms / args.steps - dense_ms - post_ms,
                          "note": "stage times from eager single-stream launches with events; ms_per_step from the timed "
                                  "region (step_minus_stages < 0: the two halves overlap on two streams; it also holds "
                                  "the assignment and fold kernels)"},
-            "roofline": {"kernel": "loss_dense_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
+            "roofline": {"kernel": kernel_name, "bound": "hbm", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_per_image * n, "avg_launch_ms": dense_ms,
                          "dense_2x4AL_bytes_per_launch_for_context": 8 * A * L * n},
@@ -531,7 +609,8 @@ def main():
                                   "step k-1 are read on the host every step",
                     "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
             # assign, dense sweep, fold, score, gather, sort, nms x2 (the sweeps run once per head tensor in the heads layout)
-            "gpu_launches": (12 if args.layout == "heads" else 8) * args.steps,
+            # fused: assign, fused sweep, fold, gather, sort, nms x2
+            "gpu_launches": (12 if args.layout == "heads" else 7 if args.fused else 8) * args.steps,
             "clocks": sampler.summary(),
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define YV3_ABI_VERSION 3
+#define YV3_ABI_VERSION 4
 #define YV3_MAX_BOX 8      /* anchors per head (reference ships 3 / 2 / 3, configs.py:37-41) */
 #define YV3_MAX_GT 256     /* label slots per image (M) */
 
@@ -195,6 +195,25 @@ int yv3_filter_packed(const yv3_config* cfg, const float* predicts, int n, float
  * have at least 4 records per image (YV3_ERR_SHAPE otherwise: a 32x32 input with fewer than 4 anchors at /32). */
 int yv3_filter_heads(const yv3_config* cfg, const float* const head_predicts[3], int n, float score_thresh, float* cand,
                      int32_t capacity, int32_t* counts, void* workspace, size_t workspace_bytes, int phases, void* stream);
+
+/* Evaluation while training: yv3_loss_fwd_bwd (phases 7) and yv3_filter_packed (phases 3) on the SAME packed predicts
+ * in one call -- what a trainer.py step followed by run.py's filter on the same head output does (yolov3_loss.py:81-138,
+ * yolov3_post_process.py:21-76).  The two HBM-bound sweeps become one: a warp lands a tile of 32 records in shared
+ * memory once, scores it, runs the loss record phase, turns the tile in place into the gradient and stores it back
+ * whole (4*A*L bytes read + 4*A*L bytes written per image instead of two reads of the tensor and a gradient written
+ * in 32-byte pieces).  Arguments as in the two calls (loss_workspace from yv3_query_workspace, post_workspace from
+ * yv3_query_postprocess_workspace); grad_predicts is required.  cand / counts / grad_predicts and every integer
+ * decision are bit-identical to the separate calls; the loss sums are folded per warp, so a detail value may differ
+ * in its last bit.  Launches: assignment, the fused sweep, the fold, the gather.
+ * phases: bit mask, 7 = the whole call; 1 = the assignment, 2 = the sweep, 4 = fold + gather, for a caller that times or
+ * schedules them separately (same arguments, in that order).  Falls back to the two separate sweeps
+ * (same results) when the fused tile shape does not apply (predicts not 16-byte aligned, fewer than 32 records per
+ * image, more than 32768 tiles per call); *fused_out (host, may be NULL) says which ran.  yv3_nms follows as usual. */
+int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
+                          int n_global, int rectified_active, float upstream, float* loss_out20, float* grad_predicts,
+                          void* loss_workspace, size_t loss_workspace_bytes, float score_thresh, float* cand,
+                          int32_t capacity, int32_t* counts, void* post_workspace, size_t post_workspace_bytes,
+                          int32_t* fused_out, int phases, void* stream);
 
 /* Class-aware greedy NMS, YOLOv3PostProcessor._apply_nms (yolov3/yolov3_post_process.py:108-159), for
  * n independent candidate lists.  cand is (n, capacity, 8) fp32; list i holds

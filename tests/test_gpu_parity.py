@@ -587,3 +587,117 @@ def test_config_errors(yv3):
     with pytest.raises(ValueError):
         yv3.YOLOv3Loss([(4, 4), (2, 2), (1, 1)], 0, CASES["tiny_32_c2"][3], 0.5, [(1, 1, 1, 1, 1)] * 3,
                        rectified_loss_weight=[1, 1])
+
+
+# ---- the fused sweep: loss fwd+bwd and the post-process filter on one read of the predicts -------------------
+@pytest.mark.parametrize("thr", [0.3, 0.001])
+@pytest.mark.parametrize("rect", [False, True])
+@pytest.mark.parametrize("name", SMALL)
+def test_fused_loss_and_filter_equals_the_separate_calls(yv3, name, rect, thr):
+    """yv3_loss_filter_fused against yv3_loss_fwd_bwd + yv3_filter_packed (each pinned to the oracle above): gradient,
+    candidate rows and counts bit for bit; the loss sums are folded per warp instead of per CTA, so the detail values
+    are compared to 1e-6 and to the fp64 oracle at the tolerance of the separate call."""
+    spec, p, t = _inputs(name, 5, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    pd, td = torch.from_numpy(p).cuda(), torch.from_numpy(t).cuda()
+    ref = yv3.YOLOv3Loss(rectified_coord_num=(0 if rect else -1), **product_loss_args(spec))
+    total_r, grad_r = ref.loss_and_grad(td, pd)
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    cand_r, counts_r = post.filter(pd, thr)
+    cand_r, counts_r = cand_r.clone(), counts_r.clone()
+
+    loss = yv3.YOLOv3Loss(rectified_coord_num=(0 if rect else -1), **product_loss_args(spec))
+    total, grad, cand, counts = loss.loss_grad_and_filter(td, pd, post, thr)
+    loss.check_status()
+    post.check_status()
+    assert loss.last_fused
+    assert torch.equal(grad, grad_r)
+    assert torch.equal(counts, counts_r)
+    for i in range(5):
+        k = int(counts[i].sum().item())
+        assert torch.equal(cand[i, :k], cand_r[i, :k])
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), ref.loss_detail.cpu().numpy(), rtol=1e-6, atol=1e-7)
+    _, detail64, _ = rt.loss_and_grad(t, p, spec, rectified_active=rect, dtype=torch.float64)
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), detail64, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(total.item(), total_r.item(), rtol=1e-6)
+
+
+def test_fused_loss_and_filter_at_the_benchmark_shape(yv3):
+    """416x416, 80 classes: duplicate labels on one anchor (read-modify-write on top of the stored tile), an empty
+    image, the NMS survivors of the fused candidates against the C oracle, and the same bits on a second call."""
+    spec, p, t = _inputs("coco_416_c80", 3, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    t = t.reshape(3, 8, 5)
+    t[1] = -1.0
+    t[2, 1] = t[2, 0]
+    t = t.reshape(3, 40)
+    pd, td = torch.from_numpy(p).cuda(), torch.from_numpy(t).cuda()
+    ref = yv3.YOLOv3Loss(rectified_coord_num=0, **product_loss_args(spec))
+    _, grad_r = ref.loss_and_grad(td, pd)
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    cand_r, counts_r = [x.clone() for x in post.filter(pd, 0.1)]
+    loss = yv3.YOLOv3Loss(rectified_coord_num=0, **product_loss_args(spec))
+    total, grad, cand, counts = loss.loss_grad_and_filter(td, pd, post, 0.1)
+    loss.check_status()
+    assert loss.last_fused
+    assert torch.equal(grad, grad_r) and torch.equal(counts, counts_r)
+    keep = post.nms(cand, counts, 0.45)
+    for i in range(3):
+        k = int(counts[i].sum().item())
+        assert torch.equal(cand[i, :k], cand_r[i, :k])
+        rows = cand[i, :k].cpu().numpy().astype(np.float64)
+        assert np.array_equal(np.nonzero(keep[i, :k].cpu().numpy())[0], np.sort(nms_c.greedy_nms(rows, 0.45)))
+    _, detail64, _ = rt.loss_and_grad(t, p, spec, rectified_active=True, dtype=torch.float64)
+    np.testing.assert_allclose(loss.loss_detail.cpu().numpy(), detail64, rtol=1e-5, atol=1e-6)
+    loss2 = yv3.YOLOv3Loss(rectified_coord_num=0, **product_loss_args(spec))
+    total2, grad2, _, _ = loss2.loss_grad_and_filter(td, pd, post, 0.1)
+    assert torch.equal(grad, grad2) and total.item() == total2.item()
+
+
+def test_fused_call_falls_back_on_unaligned_predicts(yv3):
+    """a predicts tensor off the 16-byte grid cannot be tiled by bulk copies: the call runs the two sweeps instead
+    (same results) and says so."""
+    spec, p, t = _inputs("coco_64_c20", 3, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    pd, td = torch.from_numpy(p).cuda(), torch.from_numpy(t).cuda()
+    buf = torch.empty(pd.numel() + 1, dtype=torch.float32, device="cuda")
+    pu = buf[1:].view(pd.shape)
+    pu.copy_(pd)
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    a = yv3.YOLOv3Loss(**product_loss_args(spec))
+    _, grad_a, cand_a, counts_a = a.loss_grad_and_filter(td, pd, post, 0.2)
+    assert a.last_fused
+    cand_a, counts_a = cand_a.clone(), counts_a.clone()
+    b = yv3.YOLOv3Loss(**product_loss_args(spec))
+    _, grad_b, cand_b, counts_b = b.loss_grad_and_filter(td, pu, post, 0.2)
+    assert not b.last_fused
+    assert torch.equal(grad_a, grad_b) and torch.equal(counts_a, counts_b)
+    for i in range(3):
+        k = int(counts_a[i].sum().item())
+        assert torch.equal(cand_a[i, :k], cand_b[i, :k])
+
+
+def test_fused_call_issued_phase_by_phase(yv3):
+    """phases 1 (assignment), 2 (sweep), 4 (fold + gather) as three calls -- what a scheduler does to put them on
+    streams of its choice -- give the bits of the single call."""
+    spec, p, t = _inputs("coco_96x64_c13", 4, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    pd, td = torch.from_numpy(p).cuda(), torch.from_numpy(t).cuda()
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    a = yv3.YOLOv3Loss(rectified_coord_num=0, **product_loss_args(spec))
+    total_a, grad_a, cand_a, counts_a = a.loss_grad_and_filter(td, pd, post, 0.05)
+    cand_a, counts_a, detail_a = cand_a.clone(), counts_a.clone(), a.loss_detail.clone()
+    b = yv3.YOLOv3Loss(rectified_coord_num=0, **product_loss_args(spec))
+    post_b = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    grad_b = torch.empty_like(pd)
+    out = torch.zeros(20, dtype=torch.float32, device="cuda")
+    for ph in (1, 2, 4):
+        total_b, _, cand_b, counts_b = b.loss_grad_and_filter(td, pd, post_b, 0.05, grad_out=grad_b, out=out, phases=ph)
+        assert (total_b is None) == (ph != 4)
+    b.check_status()
+    assert b.current_num == a.current_num == 4
+    assert torch.equal(grad_a, grad_b) and torch.equal(counts_a, counts_b)
+    assert torch.equal(detail_a, b.loss_detail) and total_a.item() == total_b.item()
+    for i in range(4):
+        k = int(counts_a[i].sum().item())
+        assert torch.equal(cand_a[i, :k], cand_b[i, :k])

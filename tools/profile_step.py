@@ -31,9 +31,13 @@ def main():
     cand = torch.empty((n, post.capacity, 8), dtype=torch.float32, device="cuda")
     counts = torch.empty((n, 3), dtype=torch.int32, device="cuda")
     keep = torch.empty((n, post.capacity), dtype=torch.uint8, device="cuda")
+    fused = os.environ.get("YV3_PROFILE_FUSED", "0") == "1"     # assign, fused sweep, fold, gather, sort, NMS x2
     for _ in range(steps):
-        total, _ = loss.loss_and_grad(td, pd, grad_out=grad)
-        post.filter(pd, w["score_thresh"], out=(cand, counts))
+        if fused:
+            total, _, _, _ = loss.loss_grad_and_filter(td, pd, post, w["score_thresh"], grad_out=grad, filter_out=(cand, counts))
+        else:
+            total, _ = loss.loss_and_grad(td, pd, grad_out=grad)
+            post.filter(pd, w["score_thresh"], out=(cand, counts))
         post.nms(cand, counts, w["nms_thresh"], out=keep)
     torch.cuda.synchronize()
     loss.check_status()

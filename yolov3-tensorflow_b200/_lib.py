@@ -81,6 +81,10 @@ _SIGNATURES = {
                                          ctypes.c_size_t, ctypes.c_int, _P]),
     "yv3_filter_heads": (ctypes.c_int, [_P, ctypes.POINTER(_P), ctypes.c_int, ctypes.c_float, _P, ctypes.c_int32, _P,
                                         _P, ctypes.c_size_t, ctypes.c_int, _P]),
+    "yv3_loss_filter_fused": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                             ctypes.c_float, _P, _P, _P, ctypes.c_size_t, ctypes.c_float, _P,
+                                             ctypes.c_int32, _P, _P, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int32),
+                                             ctypes.c_int, _P]),
     "yv3_nms": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int32, ctypes.c_int,
                                ctypes.c_double, _P, _P, ctypes.c_size_t, _P]),
 }
@@ -109,7 +113,7 @@ def lib():
         fn = getattr(handle, name)             # AttributeError = header and library disagree
         fn.restype = res
         fn.argtypes = args
-    if handle.yv3_abi_version() != 3:
+    if handle.yv3_abi_version() != 4:
         raise RuntimeError("libyv3head.so ABI version mismatch")
     _LIB = handle
     return _LIB

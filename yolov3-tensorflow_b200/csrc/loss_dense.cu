@@ -30,7 +30,7 @@
 //    fixed order (double) and writes the 18 detail values + their sum.  No float atomics.
 #include <stdlib.h>
 
-#include "tile_ops.cuh"
+#include "sweep_parts.cuh"
 #include "yv3_kernels.cuh"
 
 namespace yv3 {
@@ -91,27 +91,6 @@ __device__ __forceinline__ Win12 compose(const float (&gv)[5], int pos) {
     w.b = make_float4(z[4], z[5], z[6], z[7]);
     w.c = make_float4(z[8], z[9], z[10], z[11]);
     return w;
-}
-
-// The background test of yolov3_loss.py:294,331 for one (anchor, label) pair: is IoU < iou_thresh?  The IoU itself
-// is fl(inter / fl(fl(aP + aT) - inter)); the quotient is only needed when it lands close to the threshold.  With
-// thr_lo = fl(thr * (1 - 2^-19)):   inter < fl(thr_lo * uni)   implies   inter / uni < thr * (1 - 2^-20)   (two
-// roundings of at most 2^-24 each), hence fl(inter / uni) < thr.  `surely_below` is that one-multiply test; whatever
-// it does not settle -- the band below the threshold, everything above it, NaNs, uni <= 0, thr <= 0, the TIoU variant
-// -- takes the exact expression of iou_ref (`iou_below_exact`), so the decision is the reference's bit for bit.
-__device__ __forceinline__ bool surely_below(float px0, float py0, float px1, float py1, float parea, const float4& t,
-                                             float tarea, float thr_lo) {
-    const float iw = fmaxf(__fsub_rn(fminf(px1, t.z), fmaxf(px0, t.x)), 0.0f);
-    const float ih = fmaxf(__fsub_rn(fminf(py1, t.w), fmaxf(py0, t.y)), 0.0f);
-    const float inter = __fmul_rn(iw, ih);
-    const float uni = __fsub_rn(__fadd_rn(parea, tarea), inter);
-    return inter < __fmul_rn(thr_lo, uni);
-}
-__device__ __forceinline__ bool iou_below_exact(float px0, float py0, float px1, float py1, float parea, const float4& t,
-                                                float tarea, float thr, int tiou) {
-    GtBox g;
-    g.x0 = t.x; g.y0 = t.y; g.x1 = t.z; g.y1 = t.w; g.area = tarea;
-    return iou_ref(px0, py0, px1, py1, parea, g, tiou) < thr;
 }
 
 struct Logits {
@@ -534,6 +513,8 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
 // rows t, t + T, ... in index order, in double; lanes fold by shuffles, warps through shared memory -- a fixed order,
 // hence a deterministic sum -- then the 18 detail values (:115-138) and their sum (:137).
 constexpr int kFoldThreads = 256;
+constexpr int kFoldThreadsWide = 1024;      // for the one-row-per-warp tables of the fused sweep (tens of thousands of rows)
+template <int kFoldThreads>
 __global__ void __launch_bounds__(kFoldThreads) loss_fold_kernel(const __grid_constant__ Geo g,
                                                                  const __grid_constant__ DenseArgs a, int nrows) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -602,12 +583,13 @@ static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, bool
         if (err != cudaSuccess) return err;
     }
     if (grid_out) *grid_out = grid;
-    if (fold) loss_fold_kernel<<<1, kFoldThreads, 0, stream>>>(g, a, a.row_base + grid);      // the grid is a function of the arguments
+    if (fold) loss_fold_kernel<kFoldThreads><<<1, kFoldThreads, 0, stream>>>(g, a, a.row_base + grid);      // the grid is a function of the arguments
     return cudaGetLastError();
 }
 
 cudaError_t launch_loss_fold(const Geo& g, const DenseArgs& a, int nrows, cudaStream_t stream) {
-    loss_fold_kernel<<<1, kFoldThreads, 0, stream>>>(g, a, nrows);
+    if (nrows > 16 * kFoldThreads) loss_fold_kernel<kFoldThreadsWide><<<1, kFoldThreadsWide, 0, stream>>>(g, a, nrows);
+    else loss_fold_kernel<kFoldThreads><<<1, kFoldThreads, 0, stream>>>(g, a, nrows);
     return cudaGetLastError();
 }
 

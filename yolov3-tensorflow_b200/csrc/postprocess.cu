@@ -23,13 +23,12 @@
 #include <stdlib.h>
 #include <string.h>
 
-#include "tile_ops.cuh"
+#include "sweep_parts.cuh"
 #include "yv3_kernels.cuh"
 
 namespace yv3 {
 
 constexpr int kScoreThreads = 128;
-constexpr int kSerialExactFrom = 6;     // exact scores: warp-cooperative per record up to this many per tile, per lane beyond
 
 // ---- fused score + threshold over the packed logits ---------------------------------------------------------
 // One CTA per tile of <= 128 consecutive records (<= 2 images), one thread per record:
@@ -44,15 +43,6 @@ constexpr int kSerialExactFrom = 6;     // exact scores: warp-cooperative per re
 //     staging rows (score, prob, class, record-in-head); six counts per tile.
 // gather_kernel then turns counts into the reference's order (head /8,/16,/32, raster inside a head) per image and
 // writes the candidate rows, decoding each survivor's box from its five logits.
-struct ScoreTiles {
-    int tr;                 // records per tile = per WARP (multiple of 4, <= 32, <= records per image)
-    int wpc;                // warps (tiles) per CTA
-    int tile_floats;        // shared-memory floats reserved per tile (tr * L rounded up to 16 bytes)
-    int num_tiles;
-    long long total_rec;
-    int tma;
-    int early;              // threshold large enough for the approximate early-out (thresh > 2 * eps)
-};
 
 // A tile is the <= 32 consecutive records of ONE WARP: the warp lands it in its own slice of shared memory with
 // its own bulk copy and mbarrier, scores, ranks and stages it without ever meeting the other warps of the CTA (the
@@ -91,107 +81,7 @@ __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_
         __syncwarp();
     }
 
-    const bool have = lane < nrec;
-    const float* r = tile + (size_t)lane * L;
-    float conf = 0.f;
-    bool maybe = false;
-    if (have) {
-        conf = clip_ref(sigmoid_ref(r[4]), g.lo, g.hi);
-        if (C == 0) {
-            maybe = false;
-        } else if (!q.early) {
-            maybe = true;
-        } else if (conf > thresh) {                                  // fl(prob * conf) <= conf for prob <= 1
-            // ONE pass over the class logits: the sum is taken relative to the first logit c (S = sum 2^((z_k - c) log2e))
-            // while the maximum M is tracked, then sum_k exp(z_k - M) = S * 2^(-(M - c) log2e).  The product of c
-            // and log2e is the same rounded constant in every term, so it cancels; what is left is the rounding of
-            // each exponent (|.| < 128, else a term is inf or 0 and the record goes to the exact path below).
-            const float l2e = 1.4426950408889634f;
-            const float z0 = r[5];
-            const float cl = __fmul_rn(z0, l2e);
-            float mx = z0;
-            float s0 = 1.0f, s1 = 0.f, s2 = 0.f, s3 = 0.f;              // the first logit's own term is 2^0
-            int k = 1;
-            for (; k + 4 <= C; k += 4) {
-                const float a0 = r[5 + k], a1 = r[6 + k], a2 = r[7 + k], a3 = r[8 + k];
-                mx = fmaxf(fmaxf(mx, a0), a1);                         // FMNMX3
-                mx = fmaxf(fmaxf(mx, a2), a3);
-                s0 += exp2f_approx(__fmaf_rn(a0, l2e, -cl));
-                s1 += exp2f_approx(__fmaf_rn(a1, l2e, -cl));
-                s2 += exp2f_approx(__fmaf_rn(a2, l2e, -cl));
-                s3 += exp2f_approx(__fmaf_rn(a3, l2e, -cl));
-            }
-            for (; k < C; ++k) {
-                const float a0 = r[5 + k];
-                mx = fmaxf(mx, a0);
-                s0 += exp2f_approx(__fmaf_rn(a0, l2e, -cl));
-            }
-            const float S = (s0 + s1) + (s2 + s3);
-            const float E = exp2f_approx(__fmaf_rn(-mx, l2e, cl));
-            // true score <= conf / (S * E) * (1 + 1e-5); keep a 1e-3 band around the threshold for the exact path.
-            // A sum that overflowed (or a NaN) proves nothing: both comparisons are written so that they fail then.
-            maybe = !(conf < thresh * (S * E) * 0.999f) || !(S <= 3.0e38f);
-        }
-    }
-    // ---- exact scores of the queued records: one record at a time, the classes spread over the warp's lanes ------
-    float4 mine = make_float4(conf, 1.0f, __int_as_float(0), (have && conf > thresh) ? 1.f : 0.f);   // :53-55 (C = 0)
-    if (C > 0) {
-        mine = make_float4(0.f, 0.f, 0.f, 0.f);
-        unsigned mb = __ballot_sync(0xffffffffu, maybe);
-        if (__popc(mb) > kSerialExactFrom) {
-            // many records of the tile need the exact score (a low threshold: nearly all of them): one record per lane,
-            // the thread-serial class_stats -- bit-identical to the warp version by construction (tile_ops.cuh) -- costs
-            // about six warp-cooperative records, whatever the count
-            if (maybe) {
-                const ClassStats cs = class_stats(r + 5, C);
-                float best;
-                int arg;
-                class_best(r + 5, C, cs, g.lo, g.hi, best, arg);
-                const float sc = __fmul_rn(best, conf);                                  // :59
-                mine = make_float4(sc, best, __int_as_float(arg), (sc > thresh) ? 1.f : 0.f);   // :62 strict, fp32
-            }
-            mb = 0u;
-        }
-        while (mb) {
-            const int src = __ffs(mb) - 1;
-            mb &= mb - 1;
-            const float* rr = tile + (size_t)src * L;
-            const ClassStats cs = class_stats_warp(rr + 5, C, lane);
-            float best = clip_ref(cs.inv, g.lo, g.hi);
-            int arg = cs.arg;
-            if (cs.near > 1) {                                                       // rounding tie: the serial rule
-                if (lane == 0) class_best(rr + 5, C, cs, g.lo, g.hi, best, arg);
-                best = __shfl_sync(0xffffffffu, best, 0);
-                arg = __shfl_sync(0xffffffffu, arg, 0);
-            }
-            if (lane == src) {
-                const float sc = __fmul_rn(best, conf);                              // :59
-                mine = make_float4(sc, best, __int_as_float(arg), (sc > thresh) ? 1.f : 0.f);   // :62 strict, fp32
-            }
-        }
-    }
-    const bool pass = have && mine.w != 0.f;
-
-    // ---- rank inside the tile per (image slot, head): ballots only -----------------------------------------
-    const int n_first = (int)(rec0 / g.rpi);
-    int n_img = n_first, r_img = (int)(rec0 - (long long)n_first * g.rpi) + lane;
-    if (r_img >= g.rpi) { r_img -= g.rpi; ++n_img; }
-    RecLoc p = {0, 0, 0, 0};
-    if (have) p = locate(g, r_img);
-    const int grp = have ? (n_img - n_first) * 3 + p.h : 7;
-    int my_rank = 0, my_base = 0, run = 0, cnt_lane = 0;
-#pragma unroll
-    for (int gi = 0; gi < 6; ++gi) {
-        const unsigned b = __ballot_sync(0xffffffffu, pass && grp == gi);
-        if (grp == gi) { my_rank = __popc(b & ((1u << lane) - 1u)); my_base = run; }
-        if (lane == gi) cnt_lane = __popc(b);
-        run += __popc(b);
-    }
-    if (pass) {
-        const int rih = (p.y * g.W[p.h] + p.x) * g.B[p.h] + p.b;
-        stage[(size_t)unit * tr + my_base + my_rank] = make_float4(mine.x, mine.y, mine.z, __int_as_float(rih));
-    }
-    if (lane < 6) tcount[(size_t)unit * 8 + lane] = cnt_lane;
+    score_tile_records(g, q, tile, unit, lane, rec0, nrec, thresh, stage, tcount);
 }
 
 // One CTA per image: per head, the counts of the tiles that hold the image's records of that head go to shared memory
@@ -1136,6 +1026,10 @@ static ScoreTiles score_tiles(const Geo& g, const float* predicts, int n, float 
     q.tma = (((uintptr_t)predicts & 15u) == 0) ? 1 : 0;
     q.early = (thresh > 2.0f * g.lo) ? 1 : 0;
     return q;
+}
+
+ScoreTiles packed_score_tiles(const Geo& g, const float* predicts, int n, float thresh) {
+    return score_tiles(g, predicts, n, thresh);
 }
 
 // records per tile when every head tensor is swept on its own: the smallest of the three (a tile touches two images at most)

@@ -463,6 +463,70 @@ int yv3_filter_heads(const yv3_config* cfg, const float* const head_predicts[3],
                        stream);
 }
 
+int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
+                          int n_global, int rectified_active, float upstream, float* loss_out20, float* grad_predicts,
+                          void* loss_workspace, size_t loss_workspace_bytes, float score_thresh, float* cand,
+                          int32_t capacity, int32_t* counts, void* post_workspace, size_t post_workspace_bytes,
+                          int32_t* fused_out, int phases, void* stream) {
+    if ((phases & 7) == 0) return YV3_ERR_SHAPE;
+    int rc = loss_common_checks(cfg, predicts, targets, n, m, loss_workspace, loss_workspace_bytes);
+    if (rc != YV3_OK) return rc;
+    if (!loss_out20 || !grad_predicts || !cand || !counts) return YV3_ERR_NULL;
+    if (!aligned16(grad_predicts) || !aligned16(cand)) return YV3_ERR_ALIGN;
+    if (n_global < n) return YV3_ERR_SHAPE;
+    if ((long long)n * yv3_records_per_image(cfg) >= (1LL << 31)) return YV3_ERR_CAPACITY;
+    PostWs pws;
+    rc = post_checks(cfg, n, capacity, post_workspace, post_workspace_bytes, &pws);
+    if (rc != YV3_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const Geo g = make_geo(cfg);
+    Workspace ws = carve_workspace(loss_workspace, n, m, g.rpi);
+    DenseArgs d;
+    memset(&d, 0, sizeof(d));
+    d.predicts = predicts; d.grad = grad_predicts;
+    d.own = ws.own; d.img_terms = ws.img_terms; d.partials = ws.partials; d.status = ws.status;
+    d.objbits = ws.objbits; d.gtab = ws.gtab; d.vcount = ws.vcount;
+    d.detail = loss_out20;
+    d.n = n; d.m = m; d.n_global = n_global;
+    d.kappa = upstream / (float)n_global; d.upstream = upstream;
+    d.rect_active = rectified_active ? 1 : 0;
+    const char* dbg = getenv("YV3_DEBUG");
+    d.debug = dbg ? atoi(dbg) : 0;
+    d.vec_ok = (aligned16(predicts) && !(d.debug & 1)) ? 1 : 0;
+    const bool fused = fused_sweep_supported(g, d, n, score_thresh);
+    if (fused_out) *fused_out = fused ? 1 : 0;
+    if (!fused) {
+        // the two sweeps one after the other (unaligned tensors, records too long for a tile, more tiles than partial rows)
+        rc = yv3_loss_fwd_bwd(cfg, predicts, targets, n, m, n_global, rectified_active, upstream, loss_out20, grad_predicts,
+                              loss_workspace, loss_workspace_bytes, phases & 7, stream);
+        if (rc != YV3_OK) return rc;
+        const int fp = ((phases & 2) ? 1 : 0) | ((phases & 4) ? 2 : 0);
+        if (!fp) return YV3_OK;
+        return yv3_filter_packed(cfg, predicts, n, score_thresh, cand, capacity, counts, post_workspace, post_workspace_bytes,
+                                 fp, stream);
+    }
+    // 1: assignment (labels, object bits, owner terms); 2: the one sweep; 4: the two small tails (fold, gather)
+    if (phases & 1) {
+        rc = yv3_loss_fwd_bwd(cfg, predicts, targets, n, m, n_global, rectified_active, upstream, loss_out20, grad_predicts,
+                              loss_workspace, loss_workspace_bytes, 1, stream);
+        if (rc != YV3_OK) return rc;
+    }
+    int rows = packed_tile_count(g, predicts, n, score_thresh);
+    if (phases & 2) {
+        if (!cuda_ok(cudaMemsetAsync(pws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
+        if (!cuda_ok(launch_fused_sweep(g, d, n, score_thresh, pws.stage, pws.tcount, &rows, st), "launch_fused_sweep"))
+            return YV3_ERR_CUDA;
+    }
+    if (phases & 4) {
+        if (!cuda_ok(launch_loss_fold(g, d, rows, st), "launch_loss_fold")) return YV3_ERR_CUDA;
+        const float* pred[3] = {predicts, nullptr, nullptr};
+        if (!cuda_ok(launch_filter_packed(g, pred, false, n, score_thresh, cand, capacity, counts, pws.status, pws.stage,
+                                          pws.tcount, false, true, st), "launch_filter_packed"))
+            return YV3_ERR_CUDA;
+    }
+    return YV3_OK;
+}
+
 int yv3_filter_decoded(const yv3_config* cfg, const float* const decoded[3], const float* const boxes[3],
                        float score_thresh, float* cand, int32_t capacity, int32_t* counts, void* workspace,
                        size_t workspace_bytes, void* stream) {

@@ -61,6 +61,13 @@ struct DenseArgs {
 cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool sweep, bool fold, cudaStream_t stream, int* grid_out = nullptr);
 cudaError_t launch_loss_fold(const Geo& g, const DenseArgs& a, int nrows, cudaStream_t stream);
 
+// ---- fused_sweep.cu ----------------------------------------------------------------------------
+// score sweep + dense loss sweep on one read of the packed tensor (a: as for launch_loss_dense, grad required)
+int packed_tile_count(const Geo& g, const float* predicts, int n, float thresh);     // tiles (= partial rows) of the sweep
+bool fused_sweep_supported(const Geo& g, const DenseArgs& a, int n, float thresh);
+cudaError_t launch_fused_sweep(const Geo& g, DenseArgs a, int n, float thresh, float4* stage, int32_t* tcount,
+                               int* rows_out, cudaStream_t stream);
+
 // ---- decode.cu ---------------------------------------------------------------------------------
 struct DecodeArgs {
     const float* predicts;

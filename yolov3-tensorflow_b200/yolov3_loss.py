@@ -6,6 +6,7 @@ d loss / d predicts in a single pass, so ``loss()`` hands torch.autograd a ready
 """
 import ctypes
 
+import numpy as np
 import torch
 
 from . import _lib
@@ -109,7 +110,7 @@ class YOLOv3Loss(object):
         return t, p
 
     def _run(self, targets, predicts, want_grad, upstream=1.0, events=None, grad_out=None, sweep_after=None,
-             sweep_done=None, out=None):
+             sweep_done=None, out=None, fuse=None):
         t, p = self._prepare(targets, predicts)
         n, m = p.shape[0], t.shape[1] // 5
         world = self._world()
@@ -128,7 +129,44 @@ class YOLOv3Loss(object):
         args = (ctypes.byref(self._cfg), _lib.ptr(p), _lib.ptr(t), n, m, n_global, 1 if rect_active else 0,
                 float(upstream), _lib.ptr(out), _lib.ptr(grad), _lib.ptr(ws), ws.numel())
         stream = _lib.current_stream_ptr(p.device)
-        if sweep_after is not None or sweep_done is not None:
+        if fuse is not None:
+            # the loss and the post-process filter of the same predicts on one read of the tensor (fused_sweep.cu)
+            post, score_thresh, filter_out, before_tail, phases = fuse
+            if post.packed_floats_per_image != self.packed_floats_per_image:
+                raise ValueError("the post-processor was built for another head configuration")
+            pws = post._workspace(n, p.device)
+            if filter_out is None:
+                cand = torch.empty((n, post.capacity, 8), dtype=torch.float32, device=p.device)
+                counts = torch.empty((n, 3), dtype=torch.int32, device=p.device)
+            else:
+                cand, counts = filter_out
+            fused = ctypes.c_int32(0)
+            fargs = args + (float(np.float32(score_thresh)), _lib.ptr(cand), post.capacity, _lib.ptr(counts),
+                            _lib.ptr(pws), pws.numel(), ctypes.byref(fused))
+            if phases != 7:
+                _lib.check(self._lib.yv3_loss_filter_fused(*fargs, phases, stream), "yv3_loss_filter_fused[%d]" % phases)
+            elif events is None and before_tail is None:
+                _lib.check(self._lib.yv3_loss_filter_fused(*fargs, 7, stream), "yv3_loss_filter_fused")
+            else:
+                # (start, stop) events around the sweep alone; `before_tail`: an event (of another stream) the fold +
+                # gather tail waits for, e.g. the previous step's NMS still reading cand / counts
+                cur = torch.cuda.current_stream(p.device)
+                _lib.check(self._lib.yv3_loss_filter_fused(*fargs, 1, stream), "yv3_loss_filter_fused[assign]")
+                if events is not None:
+                    events[0].record()
+                _lib.check(self._lib.yv3_loss_filter_fused(*fargs, 2, stream), "yv3_loss_filter_fused[sweep]")
+                if events is not None:
+                    events[1].record()
+                if before_tail is not None:
+                    cur.wait_event(before_tail)
+                _lib.check(self._lib.yv3_loss_filter_fused(*fargs, 4, stream), "yv3_loss_filter_fused[tail]")
+            post._last_ws = pws
+            self.last_fused = bool(fused.value)
+            self._last_filter = (cand, counts)
+            if not phases & 4:
+                # a scheduler issuing the phases one by one: the step's bookkeeping belongs to its last phase
+                return None, grad
+        elif sweep_after is not None or sweep_done is not None:
             # a scheduler's hooks around the HBM-bound sweep: it starts after `sweep_after` (an event of another
             # stream) and `sweep_done` is recorded right behind it; the small assignment and fold kernels are free
             cur = torch.cuda.current_stream(p.device)
@@ -179,6 +217,23 @@ class YOLOv3Loss(object):
         row k of a (steps, 20) buffer that is all-reduced once for several steps)."""
         return self._run(targets, predicts, want_grad=True, upstream=upstream, events=events, grad_out=grad_out,
                          sweep_after=sweep_after, sweep_done=sweep_done, out=out)
+
+    def loss_grad_and_filter(self, targets, predicts, post, score_thresh, upstream=1.0, grad_out=None, out=None,
+                             filter_out=None, events=None, before_tail=None, phases=7):
+        """Evaluation while training: ``loss_and_grad`` and ``post.filter(predicts, score_thresh)`` (a
+        ``HeadPostProcessor`` of the same head configuration) in one call that reads the head tensor once
+        (``yv3_loss_filter_fused``).  Returns (total, grad, cand, counts); gradient, candidates and counts are
+        bit-identical to the two separate calls.  ``self.last_fused`` tells whether the one-sweep kernel ran or the call
+        fell back to the two sweeps (unaligned tensor, more than 32768 tiles).  ``post.nms(cand, counts, thr)``
+        follows as usual.  ``events`` = (start, stop) CUDA events recorded around the sweep alone; ``before_tail`` = an
+        event the fold + gather tail waits for (a scheduler's hook: the previous step's NMS on another stream).
+        ``phases`` (1 assignment, 2 sweep, 4 fold + gather; 7 = all): a scheduler may issue the three parts as three
+        calls with the same arguments on streams of its choice (bench.py runs the sweeps back to back on one stream and
+        everything small on another, two workspaces alternating); total is None until the call that includes phase 4."""
+        total, grad = self._run(targets, predicts, want_grad=True, upstream=upstream, grad_out=grad_out, out=out,
+                                events=events, fuse=(post, score_thresh, filter_out, before_tail, int(phases)))
+        cand, counts = self._last_filter
+        return total, grad, cand, counts
 
     def loss_and_grad_heads(self, targets, head_predicts, upstream=1.0, want_grad=True, grads_out=None):
         """The same loss on the three head tensors BEFORE yolov3_detector.py:80-85 packs them: ``head_predicts`` =
