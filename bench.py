@@ -263,6 +263,7 @@ def main():
     if args.overlap:
         # the block scheduler serves the high-priority stream first whenever an SM slot frees up
         post_stream = torch.cuda.Stream(priority=-1 if args.priority == "post" else 0)
+        aux_stream = torch.cuda.Stream(priority=-1 if args.priority == "post" else 0)       # fused schedule: assignment and fold
         if args.priority == "loss":
             torch.cuda.set_stream(torch.cuda.Stream(priority=-1))
 
@@ -294,11 +295,9 @@ def main():
         post.nms(cand, counts, w["nms_thresh"], out=keep)
 
     def fused_steps(count, events=None, outs=None):
-        """`count` complete steps with the one-sweep call.  Two streams, two (loss, post-process) workspace pairs
-        alternating by step: the HBM-bound sweeps run back to back on the current stream; everything small -- the
-        assignment of step k + 1, then fold + gather + sort + NMS of step k -- runs on the high-priority stream under
-        sweep k + 1 / k.  Order on the small stream: assign(k + 1), wait sweep(k), tail(k); so assign(k + 2), which
-        rewrites the workspace of step k, comes after tail(k), and sweep(k) only has to wait for assign(k)."""
+        """`count` complete steps with the one-sweep call (yv3_loss_filter_fused issued phase by phase), two (loss,
+        post-process) workspace pairs alternating by step: the HBM-bound sweeps run back to back on the current stream,
+        the small kernels under them on two other streams (see below).  Every step does all of its work."""
         thr = w["score_thresh"]
         cur = torch.cuda.current_stream()
         if post_stream is None or events is not None:
@@ -315,26 +314,40 @@ def main():
                                            filter_out=(cand, counts), phases=phases)[0]
 
         def assign(k):
-            with torch.cuda.stream(post_stream):
+            with torch.cuda.stream(aux_stream):
                 part(k, 1)
                 e = torch.cuda.Event()
-                e.record(post_stream)
+                e.record(aux_stream)
             return e
 
+        # three streams.  cur: the sweeps, back to back.  aux: fold(k) then assign(k + 2) -- the assignment rewrites the
+        # loss workspace step k used, so it follows that step's sweep and fold.  post: gather(k), sort, NMS(k); sweep(k + 2)
+        # rewrites the staging rows gather(k) reads, so it waits for that chain (long finished by then).
+        aux_stream.wait_stream(cur)
         post_stream.wait_stream(cur)
-        a_done = assign(0)
+        a_done = [assign(0), assign(1) if count > 1 else None]
+        g_done = [None, None]
         for k in range(count):
-            a_next = assign(k + 1) if k + 1 < count else None
-            cur.wait_event(a_done)
+            b = k & 1
+            cur.wait_event(a_done[b])
+            if g_done[b] is not None:
+                cur.wait_event(g_done[b])
             part(k, 2)
             swept = torch.cuda.Event()
             swept.record(cur)
             with torch.cuda.stream(post_stream):
                 post_stream.wait_event(swept)
+                part(k, 8)
+                pairs[b][1].nms(cand, counts, w["nms_thresh"], out=keep)
+                g_done[b] = torch.cuda.Event()
+                g_done[b].record(post_stream)
+            with torch.cuda.stream(aux_stream):
+                aux_stream.wait_event(swept)
                 total = part(k, 4)
-                pairs[k & 1][1].nms(cand, counts, w["nms_thresh"], out=keep)
-            a_done = a_next
+            if k + 2 < count:
+                a_done[b] = assign(k + 2)
         cur.wait_stream(post_stream)
+        cur.wait_stream(aux_stream)
         return total
 
     def steps(count, events=None, outs=None):
@@ -587,10 +600,10 @@ def main():
                        "l2": "inputs larger than L2: predicts %.0f MB + gradient %.0f MB per GPU vs 126 MB L2" % (
                            pd.numel() * 4 / 1e6, grad.numel() * 4 / 1e6),
                        "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image,
-                       "layout": args.layout, "fused_sweep": bool(args.fused), "serialize_sweeps": bool(args.serialize_sweeps), "launch": mode, "streams": 2 if args.overlap else 1,
+                       "layout": args.layout, "fused_sweep": bool(args.fused), "serialize_sweeps": bool(args.serialize_sweeps), "launch": mode, "streams": (3 if args.fused else 2) if args.overlap else 1,
                        "high_priority_stream": args.priority if args.overlap else None,
-                       "fused_schedule": "sweeps back to back on one stream; assignment of step k+1 and fold/gather/sort/NMS of step k on "
-                                         "the high-priority stream, two workspaces alternating" if (args.fused and args.overlap) else None,
+                       "fused_schedule": "three streams: sweeps back to back; fold of step k and assignment of step k+2; "
+                                         "gather/sort/NMS of step k (the last two at high priority); two workspaces alternating" if (args.fused and args.overlap) else None,
                        "stream_join": ("once per %d-step graph" % unroll if graph is not None else "once per timed region")
                        if (args.overlap and args.pipeline) else "every step"},
             "stage_ms": {kernel_name: dense_ms, ("fold_gather_sort_nms" if args.fused else "filter_plus_nms"): post_ms,

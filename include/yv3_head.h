@@ -205,8 +205,8 @@ int yv3_filter_heads(const yv3_config* cfg, const float* const head_predicts[3],
  * yv3_query_postprocess_workspace); grad_predicts is required.  cand / counts / grad_predicts and every integer
  * decision are bit-identical to the separate calls; the loss sums are folded per warp, so a detail value may differ
  * in its last bit.  Launches: assignment, the fused sweep, the fold, the gather.
- * phases: bit mask, 7 = the whole call; 1 = the assignment, 2 = the sweep, 4 = fold + gather, for a caller that times or
- * schedules them separately (same arguments, in that order).  Falls back to the two separate sweeps
+ * phases: bit mask, 15 = the whole call; 1 = the assignment, 2 = the sweep, 4 = the fold, 8 = the gather, for a caller that
+ * times them or puts them on streams of its choice (same arguments; 2 after 1, 4 and 8 after 2).  Falls back to the two separate sweeps
  * (same results) when the fused tile shape does not apply (predicts not 16-byte aligned, fewer than 32 records per
  * image, more than 32768 tiles per call); *fused_out (host, may be NULL) says which ran.  yv3_nms follows as usual. */
 int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,

@@ -678,7 +678,7 @@ def test_fused_call_falls_back_on_unaligned_predicts(yv3):
 
 
 def test_fused_call_issued_phase_by_phase(yv3):
-    """phases 1 (assignment), 2 (sweep), 4 (fold + gather) as three calls -- what a scheduler does to put them on
+    """phases 1 (assignment), 2 (sweep), 8 (gather), 4 (fold) as four calls -- what a scheduler does to put them on
     streams of its choice -- give the bits of the single call."""
     spec, p, t = _inputs("coco_96x64_c13", 4, 8)
     yv3.backend.set_epsilon(spec.eps)
@@ -691,7 +691,7 @@ def test_fused_call_issued_phase_by_phase(yv3):
     post_b = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
     grad_b = torch.empty_like(pd)
     out = torch.zeros(20, dtype=torch.float32, device="cuda")
-    for ph in (1, 2, 4):
+    for ph in (1, 2, 8, 4):
         total_b, _, cand_b, counts_b = b.loss_grad_and_filter(td, pd, post_b, 0.05, grad_out=grad_b, out=out, phases=ph)
         assert (total_b is None) == (ph != 4)
     b.check_status()

@@ -513,24 +513,14 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
 // rows t, t + T, ... in index order, in double; lanes fold by shuffles, warps through shared memory -- a fixed order,
 // hence a deterministic sum -- then the 18 detail values (:115-138) and their sum (:137).
 constexpr int kFoldThreads = 256;
-constexpr int kFoldThreadsWide = 1024;      // for the one-row-per-warp tables of the fused sweep (tens of thousands of rows)
-template <int kFoldThreads>
-__global__ void __launch_bounds__(kFoldThreads) loss_fold_kernel(const __grid_constant__ Geo g,
-                                                                 const __grid_constant__ DenseArgs a, int nrows) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+constexpr int kFoldWideCtas = 48;           // first level of the two-level fold (tables of tens of thousands of rows)
+
+// per-thread partial sums (double) -> the 18 detail values (:115-138) and their sum (:137): lanes fold by shuffles,
+// warps through shared memory, in a fixed order.  part[]: noobj 0..2, cls 3..5, rect 6..8, xy 9..11, wh 12..14, obj 15..17
+__device__ __forceinline__ void fold_tail(const Geo& g, const DenseArgs& a, double (&part)[18], int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
     constexpr int nwarps = kFoldThreads / 32;
     __shared__ double fold_s[nwarps][18];
-    double part[18];
-#pragma unroll
-    for (int k = 0; k < 18; ++k) part[k] = 0.0;
-#pragma unroll 4
-    for (int b = tid; b < nrows; b += kFoldThreads) {
-        const float4* row = reinterpret_cast<const float4*>(a.partials + (size_t)b * kPartialFloats);
-        const float4 r0 = __ldcg(row), r1 = __ldcg(row + 1), r2 = __ldcg(row + 2);
-        part[0] += (double)r0.x; part[1] += (double)r0.y; part[2] += (double)r0.z;      // noobj
-        part[3] += (double)r0.w; part[4] += (double)r1.x; part[5] += (double)r1.y;      // cls
-        part[6] += (double)r1.z; part[7] += (double)r1.w; part[8] += (double)r2.x;      // rect
-    }
     for (int i = tid; i < a.n; i += kFoldThreads) {
 #pragma unroll
         for (int k = 0; k < 9; ++k) part[9 + k] += (double)__ldcg(a.img_terms + (size_t)i * 9 + k);   // xy, wh, obj
@@ -546,7 +536,6 @@ __global__ void __launch_bounds__(kFoldThreads) loss_fold_kernel(const __grid_co
     __shared__ float fin[18];
     if (tid < 18) {
         const int row = tid / 3, h = tid - row * 3;       // rows: xy, wh, noobj, obj, cls, rect
-        // source column in part[]: noobj 0..2, cls 3..5, rect 6..8, xy 9..11, wh 12..14, obj 15..17
         const int src = (row == 0) ? 9 + h : (row == 1) ? 12 + h : (row == 2) ? h : (row == 3) ? 15 + h
                       : (row == 4) ? 3 + h : 6 + h;
         double acc = 0.0;
@@ -568,6 +557,81 @@ __global__ void __launch_bounds__(kFoldThreads) loss_fold_kernel(const __grid_co
     }
 }
 
+// rows b0, b0 + stride, ... < b1 of the partial table into part[0..8], in index order, in double
+__device__ __forceinline__ void fold_rows(const float* partials, int b0, int b1, int stride, double (&part)[18]) {
+#pragma unroll 4
+    for (int b = b0; b < b1; b += stride) {
+        const float4* row = reinterpret_cast<const float4*>(partials + (size_t)b * kPartialFloats);
+        const float4 r0 = __ldcg(row), r1 = __ldcg(row + 1), r2 = __ldcg(row + 2);
+        part[0] += (double)r0.x; part[1] += (double)r0.y; part[2] += (double)r0.z;      // noobj
+        part[3] += (double)r0.w; part[4] += (double)r1.x; part[5] += (double)r1.y;      // cls
+        part[6] += (double)r1.z; part[7] += (double)r1.w; part[8] += (double)r2.x;      // rect
+    }
+}
+
+// The fold of the per-CTA partial rows (the launch boundary orders it after every row is written): thread t takes
+// rows t, t + T, ... in index order, in double -- a fixed order, hence a deterministic sum.
+__global__ void __launch_bounds__(kFoldThreads) loss_fold_kernel(const __grid_constant__ Geo g,
+                                                                 const __grid_constant__ DenseArgs a, int nrows) {
+    double part[18];
+#pragma unroll
+    for (int k = 0; k < 18; ++k) part[k] = 0.0;
+    fold_rows(a.partials, threadIdx.x, nrows, kFoldThreads, part);
+    fold_tail(g, a, part, threadIdx.x);
+}
+
+// Two levels for long tables (one row per warp of the fused sweep: a single SM would spend 20 us pulling a megabyte
+// through its L2 port): CTA c folds its contiguous slice of rows into nine doubles (fixed order inside the CTA), the
+// last CTA to finish -- a ticket in status[1], zeroed with the status word by the assignment phase -- adds the slices
+// in index order and finishes like the one-level kernel.  The result does not depend on which CTA comes last.
+__global__ void __launch_bounds__(kFoldThreads) loss_fold_wide_kernel(const __grid_constant__ Geo g,
+                                                                      const __grid_constant__ DenseArgs a, int nrows,
+                                                                      double* __restrict__ slices) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int nwarps = kFoldThreads / 32;
+    __shared__ double lvl_s[nwarps][9];
+    __shared__ int last_s;
+    double part[18];
+#pragma unroll
+    for (int k = 0; k < 18; ++k) part[k] = 0.0;
+    const int per = (nrows + gridDim.x - 1) / gridDim.x;
+    const int b0 = blockIdx.x * per, b1 = min(b0 + per, nrows);
+    fold_rows(a.partials, b0 + tid, b1, kFoldThreads, part);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+        double x = part[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if (lane == 0) lvl_s[warp][k] = x;
+    }
+    __syncthreads();
+    if (tid < 9) {
+        double acc = 0.0;
+        for (int w = 0; w < nwarps; ++w) acc += lvl_s[w][tid];
+        slices[(size_t)blockIdx.x * 9 + tid] = acc;
+        __threadfence();
+    }
+    __syncthreads();
+    if (tid == 0) last_s = (atomicAdd((int*)a.status + 1, 1) == (int)gridDim.x - 1) ? 1 : 0;
+    __syncthreads();
+    if (!last_s) return;
+    __threadfence();
+#pragma unroll
+    for (int k = 0; k < 18; ++k) part[k] = 0.0;
+    // slices to shared memory in parallel (one load per thread), then thread 0 adds them in index order
+    __shared__ double all_s[kFoldWideCtas * 9];
+    for (int i = tid; i < (int)gridDim.x * 9; i += kFoldThreads) all_s[i] = __ldcg(slices + i);
+    __syncthreads();
+    if (tid == 0) {
+        for (int c = 0; c < (int)gridDim.x; ++c) {
+#pragma unroll
+            for (int k = 0; k < 9; ++k) part[k] += all_s[c * 9 + k];
+        }
+        ((int*)a.status)[1] = 0;                           // ready for a fold that is not preceded by the assignment
+    }
+    fold_tail(g, a, part, tid);
+}
+
 template <int VEC, int SGT, int ZW>
 static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, bool sweep, bool fold, cudaStream_t stream, int* grid_out) {
     a.bulk = (VEC && !ZW && g.L >= kWideL && !(a.debug & 64)) ? 1 : 0;
@@ -583,13 +647,13 @@ static cudaError_t launch_variant(const Geo& g, DenseArgs& a, int sm_count, bool
         if (err != cudaSuccess) return err;
     }
     if (grid_out) *grid_out = grid;
-    if (fold) loss_fold_kernel<kFoldThreads><<<1, kFoldThreads, 0, stream>>>(g, a, a.row_base + grid);      // the grid is a function of the arguments
+    if (fold) loss_fold_kernel<<<1, kFoldThreads, 0, stream>>>(g, a, a.row_base + grid);      // the grid is a function of the arguments
     return cudaGetLastError();
 }
 
 cudaError_t launch_loss_fold(const Geo& g, const DenseArgs& a, int nrows, cudaStream_t stream) {
-    if (nrows > 16 * kFoldThreads) loss_fold_kernel<kFoldThreadsWide><<<1, kFoldThreadsWide, 0, stream>>>(g, a, nrows);
-    else loss_fold_kernel<kFoldThreads><<<1, kFoldThreads, 0, stream>>>(g, a, nrows);
+    if (nrows > 16 * kFoldThreads && a.fold_slices) loss_fold_wide_kernel<<<kFoldWideCtas, kFoldThreads, 0, stream>>>(g, a, nrows, a.fold_slices);
+    else loss_fold_kernel<<<1, kFoldThreads, 0, stream>>>(g, a, nrows);
     return cudaGetLastError();
 }
 

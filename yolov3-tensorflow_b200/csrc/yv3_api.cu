@@ -468,7 +468,7 @@ int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const fl
                           void* loss_workspace, size_t loss_workspace_bytes, float score_thresh, float* cand,
                           int32_t capacity, int32_t* counts, void* post_workspace, size_t post_workspace_bytes,
                           int32_t* fused_out, int phases, void* stream) {
-    if ((phases & 7) == 0) return YV3_ERR_SHAPE;
+    if ((phases & 15) == 0) return YV3_ERR_SHAPE;
     int rc = loss_common_checks(cfg, predicts, targets, n, m, loss_workspace, loss_workspace_bytes);
     if (rc != YV3_OK) return rc;
     if (!loss_out20 || !grad_predicts || !cand || !counts) return YV3_ERR_NULL;
@@ -486,6 +486,7 @@ int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const fl
     d.predicts = predicts; d.grad = grad_predicts;
     d.own = ws.own; d.img_terms = ws.img_terms; d.partials = ws.partials; d.status = ws.status;
     d.objbits = ws.objbits; d.gtab = ws.gtab; d.vcount = ws.vcount;
+    d.fold_slices = ws.fold_slices;
     d.detail = loss_out20;
     d.n = n; d.m = m; d.n_global = n_global;
     d.kappa = upstream / (float)n_global; d.upstream = upstream;
@@ -499,13 +500,13 @@ int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const fl
         // the two sweeps one after the other (unaligned tensors, records too long for a tile, more tiles than partial rows)
         rc = yv3_loss_fwd_bwd(cfg, predicts, targets, n, m, n_global, rectified_active, upstream, loss_out20, grad_predicts,
                               loss_workspace, loss_workspace_bytes, phases & 7, stream);
-        if (rc != YV3_OK) return rc;
-        const int fp = ((phases & 2) ? 1 : 0) | ((phases & 4) ? 2 : 0);
+        if ((phases & 7) && rc != YV3_OK) return rc;
+        const int fp = ((phases & 2) ? 1 : 0) | ((phases & 8) ? 2 : 0);
         if (!fp) return YV3_OK;
         return yv3_filter_packed(cfg, predicts, n, score_thresh, cand, capacity, counts, post_workspace, post_workspace_bytes,
                                  fp, stream);
     }
-    // 1: assignment (labels, object bits, owner terms); 2: the one sweep; 4: the two small tails (fold, gather)
+    // 1: assignment (labels, object bits, owner terms); 2: the one sweep; 4, 8: the two small tails (fold, gather)
     if (phases & 1) {
         rc = yv3_loss_fwd_bwd(cfg, predicts, targets, n, m, n_global, rectified_active, upstream, loss_out20, grad_predicts,
                               loss_workspace, loss_workspace_bytes, 1, stream);
@@ -517,8 +518,8 @@ int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const fl
         if (!cuda_ok(launch_fused_sweep(g, d, n, score_thresh, pws.stage, pws.tcount, &rows, st), "launch_fused_sweep"))
             return YV3_ERR_CUDA;
     }
-    if (phases & 4) {
-        if (!cuda_ok(launch_loss_fold(g, d, rows, st), "launch_loss_fold")) return YV3_ERR_CUDA;
+    if ((phases & 4) && !cuda_ok(launch_loss_fold(g, d, rows, st), "launch_loss_fold")) return YV3_ERR_CUDA;
+    if (phases & 8) {
         const float* pred[3] = {predicts, nullptr, nullptr};
         if (!cuda_ok(launch_filter_packed(g, pred, false, n, score_thresh, cand, capacity, counts, pws.status, pws.stage,
                                           pws.tcount, false, true, st), "launch_filter_packed"))

@@ -269,6 +269,7 @@ struct Workspace {
     float* gtab;
     int32_t* vcount;
     float* partials;
+    double* fold_slices;    // [64][9] first level of the two-level fold
     size_t bytes;
 };
 constexpr int kMaxGrid = 32768;         // upper bound on CTAs of the dense pass
@@ -294,6 +295,8 @@ inline Workspace carve_workspace(void* base, int n, int m, long long rpi) {
     off = align_up(off + sizeof(int32_t) * (size_t)n, 256);
     w.partials = (float*)(p + off);
     off = align_up(off + sizeof(float) * kPartialFloats * kMaxGrid, 256);
+    w.fold_slices = (double*)(p + off);
+    off = align_up(off + sizeof(double) * 9 * 64, 256);
     w.bytes = off;
     return w;
 }

@@ -41,6 +41,7 @@ struct DenseArgs {
     const float* gtab;
     const int32_t* vcount;
     float* partials;
+    double* fold_slices;              // [64][9] first-level sums of the two-level fold (may be NULL: one level)
     int32_t* status;
     float* detail;                    // 20 floats: 18 detail values, their sum, pad
     int n, m, n_global;

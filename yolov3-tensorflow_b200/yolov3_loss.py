@@ -143,10 +143,10 @@ class YOLOv3Loss(object):
             fused = ctypes.c_int32(0)
             fargs = args + (float(np.float32(score_thresh)), _lib.ptr(cand), post.capacity, _lib.ptr(counts),
                             _lib.ptr(pws), pws.numel(), ctypes.byref(fused))
-            if phases != 7:
+            if phases != 15:
                 _lib.check(self._lib.yv3_loss_filter_fused(*fargs, phases, stream), "yv3_loss_filter_fused[%d]" % phases)
             elif events is None and before_tail is None:
-                _lib.check(self._lib.yv3_loss_filter_fused(*fargs, 7, stream), "yv3_loss_filter_fused")
+                _lib.check(self._lib.yv3_loss_filter_fused(*fargs, 15, stream), "yv3_loss_filter_fused")
             else:
                 # (start, stop) events around the sweep alone; `before_tail`: an event (of another stream) the fold +
                 # gather tail waits for, e.g. the previous step's NMS still reading cand / counts
@@ -159,7 +159,7 @@ class YOLOv3Loss(object):
                     events[1].record()
                 if before_tail is not None:
                     cur.wait_event(before_tail)
-                _lib.check(self._lib.yv3_loss_filter_fused(*fargs, 4, stream), "yv3_loss_filter_fused[tail]")
+                _lib.check(self._lib.yv3_loss_filter_fused(*fargs, 12, stream), "yv3_loss_filter_fused[tail]")
             post._last_ws = pws
             self.last_fused = bool(fused.value)
             self._last_filter = (cand, counts)
@@ -219,7 +219,7 @@ class YOLOv3Loss(object):
                          sweep_after=sweep_after, sweep_done=sweep_done, out=out)
 
     def loss_grad_and_filter(self, targets, predicts, post, score_thresh, upstream=1.0, grad_out=None, out=None,
-                             filter_out=None, events=None, before_tail=None, phases=7):
+                             filter_out=None, events=None, before_tail=None, phases=15):
         """Evaluation while training: ``loss_and_grad`` and ``post.filter(predicts, score_thresh)`` (a
         ``HeadPostProcessor`` of the same head configuration) in one call that reads the head tensor once
         (``yv3_loss_filter_fused``).  Returns (total, grad, cand, counts); gradient, candidates and counts are
@@ -227,9 +227,10 @@ class YOLOv3Loss(object):
         fell back to the two sweeps (unaligned tensor, more than 32768 tiles).  ``post.nms(cand, counts, thr)``
         follows as usual.  ``events`` = (start, stop) CUDA events recorded around the sweep alone; ``before_tail`` = an
         event the fold + gather tail waits for (a scheduler's hook: the previous step's NMS on another stream).
-        ``phases`` (1 assignment, 2 sweep, 4 fold + gather; 7 = all): a scheduler may issue the three parts as three
+        ``phases`` (1 assignment, 2 sweep, 4 fold, 8 gather; 15 = all): a scheduler may issue the parts as separate
         calls with the same arguments on streams of its choice (bench.py runs the sweeps back to back on one stream and
-        everything small on another, two workspaces alternating); total is None until the call that includes phase 4."""
+        the small kernels on two others, two workspaces alternating); total is None unless the call includes the fold,
+        which is also the call that does the step's bookkeeping (rectified counter, all-reduce, detail attributes)."""
         total, grad = self._run(targets, predicts, want_grad=True, upstream=upstream, grad_out=grad_out, out=out,
                                 events=events, fuse=(post, score_thresh, filter_out, before_tail, int(phases)))
         cand, counts = self._last_filter
