@@ -691,8 +691,11 @@ def test_fused_call_issued_phase_by_phase(yv3):
     post_b = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
     grad_b = torch.empty_like(pd)
     out = torch.zeros(20, dtype=torch.float32, device="cuda")
-    for ph in (1, 2, 8, 4):
-        total_b, _, cand_b, counts_b = b.loss_grad_and_filter(td, pd, post_b, 0.05, grad_out=grad_b, out=out, phases=ph)
+    cand_b = torch.empty((4, post_b.capacity, 8), dtype=torch.float32, device="cuda")
+    counts_b = torch.empty((4, 3), dtype=torch.int32, device="cuda")
+    for ph in (1, 2, 8, 4):              # the same caller-owned buffers in every call
+        total_b, _, _, _ = b.loss_grad_and_filter(td, pd, post_b, 0.05, grad_out=grad_b, out=out,
+                                                  filter_out=(cand_b, counts_b), phases=ph)
         assert (total_b is None) == (ph != 4)
     b.check_status()
     assert b.current_num == a.current_num == 4
