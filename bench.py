@@ -205,7 +205,7 @@ def main():
     ap.add_argument("--fused", type=int, default=1,
                     help="1 (packed layout): loss fwd+bwd and the post-process filter of a step in one call that reads the "
                          "head tensor once (yv3_loss_filter_fused); 0: the two sweeps as separate calls")
-    ap.add_argument("--graph-steps", type=int, default=8, help="steps captured per CUDA graph (N = 1)")
+    ap.add_argument("--graph-steps", type=int, default=16, help="steps captured per CUDA graph (N = 1)")
     ap.add_argument("--pipeline", type=int, default=1,
                     help="1: the two streams are joined once per graph / timed region, 0: after every step")
     ap.add_argument("--force-graph", action="store_true", help="skip the eager-vs-graph trial")
