@@ -208,7 +208,7 @@ int yv3_filter_heads(const yv3_config* cfg, const float* const head_predicts[3],
  * phases: bit mask, 15 = the whole call; 1 = the assignment, 2 = the sweep, 4 = the fold, 8 = the gather, for a caller that
  * times them or puts them on streams of its choice (same arguments; 2 after 1, 4 and 8 after 2).  Falls back to the two separate sweeps
  * (same results) when the fused tile shape does not apply (predicts not 16-byte aligned, fewer than 32 records per
- * image, more than 32768 tiles per call); *fused_out (host, may be NULL) says which ran.  yv3_nms follows as usual. */
+ * image, more than 262144 tiles of 32 records per call); *fused_out (host, may be NULL) says which ran.  yv3_nms follows as usual. */
 int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const float* targets, int n, int m,
                           int n_global, int rectified_active, float upstream, float* loss_out20, float* grad_predicts,
                           void* loss_workspace, size_t loss_workspace_bytes, float score_thresh, float* cand,

@@ -20,7 +20,7 @@ namespace yv3 {
 
 __global__ void __launch_bounds__(32) fused_sweep_kernel(const __grid_constant__ Geo g, const __grid_constant__ DenseArgs a,
                                                          const ScoreTiles q, float thresh, float4* __restrict__ stage,
-                                                         int32_t* __restrict__ tcount) {
+                                                         int32_t* __restrict__ tcount, int32_t* __restrict__ post_status) {
     extern __shared__ __align__(128) unsigned char ssm[];
     __shared__ uint64_t bar_s;
     const int L = g.L, C = g.C, m = a.m;
@@ -41,6 +41,8 @@ __global__ void __launch_bounds__(32) fused_sweep_kernel(const __grid_constant__
         }
     }
     const unsigned objw = __ldg(a.objbits + unit);     // rec0 is a multiple of 32: one word per tile
+    // the post-process status word starts clean with the sweep (the gather that may set bits in it comes after)
+    if (unit == 0 && lane < kStatusInts) post_status[lane] = 0;
     for (int i = (int)(bulk / 4) + lane; i < nfl; i += 32) tile[i] = __ldg(src + i);
     __syncwarp();                                      // barrier init visible to every lane
     if (bulk) mbar_wait(&bar_s, 0);
@@ -237,14 +239,14 @@ bool fused_sweep_supported(const Geo& g, const DenseArgs& a, int n, float thresh
 }
 
 cudaError_t launch_fused_sweep(const Geo& g, DenseArgs a, int n, float thresh, float4* stage, int32_t* tcount,
-                               int* rows_out, cudaStream_t stream) {
+                               int32_t* post_status, int* rows_out, cudaStream_t stream) {
     const ScoreTiles q = packed_score_tiles(g, a.predicts, n, thresh);
     a.total_rec = q.total_rec;
     a.num_chunks = q.num_tiles;
     const size_t smem = (size_t)q.tile_floats * 4;
     cudaError_t err = cudaFuncSetAttribute(fused_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
-    fused_sweep_kernel<<<q.num_tiles, 32, smem, stream>>>(g, a, q, thresh, stage, tcount);
+    fused_sweep_kernel<<<q.num_tiles, 32, smem, stream>>>(g, a, q, thresh, stage, tcount, post_status);
     if (rows_out) *rows_out = q.num_tiles;
     return cudaGetLastError();
 }

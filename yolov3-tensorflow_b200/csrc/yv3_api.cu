@@ -514,8 +514,7 @@ int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const fl
     }
     int rows = packed_tile_count(g, predicts, n, score_thresh);
     if (phases & 2) {
-        if (!cuda_ok(cudaMemsetAsync(pws.status, 0, sizeof(int32_t) * kStatusInts, st), "cudaMemsetAsync")) return YV3_ERR_CUDA;
-        if (!cuda_ok(launch_fused_sweep(g, d, n, score_thresh, pws.stage, pws.tcount, &rows, st), "launch_fused_sweep"))
+        if (!cuda_ok(launch_fused_sweep(g, d, n, score_thresh, pws.stage, pws.tcount, pws.status, &rows, st), "launch_fused_sweep"))
             return YV3_ERR_CUDA;
     }
     if ((phases & 4) && !cuda_ok(launch_loss_fold(g, d, rows, st), "launch_loss_fold")) return YV3_ERR_CUDA;

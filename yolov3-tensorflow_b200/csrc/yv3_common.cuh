@@ -272,7 +272,7 @@ struct Workspace {
     double* fold_slices;    // [64][9] first level of the two-level fold
     size_t bytes;
 };
-constexpr int kMaxGrid = 32768;         // upper bound on CTAs of the dense pass
+constexpr int kMaxGrid = 262144;        // rows of the partial-sum table: upper bound on CTAs of the dense pass / tiles of the fused sweep
 constexpr int kPartialFloats = 12;      // noobj[3], cls[3], rect[3], pad[3]
 
 __host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }

@@ -67,7 +67,7 @@ cudaError_t launch_loss_fold(const Geo& g, const DenseArgs& a, int nrows, cudaSt
 int packed_tile_count(const Geo& g, const float* predicts, int n, float thresh);     // tiles (= partial rows) of the sweep
 bool fused_sweep_supported(const Geo& g, const DenseArgs& a, int n, float thresh);
 cudaError_t launch_fused_sweep(const Geo& g, DenseArgs a, int n, float thresh, float4* stage, int32_t* tcount,
-                               int* rows_out, cudaStream_t stream);
+                               int32_t* post_status, int* rows_out, cudaStream_t stream);
 
 // ---- decode.cu ---------------------------------------------------------------------------------
 struct DecodeArgs {

@@ -224,7 +224,7 @@ class YOLOv3Loss(object):
         ``HeadPostProcessor`` of the same head configuration) in one call that reads the head tensor once
         (``yv3_loss_filter_fused``).  Returns (total, grad, cand, counts); gradient, candidates and counts are
         bit-identical to the two separate calls.  ``self.last_fused`` tells whether the one-sweep kernel ran or the call
-        fell back to the two sweeps (unaligned tensor, more than 32768 tiles).  ``post.nms(cand, counts, thr)``
+        fell back to the two sweeps (unaligned tensor, more than 262144 tiles).  ``post.nms(cand, counts, thr)``
         follows as usual.  ``events`` = (start, stop) CUDA events recorded around the sweep alone; ``before_tail`` = an
         event the fold + gather tail waits for (a scheduler's hook: the previous step's NMS on another stream).
         ``phases`` (1 assignment, 2 sweep, 4 fold, 8 gather; 15 = all): a scheduler may issue the parts as separate
