@@ -205,6 +205,9 @@ def main():
     ap.add_argument("--fused", type=int, default=1,
                     help="1 (packed layout): loss fwd+bwd and the post-process filter of a step in one call that reads the "
                          "head tensor once (yv3_loss_filter_fused); 0: the two sweeps as separate calls")
+    ap.add_argument("--fused-depth", type=int, default=3,
+                    help="workspace pairs the fused schedule alternates between (the assignment of step k + depth follows "
+                         "the fold of step k)")
     ap.add_argument("--graph-steps", type=int, default=16, help="steps captured per CUDA graph (N = 1)")
     ap.add_argument("--pipeline", type=int, default=1,
                     help="1: the two streams are joined once per graph / timed region, 0: after every step")
@@ -246,7 +249,7 @@ def main():
     post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
     # a second workspace pair for the fused schedule (steps alternate; the C ABI is re-entrant per workspace)
     pairs = [(loss, post)]
-    if args.fused:
+    for _ in range(max(args.fused_depth, 2) - 1 if args.fused else 0):
         pairs.append((yv3.YOLOv3Loss(rectified_coord_num=w["rect"], **spec.loss_args),
                       yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)))
 
@@ -309,6 +312,7 @@ def main():
         post-process) workspace pairs alternating by step: the HBM-bound sweeps run back to back on the current stream,
         the small kernels under them on two other streams (see below).  Every step does all of its work."""
         thr = w["score_thresh"]
+        depth = len(pairs)
         cur = torch.cuda.current_stream()
         if post_stream is None or events is not None:
             for k in range(count):
@@ -319,7 +323,7 @@ def main():
             return total
 
         def part(k, phases):
-            lo, po = pairs[k & 1]
+            lo, po = pairs[k % depth]
             return lo.loss_grad_and_filter(td, pd, po, thr, grad_out=grad, out=None if outs is None else outs[k],
                                            filter_out=(cand, counts), phases=phases)[0]
 
@@ -330,15 +334,17 @@ def main():
                 e.record(aux_stream)
             return e
 
-        # three streams.  cur: the sweeps, back to back.  aux: fold(k) then assign(k + 2) -- the assignment rewrites the
-        # loss workspace step k used, so it follows that step's sweep and fold.  post: gather(k), sort, NMS(k); sweep(k + 2)
-        # rewrites the staging rows gather(k) reads, so it waits for that chain (long finished by then).
+        # three streams, `depth` workspace pairs used round-robin.  cur: the sweeps, back to back.  aux: fold(k) then
+        # assign(k + depth) -- the assignment rewrites the loss workspace step k used, so it follows that step's sweep and
+        # fold.  post: gather(k), sort, NMS(k); sweep(k + depth) rewrites the staging rows gather(k) reads, so it waits for
+        # that chain (long finished by then).  depth 3 instead of 2 gives the fold -> assignment chain a whole extra sweep
+        # of slack before sweep(k + depth) needs it (measured 104.8 -> 99.6 us/step at cfg2; depth 4: 99.2).
         aux_stream.wait_stream(cur)
         post_stream.wait_stream(cur)
-        a_done = [assign(0), assign(1) if count > 1 else None]
-        g_done = [None, None]
+        a_done = [assign(j) if j < count else None for j in range(depth)]
+        g_done = [None] * depth
         for k in range(count):
-            b = k & 1
+            b = k % depth
             cur.wait_event(a_done[b])
             if g_done[b] is not None:
                 cur.wait_event(g_done[b])
@@ -354,8 +360,8 @@ def main():
             with torch.cuda.stream(aux_stream):
                 aux_stream.wait_event(swept)
                 total = part(k, 4)
-            if k + 2 < count:
-                a_done[b] = assign(k + 2)
+            if k + depth < count:
+                a_done[b] = assign(k + depth)
         cur.wait_stream(post_stream)
         cur.wait_stream(aux_stream)
         return total
@@ -613,7 +619,7 @@ def main():
                        "layout": args.layout, "fused_sweep": bool(args.fused), "serialize_sweeps": bool(args.serialize_sweeps), "launch": mode, "streams": (3 if args.fused else 2) if args.overlap else 1,
                        "high_priority_stream": args.priority if args.overlap else None,
                        "fused_schedule": "three streams: sweeps back to back; fold of step k and assignment of step k+2; "
-                                         "gather/sort/NMS of step k (the last two at high priority); two workspaces alternating" if (args.fused and args.overlap) else None,
+                                         "gather/sort/NMS of step k (the last two at high priority); %d workspaces alternating" % len(pairs) if (args.fused and args.overlap) else None,
                        "stream_join": ("once per %d-step graph" % unroll if graph is not None else "once per timed region")
                        if (args.overlap and args.pipeline) else "every step"},
             "stage_ms": {kernel_name: dense_ms, ("fold_gather_sort_nms" if args.fused else "filter_plus_nms"): post_ms,
