@@ -618,7 +618,7 @@ def main():
                        "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image,
                        "layout": args.layout, "fused_sweep": bool(args.fused), "serialize_sweeps": bool(args.serialize_sweeps), "launch": mode, "streams": (3 if args.fused else 2) if args.overlap else 1,
                        "high_priority_stream": args.priority if args.overlap else None,
-                       "fused_schedule": "three streams: sweeps back to back; fold of step k and assignment of step k+2; "
+                       "fused_schedule": "three streams: sweeps back to back; fold of step k and assignment of step k+depth; "
                                          "gather/sort/NMS of step k (the last two at high priority); %d workspaces alternating" % len(pairs) if (args.fused and args.overlap) else None,
                        "stream_join": ("once per %d-step graph" % unroll if graph is not None else "once per timed region")
                        if (args.overlap and args.pipeline) else "every step"},
