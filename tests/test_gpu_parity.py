@@ -704,3 +704,36 @@ def test_fused_call_issued_phase_by_phase(yv3):
     for i in range(4):
         k = int(counts_a[i].sum().item())
         assert torch.equal(cand_a[i, :k], cand_b[i, :k])
+
+
+def test_fused_entry_point_rejects_bad_arguments(yv3):
+    """yv3_loss_filter_fused through the C ABI: no gradient buffer, an empty phase mask, a post-process workspace that is
+    too small, and a post-processor of another head configuration on the host side."""
+    import ctypes
+    from yolov3_tensorflow_b200 import _lib
+    spec, p, t = _inputs("coco_64x96_c4", 2, 4)
+    n = p.shape[0]
+    pd, td = torch.from_numpy(p).cuda(), torch.from_numpy(t).cuda()
+    loss = yv3.YOLOv3Loss(**product_loss_args(spec))
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    ws, pws = loss._workspace(n, 4, pd.device), post._workspace(n, pd.device)
+    out = torch.empty(20, device="cuda")
+    grad = torch.empty_like(pd)
+    cand = torch.empty((n, post.capacity, 8), device="cuda")
+    counts = torch.empty((n, 3), dtype=torch.int32, device="cuda")
+    fused = ctypes.c_int32(-1)
+
+    def call(grad_ptr, pws_bytes, phases):
+        return _lib.lib().yv3_loss_filter_fused(ctypes.byref(loss._cfg), _lib.ptr(pd), _lib.ptr(td), n, 4, n, 0, 1.0,
+                                                _lib.ptr(out), grad_ptr, _lib.ptr(ws), ws.numel(), 0.3, _lib.ptr(cand),
+                                                post.capacity, _lib.ptr(counts), _lib.ptr(pws), pws_bytes,
+                                                ctypes.byref(fused), phases, None)
+
+    assert call(None, pws.numel(), 15) == _lib.YV3_ERR_NULL
+    assert call(_lib.ptr(grad), pws.numel(), 0) == _lib.YV3_ERR_SHAPE
+    assert call(_lib.ptr(grad), 1024, 15) == _lib.YV3_ERR_WORKSPACE
+    assert call(_lib.ptr(grad), pws.numel(), 15) == _lib.YV3_OK and fused.value == 1
+    torch.cuda.synchronize()
+    other = make_spec("coco_64_c20")
+    with pytest.raises(ValueError):
+        loss.loss_grad_and_filter(td, pd, yv3.HeadPostProcessor(other.head_grid_sizes, other.class_num, other.anchor_boxes), 0.3)

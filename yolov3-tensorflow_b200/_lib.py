@@ -21,6 +21,7 @@ YV3_OK = 0
 YV3_ERR_NULL = -1
 YV3_ERR_SHAPE = -2
 YV3_ERR_ALIGN = -4
+YV3_ERR_WORKSPACE = -5
 YV3_ERR_GT_RANGE = -8
 YV3_ERR_NONFINITE = -9
 YV3_ERR_CAPACITY = -7
