@@ -12,10 +12,13 @@ Follows, line by line:
               :225-252 (_get_valid_target), :254-303 (_calc_iou), :305-369 (_single_head_loss)
   epsilon     run.py:26   padding  dataset/file_util.py:97
 
-Parity status: **parity unpinned** -- TensorFlow cannot be imported here and the
-reference has no tests/golden vectors for these functions.  TF op semantics assumed
-are listed in SURVEY.md Appendix B (clip gradient inclusive, argmax first index,
-softmax = exp(x-max) * (1/sum), python scalars rounded once to the tensor dtype).
+Parity status: **pinned** -- tests/test_oracle_pinned.py holds this file to tests/golden/loss_*.npz, the outputs of
+the reference's own yolov3_loss.py / yolov3_decoder.py / label_decoder.py run unmodified under the torch-backed
+``tensorflow`` stand-in (oracle/tf_standin, generator tests/golden/make_loss_golden.py): integer decisions and masks
+bit for bit, fp32 values to the ulp differences of NumPy's vs torch's exp/log and summation order, fp64 <= 1e-12.
+What stays assumed about TensorFlow itself is listed in oracle/tf_standin/tensorflow/__init__.py (A1-A6) and
+SURVEY.md Appendix B (clip gradient inclusive, argmax first index, softmax = exp(x-max) * (1/sum), python scalars
+rounded once to fp32).
 """
 import numpy as np
 
@@ -55,14 +58,19 @@ def packed_offset(spec: HeadSpec, n, h, y, x, b, ch):
 
 
 # --------------------------------------------------------------------------- decode
+def _const(v, dtype):
+    """a graph constant: rounded once to fp32 (convert_to_tensor(v, float32)), then widened for the fp64 twin."""
+    return np.asarray(v, dtype=np.float32).astype(dtype)[()]
+
+
 def _sigmoid(x):
     one = x.dtype.type(1)
     return one / (one + np.exp(-x))
 
 
 def clip_bounds(spec: HeadSpec, dtype):
-    """python floats eps and 1-eps rounded once to the tensor dtype (Appendix B)."""
-    return dtype(spec.eps), dtype(1.0 - spec.eps)
+    """python floats eps and 1-eps rounded once to fp32 (Appendix B), widened in the fp64 twin."""
+    return dtype(np.float32(spec.eps)), dtype(np.float32(1.0 - spec.eps))
 
 
 def decode_head(raw, spec: HeadSpec, h, dtype=np.float32):
@@ -184,8 +192,9 @@ def single_image(dec, lab, spec: HeadSpec, dtype):
 
     loss = np.zeros((5, 3), dtype)
     decisions = dict(valid_index=vidx.astype(np.int32), heads=[])
-    lw = np.asarray(spec.loss_weights, dtype=dtype)                          # (3,5): xy, wh, noobj, obj, cls
-    thresh = dtype(spec.iou_thresh)
+    lw = _const(spec.loss_weights, dtype)                                    # (3,5): xy, wh, noobj, obj, cls
+    thresh = _const(spec.iou_thresh, dtype)
+    gamma, alpha = _const(spec.focal_gamma, dtype), _const(spec.focal_alpha, dtype)
     for h in range(3):
         p = per_head[h]
         H, W = spec.head_grid_sizes[h]
@@ -201,13 +210,13 @@ def single_image(dec, lab, spec: HeadSpec, dtype):
         with np.errstate(divide="ignore", invalid="ignore"):
             noobj = -np.log(one - conf)                                      # :335
             if spec.is_focal_loss:
-                noobj = noobj * np.power(conf, dtype(spec.focal_gamma))      # :337
+                noobj = noobj * np.power(conf, gamma)      # :337
             noobj_l = lw[h, 2] * np.sum(noobj * bg.astype(dtype))            # :338
             rt = p["tgt"][pos]                                               # :341
             rp = decoded[rows, cols, best]                                   # :342 (R,L)
             objl = -np.log(rp[:, 4])                                         # :344
             if spec.is_focal_loss:
-                objl = objl * (np.power(one - rp[:, 4], dtype(spec.focal_gamma)) * dtype(spec.focal_alpha))  # :346
+                objl = objl * (np.power(one - rp[:, 4], gamma) * alpha)  # :346
             obj_l = lw[h, 3] * np.sum(objl)                                  # :347
             scale = (dtype(2) - rt[:, 2] * rt[:, 3] / dtype(H * W))[:, None]  # :350
             cint = np.floor(rt[:, 0:2])                                      # :352
@@ -261,7 +270,7 @@ def loss(targets, predicts, spec: HeadSpec, rectified_active=False, dtype=np.flo
     detail = np.zeros((6, 3), dtype)
     detail[:5] = mean
     if rectified_active:                                                     # :125-134, :140-164
-        rw = np.asarray(spec.rectified_loss_weight, dtype=dtype)
+        rw = _const(spec.rectified_loss_weight, dtype)
         for h in range(3):
             per_img = np.sum(np.square(dec[h][0]).reshape(n, -1), axis=1)    # :153-155
             detail[5, h] = rw[h] * (np.sum(per_img) / dtype(n))              # :157-162
@@ -281,10 +290,10 @@ def loss_grad(targets, predicts, spec: HeadSpec, rectified_active=False, upstrea
     dec = decode(predicts, spec, dtype)
     lab = label_decode(targets, spec, dtype)
     lo, hi = clip_bounds(spec, dtype)
-    lw = np.asarray(spec.loss_weights, dtype=dtype)
-    rw = np.asarray(spec.rectified_loss_weight, dtype=dtype)
+    lw = _const(spec.loss_weights, dtype)
+    rw = _const(spec.rectified_loss_weight, dtype)
     kappa = dtype(upstream) / dtype(n)
-    gam, alpha = dtype(spec.focal_gamma), dtype(spec.focal_alpha)
+    gam, alpha = _const(spec.focal_gamma, dtype), _const(spec.focal_alpha, dtype)
     one = dtype(1)
     grads = [np.zeros_like(r) for r in raws]
     for h in range(3):

@@ -12,7 +12,12 @@ yolov3/yolov3_loss.py:81-369.  TF semantics mirrored:
 ``torch.argmax`` = first index, ``amax`` splits ties like reduce_max's gradient,
 advanced-index gather backward accumulates duplicates like gather_nd's.
 
-Parity status: **parity unpinned** (no TensorFlow here, no reference fixtures).
+Parity status: **pinned** -- tests/test_oracle_pinned.py holds this file to tests/golden/loss_*.npz, the outputs of the
+reference's own yolov3_loss.py / yolov3_decoder.py / label_decoder.py run unmodified under the torch-backed ``tensorflow``
+stand-in (oracle/tf_standin, tests/golden/make_loss_golden.py): fp32 forward bit for bit, fp64 twin <= 1e-12.  What stays
+assumed about TensorFlow itself is listed in oracle/tf_standin/tensorflow/__init__.py (A1-A6).
+Graph constants (eps, 1-eps, anchors, loss weights, iou_thresh, focal alpha/gamma, rectified weights) are rounded to
+fp32 once and widened in the fp64 twin: the twin is "the fp32 graph's constants and inputs, exact arithmetic".
 Also used, timed, as bench.py's ``cpu_baseline`` / ``--impl reference`` arm.
 """
 import torch
@@ -30,29 +35,65 @@ def unpack(predicts, spec: HeadSpec):
     return out
 
 
-def _const(x, ref):
-    return torch.tensor(x, dtype=ref.dtype)
+def _const(x, dt):
+    """a graph constant: rounded once to fp32 (ops.convert_to_tensor(v, dtype=float32)), then widened for the twin."""
+    return torch.tensor(x, dtype=torch.float32).to(dt)
+
+
+class _Sigmoid(torch.autograd.Function):
+    """tf.sigmoid: 1 / (1 + exp(-x)); registered gradient dy * y * (1 - y) (math_grad._SigmoidGrad)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        one = torch.ones((), dtype=x.dtype)
+        y = one / (one + torch.exp(-x))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return dy * (y * (1 - y))
+
+
+class _Softmax(torch.autograd.Function):
+    """tf.nn.softmax: exp(x - max x) * (1 / sum); registered gradient (dy - sum(dy * y)) * y (nn_grad._SoftmaxGrad)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        e = torch.exp(x - torch.amax(x, dim=-1, keepdim=True))
+        y = e * (torch.ones((), dtype=x.dtype) / torch.sum(e, dim=-1, keepdim=True))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return (dy - torch.sum(dy * y, dim=-1, keepdim=True)) * y
+
+
+def _clip(x, lo, hi):
+    """tf.clip_by_value = maximum(minimum(x, hi), lo); at equality the gradient goes to x (math_grad._MaximumMinimumGrad)."""
+    x = torch.where(x <= hi, x, hi)
+    return torch.where(x >= lo, x, lo)
 
 
 def decode_head(raw, spec: HeadSpec, h):
     H, W = spec.head_grid_sizes[h]
     dt = raw.dtype
-    lo = torch.tensor(spec.eps, dtype=dt)
-    hi = torch.tensor(1.0 - spec.eps, dtype=dt)
-    anchors = torch.tensor(spec.anchor_boxes[h], dtype=torch.float32).to(dt) * torch.tensor([W, H], dtype=dt)
+    lo = _const(spec.eps, dt)
+    hi = _const(1.0 - spec.eps, dt)
+    anchors = _const(spec.anchor_boxes[h], dt) * torch.tensor([W, H], dtype=dt)
     ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
     lt = torch.stack([xs, ys], dim=-1).reshape(H, W, 1, 2).to(dt)
-    one = torch.ones((), dtype=dt)
-    xy = torch.clamp(one / (one + torch.exp(-raw[..., 0:2])), lo, hi) + lt
+    xy = _clip(_Sigmoid.apply(raw[..., 0:2]), lo, hi) + lt
     wh = torch.exp(raw[..., 2:4]) * anchors
-    conf = torch.clamp(one / (one + torch.exp(-raw[..., 4:5])), lo, hi)
+    conf = _clip(_Sigmoid.apply(raw[..., 4:5]), lo, hi)
     parts = [xy, wh, conf]
     if spec.class_num >= 1:
         z = raw[..., 5:]
-        z = z - torch.amax(z, dim=-1, keepdim=True)
-        e = torch.exp(z - torch.amax(z, dim=-1, keepdim=True))
-        q = e * (one / torch.sum(e, dim=-1, keepdim=True))
-        parts.append(torch.clamp(q, lo, hi))
+        z = z - torch.amax(z, dim=-1, keepdim=True)                     # yolov3_decoder.py:189-190
+        parts.append(_clip(_Softmax.apply(z), lo, hi))                  # :190-191
     decoded = torch.cat(parts, dim=-1)
     half = wh / 2
     return decoded, torch.cat([xy - half, xy + half], dim=-1)
@@ -117,7 +158,8 @@ def _single_image(dec, lab, spec: HeadSpec):
         heads.append((tgt, max_iou, rho, rows, cols, best))
     rhos = [hd[2] for hd in heads]
     out = []
-    lw = torch.tensor(spec.loss_weights, dtype=dt)
+    lw = _const(spec.loss_weights, dt)
+    gamma, alpha = _const(spec.focal_gamma, dt), _const(spec.focal_alpha, dt)
     one = torch.ones((), dtype=dt)
     for h in range(3):
         tgt, max_iou, rho, rows, cols, best = heads[h]
@@ -127,18 +169,18 @@ def _single_image(dec, lab, spec: HeadSpec):
         rows, cols, best = rows[pos], cols[pos], best[pos]
         obj = torch.zeros((H, W, spec.box_num[h]), dtype=dt)
         obj[rows, cols, best] = 1.0
-        bg = (max_iou < torch.tensor(spec.iou_thresh, dtype=dt)).to(dt) * (one - obj)
+        bg = (max_iou < _const(spec.iou_thresh, dt)).to(dt) * (one - obj)
         pred = dec[h][0]
         conf = pred[..., 4]
         noobj = -torch.log(one - conf)
         if spec.is_focal_loss:
-            noobj = noobj * torch.pow(conf, spec.focal_gamma)
+            noobj = noobj * torch.pow(conf, gamma)
         noobj_l = lw[h, 2] * torch.sum(noobj * bg)
         rt = tgt[pos]
         rp = pred[rows, cols, best]
         objl = -torch.log(rp[:, 4])
         if spec.is_focal_loss:
-            objl = objl * (torch.pow(one - rp[:, 4], spec.focal_gamma) * spec.focal_alpha)
+            objl = objl * (torch.pow(one - rp[:, 4], gamma) * alpha)
         obj_l = lw[h, 3] * torch.sum(objl)
         scale = (2 - rt[:, 2] * rt[:, 3] / (H * W)).unsqueeze(-1)
         cint = torch.floor(rt[:, 0:2])
@@ -170,7 +212,7 @@ def loss(targets, predicts, spec: HeadSpec, rectified_active=False):
     mean = torch.mean(torch.stack(per_image, dim=0), dim=0)
     rect = torch.zeros((1, 3), dtype=predicts.dtype)
     if rectified_active:
-        rw = spec.rectified_loss_weight
+        rw = _const(list(spec.rectified_loss_weight), predicts.dtype)
         rect = torch.stack([rw[h] * torch.mean(torch.sum(torch.square(dec[h][0]), dim=[1, 2, 3, 4]), dim=0, keepdim=True)
                             for h in range(3)], dim=-1)
         total = torch.sum(torch.cat([mean, rect], dim=0))
