@@ -244,14 +244,22 @@ def save_case(name, spec_name, p, t, rects, spec=None, seeds=None, note="", samp
             save[f"per_image{tag}{sfx}"] = r["per_image"]
         if rect == rects[0]:
             save.update(decisions_arrays(spec, r32["rec"], n, t))
+            d32 = decisions_arrays(spec, r32["rec"], n, t)
             d64 = decisions_arrays(spec, r64["rec"], n, t)
             save["dec_rho64"], save["dec_margin_best"] = d64["dec_rho"], d64["dec_margin_best"]     # margins from the fp64 twin
+            # does the fp64 twin take the same discrete decisions?  (a label centre within an fp32 ulp of a cell border
+            # lands in another cell in fp64: then only the fp32 run is a valid target for VALUES)
+            meta["twin_agrees"] = bool(all(np.array_equal(d32[k], d64[k]) for k in
+                                           ("dec_rows", "dec_cols", "dec_best", "dec_own", "obj_bits0", "obj_bits1", "obj_bits2",
+                                            "bg_bits0", "bg_bits1", "bg_bits2")))
         meta[f"current_num_after{sfx}"] = r32["current_num"]
     save["meta"] = np.array(json.dumps(meta))
     path = os.path.join(HERE, f"loss_{name}.npz")
     np.savez_compressed(path, **save)
-    print("%-34s n=%d total32=%s  nnz grad=%d  %.0f KB" % (name, n, [float(save[f"total32_rect{int(r)}"]) for r in rects],
-                                                          len(idx), os.path.getsize(path) / 1024))
+    print("%-34s n=%d total32=%s  nnz grad=%d  %.0f KB  twin_agrees=%s" % (
+        name, n, [float(save[f"total32_rect{int(r)}"]) for r in rects], len(idx), os.path.getsize(path) / 1024,
+        meta["twin_agrees"]))
+    return meta
 
 
 # ------------------------------------------------------------------------------------------------ label pipeline
@@ -323,13 +331,26 @@ def border_labels(spec, n, m, seed):
     rng = np.random.default_rng(seed)
     t = np.full((n, m, 5), -1.0, np.float32)
     (H8, W8), (H16, W16), (H32, W32) = spec.head_grid_sizes
+
+    def same_cell_in_both(k, W):
+        """fl32(k / W) * W lands in the same cell of all three grids whether the product is rounded to fp32 or not
+        (the other kind -- fp32 says cell k, exact arithmetic k - 1 -- is the demo set's x = 232/480 label)"""
+        v = np.float32(k / W)
+        return all(np.floor(np.float32(v * np.float32(g))) == np.floor(np.float64(v) * g) for g in (W8, W16, W32))
+
     for i in range(n):
         for j in range(m - 2):
             W, H = [(W8, H8), (W16, H16), (W32, H32)][j % 3]
-            kx, ky = int(rng.integers(1, W)), int(rng.integers(1, H))
+            while True:
+                kx, ky = int(rng.integers(1, W)), int(rng.integers(1, H))
+                if same_cell_in_both(kx, W) and same_cell_in_both(ky, H):
+                    break
             w, h = rng.uniform(0.03, 0.3, 2)
             t[i, j] = [np.float32(kx / W), np.float32(ky / H), w, h, int(rng.integers(0, max(spec.class_num, 1)))]
-        t[i, m - 2] = [np.float32((W8 - 1) / W8), np.float32((H8 - 1) / H8), 0.02, 0.02, 0]     # c = W8 - 1 (75 at 608)
+        k = W8 - 1
+        while not same_cell_in_both(k, W8):
+            k -= 1
+        t[i, m - 2] = [np.float32(k / W8), np.float32(k / H8), 0.02, 0.02, 0]     # the last /8 columns (c = 75 at 608)
     return t.reshape(n, m * 5)
 
 
@@ -377,8 +398,10 @@ def main(only=None):
     if want("coco_608_c80"):
         spec = make_spec("coco_608_c80")
         p = make_predicts(spec, 2, seed=41)
-        save_case("coco_608_c80", "coco_608_c80", p, border_labels(spec, 2, 12, 42), [False], seeds=dict(predicts=41, targets=42),
-                  note="centres exactly on /8, /16, /32 cell borders; one label in the last /8 column (c = 75)")
+        meta = save_case("coco_608_c80", "coco_608_c80", p, border_labels(spec, 2, 12, 42), [False],
+                         seeds=dict(predicts=41, targets=42),
+                         note="centres exactly on /8, /16, /32 cell borders; one label in the last /8 columns (c = 75)")
+        assert meta["twin_agrees"]
     # BASELINE configs[4]: 512^2, class_num 0, three anchors per head, focal + rectified
     if want("single_512"):
         spec = make_spec("single_512_c0_focal")

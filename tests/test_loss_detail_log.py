@@ -21,12 +21,14 @@ def test_console_values_follow_the_reference_order():
     assert len(v) == 24
 
 
-def test_console_text_hides_small_numbers_like_the_reference():
+def test_console_text_switches_format_for_small_numbers_like_the_reference():
     from yolov3_tensorflow_b200 import format_detail
     text = format_detail(_detail())
-    assert text.startswith(" - head: /8:\n - xy_loss: 0.5000 - wh_loss: 1.5000 - noobj_iou_loss: 10.0000")
-    assert "rectified_loss" not in text                 # 0.0 is not > 1e-3 (logger_callback.py:133)
-    assert " - head: /32:\n - wh_loss: 3.5000" in text   # the /32 xy term (0.0005) is dropped
+    # logger_callback.py:130-136: > 1e-3 as %.4f, everything else as %.4e -- nothing is dropped
+    assert text.startswith(" - head: /8:\n - rectified_loss: 0.0000e+00 - xy_loss: 0.5000 - wh_loss: 1.5000"
+                           " - noobj_iou_loss: 10.0000")
+    assert " - head: /32:\n - rectified_loss: 0.0000e+00 - xy_loss: 5.0000e-04 - wh_loss: 3.5000" in text
+    assert text.count("rectified_loss") == 3
 
 
 def test_board_scalars_names():

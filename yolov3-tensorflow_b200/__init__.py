@@ -9,6 +9,7 @@ structures) over the C-ABI library ``lib/libyv3head.so`` (include/yv3_head.h):
     YOLOv3Loss           yolov3/yolov3_loss.py   (forward + analytic backward, fused)
     YOLOv3PostProcessor  yolov3/yolov3_post_process.py
     HeadPostProcessor    batched device-resident filter + NMS (the run.py:59-74 loop as one call)
+    FusedPipeline        loss fwd+bwd + filter + NMS of consecutive steps on three streams (what bench.py times)
     backend              keras.backend.epsilon() / set_epsilon()
     configs              the configs.py switches the path consumes
 """
@@ -20,6 +21,7 @@ from .loss_detail_log import detail_log_values, detail_scalars, format_detail  #
 from .yolov3_decoder import YOLOv3Decoder  # noqa: F401
 from .yolov3_loss import YOLOv3Loss  # noqa: F401
 from .yolov3_post_process import HeadPostProcessor, YOLOv3PostProcessor  # noqa: F401
+from .pipeline import FusedPipeline  # noqa: F401
 
-__all__ = ["YOLOv3Decoder", "LabelDecoder", "LabelBatcher", "parse_label_line", "read_label_file", "YOLOv3Loss", "YOLOv3PostProcessor", "HeadPostProcessor", "backend", "to_device",
+__all__ = ["YOLOv3Decoder", "LabelDecoder", "LabelBatcher", "parse_label_line", "read_label_file", "YOLOv3Loss", "YOLOv3PostProcessor", "HeadPostProcessor", "FusedPipeline", "backend", "to_device",
            "detail_log_values", "detail_scalars", "format_detail"]

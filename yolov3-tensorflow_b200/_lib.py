@@ -106,9 +106,10 @@ def lib():
         path = _build.build_library()          # raises when nvcc is absent: no fallback path exists
     else:
         try:
-            path = _build.build_library()      # rebuild only if sources are newer
-        except Exception:
+            path = _build.build_library()      # rebuild only if the sources changed (file lock: safe under torchrun)
+        except _build.NvccMissing:
             pass                                # no compiler on this box: use the shipped .so
+        # a compile or link FAILURE propagates: an old .so that no longer matches the sources must not load silently
     handle = ctypes.CDLL(path)
     for name, (res, args) in _SIGNATURES.items():
         fn = getattr(handle, name)             # AttributeError = header and library disagree

@@ -50,33 +50,58 @@ def _stale():
         return f.read().strip() != _fingerprint()
 
 
+class NvccMissing(RuntimeError):
+    pass
+
+
 def build_library(force=False, verbose=False):
-    """Compile the library if it is missing or older than its sources.  Returns its path."""
+    """Compile the library if it is missing or its sources changed.  Returns its path.  Safe when several processes
+    (the ranks of one torchrun) call it at once: the build runs under an exclusive file lock, objects and the library
+    are written under temporary names and moved into place, and a rank that waited for the lock finds a fresh stamp."""
+    import fcntl
     if not force and not _stale():
         return LIB_PATH
     os.makedirs(LIB_DIR, exist_ok=True)
-    nvcc = _nvcc()
+    with open(os.path.join(LIB_DIR, ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not _stale():          # another process built it while this one waited
+                return LIB_PATH
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose):
+    try:
+        nvcc = _nvcc()
+    except RuntimeError as e:
+        raise NvccMissing(str(e))
     objs = []
     log = []
+    tag = ".tmp%d" % os.getpid()
     for src in SOURCES:
         obj = os.path.join(LIB_DIR, src.replace(".cu", ".o"))
-        cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj + tag]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log.append("$ " + " ".join(cmd) + "\n" + r.stdout + r.stderr)
         if r.returncode != 0:
             sys.stderr.write(log[-1])
             raise RuntimeError("nvcc failed on %s" % src)
+        os.replace(obj + tag, obj)
         objs.append(obj)
-    cmd = [nvcc, "-shared", "-o", LIB_PATH] + objs + ["-lcudart"]
+    cmd = [nvcc, "-shared", "-o", LIB_PATH + tag] + objs + ["-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log.append("$ " + " ".join(cmd) + "\n" + r.stdout + r.stderr)
     if r.returncode != 0:
         sys.stderr.write(log[-1])
         raise RuntimeError("link failed")
+    os.replace(LIB_PATH + tag, LIB_PATH)
     with open(os.path.join(LIB_DIR, "build.log"), "w") as f:
         f.write("\n".join(log))
-    with open(os.path.join(LIB_DIR, "build.hash"), "w") as f:
+    with open(os.path.join(LIB_DIR, "build.hash" + tag), "w") as f:
         f.write(_fingerprint())
+    os.replace(os.path.join(LIB_DIR, "build.hash" + tag), os.path.join(LIB_DIR, "build.hash"))
     if verbose:
         print("\n".join(log))
     return LIB_PATH

@@ -117,6 +117,10 @@ __global__ void __launch_bounds__(32) fused_sweep_kernel(const __grid_constant__
             gv[2] = rg * t2 / nf; gv[3] = rg * t3 / nf;
         }
         gv[4] = a.kappa * bg * g.lw[p.h][2] * fprime * pass * d.sc * (one - d.sc);
+        // TF's Exp gradient is dy * exp(t) (math_grad._ExpGrad) with a dense zero dy for anchors that own no label:
+        // an overflowed exp(t2 / t3) turns it into 0 * inf = NaN, and so does the reference
+        gv[2] = __fadd_rn(gv[2], __fmul_rn(0.f, d.ew));
+        gv[3] = __fadd_rn(gv[3], __fmul_rn(0.f, d.eh));
     }
 
     // ---- the tile becomes the gradient of its records: zeros, then the five values of every record ----------

@@ -43,13 +43,16 @@ def detail_log_values(loss_or_detail):
 
 
 def format_detail(loss_or_detail):
-    """The console text of logger_callback.py:130-134: strings verbatim, numbers only when > 1e-3, as ' - %s: %.4f'."""
+    """The console text of logger_callback.py:130-136: strings verbatim, numbers as ' - %s: %.4f' when > 1e-3 and as
+    ' - %s: %.4e' otherwise (nothing is hidden; only the format switches)."""
     info = ""
     for key, value in detail_log_values(loss_or_detail):
         if isinstance(value, str):
             info += " - %s: %s" % (key, value)
         elif value > 1e-3:
             info += " - %s: %.4f" % (key, value)
+        else:
+            info += " - %s: %.4e" % (key, value)
     return info
 
 

@@ -25,9 +25,10 @@ class _FusedLoss(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_output):
         (grad,) = ctx.saved_tensors
-        # upstream is 1 under Keras (the loss IS the objective, trainer.py:84); the product is kept so
-        # that any other use of the scalar stays correct
-        return grad * grad_output, None, None
+        # upstream is 1 under Keras (the loss IS the objective, trainer.py:84) but it arrives as a device scalar: reading
+        # it would stall the host, so the saved gradient is scaled in place (one pass, no second tensor) -- it is this
+        # function's own buffer, nobody else holds it.  loss_and_grad(upstream=...) scales inside the kernel instead.
+        return grad.mul_(grad_output), None, None
 
 
 class YOLOv3Loss(object):
@@ -65,6 +66,11 @@ class YOLOv3Loss(object):
         # False: the caller sums the 20 loss floats over the ranks itself with all_reduce_detail() (e.g. after replaying
         # a CUDA graph that holds this rank's launches)
         self.auto_all_reduce = True
+        # Equal shards are assumed (n_global = n * world) and verified ONCE, on the first sharded call, by an all-reduce
+        # of the local batch size; a caller with ragged shards (a last, shorter batch) passes ``global_batch``.
+        self.global_batch = None
+        self._shards_checked = False
+        self._latched_rect = None           # the tf.cond of a step, latched by the step's first phase call
         self._last_out = None
         # host-visible state of the tf.cond at yolov3_loss.py:125 (a bare backend variable there, :69)
         self.current_num = 0
@@ -86,6 +92,20 @@ class YOLOv3Loss(object):
     def _all_reduce(self, t):
         import torch.distributed as dist
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.process_group)
+
+    def _n_global(self, n, world, device):
+        """The N of the batch mean (yolov3_loss.py:112) when the batch is sharded over ranks."""
+        if self.global_batch is not None:
+            return int(self.global_batch)
+        if world > 1 and not self._shards_checked:
+            import torch.distributed as dist
+            v = torch.tensor([n, -n], dtype=torch.int64, device=device)
+            dist.all_reduce(v, op=dist.ReduceOp.MAX, group=self.process_group)
+            if int(v[0]) != -int(v[1]):
+                raise ValueError("ranks hold shards of different sizes (%d..%d images): set loss.global_batch to the "
+                                 "global batch size; n * world would give a wrong batch mean" % (-int(v[1]), int(v[0])))
+            self._shards_checked = True
+        return n * world
 
     # ---- the fused call --------------------------------------------------------------------------
     def _workspace(self, n, m, device):
@@ -110,12 +130,25 @@ class YOLOv3Loss(object):
         return t, p
 
     def _run(self, targets, predicts, want_grad, upstream=1.0, events=None, grad_out=None, sweep_after=None,
-             sweep_done=None, out=None, fuse=None):
+             sweep_done=None, out=None, fuse=None, rect_override=None):
         t, p = self._prepare(targets, predicts)
+        with torch.cuda.device(p.device):           # launches go to the tensors' device, whatever the current one is
+            return self._run_on(t, p, want_grad, upstream, events, grad_out, sweep_after, sweep_done, out, fuse,
+                                rect_override)
+
+    def _run_on(self, t, p, want_grad, upstream, events, grad_out, sweep_after, sweep_done, out, fuse, rect_override):
         n, m = p.shape[0], t.shape[1] // 5
         world = self._world()
-        n_global = n * world
-        rect_active = self.current_num <= self.rectified_coord_num            # :125 (read before the add)
+        n_global = self._n_global(n, world, p.device)
+        # :125 -- the predicate is read once per step, before the add.  A scheduler that issues the phases of a step
+        # as separate calls gets the value latched by the step's first call (the counter moves in the call that holds
+        # the fold); a pipeline that interleaves steps of several instances passes it explicitly (rect_override).
+        if rect_override is not None:
+            rect_active = bool(rect_override)
+        elif self._latched_rect is not None:
+            rect_active = self._latched_rect
+        else:
+            rect_active = self.current_num <= self.rectified_coord_num
         ws = self._workspace(n, m, p.device)
         if out is None:
             out = torch.empty(20, dtype=torch.float32, device=p.device)
@@ -164,7 +197,9 @@ class YOLOv3Loss(object):
             self.last_fused = bool(fused.value)
             self._last_filter = (cand, counts)
             if not phases & 4:
-                # a scheduler issuing the phases one by one: the step's bookkeeping belongs to its last phase
+                # a scheduler issuing the phases one by one: the step's bookkeeping belongs to the call with the fold
+                if rect_override is None:
+                    self._latched_rect = rect_active
                 return None, grad
         elif sweep_after is not None or sweep_done is not None:
             # a scheduler's hooks around the HBM-bound sweep: it starts after `sweep_after` (an event of another
@@ -186,7 +221,8 @@ class YOLOv3Loss(object):
             _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 2, stream), "yv3_loss_fwd_bwd[dense]")
             events[1].record()
             _lib.check(self._lib.yv3_loss_fwd_bwd(*args, 4, stream), "yv3_loss_fwd_bwd[fold]")
-        if rect_active:
+        self._latched_rect = None
+        if rect_active and rect_override is None:
             self.current_num += n_global                                       # update_add (:152)
         if world > 1 and self.auto_all_reduce:
             self._all_reduce(out)
@@ -219,7 +255,7 @@ class YOLOv3Loss(object):
                          sweep_after=sweep_after, sweep_done=sweep_done, out=out)
 
     def loss_grad_and_filter(self, targets, predicts, post, score_thresh, upstream=1.0, grad_out=None, out=None,
-                             filter_out=None, events=None, before_tail=None, phases=15):
+                             filter_out=None, events=None, before_tail=None, phases=15, rect_override=None):
         """Evaluation while training: ``loss_and_grad`` and ``post.filter(predicts, score_thresh)`` (a
         ``HeadPostProcessor`` of the same head configuration) in one call that reads the head tensor once
         (``yv3_loss_filter_fused``).  Returns (total, grad, cand, counts); gradient, candidates and counts are
@@ -232,7 +268,8 @@ class YOLOv3Loss(object):
         the small kernels on two others, two workspaces alternating); total is None unless the call includes the fold,
         which is also the call that does the step's bookkeeping (rectified counter, all-reduce, detail attributes)."""
         total, grad = self._run(targets, predicts, want_grad=True, upstream=upstream, grad_out=grad_out, out=out,
-                                events=events, fuse=(post, score_thresh, filter_out, before_tail, int(phases)))
+                                events=events, fuse=(post, score_thresh, filter_out, before_tail, int(phases)),
+                                rect_override=rect_override)
         cand, counts = self._last_filter
         return total, grad, cand, counts
 
@@ -255,7 +292,7 @@ class YOLOv3Loss(object):
             raise ValueError("targets must be (N, M*5) with the same N as the head tensors")
         m = t.shape[1] // 5
         world = self._world()
-        n_global = n * world
+        n_global = self._n_global(n, world, heads[0].device)
         rect_active = self.current_num <= self.rectified_coord_num            # :125 (read before the add)
         ws = self._workspace(n, m, heads[0].device)
         out = torch.empty(20, dtype=torch.float32, device=heads[0].device)
@@ -267,9 +304,10 @@ class YOLOv3Loss(object):
                     raise ValueError("grads_out must be contiguous fp32 tensors shaped like the head tensors")
         pp = (ctypes.c_void_p * 3)(*[_lib.ptr(p) for p in heads])
         gp = (ctypes.c_void_p * 3)(*[_lib.ptr(g) for g in grads]) if grads is not None else None
-        rc = self._lib.yv3_loss_fwd_bwd_heads(ctypes.byref(self._cfg), pp, _lib.ptr(t), n, m, n_global,
-                                              1 if rect_active else 0, float(upstream), _lib.ptr(out), gp, _lib.ptr(ws),
-                                              ws.numel(), 7, _lib.current_stream_ptr(heads[0].device))
+        with torch.cuda.device(heads[0].device):
+            rc = self._lib.yv3_loss_fwd_bwd_heads(ctypes.byref(self._cfg), pp, _lib.ptr(t), n, m, n_global,
+                                                  1 if rect_active else 0, float(upstream), _lib.ptr(out), gp, _lib.ptr(ws),
+                                                  ws.numel(), 7, _lib.current_stream_ptr(heads[0].device))
         _lib.check(rc, "yv3_loss_fwd_bwd_heads")
         if rect_active:
             self.current_num += n_global                                       # update_add (:152)
@@ -296,8 +334,9 @@ class YOLOv3Loss(object):
         ws = self._workspace(n, m, p.device)
         table = torch.empty((n, m, 3, 4), dtype=torch.int32, device=p.device)
         iou = torch.empty((n, m, 3), dtype=torch.float32, device=p.device)
-        rc = self._lib.yv3_assign(ctypes.byref(self._cfg), _lib.ptr(p), _lib.ptr(t), n, m, _lib.ptr(table),
-                                  _lib.ptr(iou), _lib.ptr(ws), ws.numel(), _lib.current_stream_ptr(p.device))
+        with torch.cuda.device(p.device):
+            rc = self._lib.yv3_assign(ctypes.byref(self._cfg), _lib.ptr(p), _lib.ptr(t), n, m, _lib.ptr(table),
+                                      _lib.ptr(iou), _lib.ptr(ws), ws.numel(), _lib.current_stream_ptr(p.device))
         _lib.check(rc, "yv3_assign")
         self._last_ws = ws
         return table, iou
