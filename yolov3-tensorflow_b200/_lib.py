@@ -102,7 +102,9 @@ def lib():
     if _LIB is not None:
         return _LIB
     path = _build.LIB_PATH
-    if not os.path.exists(path):
+    if os.environ.get("YV3_LIB"):              # developer A/B: load this build of the library instead of the in-tree one
+        path = os.environ["YV3_LIB"]
+    elif not os.path.exists(path):
         path = _build.build_library()          # raises when nvcc is absent: no fallback path exists
     else:
         try:

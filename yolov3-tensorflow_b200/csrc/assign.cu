@@ -127,8 +127,8 @@ __global__ void assign_kernel(const __grid_constant__ Geo g, const AssignArgs a)
         float gp;                                                                         // d lobj / d p
         if (g.focal) {
             float om = one - p;
-            lobj = lobj * (powf(om, g.gamma) * g.alpha);                                  // :346
-            gp = g.alpha * (-powf(om, g.gamma) / p + g.gamma * powf(om, g.gamma - one) * logf(p));
+            lobj = lobj * (pow_ref(om, g.gamma) * g.alpha);                               // :346
+            gp = g.alpha * (-pow_ref(om, g.gamma) / p + g.gamma * pow_ref(om, g.gamma - one) * logf(p));
         } else {
             gp = -one / p;
         }

@@ -130,12 +130,9 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
     const int nthreads = kThreads + 32 * ZW, nwarps = kWarps + ZW;
     const bool with_grad = a.grad != nullptr && !(a.debug & 8);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int L = g.L, C = g.C, m = a.m;
-    const int nw = gridDim.x * kWarps;
+    const int L = g.L, m = a.m;
     const float thr = g.iou_thresh;
     const float thr_lo = __fmul_rn(thr, 0.99999809265136719f);      // thr * (1 - 2^-19), see surely_below
-    const float nf = (float)a.n_global;
-    const float one = 1.0f;
     const bool wide = VEC && L >= kWideL;
 
     float an0 = 0.f, an1 = 0.f, an2 = 0.f;       // noobj sums per head
@@ -310,7 +307,7 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
         }
         const bool is_obj = ok && ((objw >> lane) & 1u);     // :328 scatter of owned anchors
 
-        // ---- record phase: lane = record -----------------------------------------------------------
+        // ---- record phase: lane = record (loss_record, shared with the fused sweep) --------------------------
         float gv[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
         // one division per chunk (uniform), lanes step from there
         const int n_first = (int)((unsigned)rec0 / (unsigned)g.rpi);
@@ -321,70 +318,13 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
             const RecLoc p = locate(g, r_img);
             head = p.h;
             const BoxDec d = decode_box(g, p, t0, t1, t2, t3, t4);
-            const float parea = __fmul_rn(d.w, d.h);                                       // :267
-            int V;
-            const float4* gt;
-            if (SGT) {
-                const float* slot = slots + (n_img & 1) * gt_slot_floats(m);
-                V = reinterpret_cast<const int*>(slot)[0];
-                gt = reinterpret_cast<const float4*>(slot + 4 + p.h * gt_head_stride(m));
-            } else {
-                const float* slot = a.gtab + (size_t)n_img * gt_slot_floats(m);
-                V = __ldg(reinterpret_cast<const int*>(slot));
-                gt = reinterpret_cast<const float4*>(slot + 4 + p.h * gt_head_stride(m));
-            }
-            bool none_ge = true;                    // max over the labels < thr  <=>  every IoU < thr (V = 0: -inf < thr)
-            for (int j = 0; j < V; j += 4) {
-                // four labels in flight; past the end the last one is repeated (the decision does not change)
-                float4 bx[4];
-                float ta[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    if (SGT) {
-                        bx[u] = gt[2 * (j + u)];                                   // slots are padded to four (assign.cu)
-                        ta[u] = reinterpret_cast<const float*>(gt + 2 * (j + u) + 1)[0];
-                    } else {
-                        bx[u] = __ldg(gt + 2 * (j + u));
-                        ta[u] = __ldg(reinterpret_cast<const float*>(gt + 2 * (j + u) + 1));
-                    }
-                }
-                bool sure = !g.tiou;
-#pragma unroll
-                for (int u = 0; u < 4; ++u) sure = sure & surely_below(d.x0, d.y0, d.x1, d.y1, parea, bx[u], ta[u], thr_lo);
-                if (!sure) {                                                       // rare: some IoU near or above thr
-#pragma unroll
-                    for (int u = 0; u < 4; ++u)
-                        none_ge = none_ge && iou_below_exact(d.x0, d.y0, d.x1, d.y1, parea, bx[u], ta[u], thr, g.tiou);   // :294
-                }
-            }
-            const float bg = (none_ge ? one : 0.0f) * (one - (is_obj ? one : 0.0f));       // :331-332
-            const float pc = d.conf;
-            float l = -logf(one - pc);                                                     // :335
-            float fprime;
-            if (g.focal) {
-                const float pg = powf(pc, g.gamma);
-                fprime = pg / (one - pc) - g.gamma * powf(pc, g.gamma - one) * logf(one - pc);
-                l = l * pg;                                                                // :337
-            } else {
-                fprime = one / (one - pc);
-            }
-            const float contrib = l * bg;                                                  // :338 (0 * inf = NaN kept)
-            const float sq = t0 * t0 + t1 * t1 + t2 * t2 + t3 * t3;                        // :153-155
-            an0 += (p.h == 0) ? contrib : 0.f; an1 += (p.h == 1) ? contrib : 0.f; an2 += (p.h == 2) ? contrib : 0.f;
+            const float* slot = SGT ? slots + (n_img & 1) * gt_slot_floats(m) : a.gtab + (size_t)n_img * gt_slot_floats(m);
+            const float rc = (p.h == 0) ? a.rect_c[0] : ((p.h == 1) ? a.rect_c[1] : a.rect_c[2]);
+            float noobj, sq;
+            loss_record<SGT != 0>(g, p, d, t0, t1, t2, t3, slot, m, is_obj, with_grad, a.kappa, rc, a.rect_active, thr, thr_lo,
+                                  gv[0], gv[1], gv[2], gv[3], gv[4], noobj, sq);
+            an0 += (p.h == 0) ? noobj : 0.f; an1 += (p.h == 1) ? noobj : 0.f; an2 += (p.h == 2) ? noobj : 0.f;
             ar0 += (p.h == 0) ? sq : 0.f; ar1 += (p.h == 1) ? sq : 0.f; ar2 += (p.h == 2) ? sq : 0.f;
-            if (with_grad) {
-                const float pass = (d.sc >= g.lo && d.sc <= g.hi) ? one : 0.f;
-                if (a.rect_active) {
-                    const float rg = a.upstream * g.rw[p.h] * 2.0f;
-                    gv[0] = rg * t0 / nf; gv[1] = rg * t1 / nf;
-                    gv[2] = rg * t2 / nf; gv[3] = rg * t3 / nf;
-                }
-                gv[4] = a.kappa * bg * g.lw[p.h][2] * fprime * pass * d.sc * (one - d.sc);
-                // TF's Exp gradient is dy * exp(t) (math_grad._ExpGrad) with a dense zero dy for anchors that own no
-                // label: an overflowed exp(t2 / t3) turns it into 0 * inf = NaN, and so does the reference
-                gv[2] = __fadd_rn(gv[2], __fmul_rn(0.f, d.ew));
-                gv[3] = __fadd_rn(gv[3], __fmul_rn(0.f, d.eh));
-            }
         }
 
         // ---- the record's five gradient values ---------------------------------------------------------
@@ -433,8 +373,8 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
         }
 
         // ---- records that own a label (object bit set): the whole warp serves them one after the other ------
-        // owner-side box/conf terms of assign.cu added in label order (duplicates add, rule T3), then the class
-        // term (:361-364) and its softmax-CE gradient with the classes spread over the lanes
+        // (owner_record, shared with the fused sweep: owner-side box/conf terms of assign.cu added in label order,
+        // duplicates add, rule T3; then the class term :361-364 and its softmax-CE gradient)
         unsigned ob = __ballot_sync(0xffffffffu, is_obj);
         if (ob && !(a.debug & 4)) {
             if (with_grad) __syncwarp();      // the chunk's stores above are ordered before the read-modify-writes
@@ -445,53 +385,8 @@ __global__ void __launch_bounds__(kThreads + 32 * ZW, YV3_DENSE_MINB) loss_dense
                 const int o_r = __shfl_sync(0xffffffffu, r_img, src);
                 const int o_h = __shfl_sync(0xffffffffu, head, src);
                 const size_t o_off = (size_t)(rec0 + src) * L;
-                const OwnEntry* e0 = a.own + ((size_t)o_n * 3 + o_h) * m;
-                float mx = 0.f, inv = 0.f;
-                bool have = false, first = true;
-                float gacc = 0.f;                                   // lanes 0..4: channel `lane` of the record
-                if (with_grad && lane < 5) gacc = __ldcg(a.grad + o_off + lane);
-                bool touched = false;
-                for (int jb = 0; jb < m; jb += 32) {
-                    const int je = jb + lane;
-                    const bool hit = je < m && e0[je].rec == o_r;
-                    unsigned hits = __ballot_sync(0xffffffffu, hit);
-                    while (hits) {                                 // label order
-                        const int j = jb + __ffs(hits) - 1;
-                        hits &= hits - 1;
-                        if (with_grad && lane < 5) { gacc += e0[j].g[lane]; touched = true; }
-                        const int cls = e0[j].cls;
-                        if (C == 0 || cls < 0 || cls >= C) continue;     // zero one-hot row: no loss, no gradient
-                        const float* z = a.predicts + o_off + 5;
-                        if (!have) {                               // decoder :189-190
-                            float vmax = -INFINITY;
-                            for (int k = lane; k < C; k += 32) vmax = fmaxf(vmax, __ldg(z + k));
-                            mx = warp_max(vmax);
-                            float sum = 0.f;
-                            for (int k = lane; k < C; k += 32) sum += expf(__ldg(z + k) - mx);
-                            inv = 1.0f / warp_sum(sum);
-                            have = true;
-                        }
-                        const float qc = expf(__ldg(z + cls) - mx) * inv;
-                        const float qcc = clip_ref(qc, g.lo, g.hi);                                // :191
-                        if (lane == 0) {
-                            const float lv = -logf(qcc);                                           // loss :363-364
-                            ac0 += (o_h == 0) ? lv : 0.f; ac1 += (o_h == 1) ? lv : 0.f; ac2 += (o_h == 2) ? lv : 0.f;
-                        }
-                        if (with_grad) {
-                            const float pass = (qc >= g.lo && qc <= g.hi) ? 1.0f : 0.f;
-                            const float coef = a.kappa * g.lw[o_h][4] * (-1.0f / qcc) * pass * qc;
-                            float* go = a.grad + o_off + 5;
-                            // a second label on the same record: the same lane adds to what it wrote for the first
-                            for (int k = lane; k < C; k += 32) {
-                                const float qk = expf(__ldg(z + k) - mx) * inv;
-                                const float v = coef * ((k == cls ? 1.0f : 0.f) - qk);
-                                go[k] = first ? v : (__ldcg(go + k) + v);
-                            }
-                            first = false;
-                        }
-                    }
-                }
-                if (touched) a.grad[o_off + lane] = gacc;
+                const float gbase = (with_grad && lane < 5) ? __ldcg(a.grad + o_off + lane) : 0.f;
+                owner_record(g, a, o_n, o_r, o_h, o_off, gbase, with_grad, lane, ac0, ac1, ac2);
             }
         }
         cur = nxt;
@@ -683,7 +578,9 @@ cudaError_t launch_loss_dense(const Geo& g, DenseArgs a, int sm_count, bool swee
     // warp is done, and the hardware scheduler balances the rest (measured best on B200 once the final fold left the
     // kernel: 68 / 70 / 75 us at 1 / 2 / 3 chunks per warp, profiles/r01_dense_variants.txt); more chunks per warp
     // only when the grid would exceed the partial-row table
-    a.cpw = 1;
+    // short records (class_num < 11): the per-warp fixed costs weigh more against 32 * L * 4 bytes of payload;
+    // measured at L = 5, batch 128 on B200: 85 / 74 / 69 us at 1 / 2 / 4 chunks per warp
+    a.cpw = (g.L < 16 && a.num_chunks >= 148 * 64) ? 4 : 1;
     while (((long long)a.num_chunks + (long long)a.cpw * kWarps - 1) / ((long long)a.cpw * kWarps) > max_grid) ++a.cpw;
     if (const char* e = getenv("YV3_CPW")) {                       // developer override
         const int v = atoi(e);

@@ -81,7 +81,17 @@ __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_
         __syncwarp();
     }
 
-    score_tile_records(g, q, tile, unit, lane, rec0, nrec, thresh, stage, tcount);
+    // the lane's record: image slot of the tile (a tile touches at most two images), head / cell / anchor, confidence
+    const int n_first = (int)(rec0 / g.rpi);
+    int r_img = (int)(rec0 - (long long)n_first * g.rpi) + lane, slot = 0;
+    if (r_img >= g.rpi) { r_img -= g.rpi; slot = 1; }
+    RecLoc p = {0, 0, 0, 0};
+    float conf = 0.f;
+    if (lane < nrec) {
+        p = locate(g, r_img);
+        conf = clip_ref(sigmoid_ref(tile[(size_t)lane * L + 4]), g.lo, g.hi);
+    }
+    score_tile_records(g, q, tile, unit, lane, nrec, slot, p, conf, thresh, stage, tcount);
 }
 
 // One CTA per image: per head, the counts of the tiles that hold the image's records of that head go to shared memory

@@ -259,6 +259,7 @@ static int loss_impl(const yv3_config* cfg, const float* const pred[3], bool unp
     d.detail = loss_out20;
     d.n = n; d.m = m; d.n_global = n_global;
     d.kappa = kappa; d.upstream = upstream;
+    for (int h = 0; h < 3; ++h) d.rect_c[h] = (upstream * g.rw[h]) / (float)n_global;
     d.rect_active = rectified_active ? 1 : 0;
     const char* dbg = getenv("YV3_DEBUG");
     d.debug = dbg ? atoi(dbg) : 0;
@@ -490,6 +491,7 @@ int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const fl
     d.detail = loss_out20;
     d.n = n; d.m = m; d.n_global = n_global;
     d.kappa = upstream / (float)n_global; d.upstream = upstream;
+    for (int h = 0; h < 3; ++h) d.rect_c[h] = (upstream * g.rw[h]) / (float)n_global;
     d.rect_active = rectified_active ? 1 : 0;
     const char* dbg = getenv("YV3_DEBUG");
     d.debug = dbg ? atoi(dbg) : 0;
@@ -512,7 +514,7 @@ int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const fl
                               loss_workspace, loss_workspace_bytes, 1, stream);
         if (rc != YV3_OK) return rc;
     }
-    int rows = packed_tile_count(g, predicts, n, score_thresh);
+    int rows = fused_row_count(g, predicts, n, score_thresh);
     if (phases & 2) {
         if (!cuda_ok(launch_fused_sweep(g, d, n, score_thresh, pws.stage, pws.tcount, pws.status, &rows, st), "launch_fused_sweep"))
             return YV3_ERR_CUDA;

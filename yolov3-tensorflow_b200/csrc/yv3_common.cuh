@@ -86,8 +86,19 @@ __device__ __forceinline__ int record_of(const Geo& g, int h, int y, int x, int 
     return row * g.rpr + g.seg_base[h] + cell * g.B[h] + b;
 }
 
+// tf.sigmoid = 1 / (1 + exp(-t)): __frcp_rn is the correctly rounded reciprocal, i.e. the bits of __fdiv_rn(1, x),
+// without the generic division's slow-path call
 __device__ __forceinline__ float sigmoid_ref(float t) {
-    return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-t)));
+    return __frcp_rn(__fadd_rn(1.0f, expf(-t)));
+}
+// tf.pow(x, y) for the focal exponents (yolov3_loss.py:337, :346).  The reference's CPU kernel is std::pow, which
+// returns the correctly rounded x * x for y = 2 (the shipped focal_gamma, configs.py:70) and x itself for y = 1;
+// those two exponents (gamma and gamma - 1) take the one-instruction form here -- powf is ~100 instructions and
+// no closer to the reference.  Any other exponent goes through powf.
+__device__ __forceinline__ float pow_ref(float x, float y) {
+    if (y == 2.0f) return __fmul_rn(x, x);
+    if (y == 1.0f) return x;
+    return powf(x, y);
 }
 __device__ __forceinline__ float clip_ref(float v, float lo, float hi) {
     return fmaxf(fminf(v, hi), lo);   // maximum(minimum(v, hi), lo): tf.clip_by_value
@@ -100,12 +111,13 @@ struct BoxDec {
     float x0, y0, x1, y1;    // corners
 };
 
+// sc: the unclipped sigmoid of t4 when the caller has it already (the score half of the fused sweep), else computed here
 __device__ __forceinline__ BoxDec decode_box(const Geo& g, const RecLoc& p, float t0, float t1, float t2,
-                                             float t3, float t4) {
+                                             float t3, float t4, bool have_sc = false, float sc = 0.f) {
     BoxDec d;
     d.sx = sigmoid_ref(t0);
     d.sy = sigmoid_ref(t1);
-    d.sc = sigmoid_ref(t4);
+    d.sc = have_sc ? sc : sigmoid_ref(t4);
     d.x = __fadd_rn(clip_ref(d.sx, g.lo, g.hi), (float)p.x);
     d.y = __fadd_rn(clip_ref(d.sy, g.lo, g.hi), (float)p.y);
     d.ew = expf(t2);

@@ -53,6 +53,7 @@ struct DenseArgs {
     long long total_rec;
     float kappa;                      // upstream / n_global
     float upstream;
+    float rect_c[3];                  // (upstream * rw_h) / n_global: what reaches every squared logit of head h (:157-162)
     int rect_active;
     int vec_ok;                       // predicts and grad are 16-byte aligned
     int row_base;                     // first partial row of this launch (un-packed form: one launch per head tensor)
@@ -64,7 +65,7 @@ cudaError_t launch_loss_fold(const Geo& g, const DenseArgs& a, int nrows, cudaSt
 
 // ---- fused_sweep.cu ----------------------------------------------------------------------------
 // score sweep + dense loss sweep on one read of the packed tensor (a: as for launch_loss_dense, grad required)
-int packed_tile_count(const Geo& g, const float* predicts, int n, float thresh);     // tiles (= partial rows) of the sweep
+int fused_row_count(const Geo& g, const float* predicts, int n, float thresh);       // spans (= partial rows) of the sweep
 bool fused_sweep_supported(const Geo& g, const DenseArgs& a, int n, float thresh);
 cudaError_t launch_fused_sweep(const Geo& g, DenseArgs a, int n, float thresh, float4* stage, int32_t* tcount,
                                int32_t* post_status, int* rows_out, cudaStream_t stream);
