@@ -443,6 +443,75 @@ def test_collect_kept_rows_resized(yv3, name, bug_compat):
     assert counts.sum() > 0
 
 
+def _crowded_rows(rng, ln, cls, spread=0.05):
+    """boxes of one class crowding one region so that many pairs overlap around the threshold"""
+    cx = rng.uniform(0.3, 0.7, size=ln) + rng.normal(0, spread, size=ln)
+    cy = rng.uniform(0.3, 0.7, size=ln) + rng.normal(0, spread, size=ln)
+    w = rng.uniform(0.05, 0.3, size=ln)
+    h = rng.uniform(0.05, 0.3, size=ln)
+    r = np.zeros((ln, 8), dtype=np.float32)
+    r[:, 0], r[:, 1], r[:, 2], r[:, 3] = cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2
+    r[:, 4] = rng.uniform(0.2, 1.0, size=ln)
+    r[:, 5] = rng.uniform(0.2, 1.0, size=ln)
+    r[:, 6] = cls
+    r[:, 7] = r[:, 4] * r[:, 5]
+    return r
+
+
+@pytest.mark.parametrize("thr", [0.45, 0.3])
+def test_nms_dense_medium_segments_take_the_warp_path(yv3, thr):
+    """The dense stress shape (BASELINE configs[3]): every class of an image holds 33..256 candidates, so the sort kernel's
+    counting-sort path buckets them and nms_warp_kernel resolves each segment in one warp's registers; a few classes of
+    <= 32 (resolved inside the sort kernel) and equal scores mixed in.  Survivors equal the C oracle's greedy NMS."""
+    import bench
+    spec = bench.build_spec(bench.WORKLOADS["cfg2_416_c80_b64"])
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    rng = np.random.default_rng(11)
+    n = 3
+    cand = np.zeros((n, post.capacity, 8), dtype=np.float32)
+    counts = np.zeros((n, 3), dtype=np.int32)
+    for i in range(n):
+        lens = [33, 64, 65, 96, 97, 255, 256, 1, 17, 32] + list(rng.integers(33, 257, size=55 + i))
+        rows = np.concatenate([_crowded_rows(rng, int(ln), cls) for cls, ln in enumerate(lens)], 0)
+        rows[::5, 7] = rows[0, 7]                                  # many equal scores: order falls back to the row index
+        rows = rows[rng.permutation(len(rows))]
+        k = len(rows)
+        assert k <= post.capacity
+        cand[i, :k] = rows
+        counts[i] = [k // 3, k // 3, k - 2 * (k // 3)]
+    keep = post.nms(torch.from_numpy(cand).cuda(), torch.from_numpy(counts).cuda(), thr).cpu().numpy()
+    post.check_status()
+    for i in range(n):
+        k = int(counts[i].sum())
+        got = np.nonzero(keep[i, :k])[0]
+        want = np.sort(nms_c.greedy_nms(cand[i, :k].astype(np.float64), thr))
+        assert np.array_equal(got, want)
+        assert 0 < len(got) < k
+
+
+def test_nms_single_class_of_8000_candidates(yv3):
+    """class_num 0 with a low threshold puts every candidate of an image in ONE segment (the cluster kernel's case)."""
+    import bench
+    spec = bench.build_spec(bench.WORKLOADS["cfg5_512_c0_b16"])
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    rng = np.random.default_rng(12)
+    n, k = 2, 8200
+    cand = np.zeros((n, post.capacity, 8), dtype=np.float32)
+    counts = np.zeros((n, 3), dtype=np.int32)
+    for i in range(n):
+        rows = _crowded_rows(rng, k, 0, spread=0.15)
+        rows[:, 2:4] = rows[:, 0:2] + (rows[:, 2:4] - rows[:, 0:2]) * 0.3        # smaller boxes: a few thousand survive
+        cand[i, :k] = rows
+        counts[i] = [k - 3000, 2000, 1000]
+    keep = post.nms(torch.from_numpy(cand).cuda(), torch.from_numpy(counts).cuda(), 0.4).cpu().numpy()
+    post.check_status()
+    for i in range(n):
+        got = np.nonzero(keep[i, :k])[0]
+        want = np.sort(nms_c.greedy_nms(cand[i, :k].astype(np.float64), 0.4))
+        assert np.array_equal(got, want)
+        assert 500 < len(got) < k
+
+
 @pytest.mark.parametrize("thr", [0.45, 0.2])
 def test_nms_segment_length_boundaries(yv3, thr):
     """Class segments at the lengths where the NMS changes path or block: the warp path (<= 32), the 256-candidate

@@ -353,6 +353,43 @@ __device__ __forceinline__ bool suppresses_overlapping(const float4& a, double a
     return __ddiv_rn(inter, uni) > thresh;
 }
 
+// The same decision, cheaper: almost every overlapping pair is far from the threshold, and for those fp32 arithmetic
+// on the fp32 coordinates already decides.  inter32 and uni32 below carry a relative error of at most 3 * 2^-24 and
+// 12 * 2^-24 (differences and products of exact fp32 inputs, each rounded once; uni >= (a + b) / 2 >= inter bounds the
+// cancellation in (a + b) - inter), the threshold product 2 more: under 2^-19 in all against the exact real quotient,
+// and the reference's own fp64 roundings are 2^-52.  So outside a band of +-2^-18 (relative) around the threshold the
+// fp32 comparison IS the reference's decision; inside it -- or when a product left the normal fp32 range -- the exact
+// fp64 expression decides.  thr_lo / thr_hi: float(thresh * (1 -+ 2^-18)) rounded outward (NmsThresh below).
+struct NmsThresh {
+    double t;
+    float lo, hi;
+};
+__host__ __device__ inline NmsThresh make_nms_thresh(double t) {
+    NmsThresh q;
+    q.t = t;
+    const double band = 3.814697265625e-06;                              // 2^-18
+    const double a = t * (1.0 - band), b = t * (1.0 + band);
+    const double dlo = a < b ? a : b, dhi = a < b ? b : a;               // a negative threshold swaps them
+    float lo = (float)dlo, hi = (float)dhi;
+    if ((double)lo > dlo) lo = nextafterf(lo, -INFINITY);
+    if ((double)hi < dhi) hi = nextafterf(hi, INFINITY);
+    q.lo = lo;
+    q.hi = hi;
+    return q;
+}
+__device__ __forceinline__ bool suppresses_overlapping_fast(const float4& a, const float4& b, const NmsThresh& q) {
+    const float w = __fsub_rn(fminf(a.z, b.z), fmaxf(a.x, b.x));
+    const float h = __fsub_rn(fminf(a.w, b.w), fmaxf(a.y, b.y));
+    const float inter = __fmul_rn(w, h);
+    const float aa = __fmul_rn(__fsub_rn(a.z, a.x), __fsub_rn(a.w, a.y));
+    const float ab = __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
+    const float uni = __fsub_rn(__fadd_rn(aa, ab), inter);
+    const bool normal = inter >= 1e-30f && aa >= 1e-30f && ab >= 1e-30f && uni <= 1e30f;     // false for NaN as well
+    if (normal && inter > __fmul_rn(q.hi, uni) && q.hi >= 0.f) return true;
+    if (normal && inter < __fmul_rn(q.lo, uni) && q.lo >= 0.f) return false;
+    return suppresses_overlapping(a, box_area_d(a), b, box_area_d(b), q.t);
+}
+
 // ---- sort: (class asc, score desc, row asc) -----------------------------------------------------------
 constexpr int kSortThreads = 1024;
 constexpr int kSortSmemKeys = 16384;
@@ -414,8 +451,10 @@ constexpr int kNmsMedium = 256;         // threads = chunk size of the NMS kerne
 constexpr int kNmsLarge = 1024;         // ... and for longer ones
 constexpr int kFuseMaxK = 4096;         // lists up to this size get their short segments resolved inside the sort kernel
 constexpr int kFuseMaxSeg = 32;         // ... segments up to one warp wide
-constexpr int kBucketMaxK = 4096;       // bucket path of the sort kernel: lists up to this size ...
-constexpr int kBucketClasses = 1024;    // ... with class ids below this (= kSortThreads: thread c owns class c) and <= 32 per class
+constexpr int kBucketMaxK = 16384;      // bucket path of the sort kernel: lists up to this size (= kSortSmemKeys) ...
+constexpr int kBucketClasses = 1024;    // ... with class ids below this (= kSortThreads: thread c owns class c) and <= 256 per class
+constexpr int kWarpNmsSlots = 8;        // candidates per lane of the warp-per-segment NMS
+constexpr int kWarpNmsMax = 32 * kWarpNmsSlots;    // = kNmsMedium: the longest segment one warp resolves
 
 // One CTA per image: sort keys (class asc, score desc, row asc) in shared memory, publish the sorted order, then --
 // for lists of at most kFuseMaxK candidates -- resolve every class segment of at most 32 candidates right here, one
@@ -430,6 +469,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
                                                             int32_t* __restrict__ wl_count) {
     extern __shared__ __align__(16) unsigned long long skeys[];
     __shared__ int nseg_s;
+    const NmsThresh nq = make_nms_thresh(thresh);
     const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int K = 0;
     for (int c = 0; c < count_cols; ++c) K += count[n * count_cols + c];
@@ -450,36 +490,29 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
     }
     if (tid == 0) nseg_s = 0;
     __syncthreads();
-    // ---- bucket path: every class of this image has at most 32 candidates (the usual case at a sensible score
-    // threshold: ~6 per class at cfg2).  Sorting by (class, score desc, row) is then a counting sort by class -- a
-    // shared-memory histogram, a prefix over the classes, a scatter -- followed by a rank sort inside each bucket by
-    // one warp, which goes straight on to the greedy NMS of that bucket with the candidates in its lanes.  No global
-    // bitonic sort, no sorted key / box / row tables in global memory (only the queued long segments need those).
-    if (K <= kBucketMaxK && n2s >= 2) {          // n2s >= 2: the launch reserved the fuse area (112 KB), 36 KB are used here
-        unsigned long long* bkey = skeys;                                             // [kBucketMaxK] keys, bucketed
-        int* hist_s = reinterpret_cast<int*>(skeys + kBucketMaxK);                    // [kBucketClasses] counts -> offsets
+    // ---- bucket path: no class of this image has more than kWarpNmsMax (256) candidates -- ~6 per class at cfg2, ~133
+    // at the dense stress workload (10 647 candidates per image over 80 classes).  Sorting by (class, score desc, row) is
+    // then a counting sort by class -- a shared-memory histogram, a prefix over the classes, a scatter -- followed by a
+    // rank sort inside each bucket by one warp (up to 8 keys per lane).  A bucket of at most 32 goes straight on to the
+    // greedy NMS with the candidates in the warp's lanes; a longer one is published (sorted keys, rows, boxes) and queued
+    // for nms_warp_kernel.  No 16 384-key bitonic sort (380 us per step at the stress workload).
+    if (K <= kBucketMaxK && n2s >= 2 && n2 <= n2s) {
+        unsigned long long* bkey = skeys;                                             // [n2s] keys, bucketed
+        int* hist_s = reinterpret_cast<int*>(skeys + n2s);                            // [kBucketClasses] counts -> offsets
+        unsigned short* pos_s = reinterpret_cast<unsigned short*>(hist_s + kBucketClasses);   // [n2s] arrival order in the bucket
         __shared__ int wtot_s[kSortThreads / 32];
         hist_s[tid] = 0;                                                              // kBucketClasses == kSortThreads
         __syncthreads();
-        unsigned long long mykey[kBucketMaxK / kSortThreads];
-        int mypos[kBucketMaxK / kSortThreads];
         bool bad = false;
-#pragma unroll
-        for (int u = 0; u < kBucketMaxK / kSortThreads; ++u) {
-            const int i = tid + u * kSortThreads;
-            mypos[u] = -1;
-            mykey[u] = 0;
-            if (i < K) {
-                const float4 t = reinterpret_cast<const float4*>(rows + (size_t)i * YV3_CAND_COLS)[1];
-                mykey[u] = make_key(t.z, t.w, i);
-                const int c = (int)(mykey[u] >> 50);
-                if (c >= kBucketClasses) bad = true;
-                else mypos[u] = atomicAdd(&hist_s[c], 1);
-            }
+        for (int i = tid; i < K; i += kSortThreads) {
+            const float4 t = reinterpret_cast<const float4*>(rows + (size_t)i * YV3_CAND_COLS)[1];
+            const int c = (int)(make_key(t.z, t.w, i) >> 50);
+            if (c >= kBucketClasses) bad = true;
+            else pos_s[i] = (unsigned short)min(atomicAdd(&hist_s[c], 1), 65535);
         }
         __syncthreads();
         const int mycount = hist_s[tid];
-        if (!__syncthreads_or((bad || mycount > kFuseMaxSeg) ? 1 : 0)) {
+        if (!__syncthreads_or((bad || mycount > kWarpNmsMax) ? 1 : 0)) {
             // exclusive prefix over the classes: thread c owns class c
             int incl = mycount;
 #pragma unroll
@@ -495,9 +528,11 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
             __syncthreads();                                  // every count has been read
             hist_s[tid] = myoff;
             __syncthreads();
-#pragma unroll
-            for (int u = 0; u < kBucketMaxK / kSortThreads; ++u)
-                if (mypos[u] >= 0) bkey[hist_s[(int)(mykey[u] >> 50)] + mypos[u]] = mykey[u];
+            for (int i = tid; i < K; i += kSortThreads) {
+                const float4 t = reinterpret_cast<const float4*>(rows + (size_t)i * YV3_CAND_COLS)[1];
+                const unsigned long long key = make_key(t.z, t.w, i);
+                bkey[hist_s[(int)(key >> 50)] + pos_s[i]] = key;
+            }
             __syncthreads();
             unsigned char* keep_b = keep + (size_t)n * capacity;
             // warp w serves the classes w, w + 32, ...; count(c) = offset(c + 1) - offset(c)
@@ -506,19 +541,45 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
                 const int o1 = (c + 1 < kBucketClasses) ? hist_s[c + 1] : K;
                 const int len = o1 - o0;
                 if (len <= 0) continue;
-                const bool in = lane < len;
-                unsigned long long key = in ? bkey[o0 + lane] : kPadKey;
-                // rank sort: keys are unique (the row is part of the key)
-                int rank = 0;
+                // rank sort: keys are unique (the row is part of the key); lane holds keys lane, lane + 32, ...
+                unsigned long long key[kWarpNmsSlots];
+                int rank[kWarpNmsSlots];
+#pragma unroll
+                for (int u = 0; u < kWarpNmsSlots; ++u) {
+                    key[u] = (lane + 32 * u < len) ? bkey[o0 + lane + 32 * u] : kPadKey;
+                    rank[u] = 0;
+                }
+                const int nslot = (len + 31) >> 5;
                 for (int j = 0; j < len; ++j) {
-                    const unsigned long long other = __shfl_sync(0xffffffffu, key, j);
-                    rank += (other < key) ? 1 : 0;
+                    const unsigned long long other = bkey[o0 + j];
+#pragma unroll
+                    for (int u = 0; u < kWarpNmsSlots; ++u)
+                        if (u < nslot) rank[u] += (other < key[u]) ? 1 : 0;
                 }
                 __syncwarp();
-                if (in) bkey[o0 + rank] = key;
+#pragma unroll
+                for (int u = 0; u < kWarpNmsSlots; ++u)
+                    if (lane + 32 * u < len) bkey[o0 + rank[u]] = key[u];
                 __syncwarp();
-                if (in) key = bkey[o0 + lane];
-                const int row = (int)(key & 0x3ffffULL);
+                if (len > kFuseMaxSeg) {
+                    // publish the sorted segment and queue it: (image, first sorted position | length << 18)
+#pragma unroll
+                    for (int u = 0; u < kWarpNmsSlots; ++u) {
+                        const int p = lane + 32 * u;
+                        if (p < len) {
+                            const unsigned long long k2 = bkey[o0 + p];
+                            const int row = (int)(k2 & 0x3ffffULL);
+                            gk[o0 + p] = k2;
+                            sidx[(size_t)n * capacity + o0 + p] = row;
+                            sbox[(size_t)n * capacity + o0 + p] = reinterpret_cast<const float4*>(rows + (size_t)row * YV3_CAND_COLS)[0];
+                        }
+                    }
+                    if (lane == 0) wl[atomicAdd(wl_count, 1)] = make_int2(n, o0 | (len << 18));
+                    continue;
+                }
+                const bool in = lane < len;
+                const unsigned long long k1 = in ? bkey[o0 + lane] : kPadKey;
+                const int row = (int)(k1 & 0x3ffffULL);
                 float4 mine_f = make_float4(0.f, 0.f, 0.f, 0.f);
                 double mine_area = 0.0;
                 if (in) {
@@ -533,7 +594,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
                     fi.z = __shfl_sync(0xffffffffu, mine_f.z, i); fi.w = __shfl_sync(0xffffffffu, mine_f.w, i);
                     const bool overlap = fminf(fi.z, mine_f.z) > fmaxf(fi.x, mine_f.x) && fminf(fi.w, mine_f.w) > fmaxf(fi.y, mine_f.y);
                     bool drop = lane > i && ((alive >> lane) & 1u);
-                    if (drop) drop = overlap ? suppresses_overlapping(fi, box_area_d(fi), mine_f, mine_area, thresh) : (0.0 > thresh);
+                    if (drop) drop = overlap ? suppresses_overlapping_fast(fi, mine_f, nq) : (0.0 > thresh);
                     alive &= ~__ballot_sync(0xffffffffu, drop);
                 }
                 if (in) keep_b[row] = (unsigned char)((alive >> lane) & 1u);
@@ -541,6 +602,15 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
             return;
         }
         __syncthreads();                                      // the attempt is abandoned: the general path rebuilds everything
+        for (int i = tid; i < n2; i += kSortThreads) {        // ... including the keys the scatter area overlaps
+            unsigned long long key = kPadKey;
+            if (i < K) {
+                const float4 t = reinterpret_cast<const float4*>(rows + (size_t)i * YV3_CAND_COLS)[1];
+                key = make_key(t.z, t.w, i);
+            }
+            keys[i] = key;
+        }
+        __syncthreads();
     }
     if (keys == skeys && n2 <= kSortThreads) bitonic_sort_regs(keys, n2, tid);
     else bitonic_sort(keys, n2, tid);
@@ -595,7 +665,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
             // (width or height <= 0, :139-142) never reach the fp64 arithmetic
             const bool overlap = fminf(fi.z, mine_f.z) > fmaxf(fi.x, mine_f.x) && fminf(fi.w, mine_f.w) > fmaxf(fi.y, mine_f.y);
             bool drop = lane > i && ((alive >> lane) & 1u);
-            if (drop) drop = overlap ? suppresses_overlapping(fi, box_area_d(fi), mine_f, mine.area, thresh) : (0.0 > thresh);
+            if (drop) drop = overlap ? suppresses_overlapping_fast(fi, mine_f, nq) : (0.0 > thresh);
             alive &= ~__ballot_sync(0xffffffffu, drop);
         }
         if (in) keep_n[(int)(keys[p] & 0x3ffffULL)] = (unsigned char)((alive >> lane) & 1u);
@@ -637,6 +707,7 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nwork = *wl_count;
     const bool none_overlap_drops = 0.0 > thresh;      // a negative threshold suppresses even disjoint boxes (:124)
+    const NmsThresh nq = make_nms_thresh(thresh);
   for (int wi = blockIdx.x; wi < nwork; wi += gridDim.x) {
     __syncthreads();                                   // shared state of the previous segment is done with
     const int2 job = wl[wi];
@@ -687,7 +758,7 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
             if (!__any_sync(0xffffffffu, alive)) break;
             const float4 kb = (q < kKeptSmem) ? kept_s[q] : spill[q];
             if (alive) {
-                const bool drop = overlaps_f32(kb, mine_f) ? suppresses_overlapping(kb, box_area_d(kb), mine_f, mine.area, thresh)
+                const bool drop = overlaps_f32(kb, mine_f) ? suppresses_overlapping_fast(kb, mine_f, nq)
                                                            : none_overlap_drops;
                 if (drop) alive = false;
             }
@@ -714,7 +785,7 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
                     for (int j = jb; j < je; ++j) {
                         if (!alive_s[j]) continue;
                         const float4 oj = chunk_s[j];
-                        const bool drop = overlaps_f32(oi, oj) ? suppresses_overlapping(oi, ai, oj, box_area_d(oj), thresh)
+                        const bool drop = overlaps_f32(oi, oj) ? suppresses_overlapping_fast(oi, oj, nq)
                                                                : none_overlap_drops;
                         if (drop) bits |= 1u << (j & 31);
                     }
@@ -768,6 +839,134 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
   }
 }
 
+// ---- segments of 33..256 candidates: one WARP per segment ---------------------------------------------------------
+// The greedy sweep of _apply_nms (:117-128) in two phases, both inside one warp, no block barrier:
+//  A. pair tests, fully parallel: the segment's sorted boxes and fp32 areas are staged in the warp's shared-memory
+//     slice; candidate j (lane j & 31, slot j >> 5) is tested against every earlier candidate i -- box i is a broadcast
+//     shared-memory read -- with the branch-free fp32 form of the suppression test (the exact fp32 overlap test
+//     :139-142 and the banded IoU comparison of suppresses_overlapping_fast; the rare pair inside the band takes the
+//     fp64 expression).  The outcomes are the bits of COLUMN j of the suppression matrix: word i >> 5, bit i & 31.
+//  B. the sweep, serial in j but eight lanes wide: lane w holds word w of the kept set; candidate j is kept iff no
+//     kept i < j suppresses it, i.e. iff column j AND kept is empty -- one shared-memory word per lane, one ballot.
+// ~17 instructions per 32 pair tests and no ballot in phase A (the first version, candidates in registers and one
+// ballot per (i, slot), spent ~60 and ran 950 us at cfg4; nms_kernel<256> with CTA-wide phases 1150 us).
+constexpr int kWarpNmsThreads = 128;
+constexpr int kWarpNmsWarps = kWarpNmsThreads / 32;
+struct WarpNmsSmem {
+    float4 box[kWarpNmsMax];
+    float area[kWarpNmsMax];
+    unsigned col[kWarpNmsMax][kWarpNmsSlots + 1];      // + 1: odd row stride, conflict-free column-word reads in phase B
+};
+__global__ void __launch_bounds__(kWarpNmsThreads) nms_warp_kernel(const unsigned long long* __restrict__ gkeys,
+                                                                   const int32_t* __restrict__ count, int count_cols,
+                                                                   int capacity, int cap2, double thresh,
+                                                                   const float4* __restrict__ sbox, const int32_t* __restrict__ sidx,
+                                                                   unsigned char* __restrict__ keep,
+                                                                   const int2* __restrict__ wl, const int32_t* __restrict__ wl_count) {
+    extern __shared__ __align__(16) unsigned char wsm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpNmsSmem& sm = reinterpret_cast<WarpNmsSmem*>(wsm)[warp];
+    const int wid = (blockIdx.x * kWarpNmsThreads + threadIdx.x) >> 5;
+    const int nw = (gridDim.x * kWarpNmsThreads) >> 5;
+    const int nwork = *wl_count;
+    const bool none_overlap_drops = 0.0 > thresh;      // a negative threshold suppresses even disjoint boxes (:124)
+    const NmsThresh nq = make_nms_thresh(thresh);
+    const bool fast_ok = nq.lo >= 0.f;
+    for (int wi = wid; wi < nwork; wi += nw) {
+        const int2 job = wl[wi];
+        const int n = job.x, s0 = job.y & 0x3ffff;
+        int len = (int)((unsigned)job.y >> 18);
+        if (len == 0) {
+            // queued by the general sort path without a length: the run of this class from s0 on (at most 256 long)
+            int K = 0;
+            for (int q = 0; q < count_cols; ++q) K += count[n * count_cols + q];
+            K = max(0, min(K, capacity));
+            const unsigned long long* keys = gkeys + (size_t)n * cap2;
+            const unsigned long long c0 = keys[s0] >> 50;
+#pragma unroll
+            for (int u = 0; u < kWarpNmsSlots; ++u) {
+                const int p = s0 + lane + 32 * u;
+                len += __popc(__ballot_sync(0xffffffffu, p < K && (keys[p] >> 50) == c0));
+            }
+        }
+        const float4* boxes = sbox + (size_t)n * capacity + s0;
+        const int32_t* rowof = sidx + (size_t)n * capacity + s0;
+        const int nslot = (len + 31) >> 5;
+        float4 bx[kWarpNmsSlots];
+        float ar[kWarpNmsSlots];
+        int row[kWarpNmsSlots];
+        __syncwarp();                                                    // the previous segment's sweep is done with sm
+#pragma unroll
+        for (int u = 0; u < kWarpNmsSlots; ++u) {
+            const int idx = lane + 32 * u;
+            const bool in = idx < len;
+            bx[u] = in ? __ldg(boxes + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+            row[u] = in ? __ldg(rowof + idx) : -1;
+            ar[u] = __fmul_rn(__fsub_rn(bx[u].z, bx[u].x), __fsub_rn(bx[u].w, bx[u].y));
+            if (u < nslot) { sm.box[idx] = bx[u]; sm.area[idx] = ar[u]; }
+        }
+        __syncwarp();
+        // ---- phase A: column bits ----------------------------------------------------------------------------------
+        // sane: the area is a normal fp32 number far from overflow, so the fp32 bounds of the comparison hold (NmsThresh);
+        // anything else -- and a negative threshold -- is settled by the exact expression
+        bool sane[kWarpNmsSlots];
+#pragma unroll
+        for (int v = 0; v < kWarpNmsSlots; ++v) sane[v] = fast_ok && ar[v] >= 1e-30f && ar[v] <= 1e29f;
+        for (int ib = 0; ib < nslot; ++ib) {                              // block of 32 earlier candidates i
+            unsigned word[kWarpNmsSlots];
+#pragma unroll
+            for (int v = 0; v < kWarpNmsSlots; ++v) word[v] = 0u;
+            const int iend = min(32, len - 1 - 32 * ib);
+            for (int l = 0; l < iend; ++l) {
+                const int i = 32 * ib + l;
+                const float4 fi = sm.box[i];
+                const float ai = sm.area[i];
+                const bool sane_i = ai >= 1e-30f && ai <= 1e29f;
+                const unsigned bit = 1u << l;
+#pragma unroll
+                for (int v = 0; v < kWarpNmsSlots; ++v) {
+                    if (v < ib || v >= nslot) continue;                  // every j of slot v precedes i / slot unused (uniform)
+                    const float w = __fsub_rn(fminf(fi.z, bx[v].z), fmaxf(fi.x, bx[v].x));
+                    const float h = __fsub_rn(fminf(fi.w, bx[v].w), fmaxf(fi.y, bx[v].y));
+                    const bool overlap = w > 0.f && h > 0.f;             // :139-142, exact on fp32 coordinates
+                    const float inter = __fmul_rn(w, h);
+                    const float uni = __fsub_rn(__fadd_rn(ai, ar[v]), inter);
+                    const bool yes = inter > __fmul_rn(nq.hi, uni), no = inter < __fmul_rn(nq.lo, uni);
+                    const bool decided = (yes || no) && sane[v] && sane_i && inter >= 1e-30f;
+                    bool drop = overlap ? yes : none_overlap_drops;
+                    if (overlap && !decided)                             // inside the band or out of range: exact, rare
+                        drop = suppresses_overlapping(fi, box_area_d(fi), bx[v], box_area_d(bx[v]), thresh);
+                    word[v] |= drop ? bit : 0u;
+                }
+            }
+            // a candidate is only suppressed by EARLIER ones: in the diagonal block keep the bits below the lane's own
+#pragma unroll
+            for (int v = 0; v < kWarpNmsSlots; ++v) {
+                if (v < ib || v >= nslot) continue;
+                unsigned wv = word[v];
+                if (v == ib) wv &= (1u << lane) - 1u;
+                if (lane + 32 * v >= len) wv = 0u;
+                sm.col[lane + 32 * v][ib] = wv;
+            }
+        }
+        __syncwarp();
+        // ---- phase B: j is kept iff no kept i < j suppresses it; lane w < nslot holds word w of the kept set ---------
+        unsigned kept = 0u;
+        for (int j = 0; j < len; ++j) {
+            const int jb = j >> 5;
+            const unsigned c = (lane <= jb && lane < nslot) ? sm.col[j][lane] : 0u;     // words above jb were never written
+            const bool hit = (c & kept) != 0u;
+            if (!__any_sync(0xffffffffu, hit) && lane == jb) kept |= 1u << (j & 31);
+        }
+        unsigned char* keep_n = keep + (size_t)n * capacity;
+#pragma unroll
+        for (int u = 0; u < kWarpNmsSlots; ++u) {
+            const unsigned k = __shfl_sync(0xffffffffu, kept, u);
+            if (row[u] >= 0) keep_n[row[u]] = (unsigned char)((k >> lane) & 1u);
+        }
+    }
+}
+
 // ---- long segments: one thread-block CLUSTER per segment ------------------------------------------------------
 // A segment of thousands of candidates (a single-class head with a low threshold) is a serial chain of 1024-candidate
 // chunks, and inside a chunk the work is (candidates x boxes kept so far) + (chunk x chunk) pair tests: one CTA took
@@ -811,6 +1010,7 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
     const int* leader_nkept = cluster.map_shared_rank(&nkept_s, 0);
     const int nwork = *wl_count;
     const bool none_overlap_drops = 0.0 > thresh;
+    const NmsThresh nq = make_nms_thresh(thresh);
     for (int wi = cid; wi < nwork; wi += ncl) {
         const int2 job = wl[wi];
         const int n = job.x;
@@ -857,7 +1057,7 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
                 for (int u = 0; u < 4; ++u) {
                     if (q + u * kClu < nk && alive) {
                         const bool drop = overlaps_f32(kb[u], mine_f)
-                                              ? suppresses_overlapping(kb[u], box_area_d(kb[u]), mine_f, mine.area, thresh)
+                                              ? suppresses_overlapping_fast(kb[u], mine_f, nq)
                                               : none_overlap_drops;
                         if (drop) alive = false;
                     }
@@ -890,7 +1090,7 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
                         for (int j = jb; j < je; ++j) {
                             if (!alive_s[j]) continue;
                             const float4 oj = chunk_s[j];
-                            const bool drop = overlaps_f32(oi, oj) ? suppresses_overlapping(oi, ai, oj, box_area_d(oj), thresh)
+                            const bool drop = overlaps_f32(oi, oj) ? suppresses_overlapping_fast(oi, oj, nq)
                                                                    : none_overlap_drops;
                             if (drop) bits |= 1u << (j & 31);
                         }
@@ -1131,7 +1331,8 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     // keys, and for short lists (fused pass) the sorted boxes and the segment starts behind the first kFuseMaxK keys
     const size_t fuse_bytes = (size_t)kFuseMaxK * (8 + 16 + 4);
     const bool can_fuse = n2s >= 2;
-    const size_t smem = max((size_t)n2s * 8, can_fuse ? fuse_bytes : (size_t)0);
+    const size_t bucket_bytes = (size_t)n2s * 8 + (size_t)kBucketClasses * 4 + (size_t)n2s * 2;
+    const size_t smem = max(can_fuse ? bucket_bytes : (size_t)n2s * 8, can_fuse ? fuse_bytes : (size_t)0);
     err = cudaFuncSetAttribute(sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     err = cudaMemsetAsync(ws.wl_count, 0, 2 * sizeof(int32_t), stream);
@@ -1143,12 +1344,15 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     if (err != cudaSuccess) return err;
     // fixed grids walk the two queues of long segments; with nothing queued every CTA leaves after one load
     (void)num_classes;
-    err = cudaFuncSetAttribute(nms_kernel<kNmsMedium>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)nms_smem_bytes(kNmsMedium));
-    if (err != cudaSuccess) return err;
     err = cudaFuncSetAttribute(nms_kernel<kNmsLarge>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)nms_smem_bytes(kNmsLarge));
     if (err != cudaSuccess) return err;
-    nms_kernel<kNmsMedium><<<592, kNmsMedium, nms_smem_bytes(kNmsMedium), stream>>>(
-        ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx, ws.kspill, keep, ws.wl, ws.wl_count);
+    {
+        const size_t wsmem = sizeof(WarpNmsSmem) * kWarpNmsWarps;
+        err = cudaFuncSetAttribute(nms_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
+        if (err != cudaSuccess) return err;
+        nms_warp_kernel<<<148 * 4, kWarpNmsThreads, wsmem, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox,
+                                                                     ws.sidx, keep, ws.wl, ws.wl_count);
+    }
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
     // segments longer than 256 candidates: one cluster of CTAs per segment (falls back to one CTA per segment where
