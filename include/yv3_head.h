@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define YV3_ABI_VERSION 4
+#define YV3_ABI_VERSION 5
 #define YV3_MAX_BOX 8      /* anchors per head (reference ships 3 / 2 / 3, configs.py:37-41) */
 #define YV3_MAX_GT 256     /* label slots per image (M) */
 
@@ -239,6 +239,22 @@ int yv3_nms(const yv3_config* cfg, const float* cand, const int32_t* counts, int
 int yv3_collect_kept(const float* cand, const int32_t* counts, const uint8_t* keep, int n, int32_t capacity,
                      double target_w, double target_h, int bug_compat, double* rows_out, int32_t* counts_out,
                      void* stream);
+
+/* ---- the one exchange step of the sharded path: the batch mean of yolov3/yolov3_loss.py:112 over ALL shards ----------
+ * Sum of every rank's loss rows (20 floats per step: 18 detail values, their sum, a pad) over the GPUs of one NVLink
+ * domain, as ONE kernel over peer-mapped memory (csrc/peer_reduce.cu): ranks push their rows into each other's
+ * mailboxes, raise a flag, poll their own flags and add the rows in rank order (bit-identical sums on every rank).
+ * An ordinary stream-ordered launch: it can be captured in the CUDA graph that holds the step, which the library
+ * collective could not.  Replaces multi_gpu_model's gather-to-CPU of yolov3/trainer.py:40-41 for this path.
+ *   yv3_peer_mailbox_bytes  size of the mailbox every rank provides: device memory mapped into every peer (e.g. a
+ *                           symmetric-memory allocation), zero-initialised once, 128-byte aligned
+ *   yv3_peer_allreduce      mailboxes[r] = rank r's mailbox as mapped into THIS process; out[0..count) = sum over ranks
+ *                           of local[0..count), count <= cap; local may equal out.  Every rank makes the same calls.
+ *   yv3_peer_status         1 when a peer failed to arrive within the poll bound (~2 s) in some call, else 0 */
+int yv3_peer_mailbox_bytes(int world, int cap, size_t* bytes);
+int yv3_peer_allreduce(void* const* mailboxes, int world, int rank, int cap, const float* local, int count, float* out,
+                       void* stream);
+int yv3_peer_status(const void* mailbox, void* stream);
 
 #ifdef __cplusplus
 }

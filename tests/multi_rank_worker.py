@@ -93,9 +93,40 @@ def main():
         assert torch.equal(grads[i], grad_f[lo:hi]), "pipeline step %d: gradient shard differs" % i
         np.testing.assert_allclose(rows[i, :18].cpu().numpy(), full.loss_detail.reshape(-1).cpu().numpy(), rtol=2e-6, atol=1e-7)
     assert pipe.current_num == full.current_num == 3 * n_full
+    # ---- the peer-memory all-reduce kernel (csrc/peer_reduce.cu) against NCCL, then inside the pipeline and a CUDA graph
+    red = yv3.PeerAllReduce.create(cap=512)
+    peer = "nccl only (peers could not be mapped)"
+    if red is not None:
+        peer = "peer kernel"
+        g = torch.Generator(device=dev).manual_seed(1000 + rank)
+        for it in range(40):                                           # both parities, many epochs, varying sizes
+            cnt = [20, 320, 1, 512][it % 4]
+            x = torch.randn(cnt, generator=g, device=dev)
+            want = x.clone()
+            dist.all_reduce(want)
+            got = red(x.clone())
+            np.testing.assert_allclose(got.cpu().numpy(), want.cpu().numpy(), rtol=1e-6, atol=1e-6)
+            gathered = [torch.empty_like(got) for _ in range(world)]
+            dist.all_gather(gathered, got)
+            assert all(torch.equal(gathered[0], t) for t in gathered), "ranks hold different sums"
+        red.check_status()
+        pipe2 = yv3.FusedPipeline(product_loss_args(spec), 0.05, 0.45, depth=3, rectified_coord_num=-1, reducer=red)
+        rows2 = torch.zeros((k, 20), device=dev)
+        graph = pipe2.capture(shard_t, shard_p, grads, rows2, cand, counts, keep)
+        full2 = yv3.YOLOv3Loss(rectified_coord_num=-1, **product_loss_args(spec))
+        full2.global_batch, full2.auto_all_reduce = n_full, False
+        for rep in range(3):
+            rows2.zero_()
+            graph.replay()
+            torch.cuda.synchronize()
+            for i in range(k):
+                full2.loss_and_grad(torch.from_numpy(ts[i]).to(dev), torch.from_numpy(ps[i]).to(dev))
+                np.testing.assert_allclose(rows2[i, :18].cpu().numpy(), full2.loss_detail.reshape(-1).cpu().numpy(),
+                                           rtol=2e-6, atol=1e-7)
+        red.check_status()
     dist.barrier()
     if rank == 0:
-        print("multi-rank worker ok: world %d" % world)
+        print("multi-rank worker ok: world %d, %s" % (world, peer))
     dist.destroy_process_group()
 
 

@@ -22,3 +22,4 @@ def test_sharded_path_equals_full_batch():
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "multi-rank worker ok" in r.stdout
+    print([l for l in r.stdout.splitlines() if "multi-rank worker ok" in l][-1])     # says whether the peer kernel ran

@@ -86,6 +86,9 @@ _SIGNATURES = {
                                              ctypes.c_float, _P, _P, _P, ctypes.c_size_t, ctypes.c_float, _P,
                                              ctypes.c_int32, _P, _P, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int32),
                                              ctypes.c_int, _P]),
+    "yv3_peer_mailbox_bytes": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_size_t)]),
+    "yv3_peer_allreduce": (ctypes.c_int, [ctypes.POINTER(_P), ctypes.c_int, ctypes.c_int, ctypes.c_int, _P, ctypes.c_int, _P, _P]),
+    "yv3_peer_status": (ctypes.c_int, [_P, _P]),
     "yv3_nms": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int32, ctypes.c_int,
                                ctypes.c_double, _P, _P, ctypes.c_size_t, _P]),
 }
@@ -117,7 +120,7 @@ def lib():
         fn = getattr(handle, name)             # AttributeError = header and library disagree
         fn.restype = res
         fn.argtypes = args
-    if handle.yv3_abi_version() != 4:
+    if handle.yv3_abi_version() != 5:
         raise RuntimeError("libyv3head.so ABI version mismatch")
     _LIB = handle
     return _LIB

@@ -36,8 +36,11 @@ def _nth(x, k):
 
 class FusedPipeline(object):
     def __init__(self, loss_args, score_thresh, nms_thresh, depth=3, rectified_coord_num=0, process_group=None,
-                 high_priority=True):
-        """``loss_args``: keyword arguments of YOLOv3Loss (without rectified_coord_num)."""
+                 high_priority=True, reducer=None):
+        """``loss_args``: keyword arguments of YOLOv3Loss (without rectified_coord_num).  ``reducer``: a stream-ordered
+        in-place sum over the ranks of one 20-float row (``PeerAllReduce``); when given, every step's row is reduced
+        INSIDE the step, on the side stream right behind its fold (and inside a captured graph); without it the caller
+        reduces the collected rows with ``all_reduce_rows`` (one NCCL call for all of them)."""
         if depth < 1:
             raise ValueError("depth must be >= 1")
         self.score_thresh, self.nms_thresh = score_thresh, nms_thresh
@@ -50,6 +53,7 @@ class FusedPipeline(object):
             po = HeadPostProcessor(lo.head_grid_sizes, lo.class_num, loss_args["anchor_boxes"])
             self.pairs.append((lo, po))
         self.process_group = process_group
+        self.reducer = reducer
         self.capacity = self.pairs[0][1].capacity
         prio = -1 if high_priority else 0
         self.aux_stream = torch.cuda.Stream(priority=prio)
@@ -109,6 +113,8 @@ class FusedPipeline(object):
         if serial:
             for k in range(count):
                 part(k, 15, self.pairs[0])
+                if self.reducer is not None:
+                    self.reducer(rows[k])
                 self.pairs[0][1].nms(_nth(cand, k), _nth(counts, k), self.nms_thresh, out=_nth(keep, k))
             self.last_fused = self.pairs[0][0].last_fused
             self._finish(cur_after)
@@ -144,6 +150,8 @@ class FusedPipeline(object):
             with torch.cuda.stream(aux):
                 aux.wait_event(swept)
                 part(k, 4)
+                if self.reducer is not None:
+                    self.reducer(rows[k])              # the step's one exchange: 80 bytes over NVLink, off the sweeps' stream
             if k + depth < count:
                 a_done[b] = assign(k + depth)
         cur.wait_stream(post)
@@ -160,7 +168,7 @@ class FusedPipeline(object):
         """Sum the loss rows of the steps just issued over the ranks: ONE collective for all of them (80 bytes per step).
         Stream-ordered on the current stream."""
         lo = self.pairs[0][0]
-        if lo._world() > 1:
+        if self.reducer is None and lo._world() > 1:
             lo._all_reduce(rows)
         return rows
 
