@@ -3,13 +3,15 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-A step = one pass of the hot path over one synthetic batch: assignment + fused loss forward/backward
-(gradient written) followed by fused decode + score threshold + class-aware NMS of the same head tensors.
+A step = one pass of the hot path over one synthetic batch: assignment + fused loss forward/backward (gradient written)
+and fused decode + score threshold + class-aware NMS of the same head tensors, issued through
+``yolov3_tensorflow_b200.FusedPipeline`` (the schedule tests/test_gpu_pipeline.py checks bit for bit).
 One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every field.
 """
 import argparse
 import json
 import os
+import subprocess
 import sys
 import threading
 import time
@@ -21,25 +23,44 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 WORKLOADS = {
-    # BASELINE.json configs[1]: the configuration the metric is quoted on at N=1
+    # BASELINE.json configs[1]: the configuration the metric is quoted on at N=1 (weak scaling: 64 images per GPU)
     "cfg2_416_c80_b64": dict(size=(416, 416), class_num=80, batch=64, m=16, anchors="coco", iou_thresh=0.8,
                              focal=False, rect=-1, score_thresh=0.1, nms_thresh=0.45,
                              desc="416x416 80-class head (10647 boxes/img), batch 64 per GPU, loss fwd+bwd + "
                                   "decode+filter+NMS"),
-    # configs[2] per-GPU shard at 8 GPUs
+    # configs[2] per-GPU shard at 8 GPUs (weak form)
     "cfg3_608_c80_b64": dict(size=(608, 608), class_num=80, batch=64, m=16, anchors="coco", iou_thresh=0.8,
                              focal=False, rect=-1, score_thresh=0.1, nms_thresh=0.45,
                              desc="608x608 80-class head (22743 boxes/img), batch 64 per GPU"),
+    # configs[2] as written: global batch 512 SHARDED over the GPUs (512 / 256 / 128 / 64 images per rank)
+    "cfg3_608_c80_g512": dict(size=(608, 608), class_num=80, global_batch=512, m=16, anchors="coco", iou_thresh=0.8,
+                              focal=False, rect=-1, score_thresh=0.1, nms_thresh=0.45,
+                              desc="608x608 80-class head (22743 boxes/img), GLOBAL batch 512 sharded over the GPUs"),
     # configs[3]: post-process stress
     "cfg4_416_c80_b256_dense": dict(size=(416, 416), class_num=80, batch=256, m=16, anchors="coco", iou_thresh=0.8,
                                     focal=False, rect=-1, score_thresh=0.001, nms_thresh=0.45,
                                     desc="416x416 batch 256, score thresh 0.001, per-class NMS IoU 0.45 (dense)"),
-    # configs[4]: single class, focal + rectified
-    "cfg5_512_c0_b16": dict(size=(512, 512), class_num=0, batch=16, m=16, anchors="shipped3", iou_thresh=0.8,
-                            focal=True, rect=1 << 30, score_thresh=0.5, nms_thresh=0.4,
-                            desc="512x512 single-class head (class_num 0), focal + prior-box correction on, "
-                                 "batch 16 per GPU"),
+    # configs[4] as written: a LOSS configuration -- single class (class_num 0), focal + prior-box correction on, 512x512,
+    # global batch 128 over the GPUs (16 per rank at 8); a score threshold that leaves the usual handful of candidates
+    "cfg5_512_c0_g128": dict(size=(512, 512), class_num=0, global_batch=128, m=16, anchors="shipped3", iou_thresh=0.8,
+                             focal=True, rect=1 << 30, score_thresh=0.95, nms_thresh=0.4,
+                             desc="512x512 single-class head (class_num 0), focal + prior-box correction on, GLOBAL batch 128 "
+                                  "sharded over the GPUs"),
+    # the one-class NMS stress round 1 ran under the name cfg5 (score threshold 0.5 on N(0,1) logits: ~8000 candidates of
+    # ONE class per image) -- a post-process stress, not BASELINE configs[4]
+    "cfg5_nms_stress_b16": dict(size=(512, 512), class_num=0, batch=16, m=16, anchors="shipped3", iou_thresh=0.8,
+                                focal=True, rect=1 << 30, score_thresh=0.5, nms_thresh=0.4,
+                                desc="512x512 class_num 0, batch 16, score thresh 0.5: one class of ~8000 candidates per image"),
 }
+EXTRA_WORKLOADS = ("cfg3_608_c80_g512", "cfg5_512_c0_g128")     # short entries appended to every line (BASELINE configs[2], [4])
+
+
+def per_rank_batch(w, world):
+    if "global_batch" in w:
+        if w["global_batch"] % world:
+            raise ValueError("global batch %d does not divide over %d ranks" % (w["global_batch"], world))
+        return w["global_batch"] // world
+    return w["batch"]
 
 
 def product_spec(w):
@@ -68,6 +89,21 @@ def synth(spec, n, m, rank):
             ps.make_targets(n, spec.class_num, m, seed=4321 + rank, min_valid=1))
 
 
+def config_block(name, w, n, world, extra=None):
+    """the ``config`` object: the same keys in the product arm and the reference arm"""
+    c = {"workload": name, "desc": w["desc"], "per_gpu_batch": n, "global_batch": n * world, "label_slots": w["m"],
+         "score_thresh": w["score_thresh"], "nms_thresh": w["nms_thresh"]}
+    c.update(extra or {})
+    return c
+
+
+def git_sha():
+    try:
+        return subprocess.run(["git", "rev-parse", "--short", "HEAD"], cwd=ROOT, capture_output=True, text=True).stdout.strip() or None
+    except Exception:
+        return None
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi's clocks line through NVML, polled while the benchmark runs."""
 
@@ -93,8 +129,7 @@ class ClockSampler(threading.Thread):
             try:
                 sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
                 reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-                util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
-                self.samples.append((time.time(), sm, reasons, util, self.mark))
+                self.samples.append((time.time(), sm, reasons, self.mark))
             except Exception:
                 pass
             time.sleep(0.005)
@@ -103,7 +138,7 @@ class ClockSampler(threading.Thread):
         if not self.ok or not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_sm, "reasons": ["unavailable"]}
         nv = self.nv
-        timed = [s for s in self.samples if s[4] == "timed"] or [s for s in self.samples if s[4] is not None] \
+        timed = [s for s in self.samples if s[3] == "timed"] or [s for s in self.samples if s[3] is not None] \
             or self.samples
         names = {
             "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4),
@@ -117,10 +152,10 @@ class ClockSampler(threading.Thread):
                 "samples": len(timed)}
 
 
+# ---- CPU legs: the only place bench.py executes oracle/ ---------------------------------------------------------------
 def cpu_port_step(spec, p, t, w):
-    """The oracle port of the reference's CPU path for the same step: serial per-image loss with autograd
-    backward (tf.map_fn(parallel_iterations=1) + TF autodiff), decode, filter_boxes, apply_nms per image
-    (run.py:59-74).  Returns nothing; timed by the caller."""
+    """The oracle port of the reference's CPU path for the same step: serial per-image loss with autograd backward
+    (tf.map_fn(parallel_iterations=1) + TF autodiff), decode, filter_boxes, apply_nms per image (run.py:59-74)."""
     import torch
     from oracle import ref_numpy as rn, ref_postprocess as rp, ref_torch as rt
     rt.loss_and_grad(t, p, spec, rectified_active=w["rect"] >= 0, dtype=torch.float32)
@@ -153,13 +188,14 @@ def run_reference(args, w, spec, rank, world):
         torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
     except Exception:
         pass
-    p, t = synth(spec, w["batch"], w["m"], 0)
+    n = per_rank_batch(w, world)
+    p, t = synth(spec, n, w["m"], 0)
     cpu_port_step(spec, p[:1], t[:1], w)                       # import / first-touch warm-up
     t0 = time.time()
     cpu_port_step(spec, p[:1], t[:1], w)
     one = max(time.time() - t0, 1e-3)
     total_steps = args.steps + args.warmup
-    s = int(max(1, min(w["batch"], (120.0 / total_steps) / one)))     # whole run within a few minutes
+    s = int(max(1, min(n, (120.0 / total_steps) / one)))     # whole run within a few minutes
     for _ in range(args.warmup):
         cpu_port_step(spec, p[:s], t[:s], w)
     t0 = time.time()
@@ -168,19 +204,388 @@ def run_reference(args, w, spec, rank, world):
     dt = time.time() - t0
     value = s * args.steps / dt
     cores = torch.get_num_threads()
-    sample = "%d of %d images per step, fp32 torch-CPU restatement of the TF graph + NumPy post-process" % (s, w["batch"])
+    sample = "%d of %d images per step, fp32 torch-CPU restatement of the TF graph + NumPy post-process" % (s, n)
     print(json.dumps({
         "impl": "reference", "metric": "head loss fwd+bwd + decode+filter+NMS throughput", "value": value,
         "unit": "images/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "desc": w["desc"], "images_per_step": s},
+        "config": config_block(args.workload, w, n, world, {"images_per_step_sampled": s}),
         "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "TensorFlow is not installable on this image (no network); the reference's TF loss/decoder "
-                "cannot run, so the timed CPU arm is the oracle port (oracle/ref_torch.py, ref_numpy.py, "
-                "ref_postprocess.py) on all host threads.",
+                "cannot run on the GPU box, so the timed CPU arm is the oracle port (oracle/ref_torch.py, ref_numpy.py, "
+                "ref_postprocess.py), which tests/test_oracle_pinned.py holds bit for bit (fp32) to the reference's own "
+                "code run under the torch-backed tensorflow stand-in in the build container.",
     }), flush=True)
+
+
+# ---- the product arm ----------------------------------------------------------------------------------------------------
+class Arm(object):
+    """One workload resident on this rank's GPU: inputs, the pipeline, its output buffers, and the measurements."""
+
+    def __init__(self, name, args, rank, world, dev, reducer, pin=True):
+        import torch
+        import yolov3_tensorflow_b200 as yv3
+        self.torch, self.yv3 = torch, yv3
+        self.name, self.w, self.args = name, WORKLOADS[name], args
+        self.rank, self.world, self.dev = rank, world, dev
+        w = self.w
+        self.spec = product_spec(w)
+        yv3.backend.set_epsilon(self.spec.eps)
+        self.n, self.m = per_rank_batch(w, world), w["m"]
+        self.p_np, self.t_np = synth(self.spec, self.n, self.m, rank)
+        self.p_host, self.t_host = torch.from_numpy(self.p_np), torch.from_numpy(self.t_np)
+        if pin:                                                    # the e2e loop copies from pinned host memory every step
+            self.p_host, self.t_host = self.p_host.pin_memory(), self.t_host.pin_memory()
+        self.pd, self.td = self.p_host.to(dev), self.t_host.to(dev)
+        self.pipe = yv3.FusedPipeline(self.spec.loss_args, w["score_thresh"], w["nms_thresh"], depth=max(args.fused_depth, 1),
+                                      rectified_coord_num=w["rect"], reducer=reducer)
+        self.loss, self.post = self.pipe.pairs[0]
+        self.grad = torch.empty_like(self.pd)
+        cap = self.pipe.capacity
+        self.cand = torch.empty((self.n, cap, 8), dtype=torch.float32, device=dev)
+        self.counts = torch.empty((self.n, 3), dtype=torch.int32, device=dev)
+        self.keep = torch.empty((self.n, cap), dtype=torch.uint8, device=dev)
+        self.unroll = max(1, args.graph_steps)
+        self.rows = torch.zeros((self.unroll, 20), dtype=torch.float32, device=dev)
+        self.graphs = {}
+
+    # -- issue `count` steps (count <= unroll): the pipeline, or the separate calls one after the other
+    def issue(self, count):
+        if self.args.fused:
+            self.pipe.run(self.td, self.pd, self.grad, self.rows, self.cand, self.counts, self.keep, count=count)
+            if self.pipe.reducer is None and self.world > 1 and not self.capturing:
+                self.pipe.all_reduce_rows(self.rows)
+        else:
+            self.loss.auto_all_reduce = not self.capturing
+            for k in range(count):
+                self.loss.loss_and_grad(self.td, self.pd, grad_out=self.grad, out=self.rows[k])
+                self.post.filter(self.pd, self.w["score_thresh"], out=(self.cand, self.counts))
+                self.post.nms(self.cand, self.counts, self.w["nms_thresh"], out=self.keep)
+    capturing = False
+
+    def graph_for(self, count):
+        """a CUDA graph of `count` steps (cached); None when capture is off or failed"""
+        torch = self.torch
+        if self.args.no_graph:
+            return None
+        if count not in self.graphs:
+            try:
+                self.issue(count)                                  # warm-up outside the capture
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                self.capturing = True
+                with torch.cuda.graph(g):
+                    self.issue(count)
+                self.graphs[count] = g
+            except Exception as e:                                 # noqa: BLE001
+                self.graphs[count] = None
+                self.capture_error = type(e).__name__
+                torch.cuda.synchronize()
+            finally:
+                self.capturing = False
+        return self.graphs[count]
+
+    def run(self, count):
+        """exactly `count` steps: full graphs, then ONE graph of the remainder (no eager tail)"""
+        done = 0
+        while done < count:
+            c = min(self.unroll, count - done)
+            g = self.graph_for(c)
+            if g is None:
+                self.issue(c)
+            else:
+                g.replay()
+                if self.pipe.reducer is None and self.world > 1:
+                    self.pipe.all_reduce_rows(self.rows)           # NCCL stays outside the graph: once per replay
+            done += c
+
+    def launch_mode(self):
+        if self.graphs.get(self.unroll) is None:
+            return "eager launches" + (" (graph capture failed: %s)" % getattr(self, "capture_error", "?") if not self.args.no_graph else "")
+        red = ("the peer-memory all-reduce kernel of every step's 20 loss floats inside the graph" if self.pipe.reducer is not None
+               else "one eager NCCL all-reduce of the graph's %d x 20 loss floats per replay" % self.unroll) if self.world > 1 else None
+        return "cuda-graph replay, %d step(s) per graph, the remainder as one smaller graph" % self.unroll + (" + " + red if red else "")
+
+    def fence(self):
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def time_steps(self, steps, min_ms=100.0):
+        """CUDA events around `steps` steps repeated until the region is at least min_ms long.
+        Returns (ms per step, steps timed)."""
+        torch = self.torch
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        self.run(steps)                                            # graphs built, caches in their steady state
+        self.fence()
+        a.record()
+        self.run(steps)
+        b.record()
+        self.fence()
+        est = max(a.elapsed_time(b), 1e-3)
+        reps = int(min(max(1, np.ceil(min_ms / est)), 2000))
+        if self.world > 1:                                         # every rank must issue the same number of collectives
+            import torch.distributed as dist
+            r = torch.tensor([reps], device=self.dev)
+            dist.all_reduce(r, op=dist.ReduceOp.MAX)
+            reps = int(r)
+        self.fence()
+        a.record()
+        for _ in range(reps):
+            self.run(steps)
+        b.record()
+        self.fence()
+        ms = a.elapsed_time(b)
+        if self.world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([ms], dtype=torch.float64, device=self.dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms / (reps * steps), reps * steps
+
+    def time_sweep(self, reps):
+        """the dominant kernel alone: CUDA events on the launching stream around the sweep of an eager step"""
+        torch = self.torch
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+        for k in range(reps + 2):
+            e = ev[max(k - 2, 0)]
+            if self.args.fused:
+                self.loss.loss_grad_and_filter(self.td, self.pd, self.post, self.w["score_thresh"], grad_out=self.grad,
+                                               filter_out=(self.cand, self.counts), events=e, rect_override=self.w["rect"] >= 0)
+            else:
+                self.loss.loss_and_grad(self.td, self.pd, grad_out=self.grad, events=e)
+            self.post.nms(self.cand, self.counts, self.w["nms_thresh"], out=self.keep)
+        torch.cuda.synchronize()
+        return float(np.mean([x.elapsed_time(y) for x, y in ev]))
+
+    def alg_bytes(self, owned=0):
+        """SURVEY 8(d) algorithmic bytes of one launch of the dominant kernel"""
+        A, L, C, n, m = self.spec.anchors_per_image, self.spec.box_len, self.spec.class_num, self.n, self.m
+        if self.args.fused:
+            return n * (4 * A * L + 4 * A * L + 4 * m * 5), "fused_sweep_kernel"
+        return n * (4 * A * 5 + 4 * A * L + 4 * m * 5) + 4 * owned * C, "loss_dense_kernel"
+
+    # -- end to end through the public API with HOST buffers ---------------------------------------------------------------
+    def time_e2e(self, steps):
+        """Double-buffered: the host->device copy of step k + 1 (copy stream) runs while step k computes; the caller reads
+        step k - 1's loss AND detections from pinned host memory once that step's device->host copies have landed.  Every
+        step's inputs cross PCIe inside the timed region; the results read back are the 20 loss floats, the per-head counts,
+        the keep flags, the candidate rows and the rows yv3_collect_kept returns (resized, float64).  The gradient stays on
+        the device (it feeds the backward of the model there)."""
+        torch = self.torch
+        n, w, post, loss = self.n, self.w, self.post, self.loss
+        size = (float(w["size"][1]), float(w["size"][0]))
+        copy_stream = torch.cuda.Stream()
+        pbuf = [torch.empty_like(self.pd) for _ in range(2)]
+        tbuf = [torch.empty_like(self.td) for _ in range(2)]
+        # rows a step returns: bounded by what the workload's threshold lets through (measured once), not by capacity
+        kmax = int(self.counts.sum(dim=1).max().item())
+        kcap = max(64, min(post.capacity, int(kmax * 1.25) + 64))
+        out_h = [torch.empty(20, dtype=torch.float32).pin_memory() for _ in range(2)]
+        counts_h = [torch.empty((n, 3), dtype=torch.int32).pin_memory() for _ in range(2)]
+        kcounts_h = [torch.empty((n, 3), dtype=torch.int32).pin_memory() for _ in range(2)]
+        keep_h = [torch.empty((n, kcap), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        cand_h = [torch.empty((n, kcap, 8), dtype=torch.float32).pin_memory() for _ in range(2)]
+        rows_h = [torch.empty((n, kcap, 9), dtype=torch.float64).pin_memory() for _ in range(2)]
+        row = torch.empty(20, dtype=torch.float32, device=self.dev)
+        loss.auto_all_reduce = True
+        self.e2e_d2h = int(20 * 4 + 2 * n * 3 * 4 + n * kcap * (1 + 32 + 72))
+        self.e2e_h2d = int(self.p_host.numel() * 4 + self.t_host.numel() * 4)
+
+        def run(count):
+            main = torch.cuda.current_stream()
+            done = [None, None]
+            read = 0.0
+            for k in range(count):
+                b = k & 1
+                with torch.cuda.stream(copy_stream):
+                    if done[b] is not None:
+                        copy_stream.wait_event(done[b])               # step k - 2 is finished with this buffer pair
+                    pbuf[b].copy_(self.p_host, non_blocking=True)     # pinned host -> device, every step
+                    tbuf[b].copy_(self.t_host, non_blocking=True)
+                    ready = torch.cuda.Event()
+                    ready.record(copy_stream)
+                main.wait_event(ready)
+                if self.args.fused:
+                    loss.loss_grad_and_filter(tbuf[b], pbuf[b], post, w["score_thresh"], grad_out=self.grad, out=row,
+                                              filter_out=(self.cand, self.counts), rect_override=w["rect"] >= 0)
+                    if self.world > 1:
+                        loss._all_reduce(row)
+                else:
+                    loss.loss_and_grad(tbuf[b], pbuf[b], grad_out=self.grad, out=row)
+                    post.filter(pbuf[b], w["score_thresh"], out=(self.cand, self.counts))
+                post.nms(self.cand, self.counts, w["nms_thresh"], out=self.keep)
+                krows, kcounts = post.collect(dict(cand=self.cand, counts=self.counts, keep=self.keep), size)
+                out_h[b].copy_(row, non_blocking=True)
+                counts_h[b].copy_(self.counts, non_blocking=True)
+                kcounts_h[b].copy_(kcounts, non_blocking=True)
+                keep_h[b].copy_(self.keep[:, :kcap], non_blocking=True)
+                cand_h[b].copy_(self.cand[:, :kcap], non_blocking=True)
+                rows_h[b].copy_(krows[:, :kcap], non_blocking=True)
+                done[b] = torch.cuda.Event()
+                done[b].record(main)
+                if k > 0:
+                    done[b ^ 1].synchronize()                         # the caller reads step k - 1's results
+                    read += float(out_h[b ^ 1][18]) + float(counts_h[b ^ 1][0, 0]) + float(rows_h[b ^ 1][0, 0, 7])
+            done[(count - 1) & 1].synchronize()
+            return read + float(out_h[(count - 1) & 1][18])
+
+        run(3)
+        self.fence()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        run(steps)
+        b.record()
+        self.fence()
+        ms = a.elapsed_time(b)
+        if self.world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([ms], dtype=torch.float64, device=self.dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms / steps
+
+    def h2d_probe(self, reps=8):
+        """the platform ceiling of the e2e number: bare pinned-host -> device copies of this rank's inputs, every rank
+        copying at the same time; GB/s of this rank (max-time over ranks for the aggregate)"""
+        torch = self.torch
+        dst = torch.empty_like(self.pd)
+        for _ in range(2):
+            dst.copy_(self.p_host, non_blocking=True)
+        self.fence()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            dst.copy_(self.p_host, non_blocking=True)
+        b.record()
+        self.fence()
+        ms = a.elapsed_time(b)
+        if self.world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([ms], dtype=torch.float64, device=self.dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        nbytes = self.p_host.numel() * 4
+        gbs = nbytes * reps / (ms * 1e-3) / 1e9
+        return {"per_rank_gbs": gbs, "aggregate_gbs": gbs * self.world, "bytes_per_copy": int(nbytes),
+                "ms_per_copy": ms / reps, "note": "bare pinned->device copy of one step's logits, all ranks at once, max over ranks"}
+
+    # -- the stages taken alone (SURVEY 8(d) figures), CUDA events around eager launches ------------------------------------
+    def stage_rooflines(self, peak, reps=20):
+        torch, yv3 = self.torch, self.yv3
+        A, L, C, n, m = self.spec.anchors_per_image, self.spec.box_len, self.spec.class_num, self.n, self.m
+        table, _ = self.loss.assign(self.td, self.pd)
+        owned = int(table[..., 3].sum().item())
+        out = {}
+
+        def timed(fn):
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+            for k in range(reps + 2):
+                fn(ev[max(k - 2, 0)])
+            torch.cuda.synchronize()
+            return float(np.mean([x.elapsed_time(y) for x, y in ev]))
+
+        def entry(name, ms, nbytes, note):
+            gbs = nbytes / (ms * 1e-3) / 1e9
+            out[name] = {"avg_launch_ms": ms, "algorithmic_bytes_per_launch": int(nbytes), "achieved": gbs, "unit": "GB/s",
+                         "frac": gbs / peak, "note": note}
+
+        lo = yv3.YOLOv3Loss(rectified_coord_num=self.w["rect"], **self.spec.loss_args)
+        lo.auto_all_reduce = False
+        ms = timed(lambda e: lo.loss_and_grad(self.td, self.pd, grad_out=self.grad, events=e))
+        entry("loss_dense_kernel", ms, n * (4 * A * 5 + 4 * A * L + 4 * m * 5) + 4 * owned * C,
+              "loss fwd+bwd alone (the reference's training loop): 4A5 read + 4AL gradient + 4RC + labels per image")
+        floor = self.pattern_floor_us()
+        if floor is not None:
+            out["loss_dense_kernel"]["pattern_floor_us"] = floor
+            out["loss_dense_kernel"]["frac_of_pattern_floor"] = floor / (ms * 1e3)
+            out["loss_dense_kernel"]["pattern_floor_note"] = (
+                "tools/membench.cu on a B200 (profiles/r01_membench.txt): the access pattern alone -- 32-byte reads at a "
+                "record stride plus a streaming write of the tensor, no arithmetic; a 20-byte read costs a whole 128-byte "
+                "DRAM line and reads and writes do not overlap for this mix")
+
+        def score(e):
+            e[0].record()
+            self.post.filter(self.pd, self.w["score_thresh"], out=(self.cand, self.counts), sweep_done=e[1])
+        ms = timed(score)
+        entry("score_tile_kernel", ms, n * 4 * A * L, "decode + score + threshold sweep alone (inference): 4AL read per image")
+
+        dec = yv3.YOLOv3Decoder(self.spec.head_grid_sizes, C, self.spec.anchor_boxes)
+        keep_alive = []
+
+        def decode(e):
+            keep_alive.clear()
+            e[0].record()
+            keep_alive.append(dec.decode(self.pd))
+            e[1].record()
+        try:
+            ms = timed(decode)
+            entry("decode_kernel", ms, n * (4 * A * L + 4 * A * (L + 8)),
+                  "materialising decode (the reference's YOLOv3Decoder.decode contract): 4AL read + 4A(L+8) written; the "
+                  "events include the allocation of the nine output tensors by torch's caching allocator")
+        except Exception as e:                                     # noqa: BLE001
+            out["decode_kernel"] = {"error": type(e).__name__}
+        return out, owned
+
+    def pattern_floor_us(self):
+        """the measured floor of the loss-only access pattern at cfg2 (profiles/r01_membench.txt); other shapes: None"""
+        return 61.5 if self.name == "cfg2_416_c80_b64" else None
+
+    # -- N > 1: the sharded run against the single-GPU full batch ------------------------------------------------------------
+    def sharding_check(self):
+        """Outside the timed region rank 0 regenerates every rank's shard (seeds 1234 + r / 4321 + r), runs the GLOBAL
+        batch on one GPU, and compares: the all-reduced 20 loss floats (rtol 1e-6: per-rank partial sums are folded in
+        another order) and rank 0's own gradient shard (bit for bit).  yolov3_loss.py:111-112: the mean runs over the
+        whole batch."""
+        import torch.distributed as dist
+        torch, yv3 = self.torch, self.yv3
+        n, world = self.n, self.world
+        sharded = yv3.YOLOv3Loss(rectified_coord_num=self.w["rect"], **self.spec.loss_args)
+        total, grad = sharded.loss_and_grad(self.td, self.pd)        # NCCL all-reduce of the 20 floats inside
+        torch.cuda.synchronize()
+        res = None
+        if self.rank == 0:
+            try:
+                ps, ts = [], []
+                for r in range(world):
+                    p_np, t_np = synth(self.spec, n, self.m, r)
+                    ps.append(torch.from_numpy(p_np))
+                    ts.append(torch.from_numpy(t_np))
+                pfull, tfull = torch.cat(ps).to(self.dev), torch.cat(ts).to(self.dev)
+                full = yv3.YOLOv3Loss(rectified_coord_num=self.w["rect"], **self.spec.loss_args)
+                full.global_batch, full.auto_all_reduce = n * world, False
+                tot_f, grad_f = full.loss_and_grad(tfull, pfull)
+                a, b = sharded.loss_detail.double(), full.loss_detail.double()
+                rel = float(((a - b).abs() / b.abs().clamp_min(1e-30))[b.abs() > 1e-12].max()) if bool((b.abs() > 1e-12).any()) else 0.0
+                same = bool(torch.equal(grad, grad_f[:n]))
+                res = {"ok": bool(rel <= 1e-6 and same), "max_rel": rel, "grad_shard_bit_exact": same,
+                       "global_batch": n * world, "current_num_equal": sharded.current_num == full.current_num}
+                del pfull, tfull, grad_f
+            except Exception as e:                                 # noqa: BLE001
+                res = {"ok": False, "error": "%s: %s" % (type(e).__name__, str(e)[:200])}
+        dist.barrier()
+        return res
+
+
+def short_entry(arm, steps, peak):
+    """one extra workload: value, ms/step, the dominant kernel's roofline fraction (BASELINE configs[2], [4])"""
+    for _ in range(3):
+        arm.run(min(steps, arm.unroll))
+    arm.fence()
+    ms, timed = arm.time_steps(steps, min_ms=30.0)
+    sweep_ms = arm.time_sweep(10)
+    nbytes, kernel = arm.alg_bytes()
+    arm.pipe.check_status()
+    return {"workload": arm.name, "desc": arm.w["desc"], "per_gpu_batch": arm.n, "global_batch": arm.n * arm.world,
+            "scaling": "strong" if "global_batch" in arm.w else "weak",
+            "value": arm.world * arm.n / (ms * 1e-3), "unit": "images/s", "ms_per_step": ms, "timed_steps": timed,
+            "fused_sweep": bool(arm.pipe.last_fused) if arm.args.fused else False,
+            "roofline": {"kernel": kernel, "avg_launch_ms": sweep_ms, "algorithmic_bytes_per_launch": int(nbytes),
+                         "achieved": nbytes / (sweep_ms * 1e-3) / 1e9, "unit": "GB/s", "frac": nbytes / (sweep_ms * 1e-3) / 1e9 / peak},
+            "candidates_per_image": float(arm.counts.sum().item()) / arm.n}
 
 
 def main():
@@ -192,42 +597,25 @@ def main():
     ap.add_argument("--workload", default="cfg2_416_c80_b64", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--overlap", type=int, default=1, help="1: loss and post-process halves of a step on two streams")
-    ap.add_argument("--priority", default="post", choices=["none", "post", "loss"],
-                    help="which half of a step runs on a high-priority stream (two-stream mode)")
-    ap.add_argument("--layout", default="packed", choices=["packed", "heads"],
-                    help="packed: the reference's concatenated head tensor; heads: the three head tensors before "
-                         "yolov3_detector.py:80-85 packs them (yv3_loss_fwd_bwd_heads / yv3_filter_heads)")
-    ap.add_argument("--serialize-sweeps", type=int, default=-1,
-                    help="1: the two HBM-bound sweeps (dense pass, score pass) never run at the same time; the small "
-                         "kernels of either half run under the other half's sweep (default: on with the "
-                         "packed layout, where several steps share a graph; measured 142 -> 140.5 us/step)")
     ap.add_argument("--fused", type=int, default=1,
-                    help="1 (packed layout): loss fwd+bwd and the post-process filter of a step in one call that reads the "
-                         "head tensor once (yv3_loss_filter_fused); 0: the two sweeps as separate calls")
-    ap.add_argument("--fused-depth", type=int, default=3,
-                    help="workspace pairs the fused schedule alternates between (the assignment of step k + depth follows "
-                         "the fold of step k)")
-    ap.add_argument("--graph-steps", type=int, default=16, help="steps captured per CUDA graph (N = 1)")
-    ap.add_argument("--pipeline", type=int, default=1,
-                    help="1: the two streams are joined once per graph / timed region, 0: after every step")
-    ap.add_argument("--force-graph", action="store_true", help="skip the eager-vs-graph trial")
-    ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA-graph replay")
+                    help="1: FusedPipeline (loss fwd+bwd and the filter on one read of the head tensor, three streams); "
+                         "0: loss_and_grad, filter, nms as separate calls on one stream")
+    ap.add_argument("--fused-depth", type=int, default=3, help="workspace pairs the pipeline alternates between")
+    ap.add_argument("--graph-steps", type=int, default=16, help="steps captured per CUDA graph")
+    ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replays")
+    ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: peer = the peer-memory all-reduce kernel inside every step (falls back to nccl when the "
+                         "peers cannot be mapped); nccl = one NCCL all-reduce per graph replay, outside the graph")
+    ap.add_argument("--min-timed-ms", type=float, default=100.0)
+    ap.add_argument("--no-extras", action="store_true", help="skip extra_workloads, roofline_stages, probes")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     w = WORKLOADS[args.workload]
-    spec = build_spec(w) if args.impl == "reference" else product_spec(w)
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    if args.layout != "packed":
-        args.fused = 0
-    if args.fused:
-        args.serialize_sweeps = 0
-    if args.serialize_sweeps < 0:
-        args.serialize_sweeps = 1 if (args.layout == "packed" and args.overlap and args.pipeline) else 0
     if args.impl == "reference":
-        return run_reference(args, w, spec, rank, world)
+        return run_reference(args, w, build_spec(w), rank, world)
 
     import torch
     import torch.distributed as dist
@@ -236,419 +624,135 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU path in the product)"
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    reducer, reduce_mode = None, None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-    yv3.backend.set_epsilon(spec.eps)
-    n, m = w["batch"], w["m"]
-    p_np, t_np = synth(spec, n, m, rank)
-    p_host = torch.from_numpy(p_np).pin_memory()
-    t_host = torch.from_numpy(t_np).pin_memory()
-    pd, td = p_host.to(dev), t_host.to(dev)
-    loss = yv3.YOLOv3Loss(rectified_coord_num=w["rect"], **spec.loss_args)
-    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
-    # a second workspace pair for the fused schedule (steps alternate; the C ABI is re-entrant per workspace)
-    pairs = [(loss, post)]
-    for _ in range(max(args.fused_depth, 2) - 1 if args.fused else 0):
-        pairs.append((yv3.YOLOv3Loss(rectified_coord_num=w["rect"], **spec.loss_args),
-                      yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)))
+        if args.reduce == "peer" and args.fused:
+            reducer = yv3.PeerAllReduce.create(cap=512)
+        reduce_mode = "peer-memory kernel inside every step (yv3_peer_allreduce)" if reducer is not None else \
+            "NCCL all-reduce, once per graph replay (outside the graph)"
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
 
-    if args.fused:
-        # the one-sweep kernel covers the packed, aligned case up to 262144 tiles per call; beyond it the call runs the two
-        # sweeps itself, and the bench then schedules them as separate calls (--fused 0) and says so
-        loss.loss_grad_and_filter(td, pd, post, w["score_thresh"])
-        torch.cuda.synchronize()
-        if not loss.last_fused:
-            args.fused = 0
-            pairs = pairs[:1]
-            args.serialize_sweeps = 1 if (args.overlap and args.pipeline) else 0
-
-    def set_auto(v):
-        for lo, _ in pairs:
-            lo.auto_all_reduce = v
-
-    grad = torch.empty_like(pd)
-    cand = torch.empty((n, post.capacity, 8), dtype=torch.float32, device=dev)
-    counts = torch.empty((n, 3), dtype=torch.int32, device=dev)
-    keep = torch.empty((n, post.capacity), dtype=torch.uint8, device=dev)
-
-    post_stream = None
-    if args.overlap:
-        # the block scheduler serves the high-priority stream first whenever an SM slot frees up
-        post_stream = torch.cuda.Stream(priority=-1 if args.priority == "post" else 0)
-        aux_stream = torch.cuda.Stream(priority=-1 if args.priority == "post" else 0)       # fused schedule: assignment and fold
-        if args.priority == "loss":
-            torch.cuda.set_stream(torch.cuda.Stream(priority=-1))
-
-    heads = hgrads = None
-    if args.layout == "heads":
-        # the same logits as three contiguous head tensors (N, H, W, B*L): what the head convolutions emit
-        heads = []
-        for h in range(3):
-            gh, gw = spec.head_grid_sizes[h]
-            s0, s1 = spec.chan_base[h], spec.chan_base[h] + spec.head_channels[h]
-            heads.append(pd[..., s0:s1].reshape(n, gh, gw, -1).contiguous())
-        hgrads = [torch.empty_like(x) for x in heads]
-
-    def half_loss(events=None, sweep_after=None, sweep_done=None, out=None):
-        if sweep_after is not None or sweep_done is not None:
-            total, _ = loss.loss_and_grad(td, pd, grad_out=grad, sweep_after=sweep_after, sweep_done=sweep_done, out=out)
-            return total
-        if heads is not None and events is None:
-            total, _ = loss.loss_and_grad_heads(td, heads, grads_out=hgrads)
-            return total
-        total, _ = loss.loss_and_grad(td, pd, events=events, grad_out=grad, out=out)
-        return total
-
-    def half_post():
-        if heads is not None:
-            post.filter_heads(heads, w["score_thresh"], out=(cand, counts))
-        else:
-            post.filter(pd, w["score_thresh"], out=(cand, counts))
-        post.nms(cand, counts, w["nms_thresh"], out=keep)
-
-    def fused_steps(count, events=None, outs=None):
-        """`count` complete steps with the one-sweep call (yv3_loss_filter_fused issued phase by phase), two (loss,
-        post-process) workspace pairs alternating by step: the HBM-bound sweeps run back to back on the current stream,
-        the small kernels under them on two other streams (see below).  Every step does all of its work."""
-        thr = w["score_thresh"]
-        depth = len(pairs)
-        cur = torch.cuda.current_stream()
-        if post_stream is None or events is not None:
-            for k in range(count):
-                total, _, _, _ = loss.loss_grad_and_filter(td, pd, post, thr, grad_out=grad,
-                                                           out=None if outs is None else outs[k],
-                                                           filter_out=(cand, counts), events=events)
-                post.nms(cand, counts, w["nms_thresh"], out=keep)
-            return total
-
-        def part(k, phases):
-            lo, po = pairs[k % depth]
-            return lo.loss_grad_and_filter(td, pd, po, thr, grad_out=grad, out=None if outs is None else outs[k],
-                                           filter_out=(cand, counts), phases=phases)[0]
-
-        def assign(k):
-            with torch.cuda.stream(aux_stream):
-                part(k, 1)
-                e = torch.cuda.Event()
-                e.record(aux_stream)
-            return e
-
-        # three streams, `depth` workspace pairs used round-robin.  cur: the sweeps, back to back.  aux: fold(k) then
-        # assign(k + depth) -- the assignment rewrites the loss workspace step k used, so it follows that step's sweep and
-        # fold.  post: gather(k), sort, NMS(k); sweep(k + depth) rewrites the staging rows gather(k) reads, so it waits for
-        # that chain (long finished by then).  depth 3 instead of 2 gives the fold -> assignment chain a whole extra sweep
-        # of slack before sweep(k + depth) needs it (measured 104.8 -> 99.6 us/step at cfg2; depth 4: 99.2).
-        aux_stream.wait_stream(cur)
-        post_stream.wait_stream(cur)
-        a_done = [assign(j) if j < count else None for j in range(depth)]
-        g_done = [None] * depth
-        for k in range(count):
-            b = k % depth
-            cur.wait_event(a_done[b])
-            if g_done[b] is not None:
-                cur.wait_event(g_done[b])
-            part(k, 2)
-            swept = torch.cuda.Event()
-            swept.record(cur)
-            with torch.cuda.stream(post_stream):
-                post_stream.wait_event(swept)
-                part(k, 8)
-                pairs[b][1].nms(cand, counts, w["nms_thresh"], out=keep)
-                g_done[b] = torch.cuda.Event()
-                g_done[b].record(post_stream)
-            with torch.cuda.stream(aux_stream):
-                aux_stream.wait_event(swept)
-                total = part(k, 4)
-            if k + depth < count:
-                a_done[b] = assign(k + depth)
-        cur.wait_stream(post_stream)
-        cur.wait_stream(aux_stream)
-        return total
-
-    def steps(count, events=None, outs=None):
-        """`count` complete steps.  The training half (assignment, dense pass) and the inference half (filter, sort,
-        NMS) of a step share only their input, so they run on two streams.  --pipeline 1: the streams are joined once
-        per call (consecutive steps of either half queue behind each other, the latency-bound tail of one step's
-        post-process runs under the next step's sweeps); --pipeline 0: joined after every step."""
-        if args.fused:
-            return fused_steps(count, events, outs)
-        if post_stream is None or events is not None:
-            for k in range(count):
-                total = half_loss(events)
-                half_post()
-            return total
-        cur = torch.cuda.current_stream()
-        post_stream.wait_stream(cur)
-        dense_done = None
-        for k in range(count):
-            if args.serialize_sweeps and heads is None:
-                with torch.cuda.stream(post_stream):
-                    if dense_done is not None:
-                        post_stream.wait_event(dense_done)          # the score sweep waits for the previous dense sweep
-                    filt_done = torch.cuda.Event()
-                    post.filter(pd, w["score_thresh"], out=(cand, counts), sweep_done=filt_done)   # recorded after the sweep
-                    post.nms(cand, counts, w["nms_thresh"], out=keep)
-                dense_done = torch.cuda.Event()
-                total = half_loss(sweep_after=filt_done, sweep_done=dense_done,      # the dense sweep waits for the score sweep
-                                  out=None if outs is None else outs[k])
-                continue
-            with torch.cuda.stream(post_stream):
-                half_post()
-            total = half_loss(out=None if (outs is None or heads is not None) else outs[k])
-            if not args.pipeline:
-                cur.wait_stream(post_stream)
-                if k + 1 < count:
-                    post_stream.wait_stream(cur)
-        if args.pipeline:
-            cur.wait_stream(post_stream)
-        return total
-
-    def step(events=None):
-        return steps(1, events)
-
-    def fence():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # owned-label count for the algorithmic byte figure (SURVEY 8d): R = sum of `owned` flags
-    table, _ = loss.assign(td, pd)
-    owned = int(table[..., 3].sum().item())
-    loss.check_status()
-
+    arm = Arm(args.workload, args, rank, world, dev, reducer)
+    n, m = arm.n, arm.m
     sampler = ClockSampler(local_rank)
     sampler.start()
     sampler.mark = "warmup"
     for _ in range(args.warmup):
-        step()
-    fence()
-    # per-kernel view: eager launches with CUDA events around the dense sweep and the post-process (same K steps)
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    post_ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+        arm.run(1 if args.no_graph else min(arm.unroll, max(1, args.steps)))
+    arm.fence()
     sampler.mark = "kernels"
-    for k in range(args.steps):
-        step(ev[k])
-        post_ev[k].record()
-    fence()
-    dense_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
-    post_ms = float(np.mean([ev[k][1].elapsed_time(post_ev[k]) for k in range(args.steps)]))
-
-    # the timed region: the whole step (assignment, dense pass, all-reduce at N > 1, filter, NMS) captured once in a
-    # CUDA graph and replayed K times -- the launch-bound host loop is out of the way, the device work is identical
-    graph, mode = None, "eager"
-    # several steps per graph (no collective inside at N = 1): consecutive steps overlap like eager launches do
-    # N > 1: the NCCL call stays outside the graph (a collective inside the capture hung in round 1); the steps of a
-    # graph write their 20 loss floats into the rows of one buffer, which is all-reduced once after the replay
-    unroll = args.graph_steps if (world == 1 or args.layout == "packed") else 1
-    loss_rows = torch.zeros((unroll, 20), dtype=torch.float32, device=dev) if world > 1 else None
-    if not args.no_graph:
-        try:
-            set_auto(False)                           # the collective stays outside the graph
-            side = torch.cuda.Stream()
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(side):
-                step()
-            torch.cuda.current_stream().wait_stream(side)
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                steps(unroll, outs=loss_rows)
-            mode = "cuda-graph replay, %d step(s) per graph" % unroll + (
-                " + one eager NCCL all-reduce of the graph's %d x 20 loss floats" % unroll if world > 1 else "")
-        except Exception as e:
-            graph, mode = None, "eager (graph capture failed: %s)" % type(e).__name__
-            torch.cuda.synchronize()
-    if graph is None:
-        set_auto(True)
-
-    def run(count):
-        """exactly `count` steps"""
-        if graph is None:
-            steps(count)
-            return
-        for _ in range(count // unroll):
-            graph.replay()
-            if world > 1:
-                dist.all_reduce(loss_rows)
-        rest = count % unroll
-        if rest:
-            set_auto(True)
-            steps(rest)
-            set_auto(False)
-    run(3 * unroll)
-    fence()
-    if graph is not None and not args.force_graph:
-        # launch mode by trial: the host may launch eagerly fast enough for consecutive steps to overlap better than
-        # graph replays do; 20 steps each, the faster one is used for the timed region
-        def trial(fn):
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            fence()
-            a.record()
-            fn()
-            b.record()
-            fence()
-            return a.elapsed_time(b)
-
-        def eager20():
-            set_auto(True)
-            steps(20)
-            set_auto(False)
-
-        t_graph = trial(lambda: run(20 - 20 % unroll))
-        t_eager = trial(eager20)
-        verdict = torch.tensor([t_graph, t_eager], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(verdict, op=dist.ReduceOp.MAX)
-        if float(verdict[1]) < float(verdict[0]):
-            graph, mode = None, "eager launches (faster than graph replay in a 20-step trial: %.1f vs %.1f us/step)" % (
-                1e3 * float(verdict[1]) / 20, 1e3 * float(verdict[0]) / (20 - 20 % unroll))
-            set_auto(True)
-    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sweep_ms = arm.time_sweep(min(max(args.steps, 5), 50))
+    arm.fence()
     sampler.mark = "timed"
-    start.record()
-    run(args.steps)
-    stop.record()
-    fence()
+    ms_per_step, timed_steps = arm.time_steps(args.steps, args.min_timed_ms)
     sampler.mark = "after"
-    total_ms = start.elapsed_time(stop)
-    for lo, po in pairs:
-        lo.check_status()
-        po.check_status()
-    cand_per_image = float(counts.sum().item()) / n
-    kept_per_image = float(sum(int(keep[i, :int(counts[i].sum())].sum()) for i in range(min(n, 8)))) / min(n, 8)
-
-    # ---- end to end through the public API with host buffers -------------------------------------------
-
-    set_auto(True)
-
-    # Double-buffered: the host->device copy of step k + 1 (copy stream) runs while step k computes; the caller reads
-    # step k - 1's loss and detections from pinned host memory once that step's device->host copies have landed.
-    # Every step's inputs cross PCIe inside the timed region and every step's results are read on the host.
-    copy_stream = torch.cuda.Stream()
-    pbuf = [torch.empty_like(pd) for _ in range(2)]
-    tbuf = [torch.empty_like(td) for _ in range(2)]
-    out_hosts = [torch.empty(20, dtype=torch.float32).pin_memory() for _ in range(2)]
-    counts_hosts = [torch.empty((n, 3), dtype=torch.int32).pin_memory() for _ in range(2)]
-    keep_hosts = [torch.empty((n, post.capacity), dtype=torch.uint8).pin_memory() for _ in range(2)]
-
-    def e2e_run(count):
-        main = torch.cuda.current_stream()
-        done = [None, None]
-        read = 0.0
-        for k in range(count):
-            b = k & 1
-            with torch.cuda.stream(copy_stream):
-                if done[b] is not None:
-                    copy_stream.wait_event(done[b])                   # step k - 2 is finished with this buffer pair
-                pbuf[b].copy_(p_host, non_blocking=True)              # pinned host -> device, every step
-                tbuf[b].copy_(t_host, non_blocking=True)
-                ready = torch.cuda.Event()
-                ready.record(copy_stream)
-            main.wait_event(ready)
-            if args.fused:
-                total, _, _, _ = loss.loss_grad_and_filter(tbuf[b], pbuf[b], post, w["score_thresh"], grad_out=grad,
-                                                           filter_out=(cand, counts))
-            else:
-                total, _ = loss.loss_and_grad(tbuf[b], pbuf[b], grad_out=grad)
-                post.filter(pbuf[b], w["score_thresh"], out=(cand, counts))
-            post.nms(cand, counts, w["nms_thresh"], out=keep)
-            out_hosts[b][:18].copy_(loss.loss_detail.reshape(-1), non_blocking=True)
-            out_hosts[b][18:19].copy_(total.reshape(1), non_blocking=True)
-            counts_hosts[b].copy_(counts, non_blocking=True)
-            keep_hosts[b].copy_(keep, non_blocking=True)
-            done[b] = torch.cuda.Event()
-            done[b].record(main)
-            if k > 0:
-                done[b ^ 1].synchronize()                             # the caller reads step k - 1's results
-                read += float(out_hosts[b ^ 1][18]) + float(counts_hosts[b ^ 1][0, 0])
-        done[(count - 1) & 1].synchronize()
-        read += float(out_hosts[(count - 1) & 1][18])
-        return read
+    arm.pipe.check_status()
+    if reducer is not None:
+        reducer.check_status()
+    cand_per_image = float(arm.counts.sum().item()) / n
+    kept_per_image = float(sum(int(arm.keep[i, :int(arm.counts[i].sum())].sum()) for i in range(min(n, 8)))) / min(n, 8)
+    fused_ran = bool(arm.pipe.last_fused) if args.fused else False
 
     sampler.mark = "e2e"
-    e2e_run(3)
-    fence()
-    e2e_steps = args.steps
-    s2, t2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s2.record()
-    e2e_run(e2e_steps)
-    t2.record()
-    fence()
-    e2e_ms = s2.elapsed_time(t2)
+    e2e_steps = min(args.steps, 100)
+    e2e_ms = arm.time_e2e(e2e_steps)
+    probe = arm.h2d_probe() if not args.no_extras else None
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
-    times = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
+    stages, owned, check = None, 0, None
+    if not args.no_extras:
+        stages, owned = arm.stage_rooflines(peak)
     if world > 1:
-        dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = float(times[0]), float(times[1])
+        check = arm.sharding_check()
+    extras = []
+    if not args.no_extras:
+        mode = arm.launch_mode()
+        del arm.graphs
+        arm.graphs = {}
+        for name in EXTRA_WORKLOADS:
+            if name == args.workload or WORKLOADS[name].get("global_batch", world) % world:
+                continue
+            torch.cuda.empty_cache()
+            try:
+                extra = Arm(name, args, rank, world, dev, reducer, pin=False)
+                extras.append(short_entry(extra, 32, peak))
+                del extra
+            except Exception as e:                                 # noqa: BLE001
+                extras.append({"workload": name, "error": "%s: %s" % (type(e).__name__, str(e)[:200])})
+    else:
+        mode = arm.launch_mode()
 
     if rank == 0:
-        A, L, C = spec.anchors_per_image, spec.box_len, spec.class_num
-        alg_per_image = 4 * A * 5 + 4 * A * L + 4 * (owned / n) * C + 4 * m * 5          # SURVEY 8(d)
-        kernel_name = "loss_dense_kernel"
-        if args.fused:
-            # the fused sweep does the loss sweep's AND the score sweep's work: SURVEY 8(d)'s figures for the two added
-            # up with the tensor read counted once -- 4 A L in (every class logit feeds max / arg-max), 4 A L out
-            # (the dense gradient), the labels; the survivors' staging rows are noise
-            alg_per_image = 4 * A * L + 4 * A * L + 4 * m * 5
-            kernel_name = "fused_sweep_kernel"
-            assert all(lo.last_fused for lo, _ in pairs), "the fused call fell back to the two sweeps"
-        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-        if os.path.exists(peaks_path):
-            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-        else:
-            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        achieved = alg_per_image * n / (dense_ms * 1e-3) / 1e9
-        traffic = None
+        nbytes, kernel_name = arm.alg_bytes(owned)
+        achieved = nbytes / (sweep_ms * 1e-3) / 1e9
+        traffic, traffic_note = None, None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(args.workload, {}).get(kernel_name + "_dram_bytes_per_launch")
+            tj = json.load(open(tp))
+            traffic = tj.get(args.workload, {}).get(kernel_name + "_dram_bytes_per_launch")
+            sha = git_sha()
+            traffic_note = {"captured_at_sha": tj.get("sha"), "captured_on": tj.get("date"), "bench_sha": sha,
+                            "stale": bool(tj.get("sha") and sha and tj.get("sha") != sha),
+                            "how": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture per workload "
+                                   "(tools/run_final.sh regenerates profiles/traffic.json)"}
+        A, L = arm.spec.anchors_per_image, arm.spec.box_len
         line = {
             "metric": "head loss fwd+bwd + decode+filter+NMS throughput",
-            "value": world * n * args.steps / (total_ms * 1e-3), "unit": "images/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "desc": w["desc"], "per_gpu_batch": n, "global_batch": n * world,
-                       "label_slots": m, "score_thresh": w["score_thresh"], "nms_thresh": w["nms_thresh"],
-                       "parallelism": "batch-sharded dp%d, the 20 loss floats of every step all-reduced over NCCL "
-                                      "(one call per graph replay / per eager step)" % world,
-                       "l2": "inputs larger than L2: predicts %.0f MB + gradient %.0f MB per GPU vs 126 MB L2" % (
-                           pd.numel() * 4 / 1e6, grad.numel() * 4 / 1e6),
-                       "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image,
-                       "layout": args.layout, "fused_sweep": bool(args.fused), "serialize_sweeps": bool(args.serialize_sweeps), "launch": mode, "streams": (3 if args.fused else 2) if args.overlap else 1,
-                       "high_priority_stream": args.priority if args.overlap else None,
-                       "fused_schedule": "three streams: sweeps back to back; fold of step k and assignment of step k+depth; "
-                                         "gather/sort/NMS of step k (the last two at high priority); %d workspaces alternating" % len(pairs) if (args.fused and args.overlap) else None,
-                       "stream_join": ("once per %d-step graph" % unroll if graph is not None else "once per timed region")
-                       if (args.overlap and args.pipeline) else "every step"},
-            "stage_ms": {kernel_name: dense_ms, ("fold_gather_sort_nms" if args.fused else "filter_plus_nms"): post_ms,
-                         "step_minus_stages": total_ms / args.steps - dense_ms - post_ms,
-                         "note": "stage times from eager single-stream launches with events; ms_per_step from the timed "
-                                 "region (step_minus_stages < 0: the two halves overlap on two streams; it also holds "
-                                 "the assignment and fold kernels)"},
+            "value": world * n / (ms_per_step * 1e-3), "unit": "images/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "timed_steps": timed_steps, "timed_region_ms": ms_per_step * timed_steps,
+            "higher_is_better": True, "scaling": "strong" if "global_batch" in w else "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": config_block(args.workload, w, n, world, {
+                "parallelism": "batch-sharded dp%d; the 20 loss floats of every step summed over the ranks: %s" % (world, reduce_mode)
+                               if world > 1 else "dp1",
+                "l2": "inputs larger than L2: predicts %.0f MB + gradient %.0f MB per GPU vs 126 MB L2" % (
+                    arm.pd.numel() * 4 / 1e6, arm.grad.numel() * 4 / 1e6),
+                "candidates_per_image": cand_per_image, "kept_per_image": kept_per_image,
+                "layout": "packed", "fused_sweep": fused_ran, "launch": mode,
+                "schedule": ("FusedPipeline: three streams (sweeps back to back; fold of step k and assignment of step k+depth; "
+                             "gather/sort/NMS of step k at high priority), %d workspace pairs" % len(arm.pipe.pairs))
+                if args.fused else "separate calls on one stream"}),
+            "stage_ms": {kernel_name: sweep_ms, "step": ms_per_step,
+                         "note": "the sweep alone from eager launches with events; ms_per_step from the timed region, where "
+                                 "the small kernels run under the next step's sweep"},
             "roofline": {"kernel": kernel_name, "bound": "hbm", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_per_image * n, "avg_launch_ms": dense_ms,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_note,
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": int(nbytes), "avg_launch_ms": sweep_ms,
+                         "whole_step_frac": nbytes / (ms_per_step * 1e-3) / 1e9 / peak,
                          "dense_2x4AL_bytes_per_launch_for_context": 8 * A * L * n},
-            "e2e": {"value": world * n * e2e_steps / (e2e_ms * 1e-3), "unit": "images/s",
-                    "h2d_bytes_per_step": int(p_host.numel() * 4 + t_host.numel() * 4),
-                    "d2h_bytes_per_step": int(19 * 4 + counts_hosts[0].numel() * 4 + keep_hosts[0].numel()),
+            "roofline_stages": stages,
+            "e2e": {"value": world * n / (e2e_ms * 1e-3), "unit": "images/s",
+                    "h2d_bytes_per_step": arm.e2e_h2d, "d2h_bytes_per_step": arm.e2e_d2h,
+                    "returned": "20 loss floats, per-head counts, keep flags, candidate rows and the resized kept rows "
+                                "(yv3_collect_kept) of every image; the gradient (%.0f MB) stays on the device for the "
+                                "model's backward" % (arm.grad.numel() * 4 / 1e6),
                     "pipelining": "double-buffered: the copy of step k+1 overlaps the compute of step k; results of "
                                   "step k-1 are read on the host every step",
-                    "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
-            # assign, dense sweep, fold, score, gather, sort, nms x2 (the sweeps run once per head tensor in the heads layout)
-            # fused: assign, fused sweep, fold, gather, sort, nms x2
-            "gpu_launches": (12 if args.layout == "heads" else 7 if args.fused else 8) * args.steps,
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "h2d_probe": probe,
+                    "frac_of_h2d_probe": (arm.e2e_h2d / (e2e_ms * 1e-3) / 1e9) / probe["per_rank_gbs"] if probe else None},
+            # fused: assign, fused sweep, fold, gather, sort, warp NMS, cluster NMS (+ the peer all-reduce at N > 1)
+            "gpu_launches": ((7 + (1 if reducer is not None else 0)) if args.fused else 8) * timed_steps,
             "clocks": sampler.summary(),
+            "extra_workloads": extras,
         }
+        if check is not None:
+            line["sharding_check"] = check
         if world == 1 and not args.no_cpu_baseline:
-            v, s, cores = time_cpu_port(build_spec(w), p_np, t_np, w, args.cpu_budget)       # the oracle enters here only
+            v, s, cores = time_cpu_port(build_spec(w), arm.p_np, arm.t_np, w, args.cpu_budget)   # the oracle enters here only
             line["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
                                     "sample": "%d of %d images, one pass (oracle port: torch-CPU fp32 loss + autograd, "
                                               "NumPy decode/filter, Python NMS as run.py runs it)" % (s, n)}
         print(json.dumps(line), flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

@@ -492,7 +492,7 @@ def test_nms_dense_medium_segments_take_the_warp_path(yv3, thr):
 def test_nms_single_class_of_8000_candidates(yv3):
     """class_num 0 with a low threshold puts every candidate of an image in ONE segment (the cluster kernel's case)."""
     import bench
-    spec = bench.build_spec(bench.WORKLOADS["cfg5_512_c0_b16"])
+    spec = bench.build_spec(bench.WORKLOADS["cfg5_nms_stress_b16"])
     post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
     rng = np.random.default_rng(12)
     n, k = 2, 8200

@@ -1,5 +1,5 @@
 # developer helper: one short bench line per workload (GPU box)
-for w in cfg2_416_c80_b64 cfg3_608_c80_b64 cfg4_416_c80_b256_dense cfg5_512_c0_b16; do
+for w in cfg2_416_c80_b64 cfg3_608_c80_b64 cfg4_416_c80_b256_dense cfg5_512_c0_g128 cfg5_nms_stress_b16; do
   timeout 300 python bench.py --workload $w --steps 20 --warmup 3 --no-cpu-baseline 2>&1 | tail -1 | python -c "
 import sys, json
 l = sys.stdin.readline()
