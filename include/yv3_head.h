@@ -240,6 +240,29 @@ int yv3_collect_kept(const float* cand, const int32_t* counts, const uint8_t* ke
                      double target_w, double target_h, int bug_compat, double* rows_out, int32_t* counts_out,
                      void* stream);
 
+/* ---- evaluation after NMS: AP / mAP accumulation on the device ---------------------------------------
+ * The reference leaves this as a TODO that names the third-party tool Cartucho/mAP (run.py:78-79, README.md:137; not
+ * vendored, no version pinned).  These entry points run that tool's published algorithm (main.py: per class, detections
+ * by confidence descending, each matched to the ground-truth box of its image and class with the largest IoU, true
+ * positive iff IoU >= min_overlap and the box is not yet claimed; VOC2012 all-point AP; mAP over the classes that have
+ * ground truth) on the rows yv3_collect_kept leaves on the device and the label batch the loss takes.
+ *   yv3_map_state_bytes   bytes of the accumulator for up to max_detections kept rows over the whole evaluation
+ *   yv3_map_reset         start an evaluation (zeroes the counters)
+ *   yv3_map_accumulate    one batch: kept_rows (n, capacity, 9) float64 and kept_counts (n, 3) as written by
+ *                         yv3_collect_kept (boxes in pixels of image_w x image_h); targets (n, m * 5) fp32 as the loss
+ *                         takes them ([x, y, w, h, class] normalised, -1 padded; boxes become pixels as (x -+ w/2) * image_w);
+ *                         image_base = index of the batch's first image in the evaluation (ties keep image order);
+ *                         pixel_inclusive != 0: the tool's "+1" box widths; score_col 7 (conf * prob) or 4 (conf);
+ *                         class_agnostic != 0: every box is class 0 (class_num 0 heads)
+ *   yv3_map_finalize      ap_out[num_classes] (AP, -1 for a class without ground truth), gt_count_out[num_classes] (may be
+ *                         NULL), map_out2[2] = {mAP, 1.0 if more than max_detections rows arrived}.  Ends the evaluation. */
+int yv3_map_state_bytes(int max_detections, int num_classes, size_t* bytes);
+int yv3_map_reset(void* state, size_t state_bytes, int max_detections, int num_classes, void* stream);
+int yv3_map_accumulate(const double* kept_rows, const int32_t* kept_counts, int n, int32_t capacity, const float* targets,
+                       int m, double image_w, double image_h, int image_base, double min_overlap, int pixel_inclusive,
+                       int score_col, int class_agnostic, void* state, void* stream);
+int yv3_map_finalize(void* state, int num_classes, double* ap_out, int32_t* gt_count_out, double* map_out2, void* stream);
+
 /* ---- the one exchange step of the sharded path: the batch mean of yolov3/yolov3_loss.py:112 over ALL shards ----------
  * Sum of every rank's loss rows (20 floats per step: 18 detail values, their sum, a pad) over the GPUs of one NVLink
  * domain, as ONE kernel over peer-mapped memory (csrc/peer_reduce.cu): ranks push their rows into each other's

@@ -23,6 +23,7 @@ from .yolov3_loss import YOLOv3Loss  # noqa: F401
 from .yolov3_post_process import HeadPostProcessor, YOLOv3PostProcessor  # noqa: F401
 from .pipeline import FusedPipeline  # noqa: F401
 from .peer_reduce import PeerAllReduce  # noqa: F401
+from .map_eval import MeanAPAccumulator  # noqa: F401
 
-__all__ = ["YOLOv3Decoder", "LabelDecoder", "LabelBatcher", "parse_label_line", "read_label_file", "YOLOv3Loss", "YOLOv3PostProcessor", "HeadPostProcessor", "FusedPipeline", "PeerAllReduce", "backend", "to_device",
+__all__ = ["YOLOv3Decoder", "LabelDecoder", "LabelBatcher", "parse_label_line", "read_label_file", "YOLOv3Loss", "YOLOv3PostProcessor", "HeadPostProcessor", "FusedPipeline", "PeerAllReduce", "MeanAPAccumulator", "backend", "to_device",
            "detail_log_values", "detail_scalars", "format_detail"]

@@ -86,6 +86,11 @@ _SIGNATURES = {
                                              ctypes.c_float, _P, _P, _P, ctypes.c_size_t, ctypes.c_float, _P,
                                              ctypes.c_int32, _P, _P, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int32),
                                              ctypes.c_int, _P]),
+    "yv3_map_state_bytes": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_size_t)]),
+    "yv3_map_reset": (ctypes.c_int, [_P, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, _P]),
+    "yv3_map_accumulate": (ctypes.c_int, [_P, _P, ctypes.c_int, ctypes.c_int32, _P, ctypes.c_int, ctypes.c_double, ctypes.c_double,
+                                          ctypes.c_int, ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_int, _P, _P]),
+    "yv3_map_finalize": (ctypes.c_int, [_P, ctypes.c_int, _P, _P, _P, _P]),
     "yv3_peer_mailbox_bytes": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_size_t)]),
     "yv3_peer_allreduce": (ctypes.c_int, [ctypes.POINTER(_P), ctypes.c_int, ctypes.c_int, ctypes.c_int, _P, ctypes.c_int, _P, _P]),
     "yv3_peer_status": (ctypes.c_int, [_P, _P]),
