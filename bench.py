@@ -528,6 +528,39 @@ class Arm(object):
                   "events include the allocation of the nine output tensors by torch's caching allocator")
         except Exception as e:                                     # noqa: BLE001
             out["decode_kernel"] = {"error": type(e).__name__}
+        # the un-packed layout (the three head tensors before yolov3_detector.py:80-85 concatenates them): the one-sweep
+        # kernel once per head tensor (yv3_loss_filter_fused_heads), a whole step on one stream, against the packed call
+        try:
+            heads = []
+            for h in range(3):
+                gh, gw = self.spec.head_grid_sizes[h]
+                s0, s1 = self.spec.chan_base[h], self.spec.chan_base[h] + self.spec.head_channels[h]
+                heads.append(self.pd[..., s0:s1].reshape(n, gh, gw, -1).contiguous())
+            hgrads = [torch.empty_like(x) for x in heads]
+            lo2 = yv3.YOLOv3Loss(rectified_coord_num=self.w["rect"], **self.spec.loss_args)
+            lo2.auto_all_reduce = False
+
+            def step_heads(e):
+                e[0].record()
+                lo2.loss_grad_and_filter_heads(self.td, heads, self.post, self.w["score_thresh"], grads_out=hgrads,
+                                               filter_out=(self.cand, self.counts))
+                self.post.nms(self.cand, self.counts, self.w["nms_thresh"], out=self.keep)
+                e[1].record()
+
+            def step_packed(e):
+                e[0].record()
+                lo.loss_grad_and_filter(self.td, self.pd, self.post, self.w["score_thresh"], grad_out=self.grad,
+                                        filter_out=(self.cand, self.counts))
+                self.post.nms(self.cand, self.counts, self.w["nms_thresh"], out=self.keep)
+                e[1].record()
+            ms_h, ms_p = timed(step_heads), timed(step_packed)
+            out["heads_layout_step"] = {"ms_per_step_heads": ms_h, "ms_per_step_packed": ms_p, "fused_sweep": bool(lo2.last_fused),
+                                        "note": "one whole step (assignment, sweep(s), fold, gather, sort, NMS) issued serially on one "
+                                                "stream: three head tensors through yv3_loss_filter_fused_heads vs the packed tensor "
+                                                "through yv3_loss_filter_fused; the heads form saves the concatenate copy upstream"}
+            del heads, hgrads
+        except Exception as e:                                     # noqa: BLE001
+            out["heads_layout_step"] = {"error": "%s: %s" % (type(e).__name__, str(e)[:120])}
         return out, owned
 
     def pattern_floor_us(self):

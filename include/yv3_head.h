@@ -215,6 +215,17 @@ int yv3_loss_filter_fused(const yv3_config* cfg, const float* predicts, const fl
                           int32_t capacity, int32_t* counts, void* post_workspace, size_t post_workspace_bytes,
                           int32_t* fused_out, int phases, void* stream);
 
+/* yv3_loss_filter_fused on the three head tensors BEFORE yolov3/yolov3_detector.py:80-85 packs them (head_predicts /
+ * head_grads as for yv3_loss_fwd_bwd_heads): the one-sweep kernel runs once per head tensor, so an evaluation-while-
+ * training step neither concatenates the heads nor reads any of them twice.  Gradients, candidate rows and counts are
+ * bit-identical to yv3_loss_fwd_bwd_heads + yv3_filter_heads, to which the call falls back (same results) when a head
+ * tensor is not 16-byte aligned or has fewer than 32 records per image; *fused_out says which ran. */
+int yv3_loss_filter_fused_heads(const yv3_config* cfg, const float* const head_predicts[3], const float* targets, int n,
+                                int m, int n_global, int rectified_active, float upstream, float* loss_out20,
+                                float* const head_grads[3], void* loss_workspace, size_t loss_workspace_bytes,
+                                float score_thresh, float* cand, int32_t capacity, int32_t* counts, void* post_workspace,
+                                size_t post_workspace_bytes, int32_t* fused_out, int phases, void* stream);
+
 /* Class-aware greedy NMS, YOLOv3PostProcessor._apply_nms (yolov3/yolov3_post_process.py:108-159), for
  * n independent candidate lists.  cand is (n, capacity, 8) fp32; list i holds
  * sum(counts[i*count_cols .. +count_cols)) rows (pass yv3_filter_packed's (n,3) counts with

@@ -202,6 +202,47 @@ def test_loss_on_unpacked_head_tensors(yv3, name, rect):
         assert total_f.item() == total.item()
 
 
+@pytest.mark.parametrize("rect", [False, True])
+@pytest.mark.parametrize("name", ["coco_64x96_c4", "coco_128_c3_focal_tiou", "shipped_384x480_c0", "coco_96x64_c13", "coco_416_c80"])
+def test_fused_sweep_on_unpacked_head_tensors(yv3, name, rect):
+    """SURVEY 8f rank 2, fused form (yv3_loss_filter_fused_heads): loss fwd+bwd and the filter on ONE read of each head
+    tensor -- gradients, candidate rows and counts bit-identical to the per-head separate sweeps, which the packed calls
+    and the reference fixtures pin; the loss sums fold in another fixed order."""
+    spec, p, t = _inputs(name, 3, 8)
+    yv3.backend.set_epsilon(spec.eps)
+    n = p.shape[0]
+    heads = [torch.from_numpy(np.ascontiguousarray(h.reshape(n, h.shape[1], h.shape[2], -1))).cuda() for h in rn.unpack(p, spec)]
+    td = torch.from_numpy(t).cuda()
+    thr = 0.05
+    post = yv3.HeadPostProcessor(spec.head_grid_sizes, spec.class_num, spec.anchor_boxes)
+    sep = yv3.YOLOv3Loss(rectified_coord_num=(0 if rect else -1), **product_loss_args(spec))
+    total_s, grads_s = sep.loss_and_grad_heads(td, heads)
+    detail_s = sep.loss_detail.clone()
+    cand_s, counts_s = post.filter_heads(heads, thr)
+    cand_s, counts_s = cand_s.clone(), counts_s.clone()
+    fus = yv3.YOLOv3Loss(rectified_coord_num=(0 if rect else -1), **product_loss_args(spec))
+    total_f, grads_f, cand_f, counts_f = fus.loss_grad_and_filter_heads(td, heads, post, thr)
+    fus.check_status()
+    post.check_status()
+    assert fus.last_fused == (min(spec.head_grid_sizes[2][0] * spec.head_grid_sizes[2][1] * spec.box_num[2], 32) == 32)
+    for h in range(3):
+        assert torch.equal(grads_f[h], grads_s[h]), "gradient of head %d differs" % h
+    assert torch.equal(counts_f, counts_s)
+    for i in range(n):
+        k = int(counts_s[i].sum())
+        assert torch.equal(cand_f[i, :k], cand_s[i, :k])
+    np.testing.assert_allclose(fus.loss_detail.cpu().numpy(), detail_s.cpu().numpy(), rtol=2e-6, atol=1e-7)
+    assert fus.current_num == sep.current_num
+    # phase by phase (a scheduler's view): same bits
+    fus2 = yv3.YOLOv3Loss(rectified_coord_num=(0 if rect else -1), **product_loss_args(spec))
+    grads_2 = [torch.empty_like(h) for h in heads]
+    cand_2, counts_2 = torch.empty_like(cand_s), torch.empty_like(counts_s)
+    for ph in (1, 2, 8, 4):
+        fus2.loss_grad_and_filter_heads(td, heads, post, thr, phases=ph, grads_out=grads_2, filter_out=(cand_2, counts_2))
+    assert all(torch.equal(a, b) for a, b in zip(grads_2, grads_s)) and torch.equal(counts_2, counts_s)
+    assert torch.equal(fus2.loss_detail, fus.loss_detail)
+
+
 def test_unpacked_head_tensors_at_the_benchmark_shape(yv3):
     import bench
     w = bench.WORKLOADS["cfg2_416_c80_b64"]

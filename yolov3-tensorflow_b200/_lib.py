@@ -94,6 +94,10 @@ _SIGNATURES = {
     "yv3_peer_mailbox_bytes": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_size_t)]),
     "yv3_peer_allreduce": (ctypes.c_int, [ctypes.POINTER(_P), ctypes.c_int, ctypes.c_int, ctypes.c_int, _P, ctypes.c_int, _P, _P]),
     "yv3_peer_status": (ctypes.c_int, [_P, _P]),
+    "yv3_loss_filter_fused_heads": (ctypes.c_int, [_P, ctypes.POINTER(_P), _P, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                   ctypes.c_float, _P, ctypes.POINTER(_P), _P, ctypes.c_size_t, ctypes.c_float, _P,
+                                                   ctypes.c_int32, _P, _P, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int32),
+                                                   ctypes.c_int, _P]),
     "yv3_nms": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int32, ctypes.c_int,
                                ctypes.c_double, _P, _P, ctypes.c_size_t, _P]),
 }

@@ -184,6 +184,10 @@ static int span_tiles(const Geo& g, const ScoreTiles& q) {
     return (int)S;
 }
 
+int packed_tile_count(const Geo& g, const float* predicts, int n, float thresh) {
+    return packed_score_tiles(g, predicts, n, thresh).num_tiles;
+}
+
 int fused_row_count(const Geo& g, const float* predicts, int n, float thresh) {
     const ScoreTiles q = packed_score_tiles(g, predicts, n, thresh);
     const int S = span_tiles(g, q);

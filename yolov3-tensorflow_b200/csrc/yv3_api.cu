@@ -560,6 +560,97 @@ int yv3_collect_kept(const float* cand, const int32_t* counts, const uint8_t* ke
     return YV3_OK;
 }
 
+int yv3_loss_filter_fused_heads(const yv3_config* cfg, const float* const head_predicts[3], const float* targets, int n,
+                                int m, int n_global, int rectified_active, float upstream, float* loss_out20,
+                                float* const head_grads[3], void* loss_workspace, size_t loss_workspace_bytes,
+                                float score_thresh, float* cand, int32_t capacity, int32_t* counts, void* post_workspace,
+                                size_t post_workspace_bytes, int32_t* fused_out, int phases, void* stream) {
+    if ((phases & 15) == 0) return YV3_ERR_SHAPE;
+    if (!head_predicts || !head_grads) return YV3_ERR_NULL;
+    int rc = loss_common_checks(cfg, head_predicts[0], targets, n, m, loss_workspace, loss_workspace_bytes);
+    if (rc != YV3_OK) return rc;
+    if (!loss_out20 || !cand || !counts) return YV3_ERR_NULL;
+    if (!aligned16(cand)) return YV3_ERR_ALIGN;
+    if (n_global < n) return YV3_ERR_SHAPE;
+    if ((long long)n * yv3_records_per_image(cfg) >= (1LL << 31)) return YV3_ERR_CAPACITY;
+    for (int h = 0; h < 3; ++h) {
+        if (!head_predicts[h] || !head_grads[h]) return YV3_ERR_NULL;
+        if (!aligned4(head_predicts[h]) || !aligned16(head_grads[h])) return YV3_ERR_ALIGN;
+    }
+    PostWs pws;
+    rc = post_checks(cfg, n, capacity, post_workspace, post_workspace_bytes, &pws);
+    if (rc != YV3_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const Geo g = make_geo(cfg);
+    Workspace ws = carve_workspace(loss_workspace, n, m, g.rpi);
+    const char* dbg = getenv("YV3_DEBUG");
+    const int debug = dbg ? atoi(dbg) : 0;
+    // every head tensor is a packed tensor of a geometry that has just that head (yolov3_detector.py:80-85 without the
+    // concatenate): the one-sweep kernel runs once per tensor, on that tensor's object bits, tile range and partial rows
+    Geo gh[3];
+    uint32_t* bits[3];
+    DenseArgs d[3];
+    bool fused = heads_tr(g, n) == 32;
+    {
+        size_t word = 0;
+        for (int h = 0; h < 3; ++h) {
+            gh[h] = head_geo(g, h);
+            bits[h] = ws.objbits + word;
+            word += (size_t)(((long long)n * gh[h].rpi + 31) / 32 + 1);
+            memset(&d[h], 0, sizeof(DenseArgs));
+            d[h].predicts = head_predicts[h]; d[h].grad = head_grads[h];
+            d[h].own = ws.own; d[h].img_terms = ws.img_terms; d[h].partials = ws.partials; d[h].status = ws.status;
+            d[h].objbits = bits[h]; d[h].gtab = ws.gtab; d[h].vcount = ws.vcount; d[h].fold_slices = ws.fold_slices;
+            d[h].detail = loss_out20;
+            d[h].n = n; d[h].m = m; d[h].n_global = n_global;
+            d[h].kappa = upstream / (float)n_global; d[h].upstream = upstream;
+            for (int k = 0; k < 3; ++k) d[h].rect_c[k] = (upstream * g.rw[k]) / (float)n_global;
+            d[h].rect_active = rectified_active ? 1 : 0;
+            d[h].debug = debug;
+            d[h].vec_ok = (aligned16(head_predicts[h]) && !(debug & 1)) ? 1 : 0;
+            fused = fused && fused_sweep_supported(gh[h], d[h], n, score_thresh);
+        }
+    }
+    int rows_total = 0;
+    for (int h = 0; h < 3 && fused; ++h) rows_total += fused_row_count(gh[h], head_predicts[h], n, score_thresh);
+    if (rows_total > kMaxGrid) fused = false;
+    if (fused_out) *fused_out = fused ? 1 : 0;
+    if (!fused) {
+        // the two sweeps per head tensor, same results (unaligned tensors, a head with fewer than 32 records per image)
+        rc = yv3_loss_fwd_bwd_heads(cfg, head_predicts, targets, n, m, n_global, rectified_active, upstream, loss_out20,
+                                    head_grads, loss_workspace, loss_workspace_bytes, phases & 7, stream);
+        if ((phases & 7) && rc != YV3_OK) return rc;
+        const int fp = ((phases & 2) ? 1 : 0) | ((phases & 8) ? 2 : 0);
+        if (!fp) return YV3_OK;
+        return yv3_filter_heads(cfg, head_predicts, n, score_thresh, cand, capacity, counts, post_workspace,
+                                post_workspace_bytes, fp, stream);
+    }
+    if (phases & 1) {
+        rc = yv3_loss_fwd_bwd_heads(cfg, head_predicts, targets, n, m, n_global, rectified_active, upstream, loss_out20,
+                                    head_grads, loss_workspace, loss_workspace_bytes, 1, stream);
+        if (rc != YV3_OK) return rc;
+    }
+    if (phases & 2) {
+        int rows = 0, tbase = 0;
+        for (int h = 0; h < 3; ++h) {
+            d[h].row_base = rows;
+            int r = 0;
+            if (!cuda_ok(launch_fused_sweep(gh[h], d[h], n, score_thresh, pws.stage + (size_t)tbase * 32, pws.tcount + (size_t)tbase * 8,
+                                            pws.status, &r, st), "launch_fused_sweep"))
+                return YV3_ERR_CUDA;
+            rows += r;
+            tbase += packed_tile_count(gh[h], head_predicts[h], n, score_thresh);
+        }
+    }
+    if ((phases & 4) && !cuda_ok(launch_loss_fold(g, d[0], rows_total, st), "launch_loss_fold")) return YV3_ERR_CUDA;
+    if (phases & 8) {
+        if (!cuda_ok(launch_filter_packed(g, head_predicts, true, n, score_thresh, cand, capacity, counts, pws.status, pws.stage,
+                                          pws.tcount, false, true, st), "launch_filter_packed"))
+            return YV3_ERR_CUDA;
+    }
+    return YV3_OK;
+}
+
 int yv3_nms(const yv3_config* cfg, const float* cand, const int32_t* counts, int count_cols, int n,
             int32_t capacity, int num_classes, double nms_thresh, uint8_t* keep, void* workspace,
             size_t workspace_bytes, void* stream) {

@@ -66,6 +66,7 @@ cudaError_t launch_loss_fold(const Geo& g, const DenseArgs& a, int nrows, cudaSt
 // ---- fused_sweep.cu ----------------------------------------------------------------------------
 // score sweep + dense loss sweep on one read of the packed tensor (a: as for launch_loss_dense, grad required)
 int fused_row_count(const Geo& g, const float* predicts, int n, float thresh);       // spans (= partial rows) of the sweep
+int packed_tile_count(const Geo& g, const float* predicts, int n, float thresh);     // tiles of 32 records of the sweep
 bool fused_sweep_supported(const Geo& g, const DenseArgs& a, int n, float thresh);
 cudaError_t launch_fused_sweep(const Geo& g, DenseArgs a, int n, float thresh, float4* stage, int32_t* tcount,
                                int32_t* post_status, int* rows_out, cudaStream_t stream);

@@ -321,6 +321,71 @@ class YOLOv3Loss(object):
             setattr(self, name, detail[i])
         return out[18], grads
 
+    def loss_grad_and_filter_heads(self, targets, head_predicts, post, score_thresh, upstream=1.0, grads_out=None,
+                                   filter_out=None, phases=15):
+        """``loss_grad_and_filter`` on the three head tensors BEFORE yolov3_detector.py:80-85 packs them
+        (``yv3_loss_filter_fused_heads``): every head tensor is read once, nothing is concatenated.  Returns
+        (total, [gradient per head tensor], cand, counts); bit-identical to ``loss_and_grad_heads`` + ``post.filter_heads``.
+        ``self.last_fused`` tells whether the one-sweep kernel ran."""
+        if len(head_predicts) != 3:
+            raise ValueError("head_predicts must hold the /8, /16 and /32 head tensors")
+        heads = [_lib.to_device_f32(p) for p in head_predicts]
+        dev = heads[0].device
+        t = _lib.to_device_f32(targets, dev)
+        n = heads[0].shape[0]
+        for h, p in enumerate(heads):
+            gh, gw = self.head_grid_sizes[h]
+            if p.shape[0] != n or tuple(p.shape[1:3]) != (gh, gw) or p[0].numel() != gh * gw * self._box_num[h] * self.box_len:
+                raise ValueError("head %d must be (N, %d, %d, %d), got %s" % (
+                    h, gh, gw, self._box_num[h] * self.box_len, tuple(p.shape)))
+        if t.dim() != 2 or t.shape[0] != n or t.shape[1] % 5 != 0 or t.shape[1] == 0:
+            raise ValueError("targets must be (N, M*5) with the same N as the head tensors")
+        if post.packed_floats_per_image != self.packed_floats_per_image:
+            raise ValueError("the post-processor was built for another head configuration")
+        m = t.shape[1] // 5
+        world = self._world()
+        n_global = self._n_global(n, world, dev)
+        rect_active = self._latched_rect if self._latched_rect is not None else self.current_num <= self.rectified_coord_num
+        ws = self._workspace(n, m, dev)
+        pws = post._workspace(n, dev)
+        out = torch.empty(20, dtype=torch.float32, device=dev)
+        grads = [torch.empty_like(p) for p in heads] if grads_out is None else list(grads_out)
+        for g, p in zip(grads, heads):
+            if g.shape != p.shape or g.dtype != torch.float32 or not g.is_contiguous() or g.device != p.device:
+                raise ValueError("grads_out must be contiguous fp32 tensors shaped like the head tensors")
+        if filter_out is None:
+            cand = torch.empty((n, post.capacity, 8), dtype=torch.float32, device=dev)
+            counts = torch.empty((n, 3), dtype=torch.int32, device=dev)
+        else:
+            cand, counts = filter_out
+        pp = (ctypes.c_void_p * 3)(*[_lib.ptr(p) for p in heads])
+        gp = (ctypes.c_void_p * 3)(*[_lib.ptr(g) for g in grads])
+        fused = ctypes.c_int32(0)
+        with torch.cuda.device(dev):
+            rc = self._lib.yv3_loss_filter_fused_heads(
+                ctypes.byref(self._cfg), pp, _lib.ptr(t), n, m, n_global, 1 if rect_active else 0, float(upstream), _lib.ptr(out),
+                gp, _lib.ptr(ws), ws.numel(), float(np.float32(score_thresh)), _lib.ptr(cand), post.capacity, _lib.ptr(counts),
+                _lib.ptr(pws), pws.numel(), ctypes.byref(fused), int(phases), _lib.current_stream_ptr(dev))
+        _lib.check(rc, "yv3_loss_filter_fused_heads")
+        post._last_ws = pws
+        self.last_fused = bool(fused.value)
+        self._last_filter = (cand, counts)
+        self._last_ws = ws
+        if not phases & 4:
+            self._latched_rect = rect_active
+            return None, grads, cand, counts
+        self._latched_rect = None
+        if rect_active:
+            self.current_num += n_global                                       # update_add (:152)
+        if world > 1 and self.auto_all_reduce:
+            self._all_reduce(out)
+        self._last_out = out
+        detail = out[:18].view(6, 3)
+        self.loss_detail = detail
+        for i, name in enumerate(_DETAIL_NAMES):
+            setattr(self, name, detail[i])
+        return out[18], grads, cand, counts
+
     def all_reduce_detail(self):
         """Sum the last call's 20 loss floats over the ranks (only needed with ``auto_all_reduce = False``)."""
         if self._last_out is not None and self._world() > 1:
