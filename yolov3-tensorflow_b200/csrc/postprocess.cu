@@ -391,8 +391,10 @@ __device__ __forceinline__ bool suppresses_overlapping_fast(const float4& a, con
 }
 
 // ---- sort: (class asc, score desc, row asc) -----------------------------------------------------------
+// 1024 threads: the gather -> sort -> NMS chain of a step must stay well below a sweep's duration or the post-process
+// stream becomes the step's bottleneck (measured at cfg2: 256 threads 103 us/step like 1024, 128 threads 126 us/step)
 constexpr int kSortThreads = 1024;
-constexpr int kSortSmemKeys = 16384;
+constexpr int kSortSmemKeys = 4096;      // lists up to this size are sorted in shared memory (45 KB per CTA)
 constexpr unsigned long long kPadKey = ~0ULL;
 
 __device__ __forceinline__ unsigned long long make_key(float cls, float score, int row) {
@@ -451,8 +453,9 @@ constexpr int kNmsMedium = 256;         // threads = chunk size of the NMS kerne
 constexpr int kNmsLarge = 1024;         // ... and for longer ones
 constexpr int kFuseMaxK = 4096;         // lists up to this size get their short segments resolved inside the sort kernel
 constexpr int kFuseMaxSeg = 32;         // ... segments up to one warp wide
-constexpr int kBucketMaxK = 16384;      // bucket path of the sort kernel: lists up to this size (= kSortSmemKeys) ...
-constexpr int kBucketClasses = 1024;    // ... with class ids below this (= kSortThreads: thread c owns class c) and <= 256 per class
+constexpr int kBucketMaxK = 65535;      // bucket path of the sort kernel: lists up to this size (arrival order is 16 bits) ...
+constexpr int kBucketClasses = 1024;    // ... with class ids below this (thread t owns classes 4t .. 4t + 3) and <= 256 per class
+constexpr int kClsPerThread = kBucketClasses / kSortThreads;
 constexpr int kWarpNmsSlots = 8;        // candidates per lane of the warp-per-segment NMS
 constexpr int kWarpNmsMax = 32 * kWarpNmsSlots;    // = kNmsMedium: the longest segment one warp resolves
 
@@ -479,15 +482,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
     if (n2 < 2) n2 = 2;
     const float* rows = cand + (size_t)n * capacity * YV3_CAND_COLS;
     unsigned long long* gk = gkeys + (size_t)n * cap2;
-    unsigned long long* keys = (n2 <= n2s) ? skeys : gk;
-    for (int i = tid; i < n2; i += kSortThreads) {
-        unsigned long long key = kPadKey;
-        if (i < K) {
-            const float4 t = reinterpret_cast<const float4*>(rows + (size_t)i * YV3_CAND_COLS)[1];
-            key = make_key(t.z, t.w, i);
-        }
-        keys[i] = key;
-    }
+    unsigned long long* keys = (n2 <= n2s) ? skeys : gk;           // short lists live in shared memory, long ones in gk
     if (tid == 0) nseg_s = 0;
     __syncthreads();
     // ---- bucket path: no class of this image has more than kWarpNmsMax (256) candidates -- ~6 per class at cfg2, ~133
@@ -496,12 +491,16 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
     // rank sort inside each bucket by one warp (up to 8 keys per lane).  A bucket of at most 32 goes straight on to the
     // greedy NMS with the candidates in the warp's lanes; a longer one is published (sorted keys, rows, boxes) and queued
     // for nms_warp_kernel.  No 16 384-key bitonic sort (380 us per step at the stress workload).
-    if (K <= kBucketMaxK && n2s >= 2 && n2 <= n2s) {
-        unsigned long long* bkey = skeys;                                             // [n2s] keys, bucketed
-        int* hist_s = reinterpret_cast<int*>(skeys + n2s);                            // [kBucketClasses] counts -> offsets
-        unsigned short* pos_s = reinterpret_cast<unsigned short*>(hist_s + kBucketClasses);   // [n2s] arrival order in the bucket
+    int* hist_s = reinterpret_cast<int*>(skeys + n2s);                                // [kBucketClasses] counts -> offsets
+    if (K <= kBucketMaxK) {
+        // The shared-memory reservation is sized for SHORT lists (n2s <= 4096 keys, 45 KB: a sort CTA finds room on an SM
+        // next to the sweep's CTAs; with 16 384 keys it needed 164 KB and pushed ~15 of them out for its whole life).
+        // A longer list keeps its bucketed keys in gk and the arrival order in the (still unused) sorted-row table.
+        unsigned long long* bkey = keys;                                              // [n2] keys, bucketed
+        unsigned short* pos_s = (n2 <= n2s) ? reinterpret_cast<unsigned short*>(hist_s + kBucketClasses)
+                                            : reinterpret_cast<unsigned short*>(sidx + (size_t)n * capacity);
         __shared__ int wtot_s[kSortThreads / 32];
-        hist_s[tid] = 0;                                                              // kBucketClasses == kSortThreads
+        for (int c = tid; c < kBucketClasses; c += kSortThreads) hist_s[c] = 0;
         __syncthreads();
         bool bad = false;
         for (int i = tid; i < K; i += kSortThreads) {
@@ -511,9 +510,16 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
             else pos_s[i] = (unsigned short)min(atomicAdd(&hist_s[c], 1), 65535);
         }
         __syncthreads();
-        const int mycount = hist_s[tid];
-        if (!__syncthreads_or((bad || mycount > kWarpNmsMax) ? 1 : 0)) {
-            // exclusive prefix over the classes: thread c owns class c
+        int cnt[kClsPerThread], mycount = 0;
+        bool over = false;
+#pragma unroll
+        for (int q = 0; q < kClsPerThread; ++q) {
+            cnt[q] = hist_s[tid * kClsPerThread + q];
+            mycount += cnt[q];
+            over = over || cnt[q] > kWarpNmsMax;
+        }
+        if (!__syncthreads_or((bad || over) ? 1 : 0)) {
+            // exclusive prefix over the classes: thread t owns classes 4t .. 4t + 3
             int incl = mycount;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -524,9 +530,13 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
             __syncthreads();
             int base = 0;
             for (int w = 0; w < warp; ++w) base += wtot_s[w];
-            const int myoff = base + incl - mycount;
+            int myoff = base + incl - mycount;
             __syncthreads();                                  // every count has been read
-            hist_s[tid] = myoff;
+#pragma unroll
+            for (int q = 0; q < kClsPerThread; ++q) {
+                hist_s[tid * kClsPerThread + q] = myoff;
+                myoff += cnt[q];
+            }
             __syncthreads();
             for (int i = tid; i < K; i += kSortThreads) {
                 const float4 t = reinterpret_cast<const float4*>(rows + (size_t)i * YV3_CAND_COLS)[1];
@@ -601,74 +611,32 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
             }
             return;
         }
-        __syncthreads();                                      // the attempt is abandoned: the general path rebuilds everything
-        for (int i = tid; i < n2; i += kSortThreads) {        // ... including the keys the scatter area overlaps
-            unsigned long long key = kPadKey;
-            if (i < K) {
-                const float4 t = reinterpret_cast<const float4*>(rows + (size_t)i * YV3_CAND_COLS)[1];
-                key = make_key(t.z, t.w, i);
-            }
-            keys[i] = key;
-        }
-        __syncthreads();
+        __syncthreads();                                      // the attempt is abandoned: the general path starts over
     }
+    for (int i = tid; i < n2; i += kSortThreads) {
+        unsigned long long key = kPadKey;
+        if (i < K) {
+            const float4 t = reinterpret_cast<const float4*>(rows + (size_t)i * YV3_CAND_COLS)[1];
+            key = make_key(t.z, t.w, i);
+        }
+        keys[i] = key;
+    }
+    __syncthreads();
     if (keys == skeys && n2 <= kSortThreads) bitonic_sort_regs(keys, n2, tid);
     else bitonic_sort(keys, n2, tid);
-    const bool fuse = K <= kFuseMaxK && keys == skeys;
-    float4* box_s = reinterpret_cast<float4*>(skeys + kFuseMaxK);            // [kFuseMaxK]   (fuse only: n2 <= kFuseMaxK)
-    int* seg_s = reinterpret_cast<int*>(box_s + kFuseMaxK);                  // [kFuseMaxK]
+    // every class segment goes to a queue: nms_warp_kernel (up to 256 candidates) or the cluster kernel (longer)
     for (int i = tid; i < K; i += kSortThreads) {
         const unsigned long long key = keys[i];
         const int row = (int)(key & 0x3ffffULL);
         if (keys != gk) gk[i] = key;
         sidx[(size_t)n * capacity + i] = row;
-        const float4 b = reinterpret_cast<const float4*>(rows + (size_t)row * YV3_CAND_COLS)[0];
-        sbox[(size_t)n * capacity + i] = b;
+        sbox[(size_t)n * capacity + i] = reinterpret_cast<const float4*>(rows + (size_t)row * YV3_CAND_COLS)[0];
         const bool starts = i == 0 || (keys[i - 1] >> 50) != (key >> 50);
-        if (fuse) {
-            box_s[i] = b;
-            if (starts) seg_s[atomicAdd(&nseg_s, 1)] = i;
-        } else if (starts) {
-            // every segment of a long list goes to nms_kernel: the wide kernel when it exceeds 256 candidates
+        if (starts) {
             const bool large = i + kNmsMedium < K && (keys[i + kNmsMedium] >> 50) == (key >> 50);
             if (large) wl_large[atomicAdd(wl_count + 1, 1)] = make_int2(n, i);
-            else wl[atomicAdd(wl_count, 1)] = make_int2(n, i);
+            else wl[atomicAdd(wl_count, 1)] = make_int2(n, i);           // length 0: the warp kernel finds the end itself
         }
-    }
-    if (!fuse) return;
-    __syncthreads();
-    const int nseg = nseg_s;
-    unsigned char* keep_n = keep + (size_t)n * capacity;
-    for (int sg = warp; sg < nseg; sg += kSortThreads / 32) {
-        const int s0 = seg_s[sg];
-        const unsigned long long c0 = keys[s0] >> 50;
-        const int p = s0 + lane;
-        const bool in = p < K && (keys[p] >> 50) == c0;
-        const unsigned members = __ballot_sync(0xffffffffu, in);
-        if (members == 0xffffffffu && s0 + 32 < K && (keys[s0 + 32] >> 50) == c0) {                // longer than a warp
-            if (lane == 0) {
-                const bool large = s0 + kNmsMedium < K && (keys[s0 + kNmsMedium] >> 50) == c0;
-                if (large) wl_large[atomicAdd(wl_count + 1, 1)] = make_int2(n, s0);
-                else wl[atomicAdd(wl_count, 1)] = make_int2(n, s0);
-            }
-            continue;
-        }
-        const int len = __popc(members);            // members are the low `len` lanes (the list is sorted by class)
-        BoxD mine = {};
-        float4 mine_f = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (in) { mine_f = box_s[p]; mine = to_boxd(mine_f); }
-        unsigned alive = members;
-        for (int i = 0; i < len - 1; ++i) {
-            if (!((alive >> i) & 1u)) continue;
-            const float4 fi = box_s[s0 + i];
-            // the coordinates are fp32 values: min/max and the comparison are exact, so boxes that do not overlap
-            // (width or height <= 0, :139-142) never reach the fp64 arithmetic
-            const bool overlap = fminf(fi.z, mine_f.z) > fmaxf(fi.x, mine_f.x) && fminf(fi.w, mine_f.w) > fmaxf(fi.y, mine_f.y);
-            bool drop = lane > i && ((alive >> lane) & 1u);
-            if (drop) drop = overlap ? suppresses_overlapping_fast(fi, mine_f, nq) : (0.0 > thresh);
-            alive &= ~__ballot_sync(0xffffffffu, drop);
-        }
-        if (in) keep_n[(int)(keys[p] & 0x3ffffULL)] = (unsigned char)((alive >> lane) & 1u);
     }
 }
 
@@ -850,7 +818,8 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
 //     kept i < j suppresses it, i.e. iff column j AND kept is empty -- one shared-memory word per lane, one ballot.
 // ~17 instructions per 32 pair tests and no ballot in phase A (the first version, candidates in registers and one
 // ballot per (i, slot), spent ~60 and ran 950 us at cfg4; nms_kernel<256> with CTA-wide phases 1150 us).
-constexpr int kWarpNmsThreads = 128;
+constexpr int kWarpNmsThreads = 32;      // one warp per CTA: 14 KB of shared memory, so an idle launch (nothing queued) slips in
+                                         // next to the sweep's CTAs instead of waiting for 57 KB to drain
 constexpr int kWarpNmsWarps = kWarpNmsThreads / 32;
 struct WarpNmsSmem {
     float4 box[kWarpNmsMax];
@@ -1214,6 +1183,26 @@ cudaError_t launch_collect(const float* cand, const int32_t* counts, const unsig
 }
 
 // ---- launchers ------------------------------------------------------------------------------------------
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) sticks to the function on a device: it leaves the launch path once a
+// launch has asked for at least as much (a few microseconds of host time per call otherwise, on every step)
+static cudaError_t set_smem_once(const void* func, size_t bytes) {
+    struct Seen { const void* f; int dev; size_t bytes; };
+    static Seen seen[64];
+    static int nseen = 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    for (int i = 0; i < nseen; ++i)
+        if (seen[i].f == func && seen[i].dev == dev) {
+            if (seen[i].bytes >= bytes) return cudaSuccess;
+            cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+            if (e == cudaSuccess) seen[i].bytes = bytes;
+            return e;
+        }
+    cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess && nseen < 64) seen[nseen++] = Seen{func, dev, bytes};
+    return e;
+}
+
 static ScoreTiles score_tiles(const Geo& g, const float* predicts, int n, float thresh, int tr_force = 0) {
     ScoreTiles q;
     q.total_rec = (long long)n * g.rpi;
@@ -1272,7 +1261,7 @@ cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool 
         const ScoreTiles q = score_tiles(gh, pred[h], n, thresh, tr);
         const size_t smem = (size_t)q.wpc * q.tile_floats * 4;
         if (smem > 220 * 1024) return cudaErrorInvalidValue;
-        cudaError_t err = cudaFuncSetAttribute(score_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t err = set_smem_once((const void*)score_tile_kernel, smem);
         if (err != cudaSuccess) return err;
         const int grid = (q.num_tiles + q.wpc - 1) / q.wpc;
         if (sweep) {
@@ -1291,7 +1280,7 @@ cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool 
     if (!gather) return cudaSuccess;
     const size_t gsmem = (size_t)3 * gtiles * sizeof(int);
     if (gsmem > 200 * 1024) return cudaErrorInvalidValue;
-    cudaError_t err = cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem);
+    cudaError_t err = set_smem_once((const void*)gather_kernel, gsmem);
     if (err != cudaSuccess) return err;
     gather_kernel<<<n, kGatherThreads, gsmem, stream>>>(g, src, tr, stage, tcount, cand, capacity, counts, status);
     return cudaGetLastError();
@@ -1325,32 +1314,32 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
                        int num_classes, double thresh, unsigned char* keep, const PostWs& ws,
                        cudaStream_t stream) {
     const int cap2 = nms_cap2(capacity);
-    cudaError_t err = cudaMemsetAsync(keep, 0, (size_t)n * capacity, stream);
-    if (err != cudaSuccess) return err;
+    cudaError_t err = cudaSuccess;
+    // keep is NOT cleared here: every row below the list's count is written (0 or 1) by exactly one of the kernels below,
+    // and rows beyond the count are never read (yv3_collect_kept and every caller stop at the counts)
     const int n2s = min(cap2, kSortSmemKeys);
-    // keys, and for short lists (fused pass) the sorted boxes and the segment starts behind the first kFuseMaxK keys
-    const size_t fuse_bytes = (size_t)kFuseMaxK * (8 + 16 + 4);
-    const bool can_fuse = n2s >= 2;
-    const size_t bucket_bytes = (size_t)n2s * 8 + (size_t)kBucketClasses * 4 + (size_t)n2s * 2;
-    const size_t smem = max(can_fuse ? bucket_bytes : (size_t)n2s * 8, can_fuse ? fuse_bytes : (size_t)0);
-    err = cudaFuncSetAttribute(sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = (size_t)n2s * 8 + (size_t)kBucketClasses * 4 + (size_t)n2s * 2;
+    err = set_smem_once((const void*)sort_kernel, smem);
     if (err != cudaSuccess) return err;
     err = cudaMemsetAsync(ws.wl_count, 0, 2 * sizeof(int32_t), stream);
     if (err != cudaSuccess) return err;
     int2* wl_large = ws.wl + (size_t)n * capacity;
+    static int skip = -1;                                     // developer switch (timing experiments only): YV3_NMS_SKIP bits
+    if (skip < 0) { const char* e = getenv("YV3_NMS_SKIP"); skip = e ? atoi(e) : 0; }
+    if (!(skip & 1))
     sort_kernel<<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, n2s, thresh, ws.keys, ws.sbox,
                                                    ws.sidx, keep, ws.wl, wl_large, ws.wl_count);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
     // fixed grids walk the two queues of long segments; with nothing queued every CTA leaves after one load
-    (void)num_classes;
-    err = cudaFuncSetAttribute(nms_kernel<kNmsLarge>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)nms_smem_bytes(kNmsLarge));
+    err = set_smem_once((const void*)nms_kernel<kNmsLarge>, nms_smem_bytes(kNmsLarge));
     if (err != cudaSuccess) return err;
     {
         const size_t wsmem = sizeof(WarpNmsSmem) * kWarpNmsWarps;
-        err = cudaFuncSetAttribute(nms_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
+        err = set_smem_once((const void*)nms_warp_kernel, wsmem);
         if (err != cudaSuccess) return err;
-        nms_warp_kernel<<<148 * 4, kWarpNmsThreads, wsmem, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox,
+        if (!(skip & 2))
+        nms_warp_kernel<<<148 * 16, kWarpNmsThreads, wsmem, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox,
                                                                      ws.sidx, keep, ws.wl, ws.wl_count);
     }
     err = cudaGetLastError();
@@ -1375,6 +1364,17 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
         }
         (void)cudaGetLastError();
         if (getenv("YV3_NO_CLUSTER")) clusters = 0;                  // developer switch
+    }
+    // Segments longer than 256 candidates need an image with more than 256 candidates of ONE class: the rule with a
+    // single-class head and a low threshold, a rarity with tens of classes.  The cluster kernel's CTAs (1024 threads,
+    // 147 KB, six at a time on one GPC) cost the SMs they land on a dozen of the sweep's CTAs even when the queue is
+    // empty -- launched on every step that was most of the gap between the step and its sweep -- so with many classes the
+    // queue is walked by four CTAs of the single-CTA kernel instead: correct for any input, slow only for the rare one.
+    if (skip & 4) return cudaSuccess;
+    if (num_classes > 8) {
+        nms_kernel<kNmsLarge><<<4, kNmsLarge, nms_smem_bytes(kNmsLarge), stream>>>(
+            ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox, ws.sidx, ws.kspill, keep, wl_large, ws.wl_count + 1);
+        return cudaGetLastError();
     }
     if (clusters >= 1) {
         cudaLaunchConfig_t q = {};
