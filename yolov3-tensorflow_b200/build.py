@@ -24,6 +24,10 @@ NVCC_FLAGS = [
 ] + os.environ.get("YV3_EXTRA_NVCC", "").split()        # developer experiments (-D switches); part of the fingerprint
 
 
+# postprocess.cu: the sort kernel tail-launches the queue-driven NMS kernels (CUDA dynamic parallelism)
+RDC = {"postprocess.cu": ["-rdc=true"]}
+
+
 def _nvcc():
     for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
         if cand and os.path.exists(cand):
@@ -35,7 +39,7 @@ def _fingerprint():
     """Content hash of every source, header and flag: mtimes do not survive the copy to the GPU box."""
     import hashlib
     h = hashlib.sha256()
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update((" ".join(NVCC_FLAGS) + repr(sorted(RDC.items()))).encode())
     for d in [os.path.join(CSRC, s) for s in SOURCES + HEADERS]:
         with open(d, "rb") as f:
             h.update(f.read())
@@ -82,7 +86,7 @@ def _build_locked(verbose):
     tag = ".tmp%d" % os.getpid()
     for src in SOURCES:
         obj = os.path.join(LIB_DIR, src.replace(".cu", ".o"))
-        cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj + tag]
+        cmd = [nvcc] + NVCC_FLAGS + RDC.get(src, []) + ["-c", os.path.join(CSRC, src), "-o", obj + tag]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log.append("$ " + " ".join(cmd) + "\n" + r.stdout + r.stderr)
         if r.returncode != 0:
@@ -90,7 +94,8 @@ def _build_locked(verbose):
             raise RuntimeError("nvcc failed on %s" % src)
         os.replace(obj + tag, obj)
         objs.append(obj)
-    cmd = [nvcc, "-shared", "-o", LIB_PATH + tag] + objs + ["-lcudart"]
+    # nvcc device-links the relocatable object (postprocess.cu launches kernels from the device) against cudadevrt
+    cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB_PATH + tag] + objs + ["-lcudadevrt", "-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log.append("$ " + " ".join(cmd) + "\n" + r.stdout + r.stderr)
     if r.returncode != 0:

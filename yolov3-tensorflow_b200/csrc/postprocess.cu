@@ -464,12 +464,12 @@ constexpr int kWarpNmsMax = 32 * kWarpNmsSlots;    // = kNmsMedium: the longest 
 // warp per segment: lane j holds candidate j of the segment, the kept candidates are visited in order, each is
 // broadcast from shared memory and tested against the later lanes in fp64 (_apply_nms :117-128).  Longer segments
 // are left to nms_kernel.
-__global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restrict__ cand, const int32_t* __restrict__ count,
-                                                            int count_cols, int capacity, int cap2, int n2s, double thresh,
-                                                            unsigned long long* __restrict__ gkeys, float4* __restrict__ sbox,
-                                                            int32_t* __restrict__ sidx, unsigned char* __restrict__ keep,
-                                                            int2* __restrict__ wl, int2* __restrict__ wl_large,
-                                                            int32_t* __restrict__ wl_count) {
+__device__ __forceinline__ void sort_body(const float* __restrict__ cand, const int32_t* __restrict__ count,
+                                          int count_cols, int capacity, int cap2, int n2s, double thresh,
+                                          unsigned long long* __restrict__ gkeys, float4* __restrict__ sbox,
+                                          int32_t* __restrict__ sidx, unsigned char* __restrict__ keep,
+                                          int2* __restrict__ wl, int2* __restrict__ wl_large,
+                                          int32_t* __restrict__ wl_count) {
     extern __shared__ __align__(16) unsigned long long skeys[];
     __shared__ int nseg_s;
     const NmsThresh nq = make_nms_thresh(thresh);
@@ -821,12 +821,16 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
 constexpr int kWarpNmsThreads = 32;      // one warp per CTA: 14 KB of shared memory, so an idle launch (nothing queued) slips in
                                          // next to the sweep's CTAs instead of waiting for 57 KB to drain
 constexpr int kWarpNmsWarps = kWarpNmsThreads / 32;
+// launched from the device (sort_kernel's dispatch) a grid gets the smallest shared-memory carve-out that holds ONE of its
+// CTAs, i.e. one CTA per SM (measured: 32-thread CTAs 7.9 ms, 128-thread CTAs 2.2 ms at cfg4 against 1.1 ms from the host):
+// the device-side launch therefore uses one CTA of 14 warps (200 KB) per SM
+constexpr int kWarpNmsDevThreads = 448;
 struct WarpNmsSmem {
     float4 box[kWarpNmsMax];
     float area[kWarpNmsMax];
     unsigned col[kWarpNmsMax][kWarpNmsSlots + 1];      // + 1: odd row stride, conflict-free column-word reads in phase B
 };
-__global__ void __launch_bounds__(kWarpNmsThreads) nms_warp_kernel(const unsigned long long* __restrict__ gkeys,
+__global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsigned long long* __restrict__ gkeys,
                                                                    const int32_t* __restrict__ count, int count_cols,
                                                                    int capacity, int cap2, double thresh,
                                                                    const float4* __restrict__ sbox, const int32_t* __restrict__ sidx,
@@ -835,8 +839,8 @@ __global__ void __launch_bounds__(kWarpNmsThreads) nms_warp_kernel(const unsigne
     extern __shared__ __align__(16) unsigned char wsm[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpNmsSmem& sm = reinterpret_cast<WarpNmsSmem*>(wsm)[warp];
-    const int wid = (blockIdx.x * kWarpNmsThreads + threadIdx.x) >> 5;
-    const int nw = (gridDim.x * kWarpNmsThreads) >> 5;
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nw = (gridDim.x * blockDim.x) >> 5;
     const int nwork = *wl_count;
     const bool none_overlap_drops = 0.0 > thresh;      // a negative threshold suppresses even disjoint boxes (:124)
     const NmsThresh nq = make_nms_thresh(thresh);
@@ -1111,6 +1115,38 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
     cluster.sync();                                                  // nobody leaves while its shared memory may be read
 }
 
+// ---- the sort kernel and its device-side dispatch ----------------------------------------------------------------
+// The queue-driven NMS kernels above have nothing to do on most steps of a many-class head (no class of an image holds
+// more than 32 candidates), yet launched from the host they still had to be placed: thousands of CTAs on the
+// high-priority stream, each holding back the sweep's CTAs while the block scheduler found room -- ~6 us of a 103 us
+// step at cfg2 (tools/step_breakdown.py).  With `dispatch` set the LAST sort CTA to finish looks at the two queue
+// counters and tail-launches (CUDA dynamic parallelism, cudaStreamTailLaunch: after this grid, before the stream's
+// next kernel) only the kernels that have work, with grids sized by the queues.
+__global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restrict__ cand, const int32_t* __restrict__ count,
+                                                            int count_cols, int capacity, int cap2, int n2s, double thresh,
+                                                            unsigned long long* __restrict__ gkeys, float4* __restrict__ sbox,
+                                                            int32_t* __restrict__ sidx, unsigned char* __restrict__ keep,
+                                                            int2* __restrict__ wl, int2* __restrict__ wl_large,
+                                                            int32_t* __restrict__ wl_count, float4* __restrict__ kspill,
+                                                            int dispatch) {
+    sort_body(cand, count, count_cols, capacity, cap2, n2s, thresh, gkeys, sbox, sidx, keep, wl, wl_large, wl_count);
+    if (!dispatch) return;
+    __syncthreads();                                            // (every thread of the CTA reaches this point)
+    if (threadIdx.x != 0) return;
+    __threadfence();
+    if (atomicAdd(wl_count + 2, 1) != (int)gridDim.x - 1) return;
+    __threadfence();
+    wl_count[2] = 0;
+    const int nmed = *(volatile int32_t*)wl_count, nlarge = *(volatile int32_t*)(wl_count + 1);
+    if (nmed > 0)
+        nms_warp_kernel<<<min((nmed + kWarpNmsDevThreads / 32 - 1) / (kWarpNmsDevThreads / 32), 148), kWarpNmsDevThreads,
+                          sizeof(WarpNmsSmem) * (kWarpNmsDevThreads / 32), cudaStreamTailLaunch>>>(
+            gkeys, count, count_cols, capacity, cap2, thresh, sbox, sidx, keep, wl, wl_count);
+    if (nlarge > 0)
+        nms_kernel<kNmsLarge><<<min(nlarge, 148), kNmsLarge, nms_smem_bytes(kNmsLarge), cudaStreamTailLaunch>>>(
+            gkeys, count, count_cols, capacity, cap2, thresh, sbox, sidx, kspill, keep, wl_large, wl_count + 1);
+}
+
 // ---- kept rows, resized (yolov3_post_process.py:94-104, :162-172) -------------------------------------------
 // One CTA per image: the rows apply_nms returns, per head in local-id order, with box[:4] * target_size and the id
 // column, as float64 (the reference's rows are float64; an fp32 coordinate times an integer size is exact there).
@@ -1199,6 +1235,8 @@ static cudaError_t set_smem_once(const void* func, size_t bytes) {
             return e;
         }
     cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    // a kernel launched from the device takes its L1 / shared-memory split from the function's preference alone
+    if (e == cudaSuccess) (void)cudaFuncSetAttribute(func, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess && nseen < 64) seen[nseen++] = Seen{func, dev, bytes};
     return e;
 }
@@ -1321,31 +1359,29 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     const size_t smem = (size_t)n2s * 8 + (size_t)kBucketClasses * 4 + (size_t)n2s * 2;
     err = set_smem_once((const void*)sort_kernel, smem);
     if (err != cudaSuccess) return err;
-    err = cudaMemsetAsync(ws.wl_count, 0, 2 * sizeof(int32_t), stream);
+    err = cudaMemsetAsync(ws.wl_count, 0, 3 * sizeof(int32_t), stream);          // two queue counters, the dispatch ticket
     if (err != cudaSuccess) return err;
     int2* wl_large = ws.wl + (size_t)n * capacity;
     static int skip = -1;                                     // developer switch (timing experiments only): YV3_NMS_SKIP bits
     if (skip < 0) { const char* e = getenv("YV3_NMS_SKIP"); skip = e ? atoi(e) : 0; }
-    if (!(skip & 1))
-    sort_kernel<<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, n2s, thresh, ws.keys, ws.sbox,
-                                                   ws.sidx, keep, ws.wl, wl_large, ws.wl_count);
-    err = cudaGetLastError();
-    if (err != cudaSuccess) return err;
-    // fixed grids walk the two queues of long segments; with nothing queued every CTA leaves after one load
+    // many classes: the queue-driven kernels are launched from the device, and only when something is queued
+    const int dispatch = (num_classes > 8 && !(skip & 8)) ? 1 : 0;
     err = set_smem_once((const void*)nms_kernel<kNmsLarge>, nms_smem_bytes(kNmsLarge));
     if (err != cudaSuccess) return err;
-    {
-        const size_t wsmem = sizeof(WarpNmsSmem) * kWarpNmsWarps;
-        err = set_smem_once((const void*)nms_warp_kernel, wsmem);
-        if (err != cudaSuccess) return err;
-        if (!(skip & 2))
-        nms_warp_kernel<<<148 * 16, kWarpNmsThreads, wsmem, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox,
-                                                                     ws.sidx, keep, ws.wl, ws.wl_count);
-    }
+    const size_t wsmem = sizeof(WarpNmsSmem) * kWarpNmsWarps;
+    err = set_smem_once((const void*)nms_warp_kernel, sizeof(WarpNmsSmem) * (kWarpNmsDevThreads / 32));
+    if (err != cudaSuccess) return err;
+    if (!(skip & 1))
+    sort_kernel<<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, n2s, thresh, ws.keys, ws.sbox,
+                                                   ws.sidx, keep, ws.wl, wl_large, ws.wl_count, ws.kspill, dispatch);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
-    // segments longer than 256 candidates: one cluster of CTAs per segment (falls back to one CTA per segment where
-    // such a cluster cannot be scheduled)
+    if (dispatch) return cudaSuccess;
+    if (!(skip & 2))
+    nms_warp_kernel<<<148 * 16, kWarpNmsThreads, wsmem, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox,
+                                                                 ws.sidx, keep, ws.wl, ws.wl_count);
+    err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
     static int clusters = -1;
     if (clusters < 0) {
         clusters = 0;
