@@ -731,10 +731,15 @@ def main():
             tj = json.load(open(tp))
             traffic = tj.get(args.workload, {}).get(kernel_name + "_dram_bytes_per_launch")
             sha = git_sha()
+            from yolov3_tensorflow_b200 import build as yb
+            now_hash = yb.sweep_sources_hash()
+            # stale = the sweep kernels' sources changed since the capture (a commit that leaves them alone does not count)
             traffic_note = {"captured_at_sha": tj.get("sha"), "captured_on": tj.get("date"), "bench_sha": sha,
-                            "stale": bool(tj.get("sha") and sha and tj.get("sha") != sha),
+                            "sweep_sources_hash": now_hash, "captured_sources_hash": tj.get("sweep_sources_hash"),
+                            "stale": tj.get("sweep_sources_hash") != now_hash,
                             "how": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture per workload "
-                                   "(tools/run_final.sh regenerates profiles/traffic.json)"}
+                                   "and kernel (tools/traffic_capture.sh + tools/traffic_json.py regenerate "
+                                   "profiles/traffic.json)"}
         A, L = arm.spec.anchors_per_image, arm.spec.box_len
         line = {
             "metric": "head loss fwd+bwd + decode+filter+NMS throughput",

@@ -46,6 +46,22 @@ def _fingerprint():
     return h.hexdigest()
 
 
+SWEEP_SOURCES = ["fused_sweep.cu", "loss_dense.cu", "decode.cu", "sweep_parts.cuh", "tile_ops.cuh", "yv3_common.cuh",
+                 "yv3_kernels.cuh"]
+
+
+def sweep_sources_hash():
+    """Content hash of the files the HBM-bound sweep kernels are made of: profiles/traffic.json carries it, and bench.py
+    marks its DRAM-traffic figures stale when these files changed since the capture (a commit elsewhere does not)."""
+    import hashlib
+    h = hashlib.sha256()
+    h.update(" ".join(NVCC_FLAGS).encode())
+    for name in SWEEP_SOURCES:
+        with open(os.path.join(CSRC, name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
 def _stale():
     stamp = os.path.join(LIB_DIR, "build.hash")
     if not os.path.exists(LIB_PATH) or not os.path.exists(stamp):
