@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define YV3_ABI_VERSION 5
+#define YV3_ABI_VERSION 6
 #define YV3_MAX_BOX 8      /* anchors per head (reference ships 3 / 2 / 3, configs.py:37-41) */
 #define YV3_MAX_GT 256     /* label slots per image (M) */
 
@@ -45,7 +45,8 @@ typedef enum yv3_error {
     YV3_ERR_CAPACITY = -7,      /* candidate capacity exceeded / problem too large for the kernel */
     YV3_ERR_GT_RANGE = -8,      /* (status) a valid label's centre falls outside the grid; TF's
                                    gather_nd raises here on CPU (yolov3/yolov3_loss.py:271) */
-    YV3_ERR_NONFINITE = -9      /* (status) inf/NaN met in the loss (reported, not "fixed") */
+    YV3_ERR_NONFINITE = -9,     /* (status) inf/NaN met in the loss (reported, not "fixed") */
+    YV3_ERR_STATIC_SCRATCH = -10 /* yv3_nms_static: n x capacity needs more than YV3_NMS_STATIC_SCRATCH_BYTES of scratch */
 } yv3_error;
 
 /* The switch surface the path consumes: YOLOv3Loss.__init__ (yolov3/yolov3_loss.py:16-67),
@@ -237,6 +238,25 @@ int yv3_loss_filter_fused_heads(const yv3_config* cfg, const float* const head_p
 int yv3_nms(const yv3_config* cfg, const float* cand, const int32_t* counts, int count_cols, int n,
             int32_t capacity, int num_classes, double nms_thresh, uint8_t* keep, void* workspace,
             size_t workspace_bytes, void* stream);
+
+/* yv3_nms for callers that cannot allocate device memory and have no workspace to hand over (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same kernels and the same keep flags as yv3_nms(cfg = NULL, ...), but the
+ * scratch (sort keys, sorted boxes, row indices, spill list, segment queues) is a file-scope device array of
+ * YV3_NMS_STATIC_SCRATCH_BYTES inside the library (csrc/static_scratch.cu), which every GPU that loads the library holds
+ * until the process exits.  The call allocates nothing: no cudaMalloc / cudaFree, no allocating library routine.
+ *   limit    the scratch for n lists of `capacity` rows is, each term rounded up to 256 bytes,
+ *              8 * n * pow2ceil(capacity) + 16 * r + 4 * r + 16 * r + 8 * (r + r / 256 + 16) + 256,   r = n * capacity
+ *            (about 60 bytes per row: 64 lists of 1024 rows, 16 of 4096, 1 of 65536).  A larger request returns
+ *            YV3_ERR_STATIC_SCRATCH before anything is launched; use yv3_nms with a workspace for those.
+ *   sharing  all calls on one device use the same array and it keeps the last call's contents (the call clears the few
+ *            words that must start at zero).  Calls that OVERLAP on the GPU -- two streams with no ordering between them --
+ *            race on it: keep the calls of one device on one stream, or order them with events.
+ *   set-up   the first call on a device asks the runtime for the array's device address (cudaGetSymbolAddress, cached per
+ *            device); make that call outside stream capture. */
+#define YV3_NMS_STATIC_SCRATCH_BYTES (4u << 20)
+int yv3_nms_static(const float* cand, const int32_t* counts, int count_cols, int n, int32_t capacity, int num_classes,
+                   double nms_thresh, uint8_t* keep, void* stream);
 
 /* The rows run.py gets from apply_nms + resize_boxes (yolov3_post_process.py:94-104, :162-172), on the device: per
  * image and per head (/8, /16, /32) the returned rows in local-id order,

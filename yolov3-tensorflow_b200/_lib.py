@@ -100,6 +100,7 @@ _SIGNATURES = {
                                                    ctypes.c_int, _P]),
     "yv3_nms": (ctypes.c_int, [_P, _P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int32, ctypes.c_int,
                                ctypes.c_double, _P, _P, ctypes.c_size_t, _P]),
+    "yv3_nms_static": (ctypes.c_int, [_P, _P, ctypes.c_int, ctypes.c_int, ctypes.c_int32, ctypes.c_int, ctypes.c_double, _P, _P]),
 }
 EXPORTS = tuple(sorted(_SIGNATURES))
 
@@ -129,7 +130,7 @@ def lib():
         fn = getattr(handle, name)             # AttributeError = header and library disagree
         fn.restype = res
         fn.argtypes = args
-    if handle.yv3_abi_version() != 5:
+    if handle.yv3_abi_version() != 6:
         raise RuntimeError("libyv3head.so ABI version mismatch")
     _LIB = handle
     return _LIB

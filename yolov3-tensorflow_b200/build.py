@@ -15,7 +15,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libyv3head.so")
-SOURCES = ["yv3_api.cu", "assign.cu", "loss_dense.cu", "decode.cu", "postprocess.cu", "fused_sweep.cu", "peer_reduce.cu", "map_eval.cu"]
+SOURCES = ["yv3_api.cu", "assign.cu", "loss_dense.cu", "decode.cu", "postprocess.cu", "fused_sweep.cu", "peer_reduce.cu", "map_eval.cu",
+           "static_scratch.cu"]
 HEADERS = ["yv3_common.cuh", "yv3_kernels.cuh", "tile_ops.cuh", "sweep_parts.cuh", os.path.join("..", "..", "include", "yv3_head.h")]
 
 NVCC_FLAGS = [

@@ -130,6 +130,8 @@ const char* yv3_strerror(int code) {
         case YV3_ERR_CAPACITY: return "candidate capacity exceeded / problem too large";
         case YV3_ERR_GT_RANGE: return "a valid label's centre lies outside the grid (tf.gather_nd would raise)";
         case YV3_ERR_NONFINITE: return "inf/NaN in the loss";
+        case YV3_ERR_STATIC_SCRATCH: return "yv3_nms_static: n x capacity needs more than the library's static scratch array "
+                                            "(YV3_NMS_STATIC_SCRATCH_BYTES = 4 MiB); use yv3_nms with a workspace";
         default: return "unknown yv3 error";
     }
 }
