@@ -1,9 +1,25 @@
-# round-end evidence: plain bench lines first (never under a profiler), then the ncu captures of the same code
+# round evidence on ONE B200 (gpurun --timeout 1500 -- 'bash tools/run_final.sh [tag]'): plain bench lines first (never
+# under a profiler), then the ncu captures of the same code.  Outputs in gpurun_out/<tag>_*; copy what is to be judged
+# into profiles/.
+TAG=${1:-r02}
+mkdir -p gpurun_out
 set -x
-timeout 600 python bench.py > gpurun_out/final_bench.log 2>&1; tail -1 gpurun_out/final_bench.log | cut -c1-300
-timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/final_ref.log 2>&1; tail -1 gpurun_out/final_ref.log | cut -c1-200
-timeout 300 python bench.py --no-cpu-baseline --fused 0 > gpurun_out/final_separate.log 2>&1; tail -1 gpurun_out/final_separate.log | cut -c1-200
-timeout 300 python bench.py --no-cpu-baseline --layout heads > gpurun_out/final_heads.log 2>&1; tail -1 gpurun_out/final_heads.log | cut -c1-200
+timeout 900 python bench.py > gpurun_out/${TAG}_bench_n1.log 2>&1; tail -1 gpurun_out/${TAG}_bench_n1.log | cut -c1-300
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${TAG}_bench_reference.log 2>&1; tail -1 gpurun_out/${TAG}_bench_reference.log | cut -c1-200
+timeout 300 python bench.py --no-cpu-baseline --no-extras --fused 0 > gpurun_out/${TAG}_bench_separate.log 2>&1; tail -1 gpurun_out/${TAG}_bench_separate.log | cut -c1-200
+for w in cfg3_608_c80_b64 cfg4_416_c80_b256_dense cfg5_512_c0_g128 cfg5_nms_stress_b16; do
+  timeout 300 python bench.py --workload $w --no-cpu-baseline --no-extras > gpurun_out/${TAG}_bench_$w.log 2>&1
+  tail -1 gpurun_out/${TAG}_bench_$w.log | cut -c1-200
+done
+# launch list of the eager schedule (per-launch times are cold-cache and serialised: shares, not absolutes)
+timeout 300 python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-extras --no-graph > gpurun_out/${TAG}_nograph.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${TAG}_launches.csv \
+    python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-extras --no-graph > gpurun_out/${TAG}_ncu_bench.log 2>&1
+tail -1 gpurun_out/${TAG}_ncu_bench.log | cut -c1-100
+# one fused step, every kernel, full sections (ncu does not see device-launched grids: the NMS kernels are launched from
+# the host for this capture, YV3_NMS_SKIP=8 -- 7 launches per step)
 export YV3_PROFILE_FUSED=1
-timeout 120 python tools/profile_step.py && timeout 600 ncu --set full --clock-control none --import-source on --launch-skip 14 --launch-count 7 -o gpurun_out/prof_r01_final_step -f python tools/profile_step.py > gpurun_out/ncu_final_step.log 2>&1; tail -1 gpurun_out/ncu_final_step.log
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_r01_final.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-graph > gpurun_out/ncu_bench.log 2>&1; tail -1 gpurun_out/ncu_bench.log | cut -c1-100
+export YV3_NMS_SKIP=8
+timeout 120 python tools/profile_step.py && timeout 600 ncu --set full --clock-control none --import-source on --launch-skip 14 \
+    --launch-count 7 -o gpurun_out/${TAG}_step -f python tools/profile_step.py > gpurun_out/${TAG}_ncu_step.log 2>&1
+tail -1 gpurun_out/${TAG}_ncu_step.log
