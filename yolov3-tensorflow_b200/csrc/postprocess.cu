@@ -551,41 +551,28 @@ __device__ __forceinline__ void sort_body(const float* __restrict__ cand, const 
                 const int o1 = (c + 1 < kBucketClasses) ? hist_s[c + 1] : K;
                 const int len = o1 - o0;
                 if (len <= 0) continue;
-                // rank sort: keys are unique (the row is part of the key); lane holds keys lane, lane + 32, ...
-                unsigned long long key[kWarpNmsSlots];
-                int rank[kWarpNmsSlots];
-#pragma unroll
-                for (int u = 0; u < kWarpNmsSlots; ++u) {
-                    key[u] = (lane + 32 * u < len) ? bkey[o0 + lane + 32 * u] : kPadKey;
-                    rank[u] = 0;
-                }
-                const int nslot = (len + 31) >> 5;
-                for (int j = 0; j < len; ++j) {
-                    const unsigned long long other = bkey[o0 + j];
-#pragma unroll
-                    for (int u = 0; u < kWarpNmsSlots; ++u)
-                        if (u < nslot) rank[u] += (other < key[u]) ? 1 : 0;
-                }
-                __syncwarp();
-#pragma unroll
-                for (int u = 0; u < kWarpNmsSlots; ++u)
-                    if (lane + 32 * u < len) bkey[o0 + rank[u]] = key[u];
-                __syncwarp();
                 if (len > kFuseMaxSeg) {
-                    // publish the sorted segment and queue it: (image, first sorted position | length << 18)
-#pragma unroll
-                    for (int u = 0; u < kWarpNmsSlots; ++u) {
-                        const int p = lane + 32 * u;
-                        if (p < len) {
-                            const unsigned long long k2 = bkey[o0 + p];
-                            const int row = (int)(k2 & 0x3ffffULL);
-                            gk[o0 + p] = k2;
-                            sidx[(size_t)n * capacity + o0 + p] = row;
-                            sbox[(size_t)n * capacity + o0 + p] = reinterpret_cast<const float4*>(rows + (size_t)row * YV3_CAND_COLS)[0];
-                        }
-                    }
-                    if (lane == 0) wl[atomicAdd(wl_count, 1)] = make_int2(n, o0 | (len << 18));
+                    // a bucket of 33..256: published as it is (keys of one class, arrival order) and queued with its
+                    // length and the "not sorted yet" flag: (image, first position | length << 18 | 1 << 27).  The warp
+                    // that takes it off the queue in nms_warp_kernel rank-sorts it in its shared memory -- 20 000
+                    // buckets spread over every SM instead of 80 per image serialised on this CTA's 32 warps, where
+                    // the rank sort was 79 % of this kernel's instructions at the dense stress workload.
+                    if (bkey != gk)
+                        for (int p = lane; p < len; p += 32) gk[o0 + p] = bkey[o0 + p];
+                    if (lane == 0) wl[atomicAdd(wl_count, 1)] = make_int2(n, o0 | (len << 18) | (1 << 27));
                     continue;
+                }
+                // rank sort of at most 32 keys, one per lane: keys are unique (the row is part of the key)
+                {
+                    const unsigned long long mykey = (lane < len) ? bkey[o0 + lane] : kPadKey;
+                    int rank = 0;
+                    for (int j = 0; j < len; ++j) {
+                        const unsigned long long other = __shfl_sync(0xffffffffu, mykey, j);
+                        rank += (other < mykey) ? 1 : 0;
+                    }
+                    __syncwarp();
+                    if (lane < len) bkey[o0 + rank] = mykey;
+                    __syncwarp();
                 }
                 const bool in = lane < len;
                 const unsigned long long k1 = in ? bkey[o0 + lane] : kPadKey;
@@ -825,15 +812,52 @@ constexpr int kWarpNmsWarps = kWarpNmsThreads / 32;
 // CTAs, i.e. one CTA per SM (measured: 32-thread CTAs 7.9 ms, 128-thread CTAs 2.2 ms at cfg4 against 1.1 ms from the host):
 // the device-side launch therefore uses one CTA of 14 warps (200 KB) per SM
 constexpr int kWarpNmsDevThreads = 448;
+// The fp32 decision of phase A is trusted when every area of the segment is at least kWarpNmsAreaLo (and at most 1e29) and
+// the threshold at least kWarpNmsThreshLo: an intersection that leaves the normal fp32 range (below 1e-30, where the
+// relative error bound of the product no longer holds) is then still 6 orders of magnitude below lo * union >= 1e-24,
+// i.e. on the "no" side whatever its rounding; disjoint boxes (inter <= 0) are on the "no" side because lo * union > 0.
+constexpr float kWarpNmsAreaLo = 1e-18f;
+constexpr float kWarpNmsThreshLo = 1e-6f;
 struct WarpNmsSmem {
     float4 box[kWarpNmsMax];
     float area[kWarpNmsMax];
     unsigned col[kWarpNmsMax][kWarpNmsSlots + 1];      // + 1: odd row stride, conflict-free column-word reads in phase B
 };
+static_assert(sizeof(unsigned) * kWarpNmsMax * (kWarpNmsSlots + 1) >= sizeof(unsigned long long) * kWarpNmsMax,
+              "the column matrix doubles as the key buffer of the rank sort");
+
+// Rank sort of a bucket of at most 32 * NS keys (arrival order -> ascending key = score descending, row ascending) in the
+// warp's key buffer: every key is broadcast from shared memory and counted against the NS keys a lane holds; keys are
+// unique (the row is part of the key).  NS is a template parameter so that the count loop is exactly NS compares.
+template <int NS>
+__device__ __forceinline__ void warp_rank_sort(unsigned long long* skey, const int lane, const int len,
+                                               const unsigned long long* keys) {
+    unsigned long long key[NS];
+    int rank[NS];
+#pragma unroll
+    for (int u = 0; u < NS; ++u) {
+        key[u] = (lane + 32 * u < len) ? keys[lane + 32 * u] : kPadKey;
+        rank[u] = 0;
+        if (lane + 32 * u < len) skey[lane + 32 * u] = key[u];
+    }
+    __syncwarp();
+#pragma unroll 4
+    for (int j = 0; j < len; ++j) {
+        const unsigned long long other = skey[j];
+#pragma unroll
+        for (int u = 0; u < NS; ++u) rank[u] += (other < key[u]) ? 1 : 0;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < NS; ++u)
+        if (lane + 32 * u < len) skey[rank[u]] = key[u];
+    __syncwarp();
+}
+
 __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsigned long long* __restrict__ gkeys,
                                                                    const int32_t* __restrict__ count, int count_cols,
                                                                    int capacity, int cap2, double thresh,
-                                                                   const float4* __restrict__ sbox, const int32_t* __restrict__ sidx,
+                                                                   const float* __restrict__ cand,
                                                                    unsigned char* __restrict__ keep,
                                                                    const int2* __restrict__ wl, const int32_t* __restrict__ wl_count) {
     extern __shared__ __align__(16) unsigned char wsm[];
@@ -844,98 +868,145 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
     const int nwork = *wl_count;
     const bool none_overlap_drops = 0.0 > thresh;      // a negative threshold suppresses even disjoint boxes (:124)
     const NmsThresh nq = make_nms_thresh(thresh);
-    const bool fast_ok = nq.lo >= 0.f;
+    const bool fast_ok = nq.lo >= kWarpNmsThreshLo;
     for (int wi = wid; wi < nwork; wi += nw) {
         const int2 job = wl[wi];
         const int n = job.x, s0 = job.y & 0x3ffff;
-        int len = (int)((unsigned)job.y >> 18);
+        int len = (job.y >> 18) & 0x1ff;
+        const bool needs_sort = ((job.y >> 27) & 1) != 0;
+        const unsigned long long* keys = gkeys + (size_t)n * cap2 + s0;
         if (len == 0) {
             // queued by the general sort path without a length: the run of this class from s0 on (at most 256 long)
             int K = 0;
             for (int q = 0; q < count_cols; ++q) K += count[n * count_cols + q];
             K = max(0, min(K, capacity));
-            const unsigned long long* keys = gkeys + (size_t)n * cap2;
-            const unsigned long long c0 = keys[s0] >> 50;
+            const unsigned long long c0 = keys[0] >> 50;
 #pragma unroll
             for (int u = 0; u < kWarpNmsSlots; ++u) {
                 const int p = s0 + lane + 32 * u;
-                len += __popc(__ballot_sync(0xffffffffu, p < K && (keys[p] >> 50) == c0));
+                len += __popc(__ballot_sync(0xffffffffu, p < K && (keys[lane + 32 * u] >> 50) == c0));
             }
         }
-        const float4* boxes = sbox + (size_t)n * capacity + s0;
-        const int32_t* rowof = sidx + (size_t)n * capacity + s0;
+        const float* rows = cand + (size_t)n * capacity * YV3_CAND_COLS;
         const int nslot = (len + 31) >> 5;
-        float4 bx[kWarpNmsSlots];
-        float ar[kWarpNmsSlots];
-        int row[kWarpNmsSlots];
         __syncwarp();                                                    // the previous segment's sweep is done with sm
+        if (needs_sort) {
+            // the column matrix is free until phase A: it doubles as the key buffer
+            unsigned long long* skey = reinterpret_cast<unsigned long long*>(&sm.col[0][0]);
+            switch (nslot) {
+                case 1: warp_rank_sort<1>(skey, lane, len, keys); break;
+                case 2: warp_rank_sort<2>(skey, lane, len, keys); break;
+                case 3: warp_rank_sort<3>(skey, lane, len, keys); break;
+                case 4: warp_rank_sort<4>(skey, lane, len, keys); break;
+                case 5: warp_rank_sort<5>(skey, lane, len, keys); break;
+                case 6: warp_rank_sort<6>(skey, lane, len, keys); break;
+                case 7: warp_rank_sort<7>(skey, lane, len, keys); break;
+                default: warp_rank_sort<8>(skey, lane, len, keys); break;
+            }
+            keys = skey;
+        }
+        int row[kWarpNmsSlots];
+        bool sane = true;
 #pragma unroll
         for (int u = 0; u < kWarpNmsSlots; ++u) {
             const int idx = lane + 32 * u;
             const bool in = idx < len;
-            bx[u] = in ? __ldg(boxes + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-            row[u] = in ? __ldg(rowof + idx) : -1;
-            ar[u] = __fmul_rn(__fsub_rn(bx[u].z, bx[u].x), __fsub_rn(bx[u].w, bx[u].y));
-            if (u < nslot) { sm.box[idx] = bx[u]; sm.area[idx] = ar[u]; }
+            row[u] = in ? (int)(keys[idx] & 0x3ffffULL) : -1;
+            if (in) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(rows + (size_t)row[u] * YV3_CAND_COLS));
+                const float a = __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
+                sm.box[idx] = b;
+                sm.area[idx] = a;
+                sane = sane && a >= kWarpNmsAreaLo && a <= 1e29f;
+            }
         }
-        __syncwarp();
-        // ---- phase A: column bits ----------------------------------------------------------------------------------
-        // sane: the area is a normal fp32 number far from overflow, so the fp32 bounds of the comparison hold (NmsThresh);
-        // anything else -- and a negative threshold -- is settled by the exact expression
-        bool sane[kWarpNmsSlots];
-#pragma unroll
-        for (int v = 0; v < kWarpNmsSlots; ++v) sane[v] = fast_ok && ar[v] >= 1e-30f && ar[v] <= 1e29f;
-        for (int ib = 0; ib < nslot; ++ib) {                              // block of 32 earlier candidates i
-            unsigned word[kWarpNmsSlots];
-#pragma unroll
-            for (int v = 0; v < kWarpNmsSlots; ++v) word[v] = 0u;
-            const int iend = min(32, len - 1 - 32 * ib);
-            for (int l = 0; l < iend; ++l) {
-                const int i = 32 * ib + l;
-                const float4 fi = sm.box[i];
-                const float ai = sm.area[i];
-                const bool sane_i = ai >= 1e-30f && ai <= 1e29f;
-                const unsigned bit = 1u << l;
-#pragma unroll
-                for (int v = 0; v < kWarpNmsSlots; ++v) {
-                    if (v < ib || v >= nslot) continue;                  // every j of slot v precedes i / slot unused (uniform)
-                    const float w = __fsub_rn(fminf(fi.z, bx[v].z), fmaxf(fi.x, bx[v].x));
-                    const float h = __fsub_rn(fminf(fi.w, bx[v].w), fmaxf(fi.y, bx[v].y));
-                    const bool overlap = w > 0.f && h > 0.f;             // :139-142, exact on fp32 coordinates
-                    const float inter = __fmul_rn(w, h);
-                    const float uni = __fsub_rn(__fadd_rn(ai, ar[v]), inter);
-                    const bool yes = inter > __fmul_rn(nq.hi, uni), no = inter < __fmul_rn(nq.lo, uni);
-                    const bool decided = (yes || no) && sane[v] && sane_i && inter >= 1e-30f;
-                    bool drop = overlap ? yes : none_overlap_drops;
-                    if (overlap && !decided)                             // inside the band or out of range: exact, rare
-                        drop = suppresses_overlapping(fi, box_area_d(fi), bx[v], box_area_d(bx[v]), thresh);
-                    word[v] |= drop ? bit : 0u;
+        // one candidate outside that range (or a threshold below 1e-6) sends the segment to the exact expression pair by
+        // pair: correct, slow, and not met in practice
+        const bool fast = fast_ok && __all_sync(0xffffffffu, sane);
+        __syncwarp();                                                    // boxes staged; the key buffer is the column matrix again
+        // ---- phase A: column bits, one (slot of candidates j) x (block of earlier candidates i) tile at a time.  Blocks and
+        // slots are cut so that the RAGGED one comes first: block 0 = the first r = len - 32 (nslot - 1) candidates,
+        // blocks 1.. = 32 each -- the ragged block is then the one every slot meets (r iterations each) instead of the
+        // ragged slot being the one that meets every block.
+        // The inner loop has no branch, no predicate and 14 arithmetic instructions per 32 pair tests; it is small enough
+        // to stay in the instruction cache whatever the segment's length (unrolled over the slots, candidates in registers,
+        // it starved the issue slots on instruction fetches).  With w clamped at 0 a pair that does not overlap has
+        // inter <= 0 and falls on the "no" side by itself, so per (i, j) only two signs are kept, shifted into two words:
+        //   yes: fma(hi, uni, -inter) < 0  <=>  inter > hi * uni  (the product exact: tighter than the rounded one)
+        //   no:  fma(-lo, uni, inter) < 0  <=>  inter < lo * uni
+        // What neither settles (inside the +-2^-18 band) is a bit of `und`, resolved by the exact fp64 expression
+        // after the loop -- rare.
+        const int r = len - 32 * (nslot - 1);                            // 1..32
+        for (int v = 0; v < nslot; ++v) {
+            const int jbase = v == 0 ? 0 : r + 32 * (v - 1);
+            const bool inj = lane < (v == 0 ? r : 32);
+            const int jidx = jbase + lane;
+            const float4 bj = inj ? sm.box[jidx] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float aj = inj ? sm.area[jidx] : 1.f;
+            for (int ib = 0; ib <= v; ++ib) {
+                const int ibase = ib == 0 ? 0 : r + 32 * (ib - 1);
+                const int iend = ib == 0 ? r : 32;
+                const float4* bi = sm.box + ibase;
+                const float* ai_p = sm.area + ibase;
+                // a candidate is only suppressed by EARLIER ones: in the diagonal tile keep the bits below the lane's own
+                unsigned allow = iend >= 32 ? 0xffffffffu : (1u << iend) - 1u;
+                if (ib == v) allow &= (1u << lane) - 1u;
+                if (!inj) allow = 0u;
+                unsigned drop = 0u, und = 0u;
+                if (fast) {
+                    unsigned yrev = 0u, nrev = 0u;
+#pragma unroll 4
+                    for (int l = 0; l < iend; ++l) {
+                        const float4 fi = bi[l];
+                        const float ai = ai_p[l];
+                        const float w = fmaxf(__fsub_rn(fminf(fi.z, bj.z), fmaxf(fi.x, bj.x)), 0.f);
+                        const float h = __fsub_rn(fminf(fi.w, bj.w), fmaxf(fi.y, bj.y));
+                        const float inter = __fmul_rn(w, h);
+                        const float uni = __fsub_rn(__fadd_rn(ai, aj), inter);
+                        yrev = __funnelshift_l(__float_as_uint(__fmaf_rn(nq.hi, uni, -inter)), yrev, 1);
+                        nrev = __funnelshift_l(__float_as_uint(__fmaf_rn(-nq.lo, uni, inter)), nrev, 1);
+                    }
+                    // iteration l left its sign at bit iend - 1 - l
+                    const unsigned yes = __brev(yrev) >> (32 - iend), no = __brev(nrev) >> (32 - iend);
+                    drop = yes & allow;
+                    und = ~(yes | no) & allow;
+                } else {
+                    for (int l = 0; l < iend; ++l) {
+                        const float4 fi = bi[l];
+                        const bool ov = fminf(fi.z, bj.z) > fmaxf(fi.x, bj.x) && fminf(fi.w, bj.w) > fmaxf(fi.y, bj.y);   // :139-142
+                        if (ov) und |= 1u << l;
+                        else if (none_overlap_drops) drop |= 1u << l;   // a negative threshold: disjoint boxes suppress too (:124)
+                    }
+                    drop &= allow;
+                    und &= allow;
                 }
-            }
-            // a candidate is only suppressed by EARLIER ones: in the diagonal block keep the bits below the lane's own
-#pragma unroll
-            for (int v = 0; v < kWarpNmsSlots; ++v) {
-                if (v < ib || v >= nslot) continue;
-                unsigned wv = word[v];
-                if (v == ib) wv &= (1u << lane) - 1u;
-                if (lane + 32 * v >= len) wv = 0u;
-                sm.col[lane + 32 * v][ib] = wv;
+                while (und) {
+                    const int l = __ffs(und) - 1;
+                    und &= und - 1u;
+                    const float4 fi = bi[l];
+                    if (suppresses_overlapping(fi, box_area_d(fi), bj, box_area_d(bj), thresh)) drop |= 1u << l;
+                }
+                if (inj) sm.col[jidx][ib] = drop;
             }
         }
         __syncwarp();
-        // ---- phase B: j is kept iff no kept i < j suppresses it; lane w < nslot holds word w of the kept set ---------
+        // ---- phase B: j is kept iff no kept i < j suppresses it; lane w < nslot holds the kept bits of block w --------------
         unsigned kept = 0u;
         for (int j = 0; j < len; ++j) {
-            const int jb = j >> 5;
-            const unsigned c = (lane <= jb && lane < nslot) ? sm.col[j][lane] : 0u;     // words above jb were never written
+            const int jb = j < r ? 0 : 1 + ((j - r) >> 5);
+            const int jpos = j < r ? j : (j - r) & 31;
+            const unsigned c = (lane <= jb) ? sm.col[j][lane] : 0u;      // words above jb were never written
             const bool hit = (c & kept) != 0u;
-            if (!__any_sync(0xffffffffu, hit) && lane == jb) kept |= 1u << (j & 31);
+            if (!__any_sync(0xffffffffu, hit) && lane == jb) kept |= 1u << jpos;
         }
         unsigned char* keep_n = keep + (size_t)n * capacity;
 #pragma unroll
         for (int u = 0; u < kWarpNmsSlots; ++u) {
-            const unsigned k = __shfl_sync(0xffffffffu, kept, u);
-            if (row[u] >= 0) keep_n[row[u]] = (unsigned char)((k >> lane) & 1u);
+            const int idx = lane + 32 * u;
+            const int b = idx < r ? 0 : 1 + ((idx - r) >> 5);
+            const int pos = idx < r ? idx : (idx - r) & 31;
+            const unsigned k = __shfl_sync(0xffffffffu, kept, b & 31);
+            if (row[u] >= 0) keep_n[row[u]] = (unsigned char)((k >> pos) & 1u);
         }
     }
 }
@@ -1141,7 +1212,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
     if (nmed > 0)
         nms_warp_kernel<<<min((nmed + kWarpNmsDevThreads / 32 - 1) / (kWarpNmsDevThreads / 32), 148), kWarpNmsDevThreads,
                           sizeof(WarpNmsSmem) * (kWarpNmsDevThreads / 32), cudaStreamTailLaunch>>>(
-            gkeys, count, count_cols, capacity, cap2, thresh, sbox, sidx, keep, wl, wl_count);
+            gkeys, count, count_cols, capacity, cap2, thresh, cand, keep, wl, wl_count);
     if (nlarge > 0)
         nms_kernel<kNmsLarge><<<min(nlarge, 148), kNmsLarge, nms_smem_bytes(kNmsLarge), cudaStreamTailLaunch>>>(
             gkeys, count, count_cols, capacity, cap2, thresh, sbox, sidx, kspill, keep, wl_large, wl_count + 1);
@@ -1378,8 +1449,8 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     if (err != cudaSuccess) return err;
     if (dispatch) return cudaSuccess;
     if (!(skip & 2))
-    nms_warp_kernel<<<148 * 16, kWarpNmsThreads, wsmem, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, ws.sbox,
-                                                                 ws.sidx, keep, ws.wl, ws.wl_count);
+    nms_warp_kernel<<<148 * 16, kWarpNmsThreads, wsmem, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, cand,
+                                                                 keep, ws.wl, ws.wl_count);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
     static int clusters = -1;
