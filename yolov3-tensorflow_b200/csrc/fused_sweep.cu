@@ -30,7 +30,7 @@ namespace yv3 {
 constexpr int kMaxSpanTiles = 32;           // one object-bit word per tile, held by lane s
 
 __global__ void __launch_bounds__(32, 24) fused_sweep_kernel(const __grid_constant__ Geo g, const __grid_constant__ DenseArgs a,
-                                                         const ScoreTiles q, int S, float thresh, float4* __restrict__ stage,
+                                                         const ScoreTiles q, int S, float thresh, StageRow* __restrict__ stage,
                                                          int32_t* __restrict__ tcount, int32_t* __restrict__ post_status) {
     extern __shared__ __align__(128) unsigned char ssm[];
     __shared__ uint64_t bar_s;
@@ -203,7 +203,7 @@ bool fused_sweep_supported(const Geo& g, const DenseArgs& a, int n, float thresh
     return true;
 }
 
-cudaError_t launch_fused_sweep(const Geo& g, DenseArgs a, int n, float thresh, float4* stage, int32_t* tcount,
+cudaError_t launch_fused_sweep(const Geo& g, DenseArgs a, int n, float thresh, StageRow* stage, int32_t* tcount,
                                int32_t* post_status, int* rows_out, cudaStream_t stream) {
     const ScoreTiles q = packed_score_tiles(g, a.predicts, n, thresh);
     const int S = span_tiles(g, q);

@@ -49,7 +49,7 @@ constexpr int kScoreThreads = 128;
 // CTA only bundles warps so that their buffers fill the SM's shared memory).
 __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_constant__ Geo g,
                                                                    const float* __restrict__ predicts, const ScoreTiles q,
-                                                                   float thresh, float4* __restrict__ stage,
+                                                                   float thresh, StageRow* __restrict__ stage,
                                                                    int32_t* __restrict__ tcount) {
     extern __shared__ __align__(128) unsigned char ssm[];
     __shared__ uint64_t bar_s[kScoreThreads / 32];
@@ -96,8 +96,8 @@ __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_
 
 // One CTA per image: per head, the counts of the tiles that hold the image's records of that head go to shared memory
 // and an exclusive prefix puts them in the reference's order (head /8,/16,/32, raster inside a head: tiles in order,
-// staged order inside a tile); then one THREAD per candidate row finds its tile by binary search and writes the row
-// (:65-75), decoding the box from its five logits.  `src` says where head h's records and tiles live: the packed tensor
+// staged order inside a tile); then one THREAD per candidate row finds its tile by binary search and copies the row the
+// sweep finished (:65-75; sweep_parts.cuh) -- the tensor is not touched again.  `src` says where head h's records and tiles live: the packed tensor
 // (all three heads share one tile range) or one tensor per head.
 struct GatherSrc {
     const float* pred[3];
@@ -106,7 +106,7 @@ struct GatherSrc {
 };
 constexpr int kGatherThreads = 512;
 __global__ void __launch_bounds__(kGatherThreads) gather_kernel(const __grid_constant__ Geo g, const __grid_constant__ GatherSrc src,
-                                                                int tr, const float4* __restrict__ stage,
+                                                                int tr, const StageRow* __restrict__ stage,
                                                                 const int32_t* __restrict__ tcount, float* __restrict__ cand,
                                                                 int capacity, int32_t* __restrict__ counts, int32_t* status) {
     __shared__ int wsum_s[kGatherThreads / 32];
@@ -192,22 +192,10 @@ __global__ void __launch_bounds__(kGatherThreads) gather_kernel(const __grid_con
         // tiles with zero rows share the prefix of their successor: step back to the one that contains rel
         while (rel - pre[lo] >= cnt_s[lo]) --lo;
         const int e = rel - pre[lo];
-        const float4 sv = stage[(size_t)(src.tbase[h] + t0_s[h] + lo) * tr + before_s[lo] + e];
-        const int rih = __float_as_int(sv.w);
-        RecLoc p;
-        p.h = h;
-        const int cell = rih / g.B[h];
-        p.b = rih - cell * g.B[h];
-        p.y = cell / g.W[h];
-        p.x = cell - p.y * g.W[h];
-        const int row32 = cell / g.fold[h];
-        const int rec = row32 * src.rpr[h] + src.seg[h] + (cell - row32 * g.fold[h]) * g.B[h] + p.b;
-        const float* r = src.pred[h] + ((size_t)n * src.rpi[h] + rec) * g.L;
-        const BoxDec d = decode_box(g, p, __ldg(r), __ldg(r + 1), __ldg(r + 2), __ldg(r + 3), __ldg(r + 4));
+        const StageRow sv = stage[(size_t)(src.tbase[h] + t0_s[h] + lo) * tr + before_s[lo] + e];
         float4* o = reinterpret_cast<float4*>(out + (size_t)pos * YV3_CAND_COLS);
-        o[0] = make_float4(__fdiv_rn(d.x0, g.fW[h]), __fdiv_rn(d.y0, g.fH[h]), __fdiv_rn(d.x1, g.fW[h]),
-                           __fdiv_rn(d.y1, g.fH[h]));                            // :65-68
-        o[1] = make_float4(d.conf, sv.y, (float)__float_as_int(sv.z), sv.x);
+        o[0] = sv.box;
+        o[1] = sv.tail;
     }
 }
 
@@ -795,23 +783,19 @@ __global__ void __launch_bounds__(T) nms_kernel(const unsigned long long* __rest
 }
 
 // ---- segments of 33..256 candidates: one WARP per segment ---------------------------------------------------------
-// The greedy sweep of _apply_nms (:117-128) in two phases, both inside one warp, no block barrier:
-//  A. pair tests, fully parallel: the segment's sorted boxes and fp32 areas are staged in the warp's shared-memory
-//     slice; candidate j (lane j & 31, slot j >> 5) is tested against every earlier candidate i -- box i is a broadcast
-//     shared-memory read -- with the branch-free fp32 form of the suppression test (the exact fp32 overlap test
-//     :139-142 and the banded IoU comparison of suppresses_overlapping_fast; the rare pair inside the band takes the
-//     fp64 expression).  The outcomes are the bits of COLUMN j of the suppression matrix: word i >> 5, bit i & 31.
-//  B. the sweep, serial in j but eight lanes wide: lane w holds word w of the kept set; candidate j is kept iff no
-//     kept i < j suppresses it, i.e. iff column j AND kept is empty -- one shared-memory word per lane, one ballot.
-// ~17 instructions per 32 pair tests and no ballot in phase A (the first version, candidates in registers and one
-// ballot per (i, slot), spent ~60 and ran 950 us at cfg4; nms_kernel<256> with CTA-wide phases 1150 us).
-constexpr int kWarpNmsThreads = 32;      // one warp per CTA: 14 KB of shared memory, so an idle launch (nothing queued) slips in
-                                         // next to the sweep's CTAs instead of waiting for 57 KB to drain
+// The greedy sweep of _apply_nms (:117-128) inside one warp, no block barrier: the segment's keys are rank-sorted in
+// the warp's shared-memory slice when they arrive as a bucket of the counting sort, the sorted boxes and their fp32
+// areas are staged there, and the sweep runs block by block (32 candidates in the lanes against the earlier blocks'
+// survivors broadcast from shared memory) -- see the kernel body.  History at the dense stress workload (cfg4, 20 480
+// segments of ~133): nms_kernel<256> with CTA-wide phases 1150 us; candidates in registers, one ballot per (i, slot)
+// 950 us; a column bit matrix in shared memory + an 8-lane sweep 690 us; this form (sort included) ~400 us.
+constexpr int kWarpNmsThreads = 32;      // host launch: one warp per CTA, 5 KB of shared memory -- an idle launch (nothing
+                                         // queued) slips in next to the sweep's CTAs
 constexpr int kWarpNmsWarps = kWarpNmsThreads / 32;
 // launched from the device (sort_kernel's dispatch) a grid gets the smallest shared-memory carve-out that holds ONE of its
-// CTAs, i.e. one CTA per SM (measured: 32-thread CTAs 7.9 ms, 128-thread CTAs 2.2 ms at cfg4 against 1.1 ms from the host):
-// the device-side launch therefore uses one CTA of 14 warps (200 KB) per SM
-constexpr int kWarpNmsDevThreads = 448;
+// CTAs, i.e. one CTA per SM (measured with the 14 KB form: 32-thread CTAs 7.9 ms, 128-thread CTAs 2.2 ms at cfg4 against
+// 1.1 ms from the host): the device-side launch therefore uses one many-warp CTA per SM
+constexpr int kWarpNmsDevThreads = 768;      // 24 warps: 76 registers per thread, 120 KB of shared memory
 // The fp32 decision of phase A is trusted when every area of the segment is at least kWarpNmsAreaLo (and at most 1e29) and
 // the threshold at least kWarpNmsThreshLo: an intersection that leaves the normal fp32 range (below 1e-30, where the
 // relative error bound of the product no longer holds) is then still 6 orders of magnitude below lo * union >= 1e-24,
@@ -819,12 +803,50 @@ constexpr int kWarpNmsDevThreads = 448;
 constexpr float kWarpNmsAreaLo = 1e-18f;
 constexpr float kWarpNmsThreshLo = 1e-6f;
 struct WarpNmsSmem {
-    float4 box[kWarpNmsMax];
+    float4 box[kWarpNmsMax];       // the segment's boxes in sorted order (before that: the key buffer of the rank sort)
     float area[kWarpNmsMax];
-    unsigned col[kWarpNmsMax][kWarpNmsSlots + 1];      // + 1: odd row stride, conflict-free column-word reads in phase B
 };
-static_assert(sizeof(unsigned) * kWarpNmsMax * (kWarpNmsSlots + 1) >= sizeof(unsigned long long) * kWarpNmsMax,
-              "the column matrix doubles as the key buffer of the rank sort");
+static_assert(sizeof(float4) * kWarpNmsMax >= sizeof(unsigned long long) * kWarpNmsMax, "the box array doubles as the key buffer");
+
+// One tile of pair tests: candidate j (this lane: box bj, area aj) against the `iend` candidates i at bi / ai_p.
+// Returns in `drop` the bits i whose fp32 test says IoU(i, j) > thr and in `und` the bits the fp32 test does not settle
+// (to be resolved by the exact expression); both still unmasked.  The fast loop has no branch and no predicate, 14
+// arithmetic instructions per 32 pair tests: with w clamped at 0 a pair that does not overlap has inter <= 0 and falls
+// on the "no" side by itself, so per (i, j) two signs are kept, shifted into two words:
+//   yes: fma(hi, uni, -inter) < 0  <=>  inter > hi * uni  (the product exact: tighter than the rounded one)
+//   no:  fma(-lo, uni, inter) < 0  <=>  inter < lo * uni
+__device__ __forceinline__ void warp_nms_tile(const bool fast, const float4* bi, const float* ai_p, const int iend,
+                                              const float4 bj, const float aj, const NmsThresh& nq,
+                                              const bool none_overlap_drops, unsigned& drop, unsigned& und) {
+    drop = 0u;
+    und = 0u;
+    if (fast) {
+        unsigned yrev = 0u, nrev = 0u;
+#pragma unroll 4
+        for (int l = 0; l < iend; ++l) {
+            const float4 fi = bi[l];
+            const float ai = ai_p[l];
+            const float w = fmaxf(__fsub_rn(fminf(fi.z, bj.z), fmaxf(fi.x, bj.x)), 0.f);
+            const float h = __fsub_rn(fminf(fi.w, bj.w), fmaxf(fi.y, bj.y));
+            const float inter = __fmul_rn(w, h);
+            const float uni = __fsub_rn(__fadd_rn(ai, aj), inter);
+            yrev = __funnelshift_l(__float_as_uint(__fmaf_rn(nq.hi, uni, -inter)), yrev, 1);
+            nrev = __funnelshift_l(__float_as_uint(__fmaf_rn(-nq.lo, uni, inter)), nrev, 1);
+        }
+        // iteration l left its sign at bit iend - 1 - l
+        const unsigned valid = iend >= 32 ? 0xffffffffu : (1u << iend) - 1u;
+        const unsigned yes = __brev(yrev) >> (32 - iend), no = __brev(nrev) >> (32 - iend);
+        drop = yes & valid;
+        und = ~(yes | no) & valid;
+    } else {
+        for (int l = 0; l < iend; ++l) {
+            const float4 fi = bi[l];
+            const bool ov = fminf(fi.z, bj.z) > fmaxf(fi.x, bj.x) && fminf(fi.w, bj.w) > fmaxf(fi.y, bj.y);   // :139-142
+            if (ov) und |= 1u << l;
+            else if (none_overlap_drops) drop |= 1u << l;               // a negative threshold: disjoint boxes suppress too (:124)
+        }
+    }
+}
 
 // Rank sort of a bucket of at most 32 * NS keys (arrival order -> ascending key = score descending, row ascending) in the
 // warp's key buffer: every key is broadcast from shared memory and counted against the NS keys a lane holds; keys are
@@ -891,8 +913,8 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
         const int nslot = (len + 31) >> 5;
         __syncwarp();                                                    // the previous segment's sweep is done with sm
         if (needs_sort) {
-            // the column matrix is free until phase A: it doubles as the key buffer
-            unsigned long long* skey = reinterpret_cast<unsigned long long*>(&sm.col[0][0]);
+            // the box array is free until the boxes are staged: it doubles as the key buffer
+            unsigned long long* skey = reinterpret_cast<unsigned long long*>(&sm.box[0]);
             switch (nslot) {
                 case 1: warp_rank_sort<1>(skey, lane, len, keys); break;
                 case 2: warp_rank_sort<2>(skey, lane, len, keys); break;
@@ -906,98 +928,121 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
             keys = skey;
         }
         int row[kWarpNmsSlots];
+#pragma unroll
+        for (int u = 0; u < kWarpNmsSlots; ++u) row[u] = (lane + 32 * u < len) ? (int)(keys[lane + 32 * u] & 0x3ffffULL) : -1;
+        __syncwarp();                                                    // the keys are read: their buffer becomes the box array
         bool sane = true;
 #pragma unroll
         for (int u = 0; u < kWarpNmsSlots; ++u) {
-            const int idx = lane + 32 * u;
-            const bool in = idx < len;
-            row[u] = in ? (int)(keys[idx] & 0x3ffffULL) : -1;
-            if (in) {
+            if (row[u] >= 0) {
                 const float4 b = __ldg(reinterpret_cast<const float4*>(rows + (size_t)row[u] * YV3_CAND_COLS));
                 const float a = __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
-                sm.box[idx] = b;
-                sm.area[idx] = a;
+                sm.box[lane + 32 * u] = b;
+                sm.area[lane + 32 * u] = a;
                 sane = sane && a >= kWarpNmsAreaLo && a <= 1e29f;
             }
         }
         // one candidate outside that range (or a threshold below 1e-6) sends the segment to the exact expression pair by
         // pair: correct, slow, and not met in practice
         const bool fast = fast_ok && __all_sync(0xffffffffu, sane);
-        __syncwarp();                                                    // boxes staged; the key buffer is the column matrix again
-        // ---- phase A: column bits, one (slot of candidates j) x (block of earlier candidates i) tile at a time.  Blocks and
-        // slots are cut so that the RAGGED one comes first: block 0 = the first r = len - 32 (nslot - 1) candidates,
-        // blocks 1.. = 32 each -- the ragged block is then the one every slot meets (r iterations each) instead of the
-        // ragged slot being the one that meets every block.
-        // The inner loop has no branch, no predicate and 14 arithmetic instructions per 32 pair tests; it is small enough
-        // to stay in the instruction cache whatever the segment's length (unrolled over the slots, candidates in registers,
-        // it starved the issue slots on instruction fetches).  With w clamped at 0 a pair that does not overlap has
-        // inter <= 0 and falls on the "no" side by itself, so per (i, j) only two signs are kept, shifted into two words:
-        //   yes: fma(hi, uni, -inter) < 0  <=>  inter > hi * uni  (the product exact: tighter than the rounded one)
-        //   no:  fma(-lo, uni, inter) < 0  <=>  inter < lo * uni
-        // What neither settles (inside the +-2^-18 band) is a bit of `und`, resolved by the exact fp64 expression
-        // after the loop -- rare.
+        __syncwarp();
+        // ---- the greedy sweep of _apply_nms (:117-128), block by block.  Blocks are cut so that the RAGGED one comes
+        // first: block 0 = the first r = len - 32 (nslot - 1) candidates, blocks 1.. = 32 each (the ragged block is then
+        // the one every later block meets, r iterations each, instead of the one that meets every block).  Per block b:
+        //   1. diagonal tile: lane j tests its candidate against the block's earlier ones (bits below its own);
+        //   2. the block's survivors: x_j = alive_j and no kept i < j suppresses j.  Iterating
+        //      x <- alive & ~exists(x_i & S_ij) from x = alive fixes lane t after t rounds (induction on j) and stops at
+        //      the unique solution, usually in 2-3 ballots instead of a 32-step chain;
+        //   3. every later block tests its candidates against block b's SURVIVORS only (all of its members when most
+        //      survived, the survivors one by one when few did) and marks the suppressed ones dead.
+        // No suppression matrix is kept: 5 KB of shared memory per warp instead of 14, so the warps of this kernel and
+        // the CTAs of the sweep that runs next to it both fit on an SM.
         const int r = len - 32 * (nslot - 1);                            // 1..32
-        for (int v = 0; v < nslot; ++v) {
-            const int jbase = v == 0 ? 0 : r + 32 * (v - 1);
-            const bool inj = lane < (v == 0 ? r : 32);
-            const int jidx = jbase + lane;
-            const float4 bj = inj ? sm.box[jidx] : make_float4(0.f, 0.f, 0.f, 0.f);
-            const float aj = inj ? sm.area[jidx] : 1.f;
-            for (int ib = 0; ib <= v; ++ib) {
-                const int ibase = ib == 0 ? 0 : r + 32 * (ib - 1);
-                const int iend = ib == 0 ? r : 32;
-                const float4* bi = sm.box + ibase;
-                const float* ai_p = sm.area + ibase;
-                // a candidate is only suppressed by EARLIER ones: in the diagonal tile keep the bits below the lane's own
-                unsigned allow = iend >= 32 ? 0xffffffffu : (1u << iend) - 1u;
-                if (ib == v) allow &= (1u << lane) - 1u;
-                if (!inj) allow = 0u;
+        unsigned deadmask = 0u;                                          // bit v: this lane's candidate of block v is suppressed
+        unsigned keptw = 0u;                                             // lane b: the survivors of block b
+        for (int ib = 0; ib < nslot; ++ib) {
+            const int ibase = ib == 0 ? 0 : r + 32 * (ib - 1);
+            const int iend = ib == 0 ? r : 32;
+            const float4* bi = sm.box + ibase;
+            const float* ai_p = sm.area + ibase;
+            unsigned km;
+            {
+                const bool inj = lane < iend;
+                const float4 bj = inj ? bi[lane] : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float aj = inj ? ai_p[lane] : 1.f;
+                const bool alive = inj && !((deadmask >> ib) & 1u);
                 unsigned drop = 0u, und = 0u;
-                if (fast) {
-                    unsigned yrev = 0u, nrev = 0u;
-#pragma unroll 4
-                    for (int l = 0; l < iend; ++l) {
+                if (__any_sync(0xffffffffu, alive)) {
+                    warp_nms_tile(fast, bi, ai_p, iend, bj, aj, nq, none_overlap_drops, drop, und);
+                    const unsigned allow = alive ? (1u << lane) - 1u : 0u;          // only EARLIER candidates suppress
+                    drop &= allow;
+                    und &= allow;
+                    while (und) {
+                        const int l = __ffs(und) - 1;
+                        und &= und - 1u;
+                        const float4 fi = bi[l];
+                        if (suppresses_overlapping(fi, box_area_d(fi), bj, box_area_d(bj), thresh)) drop |= 1u << l;
+                    }
+                }
+                km = __ballot_sync(0xffffffffu, alive);
+                for (;;) {
+                    const unsigned nk = __ballot_sync(0xffffffffu, alive && (drop & km) == 0u);
+                    if (nk == km) break;
+                    km = nk;
+                }
+                if (lane == ib) keptw = km;
+            }
+            if (km == 0u) continue;
+            const bool sparse = __popc(km) * 4 < iend * 3;               // fewer than 3/4 survived: visit the survivors only
+            for (int v = ib + 1; v < nslot; ++v) {
+                const int jbase = r + 32 * (v - 1);                      // blocks 1.. are full: every lane holds a candidate
+                const bool alive = !((deadmask >> v) & 1u);
+                if (!__any_sync(0xffffffffu, alive)) continue;
+                const float4 bj = sm.box[jbase + lane];
+                const float aj = sm.area[jbase + lane];
+                unsigned drop = 0u, und = 0u;
+                if (sparse && fast) {
+                    unsigned ysign = 0u, decided = 0xffffffffu;
+                    for (unsigned m = km; m; m &= m - 1u) {
+                        const int l = __ffs(m) - 1;
                         const float4 fi = bi[l];
                         const float ai = ai_p[l];
                         const float w = fmaxf(__fsub_rn(fminf(fi.z, bj.z), fmaxf(fi.x, bj.x)), 0.f);
                         const float h = __fsub_rn(fminf(fi.w, bj.w), fmaxf(fi.y, bj.y));
                         const float inter = __fmul_rn(w, h);
                         const float uni = __fsub_rn(__fadd_rn(ai, aj), inter);
-                        yrev = __funnelshift_l(__float_as_uint(__fmaf_rn(nq.hi, uni, -inter)), yrev, 1);
-                        nrev = __funnelshift_l(__float_as_uint(__fmaf_rn(-nq.lo, uni, inter)), nrev, 1);
+                        const unsigned y = __float_as_uint(__fmaf_rn(nq.hi, uni, -inter));
+                        const unsigned o = __float_as_uint(__fmaf_rn(-nq.lo, uni, inter));
+                        ysign |= y;
+                        decided &= y | o;
                     }
-                    // iteration l left its sign at bit iend - 1 - l
-                    const unsigned yes = __brev(yrev) >> (32 - iend), no = __brev(nrev) >> (32 - iend);
-                    drop = yes & allow;
-                    und = ~(yes | no) & allow;
+                    if (ysign >> 31) drop = km;                          // some survivor suppresses it: which one is irrelevant
+                    else if (!(decided >> 31)) und = km;                 // a pair inside the band: the exact walk below (rare)
+                    if (und) {                                           // not every bit is undecided: only overlapping pairs go on
+                        unsigned uo = 0u;
+                        for (unsigned m = km; m; m &= m - 1u) {
+                            const int l = __ffs(m) - 1;
+                            const float4 fi = bi[l];
+                            if (fminf(fi.z, bj.z) > fmaxf(fi.x, bj.x) && fminf(fi.w, bj.w) > fmaxf(fi.y, bj.y)) uo |= 1u << l;
+                        }
+                        und = uo;
+                    }
                 } else {
-                    for (int l = 0; l < iend; ++l) {
+                    warp_nms_tile(fast, bi, ai_p, iend, bj, aj, nq, none_overlap_drops, drop, und);
+                    drop &= km;
+                    und &= km;
+                }
+                bool hit = drop != 0u;
+                if (alive && !hit) {
+                    while (und) {
+                        const int l = __ffs(und) - 1;
+                        und &= und - 1u;
                         const float4 fi = bi[l];
-                        const bool ov = fminf(fi.z, bj.z) > fmaxf(fi.x, bj.x) && fminf(fi.w, bj.w) > fmaxf(fi.y, bj.y);   // :139-142
-                        if (ov) und |= 1u << l;
-                        else if (none_overlap_drops) drop |= 1u << l;   // a negative threshold: disjoint boxes suppress too (:124)
+                        if (suppresses_overlapping(fi, box_area_d(fi), bj, box_area_d(bj), thresh)) { hit = true; break; }
                     }
-                    drop &= allow;
-                    und &= allow;
                 }
-                while (und) {
-                    const int l = __ffs(und) - 1;
-                    und &= und - 1u;
-                    const float4 fi = bi[l];
-                    if (suppresses_overlapping(fi, box_area_d(fi), bj, box_area_d(bj), thresh)) drop |= 1u << l;
-                }
-                if (inj) sm.col[jidx][ib] = drop;
+                if (hit) deadmask |= 1u << v;
             }
-        }
-        __syncwarp();
-        // ---- phase B: j is kept iff no kept i < j suppresses it; lane w < nslot holds the kept bits of block w --------------
-        unsigned kept = 0u;
-        for (int j = 0; j < len; ++j) {
-            const int jb = j < r ? 0 : 1 + ((j - r) >> 5);
-            const int jpos = j < r ? j : (j - r) & 31;
-            const unsigned c = (lane <= jb) ? sm.col[j][lane] : 0u;      // words above jb were never written
-            const bool hit = (c & kept) != 0u;
-            if (!__any_sync(0xffffffffu, hit) && lane == jb) kept |= 1u << jpos;
         }
         unsigned char* keep_n = keep + (size_t)n * capacity;
 #pragma unroll
@@ -1005,7 +1050,7 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
             const int idx = lane + 32 * u;
             const int b = idx < r ? 0 : 1 + ((idx - r) >> 5);
             const int pos = idx < r ? idx : (idx - r) & 31;
-            const unsigned k = __shfl_sync(0xffffffffu, kept, b & 31);
+            const unsigned k = __shfl_sync(0xffffffffu, keptw, b & 31);
             if (row[u] >= 0) keep_n[row[u]] = (unsigned char)((k >> pos) & 1u);
         }
     }
@@ -1209,10 +1254,11 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
     __threadfence();
     wl_count[2] = 0;
     const int nmed = *(volatile int32_t*)wl_count, nlarge = *(volatile int32_t*)(wl_count + 1);
-    if (nmed > 0)
-        nms_warp_kernel<<<min((nmed + kWarpNmsDevThreads / 32 - 1) / (kWarpNmsDevThreads / 32), 148), kWarpNmsDevThreads,
-                          sizeof(WarpNmsSmem) * (kWarpNmsDevThreads / 32), cudaStreamTailLaunch>>>(
+    if (nmed > 0) {
+        const int wpc = dispatch;                                // warps per CTA of the device-launched grid (one CTA per SM)
+        nms_warp_kernel<<<min((nmed + wpc - 1) / wpc, 148), 32 * wpc, sizeof(WarpNmsSmem) * wpc, cudaStreamTailLaunch>>>(
             gkeys, count, count_cols, capacity, cap2, thresh, cand, keep, wl, wl_count);
+    }
     if (nlarge > 0)
         nms_kernel<kNmsLarge><<<min(nlarge, 148), kNmsLarge, nms_smem_bytes(kNmsLarge), cudaStreamTailLaunch>>>(
             gkeys, count, count_cols, capacity, cap2, thresh, sbox, sidx, kspill, keep, wl_large, wl_count + 1);
@@ -1358,7 +1404,7 @@ int score_num_tiles(const Geo& g, int n) {
 
 // pred[0] alone: the packed tensor; unpacked: one tensor per head (N, H, W, B*L), each swept under its single-head geometry
 cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool unpacked, int n, float thresh, float* cand,
-                                 int capacity, int32_t* counts, int32_t* status, float4* stage, int32_t* tcount,
+                                 int capacity, int32_t* counts, int32_t* status, StageRow* stage, int32_t* tcount,
                                  bool sweep, bool gather, cudaStream_t stream) {
     GatherSrc src;
     memset(&src, 0, sizeof(src));
@@ -1436,7 +1482,14 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     static int skip = -1;                                     // developer switch (timing experiments only): YV3_NMS_SKIP bits
     if (skip < 0) { const char* e = getenv("YV3_NMS_SKIP"); skip = e ? atoi(e) : 0; }
     // many classes: the queue-driven kernels are launched from the device, and only when something is queued
-    const int dispatch = (num_classes > 8 && !(skip & 8)) ? 1 : 0;
+    static int dev_warps = -1, host_ctas = -1;                // developer switches (timing experiments only)
+    if (dev_warps < 0) {
+        const char* e = getenv("YV3_WARP_NMS_DEV_WARPS");
+        dev_warps = e ? max(1, min(atoi(e), kWarpNmsDevThreads / 32)) : kWarpNmsDevThreads / 32;
+        e = getenv("YV3_WARP_NMS_HOST_CTAS");
+        host_ctas = e ? max(1, atoi(e)) : 24;
+    }
+    const int dispatch = (num_classes > 8 && !(skip & 8)) ? dev_warps : 0;
     err = set_smem_once((const void*)nms_kernel<kNmsLarge>, nms_smem_bytes(kNmsLarge));
     if (err != cudaSuccess) return err;
     const size_t wsmem = sizeof(WarpNmsSmem) * kWarpNmsWarps;
@@ -1449,7 +1502,7 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     if (err != cudaSuccess) return err;
     if (dispatch) return cudaSuccess;
     if (!(skip & 2))
-    nms_warp_kernel<<<148 * 16, kWarpNmsThreads, wsmem, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, cand,
+    nms_warp_kernel<<<148 * host_ctas, kWarpNmsThreads, wsmem, stream>>>(ws.keys, count, count_cols, capacity, cap2, thresh, cand,
                                                                  keep, ws.wl, ws.wl_count);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;

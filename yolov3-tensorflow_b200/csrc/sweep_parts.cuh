@@ -28,7 +28,7 @@ ScoreTiles packed_score_tiles(const Geo& g, const float* predicts, int n, float 
 // clip(sigmoid(t4)) -- both are computed once by the caller, which needs them too.
 __device__ __forceinline__ void score_tile_records(const Geo& g, const ScoreTiles& q, const float* tile, int unit, int lane,
                                                    int nrec, int slot, const RecLoc& p, float conf, float thresh,
-                                                   float4* __restrict__ stage, int32_t* __restrict__ tcount) {
+                                                   StageRow* __restrict__ stage, int32_t* __restrict__ tcount) {
     const int L = g.L, C = g.C, tr = q.tr;
     const bool have = lane < nrec;
     const float* r = tile + (size_t)lane * L;
@@ -120,8 +120,13 @@ __device__ __forceinline__ void score_tile_records(const Geo& g, const ScoreTile
         run += __popc(b);
     }
     if (pass) {
-        const int rih = (p.y * g.W[p.h] + p.x) * g.B[p.h] + p.b;
-        stage[(size_t)unit * tr + my_base + my_rank] = make_float4(mine.x, mine.y, mine.z, __int_as_float(rih));
+        // the finished row (:65-75): the box is decoded here, from the logits the tile still holds
+        const BoxDec d = decode_box(g, p, r[0], r[1], r[2], r[3], r[4]);
+        StageRow o;
+        o.box = make_float4(__fdiv_rn(d.x0, g.fW[p.h]), __fdiv_rn(d.y0, g.fH[p.h]), __fdiv_rn(d.x1, g.fW[p.h]),
+                            __fdiv_rn(d.y1, g.fH[p.h]));                             // :65-68
+        o.tail = make_float4(d.conf, mine.y, (float)__float_as_int(mine.z), mine.x);
+        stage[(size_t)unit * tr + my_base + my_rank] = o;
     }
     if (lane < 6) tcount[(size_t)unit * 8 + lane] = cnt_lane;
 }

@@ -338,7 +338,7 @@ PostWs carve_post(void* base, long long rpi, int n, int capacity, int num_tiles 
     w.score = (float*)take(recs * 4);
     w.prob = (float*)take(recs * 4);
     w.cls = (int32_t*)take(recs * 4);
-    w.stage = (float4*)take((recs + 256) * 16);
+    w.stage = (StageRow*)take((recs + 256) * sizeof(StageRow));
     w.tcount = (int32_t*)take(((size_t)num_tiles + 1) * 8 * 4);
     w.keys = (unsigned long long*)take((size_t)n * nms_cap2(capacity) * 8);
     w.sbox = (float4*)take(rows * 16);

@@ -4,6 +4,13 @@
 
 namespace yv3 {
 
+// One staged survivor of the score sweep: the finished candidate row (yolov3_post_process.py:65-75), written while the
+// record's logits are in shared memory -- the gather then only compacts rows and never goes back to the tensor.
+struct __align__(16) StageRow {
+    float4 box;                 // x0 / W, y0 / H, x1 / W, y1 / H
+    float4 tail;                // conf, prob, class, score
+};
+
 // ---- assign.cu ---------------------------------------------------------------------------------
 // Where the records of head h live: the packed tensor (one base, the head's segment inside every /32 row), or one
 // tensor per head (N, H, W, B*L) -- which is the packed layout of a geometry that has only that head (a /32 row of
@@ -68,7 +75,7 @@ cudaError_t launch_loss_fold(const Geo& g, const DenseArgs& a, int nrows, cudaSt
 int fused_row_count(const Geo& g, const float* predicts, int n, float thresh);       // spans (= partial rows) of the sweep
 int packed_tile_count(const Geo& g, const float* predicts, int n, float thresh);     // tiles of 32 records of the sweep
 bool fused_sweep_supported(const Geo& g, const DenseArgs& a, int n, float thresh);
-cudaError_t launch_fused_sweep(const Geo& g, DenseArgs a, int n, float thresh, float4* stage, int32_t* tcount,
+cudaError_t launch_fused_sweep(const Geo& g, DenseArgs a, int n, float thresh, StageRow* stage, int32_t* tcount,
                                int32_t* post_status, int* rows_out, cudaStream_t stream);
 
 // ---- decode.cu ---------------------------------------------------------------------------------
@@ -92,7 +99,7 @@ struct PostWs {
     float* score;               // [n][rpi]  head-raster order (filter only)
     float* prob;                // [n][rpi]
     int32_t* cls;               // [n][rpi]
-    float4* stage;              // [num_tiles][tr] staged survivors of the fused filter (score, prob, class, record)
+    StageRow* stage;            // [num_tiles][tr] staged survivors of the filter, in ballot-rank order per (image slot, head)
     int32_t* tcount;            // [num_tiles][8] survivors per tile and (image slot, head)
     unsigned long long* keys;   // [n][cap2] sorted keys (class | ~score | row)
     float4* sbox;               // [n][capacity] boxes in sorted order
@@ -108,7 +115,7 @@ cudaError_t launch_collect(const float* cand, const int32_t* counts, const unsig
                            double tw, double th, int bug_compat, double* rows_out, int32_t* counts_out, cudaStream_t stream);
 int heads_tr(const Geo& g, int n);      // records per tile of the per-head sweeps; < 4: a head has fewer than 4 records per image
 cudaError_t launch_filter_packed(const Geo& g, const float* const pred[3], bool unpacked, int n, float thresh, float* cand,
-                                 int capacity, int32_t* counts, int32_t* status, float4* stage, int32_t* tcount,
+                                 int capacity, int32_t* counts, int32_t* status, StageRow* stage, int32_t* tcount,
                                  bool sweep, bool gather, cudaStream_t stream);
 cudaError_t launch_filter_decoded(const Geo& g, const float* const decoded[3], const float* const boxes[3],
                                   float thresh, float* cand, int capacity, int32_t* counts, int32_t* status,
