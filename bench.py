@@ -129,7 +129,11 @@ class ClockSampler(threading.Thread):
             try:
                 sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
                 reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-                self.samples.append((time.time(), sm, reasons, self.mark))
+                try:
+                    mem = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_MEM)
+                except Exception:
+                    mem = None
+                self.samples.append((time.time(), sm, reasons, self.mark, mem))
             except Exception:
                 pass
             time.sleep(0.005)
@@ -148,8 +152,9 @@ class ClockSampler(threading.Thread):
             "hw_power_brake": getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80),
         }
         seen = sorted({k for s in timed for k, bit in names.items() if s[2] & bit})
+        mems = [s[4] for s in timed if s[4] is not None]
         return {"sm_mhz": float(np.median([s[1] for s in timed])), "sm_max_mhz": self.max_sm, "reasons": seen,
-                "samples": len(timed)}
+                "samples": len(timed), "mem_mhz": float(np.median(mems)) if mems else None}
 
 
 # ---- CPU legs: the only place bench.py executes oracle/ ---------------------------------------------------------------
@@ -339,11 +344,14 @@ class Arm(object):
         b.record()
         self.fence()
         ms = a.elapsed_time(b)
+        self.per_rank_ms = None
         if self.world > 1:
             import torch.distributed as dist
             t = torch.tensor([ms], dtype=torch.float64, device=self.dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t)
+            allt = [torch.zeros_like(t) for _ in range(self.world)]
+            dist.all_gather(allt, t)
+            self.per_rank_ms = [float(x) / (reps * steps) for x in allt]     # every rank's own clock around the same region
+            ms = max(float(x) for x in allt)
         return ms / (reps * steps), reps * steps
 
     def time_sweep(self, reps):
@@ -698,6 +706,15 @@ def main():
     probe = arm.h2d_probe() if not args.no_extras else None
     sampler.stop_flag = True
     sampler.join(timeout=2)
+    clocks = sampler.summary()
+    if world > 1:
+        # every rank watched its OWN GPU: the line carries the slowest median and the union of the throttle reasons
+        allc = [None] * world
+        dist.all_gather_object(allc, clocks)
+        meds = [c["sm_mhz"] for c in allc if c.get("sm_mhz") is not None]
+        clocks = dict(clocks, sm_mhz=min(meds) if meds else None,
+                      reasons=sorted({r for c in allc for r in c.get("reasons", [])}),
+                      per_rank=[{"sm_mhz": c.get("sm_mhz"), "mem_mhz": c.get("mem_mhz"), "reasons": c.get("reasons")} for c in allc])
 
     stages, owned, check = None, 0, None
     if not args.no_extras:
@@ -746,6 +763,7 @@ def main():
             "value": world * n / (ms_per_step * 1e-3), "unit": "images/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "timed_steps": timed_steps, "timed_region_ms": ms_per_step * timed_steps,
+            "ms_per_step_per_rank": getattr(arm, "per_rank_ms", None),
             "higher_is_better": True, "scaling": "strong" if "global_batch" in w else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": config_block(args.workload, w, n, world, {
@@ -783,7 +801,7 @@ def main():
                              if args.fused else (6 + (0 if max(arm.spec.class_num, 1) > 8 else 2))) * timed_steps,
             "gpu_launches_note": "host-side launches of this library's kernels in the timed region; NMS kernels the sort "
                                  "kernel tail-launches from the device are extra",
-            "clocks": sampler.summary(),
+            "clocks": clocks,
             "extra_workloads": extras,
         }
         if check is not None:

@@ -58,6 +58,7 @@ class FusedPipeline(object):
         prio = -1 if high_priority else 0
         self.aux_stream = torch.cuda.Stream(priority=prio)
         self.post_stream = torch.cuda.Stream(priority=prio)
+        self.reduce_stream = torch.cuda.Stream(priority=prio)
         self.last_fused = None
 
     # ---- bookkeeping ---------------------------------------------------------------------------------------------
@@ -131,6 +132,8 @@ class FusedPipeline(object):
 
         aux.wait_stream(cur)
         post.wait_stream(cur)
+        if self.reducer is not None:
+            self.reduce_stream.wait_stream(cur)
         a_done = [assign(j) if j < count else None for j in range(depth)]
         g_done = [None] * depth
         for k in range(count):
@@ -151,11 +154,21 @@ class FusedPipeline(object):
                 aux.wait_event(swept)
                 part(k, 4)
                 if self.reducer is not None:
-                    self.reducer(rows[k])              # the step's one exchange: 80 bytes over NVLink, off the sweeps' stream
+                    folded = torch.cuda.Event()
+                    folded.record(aux)
+            if self.reducer is not None:
+                # the step's one exchange: 80 bytes over NVLink, on a stream of its own -- nothing of this rank's later
+                # steps waits for the peers (behind the fold on the aux stream it held back assign(k + depth), and with it
+                # sweep k + depth, until the slowest rank had folded step k: the ranks ran in lock step)
+                with torch.cuda.stream(self.reduce_stream):
+                    self.reduce_stream.wait_event(folded)
+                    self.reducer(rows[k])
             if k + depth < count:
                 a_done[b] = assign(k + depth)
         cur.wait_stream(post)
         cur.wait_stream(aux)
+        if self.reducer is not None:
+            cur.wait_stream(self.reduce_stream)
         self.last_fused = all(lo.last_fused for lo, _ in self.pairs[:min(depth, count)])
         self._finish(cur_after)
 
