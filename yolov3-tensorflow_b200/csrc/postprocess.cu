@@ -457,7 +457,7 @@ __device__ __forceinline__ void sort_body(const float* __restrict__ cand, const 
                                           unsigned long long* __restrict__ gkeys, float4* __restrict__ sbox,
                                           int32_t* __restrict__ sidx, unsigned char* __restrict__ keep,
                                           int2* __restrict__ wl, int2* __restrict__ wl_large,
-                                          int32_t* __restrict__ wl_count) {
+                                          int32_t* __restrict__ wl_count, const bool many_classes) {
     extern __shared__ __align__(16) unsigned long long skeys[];
     __shared__ int nseg_s;
     const NmsThresh nq = make_nms_thresh(thresh);
@@ -480,7 +480,9 @@ __device__ __forceinline__ void sort_body(const float* __restrict__ cand, const 
     // greedy NMS with the candidates in the warp's lanes; a longer one is published (sorted keys, rows, boxes) and queued
     // for nms_warp_kernel.  No 16 384-key bitonic sort (380 us per step at the stress workload).
     int* hist_s = reinterpret_cast<int*>(skeys + n2s);                                // [kBucketClasses] counts -> offsets
-    if (K <= kBucketMaxK) {
+    // (with a handful of classes a long list cannot have <= 256 per class: no attempt, the histogram would be 8000
+    // atomics on one word)
+    if (K <= kBucketMaxK && (many_classes || K <= 8 * kWarpNmsMax)) {
         // The shared-memory reservation is sized for SHORT lists (n2s <= 4096 keys, 45 KB: a sort CTA finds room on an SM
         // next to the sweep's CTAs; with 16 384 keys it needed 164 KB and pushed ~15 of them out for its whole life).
         // A longer list keeps its bucketed keys in gk and the arrival order in the (still unused) sorted-row table.
@@ -1072,7 +1074,7 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
 constexpr int kClu = YV3_NMS_CLUSTER;
 constexpr int kCluT = 1024;             // threads per CTA = candidates per chunk
 __host__ __device__ inline size_t nms_cluster_smem_bytes() {
-    return (size_t)kCluT * 16 + (size_t)kCluT * (kCluT / 64) * 8 + (size_t)kCluT * 3;
+    return (size_t)kCluT * 16 + (size_t)kCluT * (kCluT / 64) * 8 + (size_t)kCluT * 3 + (size_t)kCluT * 20;
 }
 
 __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned long long* __restrict__ gkeys,
@@ -1090,7 +1092,10 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
     unsigned char* alive_s = reinterpret_cast<unsigned char*>(mask_s + (size_t)T * W);       // [T] after the AND
     unsigned char* verdict_s = alive_s + T;                                                  // [T] this CTA's share
     unsigned char* kept_flag_s = verdict_s + T;                                              // [T]
+    float4* kbox_s = reinterpret_cast<float4*>(kept_flag_s + T);                            // [T] a tile of this CTA's share of the kept list
+    float* karea_s = reinterpret_cast<float*>(kbox_s + T);                                  // [T]
     __shared__ int seg_s[2];
+    __shared__ int sane_s;
     __shared__ int nkept_s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int r = (int)cluster.block_rank();
@@ -1128,29 +1133,61 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
         int nk = 0;
         for (int c0 = s0; c0 < s1; c0 += T) {
             const int cnt = min(T, s1 - c0);
-            // phase 1: this thread's candidate against this CTA's share of the boxes kept so far
+            // phase 1: this thread's candidate against this CTA's share of the boxes kept so far (kept box q belongs to CTA
+            // q mod kClu).  The share is staged through shared memory a tile of T boxes at a time, with the fp32 areas, and
+            // every warp walks the tile with the branch-free test of warp_nms_tile: two fused sign tests per pair, OR-ed
+            // (which kept box suppresses the candidate is irrelevant).  Only a candidate with a pair inside the +-2^-18
+            // band -- or a list with an area outside the trusted range -- walks its share again with the exact test.
             bool alive = tid < cnt;
             float4 mine_f = make_float4(0.f, 0.f, 0.f, 0.f);
-            BoxD mine = {};
+            float aj = 1.f;
             if (alive) {
                 mine_f = boxes[c0 + tid];
-                mine = to_boxd(mine_f);
                 chunk_s[tid] = mine_f;
+                aj = __fmul_rn(__fsub_rn(mine_f.z, mine_f.x), __fsub_rn(mine_f.w, mine_f.y));
             }
-            for (int q = r; q < nk; q += 4 * kClu) {
-                // four kept boxes in flight (the address does not depend on the verdicts)
-                float4 kb[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) kb[u] = __ldcg(spill + min(q + u * kClu, nk - 1));
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    if (q + u * kClu < nk && alive) {
-                        const bool drop = overlaps_f32(kb[u], mine_f)
-                                              ? suppresses_overlapping_fast(kb[u], mine_f, nq)
-                                              : none_overlap_drops;
-                        if (drop) alive = false;
+            const bool sane_mine = aj >= kWarpNmsAreaLo && aj <= 1e29f;
+            unsigned ysign = 0u, decided = 0xffffffffu;
+            if (tid == 0) sane_s = 1;
+            for (int base = 0; base < nk; base += kClu * T) {
+                __syncthreads();                                     // the previous tile is consumed (and sane_s is set)
+                const int q = base + r + kClu * tid;
+                if (q < nk) {
+                    const float4 b = __ldcg(spill + q);
+                    const float a = __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
+                    kbox_s[tid] = b;
+                    karea_s[tid] = a;
+                    if (!(a >= kWarpNmsAreaLo && a <= 1e29f)) sane_s = 0;
+                }
+                const int rem = nk - base - r;
+                const int cntk = rem <= 0 ? 0 : min(T, (rem + kClu - 1) / kClu);
+                __syncthreads();
+#pragma unroll 4
+                for (int l = 0; l < cntk; ++l) {
+                    const float4 fi = kbox_s[l];
+                    const float ai = karea_s[l];
+                    const float w = fmaxf(__fsub_rn(fminf(fi.z, mine_f.z), fmaxf(fi.x, mine_f.x)), 0.f);
+                    const float h = __fsub_rn(fminf(fi.w, mine_f.w), fmaxf(fi.y, mine_f.y));
+                    const float inter = __fmul_rn(w, h);
+                    const float uni = __fsub_rn(__fadd_rn(ai, aj), inter);
+                    const unsigned y = __float_as_uint(__fmaf_rn(nq.hi, uni, -inter));
+                    const unsigned o = __float_as_uint(__fmaf_rn(-nq.lo, uni, inter));
+                    ysign |= y;
+                    decided &= y | o;
+                }
+            }
+            __syncthreads();
+            {
+                const bool fast = nq.lo >= kWarpNmsThreshLo && sane_s != 0 && sane_mine;
+                bool hit = fast && (ysign >> 31) != 0u;
+                if (alive && !hit && !(fast && (decided >> 31) != 0u)) {
+                    for (int q = r; q < nk; q += kClu) {
+                        const float4 kb = __ldcg(spill + q);
+                        const bool drop = overlaps_f32(kb, mine_f) ? suppresses_overlapping_fast(kb, mine_f, nq) : none_overlap_drops;
+                        if (drop) { hit = true; break; }
                     }
                 }
+                if (hit) alive = false;
             }
             verdict_s[tid] = alive ? 1 : 0;
             cluster.sync();                                          // (A) every CTA's verdicts are in place
@@ -1245,7 +1282,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
                                                             int2* __restrict__ wl, int2* __restrict__ wl_large,
                                                             int32_t* __restrict__ wl_count, float4* __restrict__ kspill,
                                                             int dispatch) {
-    sort_body(cand, count, count_cols, capacity, cap2, n2s, thresh, gkeys, sbox, sidx, keep, wl, wl_large, wl_count);
+    sort_body(cand, count, count_cols, capacity, cap2, n2s, thresh, gkeys, sbox, sidx, keep, wl, wl_large, wl_count, dispatch != 0);
     if (!dispatch) return;
     __syncthreads();                                            // (every thread of the CTA reaches this point)
     if (threadIdx.x != 0) return;
@@ -1472,7 +1509,9 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     cudaError_t err = cudaSuccess;
     // keep is NOT cleared here: every row below the list's count is written (0 or 1) by exactly one of the kernels below,
     // and rows beyond the count are never read (yv3_collect_kept and every caller stop at the counts)
-    const int n2s = min(cap2, kSortSmemKeys);
+    // few classes (the single-class heads): lists of thousands of ONE class are the rule, the general path sorts them
+    // whole, and a 16 384-key bitonic sort in global memory took 180 us per step: those launches get the large reservation
+    const int n2s = min(cap2, num_classes <= 8 ? 16384 : kSortSmemKeys);
     const size_t smem = (size_t)n2s * 8 + (size_t)kBucketClasses * 4 + (size_t)n2s * 2;
     err = set_smem_once((const void*)sort_kernel, smem);
     if (err != cudaSuccess) return err;
