@@ -104,6 +104,33 @@ def git_sha():
         return None
 
 
+def bind_to_gpu_numa_node(index):
+    """N > 1 only: run this rank (and so first-touch its pinned host buffers) on the CPUs of the NUMA node its GPU hangs
+    off -- the e2e leg copies 232 MB per step and rank from pinned host memory, and with all ranks on one node's memory the
+    copies share that node's controllers.  Best effort: returns what was done, or why not."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.split(":", 1)
+        path = "/sys/bus/pci/devices/%s:%s/numa_node" % (dom[-4:].lower(), rest.lower())
+        node = int(open(path).read().strip())
+        if node < 0:
+            return {"bound": False, "why": "the GPU reports no NUMA node"}
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return {"bound": False, "why": "no allowed CPU on node %d" % node}
+        os.sched_setaffinity(0, cpus)
+        return {"bound": True, "node": node, "cpus": len(cpus)}
+    except Exception as e:                                          # noqa: BLE001
+        return {"bound": False, "why": "%s: %s" % (type(e).__name__, str(e)[:120])}
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi's clocks line through NVML, polled while the benchmark runs."""
 
@@ -666,6 +693,7 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     reducer, reduce_mode = None, None
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -792,7 +820,7 @@ def main():
                                 "model's backward" % (arm.grad.numel() * 4 / 1e6),
                     "pipelining": "double-buffered: the copy of step k+1 overlaps the compute of step k; results of "
                                   "step k-1 are read on the host every step",
-                    "ms_per_step": e2e_ms, "steps": e2e_steps, "h2d_probe": probe,
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "h2d_probe": probe, "numa": numa,
                     "frac_of_h2d_probe": (arm.e2e_h2d / (e2e_ms * 1e-3) / 1e9) / probe["per_rank_gbs"] if probe else None},
             # host launches of OUR kernels per step.  Fused: assign, fused sweep, fold, gather, sort (+ the peer all-reduce
             # at N > 1); the two queue-driven NMS kernels are host launches only with <= 8 classes -- with more the sort
