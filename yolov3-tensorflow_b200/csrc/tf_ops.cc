@@ -18,6 +18,11 @@
 #include "tensorflow/core/framework/op.h"
 #include "tensorflow/core/framework/op_kernel.h"
 #include "tensorflow/core/framework/shape_inference.h"
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+
 #include "yv3_head.h"
 
 namespace tf = tensorflow;
@@ -37,13 +42,14 @@ namespace {
     .Attr("focal_alpha: float = 0.25")                                                      \
     .Attr("focal_gamma: float = 2.0")                                                       \
     .Attr("is_tiou_recall: bool = false")                                                   \
-    .Attr("eps: float = 1e-7")
+    .Attr("eps: string = '1e-7'") /* decimal text of the Python double (K.epsilon()): a float attr would round it to fp32 */
 
 tf::Status ReadConfig(tf::OpKernelConstruction* c, yv3_config* cfg) {
     std::vector<int> gh, gw, bn;
     std::vector<float> anchors, lw, rw;
     bool focal, tiou;
-    float eps;
+    std::string eps;
+    memset(cfg, 0, sizeof(*cfg));               // anchors past box_num and the padding bytes are defined
     TF_RETURN_IF_ERROR(c->GetAttr("grid_h", &gh));
     TF_RETURN_IF_ERROR(c->GetAttr("grid_w", &gw));
     TF_RETURN_IF_ERROR(c->GetAttr("box_num", &bn));
@@ -72,7 +78,11 @@ tf::Status ReadConfig(tf::OpKernelConstruction* c, yv3_config* cfg) {
     }
     cfg->is_focal_loss = focal ? 1 : 0;
     cfg->is_tiou_recall = tiou ? 1 : 0;
-    cfg->eps = (double)eps;
+    {
+        char* end = nullptr;
+        cfg->eps = strtod(eps.c_str(), &end);   // the double the Python side holds, not its fp32 rounding
+        if (end == eps.c_str() || *end != '\0') return tf::errors::InvalidArgument("eps must be a decimal number");
+    }
     const int rc = yv3_config_check(cfg);
     if (rc != YV3_OK) return tf::errors::InvalidArgument(yv3_strerror(rc));
     return tf::Status::OK();
@@ -122,10 +132,12 @@ class Yolov3HeadLossOp : public tf::OpKernel {
                                         active, 1.0f, out20.flat<float>().data(), grad->flat<float>().data(),
                                         ws.flat<tf::uint8>().data(), bytes, 7, st);
         OP_REQUIRES(ctx, rc == YV3_OK, tf::errors::Internal(yv3_strerror(rc)));
-        cudaMemcpyAsync(detail->flat<float>().data(), out20.flat<float>().data(), 18 * sizeof(float),
-                        cudaMemcpyDeviceToDevice, (cudaStream_t)st);
-        cudaMemcpyAsync(loss->flat<float>().data(), out20.flat<float>().data() + 18, sizeof(float),
-                        cudaMemcpyDeviceToDevice, (cudaStream_t)st);
+        cudaError_t e = cudaMemcpyAsync(detail->flat<float>().data(), out20.flat<float>().data(), 18 * sizeof(float),
+                                        cudaMemcpyDeviceToDevice, (cudaStream_t)st);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(loss->flat<float>().data(), out20.flat<float>().data() + 18, sizeof(float),
+                                cudaMemcpyDeviceToDevice, (cudaStream_t)st);
+        OP_REQUIRES(ctx, e == cudaSuccess, tf::errors::Internal(cudaGetErrorString(e)));
     }
 
  private:
@@ -145,6 +157,9 @@ class Yolov3DecodeOp : public tf::OpKernel {
     explicit Yolov3DecodeOp(tf::OpKernelConstruction* c) : tf::OpKernel(c) { OP_REQUIRES_OK(c, ReadConfig(c, &cfg_)); }
     void Compute(tf::OpKernelContext* ctx) override {
         const tf::Tensor& p = ctx->input(0);
+        OP_REQUIRES(ctx, p.dims() == 4 && p.dim_size(0) >= 1 &&
+                             p.NumElements() == p.dim_size(0) * yv3_packed_floats_per_image(&cfg_),
+                    tf::errors::InvalidArgument("predicts does not have the packed head layout of this configuration"));
         const int n = (int)p.dim_size(0), L = 5 + cfg_.class_num;
         float* out[9];
         for (int h = 0; h < 3; ++h) {
@@ -170,8 +185,9 @@ REGISTER_OP("Yolov3FilterNms")
     .Output("candidates: float")         // (N, capacity, 8)  rows of yolov3_post_process.py:65-75
     .Output("counts: int32")             // (N, 3) per head
     .Output("keep: uint8")               // (N, capacity) true greedy survivors (the F9 quirk is layered in Python)
-    .Attr("score_thresh: float")
-    .Attr("nms_thresh: float")
+    .Attr("score_thresh: float")         // compared in fp32 (:62): the float attr IS the reference's fp32(thresh)
+    .Attr("nms_thresh: string")          // decimal text of the Python double: IoU > thresh is decided in fp64 (:124), and
+                                         // 0.45f widened would be 0.44999998807907104, another threshold
     .Attr("capacity: int")
     YV3_CONFIG_ATTRS;
 
@@ -180,11 +196,18 @@ class Yolov3FilterNmsOp : public tf::OpKernel {
     explicit Yolov3FilterNmsOp(tf::OpKernelConstruction* c) : tf::OpKernel(c) {
         OP_REQUIRES_OK(c, ReadConfig(c, &cfg_));
         OP_REQUIRES_OK(c, c->GetAttr("score_thresh", &score_));
-        OP_REQUIRES_OK(c, c->GetAttr("nms_thresh", &nms_));
+        std::string nms;
+        OP_REQUIRES_OK(c, c->GetAttr("nms_thresh", &nms));
+        char* end = nullptr;
+        nms_ = strtod(nms.c_str(), &end);
+        OP_REQUIRES(c, end != nms.c_str() && *end == '\0', tf::errors::InvalidArgument("nms_thresh must be a decimal number"));
         OP_REQUIRES_OK(c, c->GetAttr("capacity", &cap_));
     }
     void Compute(tf::OpKernelContext* ctx) override {
         const tf::Tensor& p = ctx->input(0);
+        OP_REQUIRES(ctx, p.dims() == 4 && p.dim_size(0) >= 1 &&
+                             p.NumElements() == p.dim_size(0) * yv3_packed_floats_per_image(&cfg_),
+                    tf::errors::InvalidArgument("predicts does not have the packed head layout of this configuration"));
         const int n = (int)p.dim_size(0);
         tf::Tensor *cand, *counts, *keep, ws;
         OP_REQUIRES_OK(ctx, ctx->allocate_output(0, tf::TensorShape({n, cap_, YV3_CAND_COLS}), &cand));
@@ -198,14 +221,15 @@ class Yolov3FilterNmsOp : public tf::OpKernel {
                                    counts->flat<tf::int32>().data(), ws.flat<tf::uint8>().data(), bytes, 3, st);
         OP_REQUIRES(ctx, rc == YV3_OK, tf::errors::Internal(yv3_strerror(rc)));
         rc = yv3_nms(&cfg_, cand->flat<float>().data(), counts->flat<tf::int32>().data(), 3, n, cap_,
-                     cfg_.class_num > 0 ? cfg_.class_num : 1, (double)nms_, keep->flat<tf::uint8>().data(),
+                     cfg_.class_num > 0 ? cfg_.class_num : 1, nms_, keep->flat<tf::uint8>().data(),
                      ws.flat<tf::uint8>().data(), bytes, st);
         OP_REQUIRES(ctx, rc == YV3_OK, tf::errors::Internal(yv3_strerror(rc)));
     }
 
  private:
     yv3_config cfg_;
-    float score_, nms_;
+    float score_;
+    double nms_;
     int cap_;
 };
 REGISTER_KERNEL_BUILDER(Name("Yolov3FilterNms").Device(tf::DEVICE_GPU), Yolov3FilterNmsOp);
