@@ -808,7 +808,7 @@ struct WarpNmsSmem {
     float4 box[kWarpNmsMax];       // the segment's boxes in sorted order (before that: the key buffer of the rank sort)
     float area[kWarpNmsMax];
 };
-static_assert(sizeof(float4) * kWarpNmsMax >= sizeof(unsigned long long) * kWarpNmsMax, "the box array doubles as the key buffer");
+static_assert(sizeof(float4) * kWarpNmsMax >= 2 * sizeof(unsigned long long) * kWarpNmsMax, "the box array doubles as the two key buffers");
 
 // One tile of pair tests: candidate j (this lane: box bj, area aj) against the `iend` candidates i at bi / ai_p.
 // Returns in `drop` the bits i whose fp32 test says IoU(i, j) > thr and in `und` the bits the fp32 test does not settle
@@ -850,31 +850,44 @@ __device__ __forceinline__ void warp_nms_tile(const bool fast, const float4* bi,
     }
 }
 
-// Rank sort of a bucket of at most 32 * NS keys (arrival order -> ascending key = score descending, row ascending) in the
-// warp's key buffer: every key is broadcast from shared memory and counted against the NS keys a lane holds; keys are
-// unique (the row is part of the key).  NS is a template parameter so that the count loop is exactly NS compares.
-template <int NS>
-__device__ __forceinline__ void warp_rank_sort(unsigned long long* skey, const int lane, const int len,
-                                               const unsigned long long* keys) {
-    unsigned long long key[NS];
-    int rank[NS];
+// Sort of a bucket of `len` <= 256 keys (arrival order -> ascending key = score descending, row ascending) by one warp:
+// every slot of 32 keys is sorted in the lanes by a bitonic network of shuffles (15 compare-exchange rounds) and put down
+// in `skey`; a key's final rank is then its place in its own slot plus, for every other slot, the number of keys there
+// below it -- a binary search over that sorted slot (keys are unique: the row is part of the key; the padding of the last
+// slot is the largest key and sorts to its end).  The sorted bucket is written to `sorted` (another buffer: the slots are
+// still being searched).  ~1.3 K instructions for 133 keys; counting every key against every other one took 2.3 K.
+__device__ __forceinline__ void warp_sort_bucket(unsigned long long* skey, unsigned long long* sorted, const int lane,
+                                                 const int len, const int nslot, const unsigned long long* keys) {
+    for (int u = 0; u < nslot; ++u) {
+        unsigned long long k = (lane + 32 * u < len) ? keys[lane + 32 * u] : kPadKey;
 #pragma unroll
-    for (int u = 0; u < NS; ++u) {
-        key[u] = (lane + 32 * u < len) ? keys[lane + 32 * u] : kPadKey;
-        rank[u] = 0;
-        if (lane + 32 * u < len) skey[lane + 32 * u] = key[u];
+        for (int kk = 2; kk <= 32; kk <<= 1) {
+#pragma unroll
+            for (int j = kk >> 1; j > 0; j >>= 1) {
+                const unsigned long long o = __shfl_xor_sync(0xffffffffu, k, j);
+                const bool take_min = ((lane & j) == 0) == ((lane & kk) == 0);       // (lane & 32) == 0: the last merge ascends
+                const bool less = k < o;
+                k = (take_min == less) ? k : o;
+            }
+        }
+        skey[32 * u + lane] = k;
     }
     __syncwarp();
-#pragma unroll 4
-    for (int j = 0; j < len; ++j) {
-        const unsigned long long other = skey[j];
+    for (int u = 0; u < nslot; ++u) {
+        const unsigned long long k = skey[32 * u + lane];
+        int rank = lane;
+        for (int w = 0; w < nslot; ++w) {
+            if (w == u) continue;
+            const unsigned long long* slot = skey + 32 * w;
+            int lo = 0;
 #pragma unroll
-        for (int u = 0; u < NS; ++u) rank[u] += (other < key[u]) ? 1 : 0;
+            for (int step = 16; step >= 1; step >>= 1)
+                if (slot[lo + step - 1] < k) lo += step;
+            lo += (slot[lo] < k) ? 1 : 0;                           // lo <= 31 here; elements [0, lo) are below k
+            rank += lo;
+        }
+        if (k != kPadKey) sorted[rank] = k;
     }
-    __syncwarp();
-#pragma unroll
-    for (int u = 0; u < NS; ++u)
-        if (lane + 32 * u < len) skey[rank[u]] = key[u];
     __syncwarp();
 }
 
@@ -915,18 +928,10 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
         const int nslot = (len + 31) >> 5;
         __syncwarp();                                                    // the previous segment's sweep is done with sm
         if (needs_sort) {
-            // the box array is free until the boxes are staged: it doubles as the key buffer
+            // the box array is free until the boxes are staged: its halves are the slot buffer and the sorted bucket
             unsigned long long* skey = reinterpret_cast<unsigned long long*>(&sm.box[0]);
-            switch (nslot) {
-                case 1: warp_rank_sort<1>(skey, lane, len, keys); break;
-                case 2: warp_rank_sort<2>(skey, lane, len, keys); break;
-                case 3: warp_rank_sort<3>(skey, lane, len, keys); break;
-                case 4: warp_rank_sort<4>(skey, lane, len, keys); break;
-                case 5: warp_rank_sort<5>(skey, lane, len, keys); break;
-                case 6: warp_rank_sort<6>(skey, lane, len, keys); break;
-                case 7: warp_rank_sort<7>(skey, lane, len, keys); break;
-                default: warp_rank_sort<8>(skey, lane, len, keys); break;
-            }
+            warp_sort_bucket(skey, skey + kWarpNmsMax, lane, len, nslot, keys);
+            skey += kWarpNmsMax;
             keys = skey;
         }
         int row[kWarpNmsSlots];
@@ -1281,8 +1286,8 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
                                                             int32_t* __restrict__ sidx, unsigned char* __restrict__ keep,
                                                             int2* __restrict__ wl, int2* __restrict__ wl_large,
                                                             int32_t* __restrict__ wl_count, float4* __restrict__ kspill,
-                                                            int dispatch) {
-    sort_body(cand, count, count_cols, capacity, cap2, n2s, thresh, gkeys, sbox, sidx, keep, wl, wl_large, wl_count, dispatch != 0);
+                                                            int dispatch, int many_classes) {
+    sort_body(cand, count, count_cols, capacity, cap2, n2s, thresh, gkeys, sbox, sidx, keep, wl, wl_large, wl_count, many_classes != 0);
     if (!dispatch) return;
     __syncthreads();                                            // (every thread of the CTA reaches this point)
     if (threadIdx.x != 0) return;
@@ -1536,7 +1541,7 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     if (err != cudaSuccess) return err;
     if (!(skip & 1))
     sort_kernel<<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, n2s, thresh, ws.keys, ws.sbox,
-                                                   ws.sidx, keep, ws.wl, wl_large, ws.wl_count, ws.kspill, dispatch);
+                                                   ws.sidx, keep, ws.wl, wl_large, ws.wl_count, ws.kspill, dispatch, num_classes > 8 ? 1 : 0);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
     if (dispatch) return cudaSuccess;
