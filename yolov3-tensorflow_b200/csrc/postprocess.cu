@@ -1079,7 +1079,7 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
 constexpr int kClu = YV3_NMS_CLUSTER;
 constexpr int kCluT = 1024;             // threads per CTA = candidates per chunk
 __host__ __device__ inline size_t nms_cluster_smem_bytes() {
-    return (size_t)kCluT * 16 + (size_t)kCluT * (kCluT / 64) * 8 + (size_t)kCluT * 3 + (size_t)kCluT * 20;
+    return (size_t)kCluT * 16 + (size_t)kCluT * (kCluT / 64) * 8 + (size_t)kCluT * 3 + (size_t)kCluT * 20 + (size_t)kCluT * 6;
 }
 
 __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned long long* __restrict__ gkeys,
@@ -1099,8 +1099,12 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
     unsigned char* kept_flag_s = verdict_s + T;                                              // [T]
     float4* kbox_s = reinterpret_cast<float4*>(kept_flag_s + T);                            // [T] a tile of this CTA's share of the kept list
     float* karea_s = reinterpret_cast<float*>(kbox_s + T);                                  // [T]
+    unsigned* dcol_s = reinterpret_cast<unsigned*>(karea_s + T);                            // [T] diagonal tiles, column form (leader)
+    unsigned short* cidx_s = reinterpret_cast<unsigned short*>(dcol_s + T);                 // [T] chunk position of compact candidate k
     __shared__ int seg_s[2];
     __shared__ int sane_s;
+    __shared__ int wcount_s[T / 32];
+    __shared__ int na_s;
     __shared__ int nkept_s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int r = (int)cluster.block_rank();
@@ -1196,68 +1200,124 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
             }
             verdict_s[tid] = alive ? 1 : 0;
             cluster.sync();                                          // (A) every CTA's verdicts are in place
+            bool all;
             {
-                bool all = tid < cnt;
+                all = tid < cnt;
 #pragma unroll
                 for (int k = 0; k < kClu; ++k) {
                     const unsigned char* rem = cluster.map_shared_rank(verdict_s, k);
                     all = all && (rem[tid] != 0);
                 }
-                alive_s[tid] = all ? 1 : 0;
             }
-            __syncthreads();
-            // phase 2: the rows i = r, r + 8, ... of the chunk's bit matrix (row i, bit j > i <=> i suppresses j), cut
-            // into (row, 32 columns) tasks; every half word of a row is written, straight into the leader's matrix
+            // ---- the candidates the kept list left alive, compacted in order (every CTA builds the same list): typically a
+            // third of the chunk, so the chunk's own pair tests and the sweep shrink ninefold.  cbox / carea reuse the
+            // kept-list tile of phase 1.
+            float4* cbox_s = kbox_s;
+            float* carea_s = karea_s;
             {
-                const int rows_mine = cnt > r ? (cnt - r + kClu - 1) / kClu : 0;
-                for (int task = tid; task < rows_mine * 2 * W; task += T) {
-                    const int li = task / (2 * W), hw = task - li * (2 * W);
-                    const int i = li * kClu + r;
-                    unsigned bits = 0u;
-                    const int jb = max(i + 1, hw << 5), je = min(cnt, (hw + 1) << 5);
-                    if (jb < je && alive_s[i]) {
-                        const float4 oi = chunk_s[i];
-                        const double ai = box_area_d(oi);
-                        for (int j = jb; j < je; ++j) {
-                            if (!alive_s[j]) continue;
-                            const float4 oj = chunk_s[j];
-                            const bool drop = overlaps_f32(oi, oj) ? suppresses_overlapping_fast(oi, oj, nq)
-                                                                   : none_overlap_drops;
-                            if (drop) bits |= 1u << (j & 31);
+                const unsigned bal = __ballot_sync(0xffffffffu, all);
+                if (lane == 0) wcount_s[warp] = __popc(bal);
+                __syncthreads();                                     // (also: phase 1's last tile is consumed everywhere)
+                int base = 0;
+                for (int w2 = 0; w2 < warp; ++w2) base += wcount_s[w2];
+                if (tid == T - 1) na_s = base + __popc(bal);
+                if (all) {
+                    const int pos = base + __popc(bal & ((1u << lane) - 1u));
+                    cbox_s[pos] = mine_f;
+                    carea_s[pos] = aj;
+                    cidx_s[pos] = (unsigned short)tid;
+                }
+                kept_flag_s[tid] = 0;
+                __syncthreads();
+            }
+            const int na = na_s;
+            const int nb = (na + 31) >> 5;
+            const bool fast2 = nq.lo >= kWarpNmsThreshLo && sane_s != 0;       // (a candidate with an area out of range died... or not:
+                                                                                //  checked per tile below)
+            // phase 2: the chunk's own suppression matrix over the compact list, one 32 x 32 tile (block ib of earlier
+            // candidates i, block v >= ib of later ones j) per warp and turn, dealt over the cluster's warps.  Lanes hold
+            // the j's; candidate i is a broadcast read; "i suppresses j" is one fused sign test per pair and a ballot turns
+            // the 32 verdicts into row i's word for block v, written straight into the leader's matrix (row form: the
+            // sweep ORs the rows of kept candidates).  The diagonal tiles also leave their column form (per j: the earlier
+            // i of its own block that suppress it) for the leader's in-block fixed point.
+            unsigned* leader_dcol = cluster.map_shared_rank(dcol_s, 0);
+            {
+                const int ntile = nb * (nb + 1) / 2;
+                for (int t = r * (T / 32) + warp; t < ntile; t += kClu * (T / 32)) {
+                    int v = (int)((sqrtf(8.f * (float)t + 1.f) - 1.f) * 0.5f);
+                    while (v * (v + 1) / 2 > t) --v;
+                    while ((v + 1) * (v + 2) / 2 <= t) ++v;
+                    const int ib = t - v * (v + 1) / 2;
+                    const int j = 32 * v + lane;
+                    const bool inj = j < na;
+                    const float4 bj = inj ? cbox_s[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float ajj = inj ? carea_s[j] : 1.f;
+                    const bool sane_j = ajj >= kWarpNmsAreaLo && ajj <= 1e29f;
+                    const int iend = min(32, na - 32 * ib);
+                    unsigned myrow = 0u, col = 0u;
+                    for (int l = 0; l < iend; ++l) {
+                        const float4 fi = cbox_s[32 * ib + l];
+                        const float ai = carea_s[32 * ib + l];
+                        const bool sane_i = ai >= kWarpNmsAreaLo && ai <= 1e29f;
+                        const float w = fmaxf(__fsub_rn(fminf(fi.z, bj.z), fmaxf(fi.x, bj.x)), 0.f);
+                        const float h = __fsub_rn(fminf(fi.w, bj.w), fmaxf(fi.y, bj.y));
+                        const float inter = __fmul_rn(w, h);
+                        const float uni = __fsub_rn(__fadd_rn(ai, ajj), inter);
+                        const bool yes = __fmaf_rn(nq.hi, uni, -inter) < 0.f;
+                        const bool no = __fmaf_rn(-nq.lo, uni, inter) < 0.f;
+                        const bool later = j > 32 * ib + l && inj;                       // only EARLIER candidates suppress
+                        bool drop = yes;
+                        if (!(fast2 && sane_i && sane_j && (yes || no))) {
+                            // inside the band, or outside the range the fp32 bounds are proved for: the exact expression
+                            drop = overlaps_f32(fi, bj) ? suppresses_overlapping(fi, box_area_d(fi), bj, box_area_d(bj), thresh)
+                                                        : none_overlap_drops;
                         }
+                        drop = drop && later;
+                        const unsigned bits = __ballot_sync(0xffffffffu, drop);
+                        if (lane == l) myrow = bits;
+                        col |= drop ? (1u << l) : 0u;
                     }
-                    leader_mask32[(size_t)i * 2 * W + hw] = bits;
+                    if (lane < iend) leader_mask32[(size_t)(32 * ib + lane) * 32 + v] = myrow;
+                    if (ib == v && inj) leader_dcol[j] = col;
                 }
             }
             cluster.sync();                                          // (B) the leader's matrix is complete
             if (r == 0) {
                 if (warp == 0) {
-                    unsigned long long removed = 0;
-                    for (int i0 = 0; i0 < cnt; i0 += 64) {
-                        const int blk = i0 >> 6;
-                        unsigned long long rblk = __shfl_sync(0xffffffffu, removed, blk);
-                        unsigned long long kb = 0;
-#pragma unroll 8
-                        for (int b = 0; b < 64; ++b) {
-                            const int i = i0 + b;
-                            const bool a = i < cnt && alive_s[i];
-                            const unsigned long long diag = mask_s[(size_t)i * W + blk];
-                            const unsigned long long own = (lane < W) ? mask_s[(size_t)i * W + lane] : 0ULL;
-                            const bool k = a && !((rblk >> b) & 1ULL);
-                            if (k) { rblk |= diag; removed |= own; kb |= 1ULL << b; }
+                    // phase 3, the greedy sweep over the compact list, block by block: lane w holds the removed bits of
+                    // block w; a block's survivors x_j = free_j and no kept i < j of the block suppresses j come from
+                    // iterating x <- free & ~exists(x_i & S_ij) (fixed after at most 32 rounds, usually 2-3 ballots); the
+                    // rows of the survivors are then OR-ed into the removed bits of the later blocks.
+                    const unsigned* m32 = reinterpret_cast<const unsigned*>(mask_s);
+                    unsigned removed = 0u, keptw = 0u;
+                    for (int b2 = 0; b2 < nb; ++b2) {
+                        const unsigned rem_b = __shfl_sync(0xffffffffu, removed, b2);
+                        const int j = 32 * b2 + lane;
+                        const bool fr = j < na && !((rem_b >> lane) & 1u);
+                        const unsigned dword = (j < na) ? dcol_s[j] : 0u;
+                        unsigned km = __ballot_sync(0xffffffffu, fr);
+                        for (;;) {
+                            const unsigned nkm = __ballot_sync(0xffffffffu, fr && (dword & km) == 0u);
+                            if (nkm == km) break;
+                            km = nkm;
                         }
-                        kept_flag_s[i0 + lane] = (unsigned char)((kb >> lane) & 1ULL);
-                        kept_flag_s[i0 + 32 + lane] = (unsigned char)((kb >> (lane + 32)) & 1ULL);
+                        if (lane == b2) keptw = km;
+                        for (unsigned m = km; m; m &= m - 1u) {
+                            const int i = 32 * b2 + __ffs(m) - 1;
+                            if (lane > b2 && lane < nb) removed |= m32[(size_t)i * 32 + lane];
+                        }
                     }
-                    __syncwarp();
-                    // append the chunk's survivors to the kept list (order kept)
+                    // survivors -> flags at their chunk positions, and appended to the kept list in order
                     int total = nk;
-                    for (int b = 0; b < cnt; b += 32) {
-                        const int i = b + lane;
-                        const bool k = i < cnt && kept_flag_s[i];
-                        const unsigned m = __ballot_sync(0xffffffffu, k);
-                        if (k) spill[total + __popc(m & ((1u << lane) - 1u))] = chunk_s[i];
-                        total += __popc(m);
+                    for (int b2 = 0; b2 < nb; ++b2) {
+                        const unsigned km = __shfl_sync(0xffffffffu, keptw, b2);
+                        const int k2 = 32 * b2 + lane;
+                        const bool kp = (km >> lane) & 1u;
+                        if (kp) {
+                            kept_flag_s[cidx_s[k2]] = 1;
+                            spill[total + __popc(km & ((1u << lane) - 1u))] = cbox_s[k2];
+                        }
+                        total += __popc(km);
                     }
                     if (lane == 0) nkept_s = total;
                 }
