@@ -23,6 +23,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <stdio.h>
+
 #include "sweep_parts.cuh"
 #include "yv3_kernels.cuh"
 
@@ -1078,8 +1080,10 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
 #endif
 constexpr int kClu = YV3_NMS_CLUSTER;
 constexpr int kCluT = 1024;             // threads per CTA = candidates per chunk
+constexpr int kCluRow = kCluT / 32 + 1;  // words per row of the chunk's suppression matrix: 32 + 1, so that a column
+                                        // (one word of 32 consecutive rows) is read without a bank conflict
 __host__ __device__ inline size_t nms_cluster_smem_bytes() {
-    return (size_t)kCluT * 16 + (size_t)kCluT * (kCluT / 64) * 8 + (size_t)kCluT * 3 + (size_t)kCluT * 20 + (size_t)kCluT * 6;
+    return (size_t)kCluT * 16 + (size_t)kCluT * kCluRow * 4 + (size_t)kCluT * 3 + (size_t)kCluT * 20 + (size_t)kCluT * 6;
 }
 
 __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned long long* __restrict__ gkeys,
@@ -1094,7 +1098,7 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
     extern __shared__ __align__(16) unsigned char csm[];
     float4* chunk_s = reinterpret_cast<float4*>(csm);                                         // [T]
     unsigned long long* mask_s = reinterpret_cast<unsigned long long*>(chunk_s + T);         // [T][W]  (used in the leader)
-    unsigned char* alive_s = reinterpret_cast<unsigned char*>(mask_s + (size_t)T * W);       // [T] after the AND
+    unsigned char* alive_s = reinterpret_cast<unsigned char*>(reinterpret_cast<unsigned*>(mask_s) + (size_t)T * kCluRow);   // [T] (unused)
     unsigned char* verdict_s = alive_s + T;                                                  // [T] this CTA's share
     unsigned char* kept_flag_s = verdict_s + T;                                              // [T]
     float4* kbox_s = reinterpret_cast<float4*>(kept_flag_s + T);                            // [T] a tile of this CTA's share of the kept list
@@ -1142,6 +1146,14 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
         int nk = 0;
         for (int c0 = s0; c0 < s1; c0 += T) {
             const int cnt = min(T, s1 - c0);
+#ifdef YV3_CLUSTER_TIMING
+            long long tq[8];
+            const bool tq_on = blockIdx.x == 0 && tid == 0;
+#define YV3_TQ(k) do { if (tq_on) tq[k] = clock64(); } while (0)
+            YV3_TQ(0);
+#else
+#define YV3_TQ(k) do { } while (0)
+#endif
             // phase 1: this thread's candidate against this CTA's share of the boxes kept so far (kept box q belongs to CTA
             // q mod kClu).  The share is staged through shared memory a tile of T boxes at a time, with the fp32 areas, and
             // every warp walks the tile with the branch-free test of warp_nms_tile: two fused sign tests per pair, OR-ed
@@ -1199,7 +1211,9 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
                 if (hit) alive = false;
             }
             verdict_s[tid] = alive ? 1 : 0;
+            YV3_TQ(1);
             cluster.sync();                                          // (A) every CTA's verdicts are in place
+            YV3_TQ(2);
             bool all;
             {
                 all = tid < cnt;
@@ -1232,6 +1246,7 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
             }
             const int na = na_s;
             const int nb = (na + 31) >> 5;
+            YV3_TQ(3);
             const bool fast2 = nq.lo >= kWarpNmsThreshLo && sane_s != 0;       // (a candidate with an area out of range died... or not:
                                                                                 //  checked per tile below)
             // phase 2: the chunk's own suppression matrix over the compact list, one 32 x 32 tile (block ib of earlier
@@ -1243,7 +1258,7 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
             unsigned* leader_dcol = cluster.map_shared_rank(dcol_s, 0);
             {
                 const int ntile = nb * (nb + 1) / 2;
-                for (int t = r * (T / 32) + warp; t < ntile; t += kClu * (T / 32)) {
+                for (int t = warp * kClu + r; t < ntile; t += kClu * (T / 32)) {       // tile t -> CTA t mod kClu: all CTAs busy
                     int v = (int)((sqrtf(8.f * (float)t + 1.f) - 1.f) * 0.5f);
                     while (v * (v + 1) / 2 > t) --v;
                     while ((v + 1) * (v + 2) / 2 <= t) ++v;
@@ -1252,36 +1267,42 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
                     const bool inj = j < na;
                     const float4 bj = inj ? cbox_s[j] : make_float4(0.f, 0.f, 0.f, 0.f);
                     const float ajj = inj ? carea_s[j] : 1.f;
-                    const bool sane_j = ajj >= kWarpNmsAreaLo && ajj <= 1e29f;
                     const int iend = min(32, na - 32 * ib);
-                    unsigned myrow = 0u, col = 0u;
-                    for (int l = 0; l < iend; ++l) {
-                        const float4 fi = cbox_s[32 * ib + l];
-                        const float ai = carea_s[32 * ib + l];
-                        const bool sane_i = ai >= kWarpNmsAreaLo && ai <= 1e29f;
-                        const float w = fmaxf(__fsub_rn(fminf(fi.z, bj.z), fmaxf(fi.x, bj.x)), 0.f);
-                        const float h = __fsub_rn(fminf(fi.w, bj.w), fmaxf(fi.y, bj.y));
-                        const float inter = __fmul_rn(w, h);
-                        const float uni = __fsub_rn(__fadd_rn(ai, ajj), inter);
-                        const bool yes = __fmaf_rn(nq.hi, uni, -inter) < 0.f;
-                        const bool no = __fmaf_rn(-nq.lo, uni, inter) < 0.f;
-                        const bool later = j > 32 * ib + l && inj;                       // only EARLIER candidates suppress
-                        bool drop = yes;
-                        if (!(fast2 && sane_i && sane_j && (yes || no))) {
-                            // inside the band, or outside the range the fp32 bounds are proved for: the exact expression
-                            drop = overlaps_f32(fi, bj) ? suppresses_overlapping(fi, box_area_d(fi), bj, box_area_d(bj), thresh)
-                                                        : none_overlap_drops;
-                        }
-                        drop = drop && later;
-                        const unsigned bits = __ballot_sync(0xffffffffu, drop);
-                        if (lane == l) myrow = bits;
-                        col |= drop ? (1u << l) : 0u;
+                    // column form first (lane j: the bits i of block ib that suppress j), with the pipelined sign-word loop
+                    // of warp_nms_tile and the exact expression for what it leaves open; a block with an area outside the
+                    // trusted range goes pair by pair
+                    bool sane = !inj || (ajj >= kWarpNmsAreaLo && ajj <= 1e29f);
+                    if (lane < iend) {
+                        const float ai = carea_s[32 * ib + lane];
+                        sane = sane && ai >= kWarpNmsAreaLo && ai <= 1e29f;
                     }
-                    if (lane < iend) leader_mask32[(size_t)(32 * ib + lane) * 32 + v] = myrow;
+                    const bool fast = fast2 && __all_sync(0xffffffffu, sane);
+                    unsigned col, und;
+                    warp_nms_tile(fast, cbox_s + 32 * ib, carea_s + 32 * ib, iend, bj, ajj, nq, none_overlap_drops, col, und);
+                    unsigned allow = 0u;                                                   // only EARLIER candidates suppress
+                    if (inj) allow = (ib == v) ? (1u << lane) - 1u : 0xffffffffu;
+                    col &= allow;
+                    und &= allow;
+                    while (und) {
+                        const int l = __ffs(und) - 1;
+                        und &= und - 1u;
+                        const float4 fi = cbox_s[32 * ib + l];
+                        if (suppresses_overlapping(fi, box_area_d(fi), bj, box_area_d(bj), thresh)) col |= 1u << l;
+                    }
+                    // ... then row form by ballots: row i's word for block v has bit j set iff i suppresses j
+                    unsigned myrow = 0u;
+#pragma unroll 8
+                    for (int l = 0; l < 32; ++l) {
+                        const unsigned bits = __ballot_sync(0xffffffffu, (col >> l) & 1u);
+                        if (lane == l) myrow = bits;
+                    }
+                    if (lane < iend) leader_mask32[(size_t)(32 * ib + lane) * kCluRow + v] = myrow;
                     if (ib == v && inj) leader_dcol[j] = col;
                 }
             }
+            YV3_TQ(4);
             cluster.sync();                                          // (B) the leader's matrix is complete
+            YV3_TQ(5);
             if (r == 0) {
                 if (warp == 0) {
                     // phase 3, the greedy sweep over the compact list, block by block: lane w holds the removed bits of
@@ -1302,9 +1323,13 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
                             km = nkm;
                         }
                         if (lane == b2) keptw = km;
-                        for (unsigned m = km; m; m &= m - 1u) {
-                            const int i = 32 * b2 + __ffs(m) - 1;
-                            if (lane > b2 && lane < nb) removed |= m32[(size_t)i * 32 + lane];
+                        // lane i of the block, if it survived, holds row i; word w of the rows, OR-ed over the lanes, is
+                        // what block b2's survivors remove from block w
+                        const unsigned* myrowp = m32 + (size_t)(32 * b2 + lane) * kCluRow;
+                        const bool mine_kept = (km >> lane) & 1u;
+                        for (int w = b2 + 1; w < nb; ++w) {
+                            const unsigned o = __reduce_or_sync(0xffffffffu, mine_kept ? myrowp[w] : 0u);
+                            if (lane == w) removed |= o;
                         }
                     }
                     // survivors -> flags at their chunk positions, and appended to the kept list in order
@@ -1325,7 +1350,13 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
                 if (tid < cnt) keep_n[rowof[c0 + tid]] = kept_flag_s[tid];
                 __threadfence();                                     // the kept list is visible before the barrier below
             }
+            YV3_TQ(6);
             cluster.sync();                                          // (C) kept list and count published
+            YV3_TQ(7);
+#ifdef YV3_CLUSTER_TIMING
+            if (tq_on) printf("chunk %d nk %d na %d: ph1 %lld syncA %lld and+compact %lld ph2 %lld syncB %lld ph3 %lld syncC %lld (cycles)\n",
+                              (c0 - s0) / T, nk, na, tq[1] - tq[0], tq[2] - tq[1], tq[3] - tq[2], tq[4] - tq[3], tq[5] - tq[4], tq[6] - tq[5], tq[7] - tq[6]);
+#endif
             nk = *leader_nkept;
         }
         __syncthreads();
