@@ -1068,13 +1068,21 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
 // ---- long segments: one thread-block CLUSTER per segment ------------------------------------------------------
 // A segment of thousands of candidates (a single-class head with a low threshold) is a serial chain of 1024-candidate
 // chunks, and inside a chunk the work is (candidates x boxes kept so far) + (chunk x chunk) pair tests: one CTA took
-// milliseconds per image.  Here the CTAs of a cluster share it: every CTA holds the chunk; the kept list (global
-// memory, L2-resident) is dealt round-robin, so each CTA tests all candidates against its share of it and the verdicts
-// are AND-ed through distributed shared memory; the rows of the chunk's bit matrix are dealt round-robin too and
-// written straight into the leader's shared memory; the leader sweeps, appends the survivors to the kept list and
-// publishes the count.  Four cluster barriers per chunk; the greedy order -- hence the result -- is unchanged.
-// CTAs per cluster.  Measured on B200 at cfg5 (16 single-class segments of 8 053 candidates): 8 -> 2.17 ms (15 clusters
-// fit: two rounds), 7 -> 2.56, 6 -> 1.44 (one round), 4 -> 1.86 ms per step; 8 is the portable maximum.
+// milliseconds per image.  Here the CTAs of a cluster share it.  Per chunk:
+//   1. every CTA holds the chunk (one candidate per thread) and tests it against ITS share of the kept list (kept box q
+//      belongs to CTA q mod kClu), staged through shared memory with the fp32 areas, with the branch-free fused sign
+//      test; the verdicts of the CTAs are AND-ed through distributed shared memory;
+//   2. the candidates still alive (typically a third of the chunk) are compacted, in order, by every CTA alike; the
+//      chunk's own suppression matrix is computed on the compact list as 32 x 32 warp tiles dealt over all warps of the
+//      cluster and written, row form, straight into the leader's shared memory (diagonal tiles also in column form);
+//   3. one warp of the leader sweeps the compact list block by block -- a block's survivors by the ballot fixed point,
+//      their rows OR-ed into the later blocks by one warp reduction per block -- appends the survivors to the kept list
+//      (global memory, L2-resident) and publishes the count.
+// Three cluster barriers per chunk; the greedy order -- hence the result -- is unchanged.  What is left is phase 1
+// (issue-bound: 1024 x kept / kClu pair tests per CTA and chunk, ~60 % of the kernel at the single-class stress shape).
+// CTAs per cluster.  Measured on B200 at cfg5 (16 single-class segments of 8 053 candidates) with the first version of
+// this kernel: 8 -> 2.17 ms (15 clusters fit: two rounds), 7 -> 2.56, 6 -> 1.44 (one round), 4 -> 1.86 ms per step; 8 is
+// the portable maximum.  This version: 0.35 ms for the kernel, 0.48 ms per step.
 #ifndef YV3_NMS_CLUSTER
 #define YV3_NMS_CLUSTER 6
 #endif
