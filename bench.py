@@ -84,6 +84,7 @@ def build_spec(w):
 def synth(spec, n, m, rank):
     """logits iid N(0,1) clipped to [-8,8], seed 1234+rank; labels V~U{1..M}, seed 4321+rank."""
     from yolov3_tensorflow_b200 import synth as ps
+    rank = int(os.environ.get("YV3_BENCH_SEED_RANK", rank))      # developer switch: another rank's data on this GPU
     h32, w32 = spec.head_grid_sizes[2]
     return (ps.make_predicts(n, h32 * 32, w32 * 32, spec.box_num, spec.class_num, seed=1234 + rank),
             ps.make_targets(n, spec.class_num, m, seed=4321 + rank, min_valid=1))
