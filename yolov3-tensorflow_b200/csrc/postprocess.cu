@@ -384,6 +384,8 @@ __device__ __forceinline__ bool suppresses_overlapping_fast(const float4& a, con
 // 1024 threads: the gather -> sort -> NMS chain of a step must stay well below a sweep's duration or the post-process
 // stream becomes the step's bottleneck (measured at cfg2: 256 threads 103 us/step like 1024, 128 threads 126 us/step)
 constexpr int kSortThreads = 1024;
+constexpr int kSortInlineWarps = 8;     // warps of the last sort CTA that serve a short queue of medium segments themselves
+constexpr int kSortInlineJobs = 64;     // ... up to this many segments
 constexpr int kSortSmemKeys = 4096;      // lists up to this size are sorted in shared memory (45 KB per CTA)
 constexpr unsigned long long kPadKey = ~0ULL;
 
@@ -969,23 +971,14 @@ __device__ __forceinline__ void warp_sort_bucket(unsigned long long* skey, unsig
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsigned long long* __restrict__ gkeys,
-                                                                   const int32_t* __restrict__ count, int count_cols,
-                                                                   int capacity, int cap2, double thresh,
-                                                                   const float* __restrict__ cand,
-                                                                   unsigned char* __restrict__ keep,
-                                                                   const int2* __restrict__ wl, const int32_t* __restrict__ wl_count) {
-    extern __shared__ __align__(16) unsigned char wsm[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    WarpNmsSmem& sm = reinterpret_cast<WarpNmsSmem*>(wsm)[warp];
-    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int nw = (gridDim.x * blockDim.x) >> 5;
-    const int nwork = *wl_count;
-    const bool none_overlap_drops = 0.0 > thresh;      // a negative threshold suppresses even disjoint boxes (:124)
-    const NmsThresh nq = make_nms_thresh(thresh);
-    const bool fast_ok = nq.lo >= kWarpNmsThreshLo;
-    for (int wi = wid; wi < nwork; wi += nw) {
-        const int2 job = wl[wi];
+// One queued segment, by one warp (`sm`: the warp's slice of shared memory).  Called by nms_warp_kernel and, for a short
+// queue, by the last CTA of the sort kernel itself.
+__device__ __forceinline__ void warp_nms_job(WarpNmsSmem& sm, const int lane, const int2 job,
+                                             const unsigned long long* __restrict__ gkeys, const int32_t* __restrict__ count,
+                                             const int count_cols, const int capacity, const int cap2, const double thresh,
+                                             const NmsThresh nq, const bool fast_ok, const bool none_overlap_drops,
+                                             const float* __restrict__ cand, unsigned char* __restrict__ keep) {
+    {
         const int n = job.x, s0 = job.y & 0x3ffff;
         int len = (job.y >> 18) & 0x1ff;
         const bool needs_sort = ((job.y >> 27) & 1) != 0;
@@ -1139,6 +1132,26 @@ __global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsi
             if (row[u] >= 0) keep_n[row[u]] = (unsigned char)((k >> pos) & 1u);
         }
     }
+}
+
+
+__global__ void __launch_bounds__(kWarpNmsDevThreads) nms_warp_kernel(const unsigned long long* __restrict__ gkeys,
+                                                                   const int32_t* __restrict__ count, int count_cols,
+                                                                   int capacity, int cap2, double thresh,
+                                                                   const float* __restrict__ cand,
+                                                                   unsigned char* __restrict__ keep,
+                                                                   const int2* __restrict__ wl, const int32_t* __restrict__ wl_count) {
+    extern __shared__ __align__(16) unsigned char wsm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpNmsSmem& sm = reinterpret_cast<WarpNmsSmem*>(wsm)[warp];
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nw = (gridDim.x * blockDim.x) >> 5;
+    const int nwork = *wl_count;
+    const bool none_overlap_drops = 0.0 > thresh;      // a negative threshold suppresses even disjoint boxes (:124)
+    const NmsThresh nq = make_nms_thresh(thresh);
+    const bool fast_ok = nq.lo >= kWarpNmsThreshLo;
+    for (int wi = wid; wi < nwork; wi += nw)
+        warp_nms_job(sm, lane, wl[wi], gkeys, count, count_cols, capacity, cap2, thresh, nq, fast_ok, none_overlap_drops, cand, keep);
 }
 
 // ---- long segments: one thread-block CLUSTER per segment ------------------------------------------------------
@@ -1464,14 +1477,39 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
                                                             int dispatch, int many_classes) {
     sort_body(cand, count, count_cols, capacity, cap2, n2s, thresh, gkeys, sbox, sidx, keep, wl, wl_large, wl_count, many_classes != 0);
     if (!dispatch) return;
+    __shared__ int last_s;
     __syncthreads();                                            // (every thread of the CTA reaches this point)
-    if (threadIdx.x != 0) return;
+    if (threadIdx.x == 0) {
+        __threadfence();
+        last_s = (atomicAdd(wl_count + 2, 1) == (int)gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!last_s) return;
     __threadfence();
-    if (atomicAdd(wl_count + 2, 1) != (int)gridDim.x - 1) return;
-    __threadfence();
-    wl_count[2] = 0;
     const int nmed = *(volatile int32_t*)wl_count, nlarge = *(volatile int32_t*)(wl_count + 1);
-    if (nmed > 0) {
+    // A SHORT queue of medium segments (a class of one image that happens to exceed 32 candidates: a few per step at 608^2)
+    // is served right here by the warps of this last CTA, whose shared memory is free now: a device-side launch costs
+    // ~50 us of latency on the post-process chain, more than the work (measured: 178 -> 235 us per step at cfg3 for the
+    // ranks whose data had one such class).
+    const int inline_warps = min(kSortInlineWarps, (int)(((size_t)n2s * 10 + (size_t)kBucketClasses * 4) / sizeof(WarpNmsSmem)));
+    bool launch_med = nmed > 0;
+    if (nmed > 0 && inline_warps > 0 && nmed <= kSortInlineJobs) {
+        extern __shared__ __align__(16) unsigned long long skeys_again[];
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (warp < inline_warps) {
+            WarpNmsSmem& sm = reinterpret_cast<WarpNmsSmem*>(skeys_again)[warp];
+            const bool none_overlap_drops = 0.0 > thresh;
+            const NmsThresh nq = make_nms_thresh(thresh);
+            const bool fast_ok = nq.lo >= kWarpNmsThreshLo;
+            for (int wi = warp; wi < nmed; wi += inline_warps)
+                warp_nms_job(sm, lane, wl[wi], gkeys, count, count_cols, capacity, cap2, thresh, nq, fast_ok, none_overlap_drops,
+                             cand, keep);
+        }
+        launch_med = false;
+    }
+    if (threadIdx.x != 0) return;
+    wl_count[2] = 0;
+    if (launch_med) {
         const int wpc = dispatch;                                // warps per CTA of the device-launched grid (one CTA per SM)
         nms_warp_kernel<<<min((nmed + wpc - 1) / wpc, 148), 32 * wpc, sizeof(WarpNmsSmem) * wpc, cudaStreamTailLaunch>>>(
             gkeys, count, count_cols, capacity, cap2, thresh, cand, keep, wl, wl_count);
