@@ -48,11 +48,7 @@ __global__ void __launch_bounds__(kDecThreads) decode_kernel(const __grid_consta
         r[0] = d.x; r[1] = d.y; r[2] = d.w; r[3] = d.h; r[4] = d.conf;
         if (a.raw4[p.h]) reinterpret_cast<float4*>(a.raw4[p.h])[rih] = make_float4(t0, t1, t2, t3);
         if (a.boxes[p.h]) reinterpret_cast<float4*>(a.boxes[p.h])[rih] = make_float4(d.x0, d.y0, d.x1, d.y1);
-        if (C > 0) {
-            float* z = r + 5;
-            const ClassStats cs = class_stats(z, C);                     // decoder :189-190
-            for (int k = 0; k < C; ++k) z[k] = class_prob(z[k], cs, g.lo, g.hi);   // :190-191
-        }
+        if (C > 0) class_softmax_in_place(r + 5, C, g.lo, g.hi);         // decoder :189-191
     }
     __syncthreads();
 

@@ -81,6 +81,33 @@ __device__ __forceinline__ ClassStats class_stats(const float* __restrict__ z, i
     return s;
 }
 
+// The class probabilities of one record IN PLACE (decoder :189-191): z[k] <- clip(exp(z[k] - max) * (1 / sum)).  The same
+// values as class_stats + class_prob element by element -- same maximum, the same four interleaved partial sums in the same
+// order, the same exp(z - max) -- but every exponential is taken once: it is kept in z[k] between the sum and the scaling.
+__device__ __forceinline__ void class_softmax_in_place(float* __restrict__ z, int C, float lo, float hi) {
+    float mx = z[0];
+    for (int k = 1; k < C; ++k) {
+        const float v = z[k];
+        if (v > mx) mx = v;                             // (the comparison of class_stats: a NaN never displaces the maximum)
+    }
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int k = 0;
+    for (; k + 4 <= C; k += 4) {
+        const float e0 = expf(__fsub_rn(z[k], mx)), e1 = expf(__fsub_rn(z[k + 1], mx));
+        const float e2 = expf(__fsub_rn(z[k + 2], mx)), e3 = expf(__fsub_rn(z[k + 3], mx));
+        s0 += e0; s1 += e1; s2 += e2; s3 += e3;
+        z[k] = e0; z[k + 1] = e1; z[k + 2] = e2; z[k + 3] = e3;
+    }
+    for (; k < C; ++k) {
+        const float e = expf(__fsub_rn(z[k], mx));
+        const int m = k & 3;
+        if (m == 0) s0 += e; else if (m == 1) s1 += e; else if (m == 2) s2 += e; else s3 += e;
+        z[k] = e;
+    }
+    const float inv = __fdiv_rn(1.0f, __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3)));
+    for (k = 0; k < C; ++k) z[k] = clip_ref(__fmul_rn(z[k], inv), lo, hi);
+}
+
 // The same statistics by a whole WARP (all lanes call it, all lanes get the result), bit for bit: class k lives on
 // lane k & 31 in slot k >> 5; the four interleaved partial sums of class_stats are rebuilt by lanes 0..3, lane r
 // adding the terms of classes r, r + 4, r + 8, ... in increasing order (a shuffle and an add per term); a class past
