@@ -1461,6 +1461,23 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
     cluster.sync();                                                  // nobody leaves while its shared memory may be read
 }
 
+// The short-queue service of the sort kernel's last CTA (see sort_kernel).  Not inlined: its registers (the warp NMS needs
+// 74) stay out of the sort kernel's own allocation.
+__device__ __noinline__ void sort_inline_jobs(WarpNmsSmem* sm_base, const int inline_warps, const int nmed,
+                                              const unsigned long long* __restrict__ gkeys, const int32_t* __restrict__ count,
+                                              const int count_cols, const int capacity, const int cap2, const double thresh,
+                                              const float* __restrict__ cand, unsigned char* __restrict__ keep,
+                                              const int2* __restrict__ wl) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp >= inline_warps) return;
+    const bool none_overlap_drops = 0.0 > thresh;
+    const NmsThresh nq = make_nms_thresh(thresh);
+    const bool fast_ok = nq.lo >= kWarpNmsThreshLo;
+    for (int wi = warp; wi < nmed; wi += inline_warps)
+        warp_nms_job(sm_base[warp], lane, wl[wi], gkeys, count, count_cols, capacity, cap2, thresh, nq, fast_ok, none_overlap_drops,
+                     cand, keep);
+}
+
 // ---- the sort kernel and its device-side dispatch ----------------------------------------------------------------
 // The queue-driven NMS kernels above have nothing to do on most steps of a many-class head (no class of an image holds
 // more than 32 candidates), yet launched from the host they still had to be placed: thousands of CTAs on the
@@ -1495,16 +1512,8 @@ __global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restr
     bool launch_med = nmed > 0;
     if (nmed > 0 && inline_warps > 0 && nmed <= kSortInlineJobs) {
         extern __shared__ __align__(16) unsigned long long skeys_again[];
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        if (warp < inline_warps) {
-            WarpNmsSmem& sm = reinterpret_cast<WarpNmsSmem*>(skeys_again)[warp];
-            const bool none_overlap_drops = 0.0 > thresh;
-            const NmsThresh nq = make_nms_thresh(thresh);
-            const bool fast_ok = nq.lo >= kWarpNmsThreshLo;
-            for (int wi = warp; wi < nmed; wi += inline_warps)
-                warp_nms_job(sm, lane, wl[wi], gkeys, count, count_cols, capacity, cap2, thresh, nq, fast_ok, none_overlap_drops,
-                             cand, keep);
-        }
+        sort_inline_jobs(reinterpret_cast<WarpNmsSmem*>(skeys_again), inline_warps, nmed, gkeys, count, count_cols, capacity, cap2,
+                         thresh, cand, keep, wl);
         launch_med = false;
     }
     if (threadIdx.x != 0) return;
