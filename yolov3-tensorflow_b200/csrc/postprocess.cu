@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(kScoreThreads) score_tile_kernel(const __grid_
                                                                    int32_t* __restrict__ tcount) {
     extern __shared__ __align__(128) unsigned char ssm[];
     __shared__ uint64_t bar_s[kScoreThreads / 32];
-    const int L = g.L, C = g.C, tr = q.tr;
+    const int L = g.L, tr = q.tr;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int unit = blockIdx.x * q.wpc + warp;
     if (warp >= q.wpc || unit >= q.num_tiles) return;
@@ -443,8 +443,7 @@ __device__ __forceinline__ void bitonic_sort_regs(unsigned long long* keys, int 
 
 constexpr int kNmsMedium = 256;         // threads = chunk size of the NMS kernel for segments of 33..256 candidates
 constexpr int kNmsLarge = 1024;         // ... and for longer ones
-constexpr int kFuseMaxK = 4096;         // lists up to this size get their short segments resolved inside the sort kernel
-constexpr int kFuseMaxSeg = 32;         // ... segments up to one warp wide
+constexpr int kFuseMaxSeg = 32;         // class segments up to one warp wide are resolved inside the sort kernel
 constexpr int kBucketMaxK = 65535;      // bucket path of the sort kernel: lists up to this size (arrival order is 16 bits) ...
 constexpr int kBucketClasses = 1024;    // ... with class ids below this (thread t owns classes 4t .. 4t + 3) and <= 256 per class
 constexpr int kClsPerThread = kBucketClasses / kSortThreads;
@@ -534,7 +533,6 @@ __device__ __forceinline__ void sort_body(const float* __restrict__ cand, const 
                                           int2* __restrict__ wl, int2* __restrict__ wl_large,
                                           int32_t* __restrict__ wl_count, const bool many_classes) {
     extern __shared__ __align__(16) unsigned long long skeys[];
-    __shared__ int nseg_s;
     const NmsThresh nq = make_nms_thresh(thresh);
     const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int K = 0;
@@ -546,7 +544,6 @@ __device__ __forceinline__ void sort_body(const float* __restrict__ cand, const 
     const float* rows = cand + (size_t)n * capacity * YV3_CAND_COLS;
     unsigned long long* gk = gkeys + (size_t)n * cap2;
     unsigned long long* keys = (n2 <= n2s) ? skeys : gk;           // short lists live in shared memory, long ones in gk
-    if (tid == 0) nseg_s = 0;
     __syncthreads();
     // ---- bucket path: no class of this image has more than kWarpNmsMax (256) candidates -- ~6 per class at cfg2, ~133
     // at the dense stress workload (10 647 candidates per image over 80 classes).  Sorting by (class, score desc, row) is
@@ -643,10 +640,8 @@ __device__ __forceinline__ void sort_body(const float* __restrict__ cand, const 
                 const unsigned long long k1 = in ? bkey[o0 + lane] : kPadKey;
                 const int row = (int)(k1 & 0x3ffffULL);
                 float4 mine_f = make_float4(0.f, 0.f, 0.f, 0.f);
-                double mine_area = 0.0;
                 if (in) {
                     mine_f = reinterpret_cast<const float4*>(rows + (size_t)row * YV3_CAND_COLS)[0];
-                    mine_area = box_area_d(mine_f);
                 }
                 unsigned alive = __ballot_sync(0xffffffffu, in);
                 for (int i = 0; i < len - 1; ++i) {
@@ -1191,13 +1186,13 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
                                                                const int2* __restrict__ wl, const int32_t* __restrict__ wl_count) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
-    constexpr int T = kCluT, W = T / 64;
+    constexpr int T = kCluT;
     extern __shared__ __align__(16) unsigned char csm[];
     float4* chunk_s = reinterpret_cast<float4*>(csm);                                         // [T]
-    unsigned long long* mask_s = reinterpret_cast<unsigned long long*>(chunk_s + T);         // [T][W]  (used in the leader)
-    unsigned char* alive_s = reinterpret_cast<unsigned char*>(reinterpret_cast<unsigned*>(mask_s) + (size_t)T * kCluRow);   // [T] (unused)
-    unsigned char* verdict_s = alive_s + T;                                                  // [T] this CTA's share
-    unsigned char* kept_flag_s = verdict_s + T;                                              // [T]
+    unsigned* mask_s = reinterpret_cast<unsigned*>(chunk_s + T);                             // [T][kCluRow] row form (used in the leader)
+    unsigned char* verdict_s = reinterpret_cast<unsigned char*>(mask_s + (size_t)T * kCluRow);   // [T] this CTA's share
+    unsigned char* spare_s = verdict_s + T;                                                  // [T] (free)
+    unsigned char* kept_flag_s = spare_s + T;                                                // [T]
     float4* kbox_s = reinterpret_cast<float4*>(kept_flag_s + T);                            // [T] a tile of this CTA's share of the kept list
     float* karea_s = reinterpret_cast<float*>(kbox_s + T);                                  // [T]
     unsigned* dcol_s = reinterpret_cast<unsigned*>(karea_s + T);                            // [T] diagonal tiles, column form (leader)
@@ -1210,7 +1205,7 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int r = (int)cluster.block_rank();
     const int cid = blockIdx.x / kClu, ncl = gridDim.x / kClu;
-    unsigned* leader_mask32 = cluster.map_shared_rank(reinterpret_cast<unsigned*>(mask_s), 0);
+    unsigned* leader_mask32 = cluster.map_shared_rank(mask_s, 0);
     const int* leader_nkept = cluster.map_shared_rank(&nkept_s, 0);
     const int nwork = *wl_count;
     const bool none_overlap_drops = 0.0 > thresh;
@@ -1406,7 +1401,7 @@ __global__ void __launch_bounds__(kCluT, 1) nms_cluster_kernel(const unsigned lo
                     // block w; a block's survivors x_j = free_j and no kept i < j of the block suppresses j come from
                     // iterating x <- free & ~exists(x_i & S_ij) (fixed after at most 32 rounds, usually 2-3 ballots); the
                     // rows of the survivors are then OR-ed into the removed bits of the later blocks.
-                    const unsigned* m32 = reinterpret_cast<const unsigned*>(mask_s);
+                    const unsigned* m32 = mask_s;
                     unsigned removed = 0u, keptw = 0u;
                     for (int b2 = 0; b2 < nb; ++b2) {
                         const unsigned rem_b = __shfl_sync(0xffffffffu, removed, b2);
