@@ -130,6 +130,43 @@ def test_threshold_family_is_decided_like_the_reference(yv3):
         assert kept[0] == 100 + 60
 
 
+def _small_class_lists(rng):
+    """every class at most 32 candidates: resolved inside the sort kernel, one warp per class"""
+    lists = []
+    for eps in (2.0 ** -23, 2.0 ** -20, 2.0 ** -17):
+        parts = []
+        for c in range(0, 30):
+            kind = c % 5
+            if kind == 0:
+                parts.append(_threshold_family(rng, 5 + c % 11, c, eps))            # 10..32 candidates, IoU at / around 0.5
+            elif kind == 1:
+                parts.append(_crowd(rng, 3 + c, c))
+            elif kind == 2:
+                parts.append(_crowd(rng, 32, c, spread=0.01))                        # heavy suppression
+            elif kind == 3:
+                parts.append(_crowd(rng, 20, c, scale=1e-12))                        # areas ~1e-26
+            else:
+                parts.append(_crowd(rng, 1 + c % 3, c))
+        rows = np.concatenate(parts, 0)
+        lists.append(rows[rng.permutation(len(rows))])
+    return lists
+
+
+@pytest.mark.parametrize("thr", [0.5, 0.45, 1e-9, 0.0, -0.25])
+def test_small_segments_inside_the_sort_kernel(yv3, thr):
+    post = _post(yv3, "cfg2_416_c80_b64")
+    kept = _run(post, _small_class_lists(np.random.default_rng(7)), thr)
+    assert all(k > 0 for k in kept)
+
+
+def test_small_threshold_families_are_decided_like_the_reference(yv3):
+    post = _post(yv3, "cfg2_416_c80_b64")
+    for eps in (2.0 ** -23, 2.0 ** -20, 2.0 ** -17, 2.0 ** -10):
+        rows = np.concatenate([_threshold_family(np.random.default_rng(0), 15, c, eps) for c in range(8)], 0)
+        kept = _run(post, [rows], 0.5)
+        assert kept[0] == 8 * (15 + 9)                       # per class: 15 A's and the B's with k = -2, -1, 0
+
+
 @pytest.mark.parametrize("thr", [0.5, 0.4, 1e-9, -0.25])
 def test_long_single_class_segment_edge_cases(yv3, thr):
     post = _post(yv3, "cfg5_nms_stress_b16")

@@ -441,6 +441,12 @@ __device__ __forceinline__ void bitonic_sort_regs(unsigned long long* keys, int 
     __syncthreads();
 }
 
+// The branch-free fp32 pair test of the NMS kernels (warp_nms_tile and its relatives) is trusted when every area of the segment is at least kWarpNmsAreaLo (and at most 1e29) and
+// the threshold at least kWarpNmsThreshLo: an intersection that leaves the normal fp32 range (below 1e-30, where the
+// relative error bound of the product no longer holds) is then still 6 orders of magnitude below lo * union >= 1e-24,
+// i.e. on the "no" side whatever its rounding; disjoint boxes (inter <= 0) are on the "no" side because lo * union > 0.
+constexpr float kWarpNmsAreaLo = 1e-18f;
+constexpr float kWarpNmsThreshLo = 1e-6f;
 constexpr int kNmsMedium = 256;         // threads = chunk size of the NMS kernel for segments of 33..256 candidates
 constexpr int kNmsLarge = 1024;         // ... and for longer ones
 constexpr int kFuseMaxSeg = 32;         // class segments up to one warp wide are resolved inside the sort kernel
@@ -648,15 +654,56 @@ __device__ __forceinline__ void sort_body(const float* __restrict__ cand, const 
                     mine_f = reinterpret_cast<const float4*>(rows + (size_t)row * YV3_CAND_COLS)[0];
                 }
                 unsigned alive = __ballot_sync(0xffffffffu, in);
-                for (int i = 0; i < len - 1; ++i) {
-                    if (!((alive >> i) & 1u)) continue;                                  // warp-uniform
-                    float4 fi;
-                    fi.x = __shfl_sync(0xffffffffu, mine_f.x, i); fi.y = __shfl_sync(0xffffffffu, mine_f.y, i);
-                    fi.z = __shfl_sync(0xffffffffu, mine_f.z, i); fi.w = __shfl_sync(0xffffffffu, mine_f.w, i);
-                    const bool overlap = fminf(fi.z, mine_f.z) > fmaxf(fi.x, mine_f.x) && fminf(fi.w, mine_f.w) > fmaxf(fi.y, mine_f.y);
-                    bool drop = lane > i && ((alive >> lane) & 1u);
-                    if (drop) drop = overlap ? suppresses_overlapping_fast(fi, mine_f, nq) : (0.0 > thresh);
-                    alive &= ~__ballot_sync(0xffffffffu, drop);
+                const float am = __fmul_rn(__fsub_rn(mine_f.z, mine_f.x), __fsub_rn(mine_f.w, mine_f.y));
+                const bool sane = !in || (am >= kWarpNmsAreaLo && am <= 1e29f);
+                if (nq.lo >= kWarpNmsThreshLo && __all_sync(0xffffffffu, sane)) {
+                    // every pair first, branch-free (the sign tests of warp_nms_tile, candidate i by shuffles): per lane j the
+                    // bits i < j that suppress it and the bits the fp32 test leaves open; the latter by the exact expression;
+                    // then the survivors by the ballot fixed point x <- in & ~exists(x_i & S_ij) -- 2-3 ballots.  The serial
+                    // walk over the kept candidates it replaces spent ~50 instructions per candidate.
+                    unsigned col = 0u, und = 0u;
+                    for (int i = 0; i < len - 1; ++i) {
+                        const float fx = __shfl_sync(0xffffffffu, mine_f.x, i), fy = __shfl_sync(0xffffffffu, mine_f.y, i);
+                        const float fz = __shfl_sync(0xffffffffu, mine_f.z, i), fw = __shfl_sync(0xffffffffu, mine_f.w, i);
+                        const float ai = __shfl_sync(0xffffffffu, am, i);
+                        const float w = fmaxf(__fsub_rn(fminf(fz, mine_f.z), fmaxf(fx, mine_f.x)), 0.f);
+                        const float h = __fsub_rn(fminf(fw, mine_f.w), fmaxf(fy, mine_f.y));
+                        const float inter = __fmul_rn(w, h);
+                        const float uni = __fsub_rn(__fadd_rn(ai, am), inter);
+                        const bool yes = __fmaf_rn(nq.hi, uni, -inter) < 0.f;
+                        const bool no = __fmaf_rn(-nq.lo, uni, inter) < 0.f;
+                        col |= yes ? (1u << i) : 0u;
+                        und |= (yes || no) ? 0u : (1u << i);
+                    }
+                    const unsigned earlier = in ? (1u << lane) - 1u : 0u;               // only EARLIER candidates suppress
+                    col &= earlier;
+                    und &= earlier;
+                    for (unsigned open = __reduce_or_sync(0xffffffffu, und); open; open &= open - 1u) {
+                        const int i = __ffs(open) - 1;
+                        float4 fi;
+                        fi.x = __shfl_sync(0xffffffffu, mine_f.x, i); fi.y = __shfl_sync(0xffffffffu, mine_f.y, i);
+                        fi.z = __shfl_sync(0xffffffffu, mine_f.z, i); fi.w = __shfl_sync(0xffffffffu, mine_f.w, i);
+                        if ((und >> i) & 1u) {
+                            // (an open pair overlaps: a disjoint one has inter <= 0 and falls on the "no" side)
+                            if (suppresses_overlapping(fi, box_area_d(fi), mine_f, box_area_d(mine_f), thresh)) col |= 1u << i;
+                        }
+                    }
+                    for (;;) {
+                        const unsigned nk = __ballot_sync(0xffffffffu, in && (col & alive) == 0u);
+                        if (nk == alive) break;
+                        alive = nk;
+                    }
+                } else {
+                    for (int i = 0; i < len - 1; ++i) {
+                        if (!((alive >> i) & 1u)) continue;                              // warp-uniform
+                        float4 fi;
+                        fi.x = __shfl_sync(0xffffffffu, mine_f.x, i); fi.y = __shfl_sync(0xffffffffu, mine_f.y, i);
+                        fi.z = __shfl_sync(0xffffffffu, mine_f.z, i); fi.w = __shfl_sync(0xffffffffu, mine_f.w, i);
+                        const bool overlap = fminf(fi.z, mine_f.z) > fmaxf(fi.x, mine_f.x) && fminf(fi.w, mine_f.w) > fmaxf(fi.y, mine_f.y);
+                        bool drop = lane > i && ((alive >> lane) & 1u);
+                        if (drop) drop = overlap ? suppresses_overlapping_fast(fi, mine_f, nq) : (0.0 > thresh);
+                        alive &= ~__ballot_sync(0xffffffffu, drop);
+                    }
                 }
                 if (in) keep_b[row] = (unsigned char)((alive >> lane) & 1u);
             }
@@ -877,12 +924,6 @@ constexpr int kWarpNmsWarps = kWarpNmsThreads / 32;
 // CTAs, i.e. one CTA per SM (measured with the 14 KB form: 32-thread CTAs 7.9 ms, 128-thread CTAs 2.2 ms at cfg4 against
 // 1.1 ms from the host): the device-side launch therefore uses one many-warp CTA per SM
 constexpr int kWarpNmsDevThreads = 768;      // 24 warps: 76 registers per thread, 120 KB of shared memory
-// The fp32 decision of phase A is trusted when every area of the segment is at least kWarpNmsAreaLo (and at most 1e29) and
-// the threshold at least kWarpNmsThreshLo: an intersection that leaves the normal fp32 range (below 1e-30, where the
-// relative error bound of the product no longer holds) is then still 6 orders of magnitude below lo * union >= 1e-24,
-// i.e. on the "no" side whatever its rounding; disjoint boxes (inter <= 0) are on the "no" side because lo * union > 0.
-constexpr float kWarpNmsAreaLo = 1e-18f;
-constexpr float kWarpNmsThreshLo = 1e-6f;
 struct WarpNmsSmem {
     float4 box[kWarpNmsMax];       // the segment's boxes in sorted order (before that: the key buffer of the rank sort)
     float area[kWarpNmsMax];
