@@ -1525,7 +1525,10 @@ __device__ __noinline__ void sort_inline_jobs(WarpNmsSmem* sm_base, const int in
 // step at cfg2 (tools/step_breakdown.py).  With `dispatch` set the LAST sort CTA to finish looks at the two queue
 // counters and tail-launches (CUDA dynamic parallelism, cudaStreamTailLaunch: after this grid, before the stream's
 // next kernel) only the kernels that have work, with grids sized by the queues.
-__global__ void __launch_bounds__(kSortThreads) sort_kernel(const float* __restrict__ cand, const int32_t* __restrict__ count,
+// MINB = 2: the register cap that lets two sort CTAs share an SM (32 registers per thread; the rarely run parts spill) --
+// used when there are more images than SMs, so that the grid is one wave instead of two (cfg4: 256 images).
+template <int MINB>
+__global__ void __launch_bounds__(kSortThreads, MINB) sort_kernel(const float* __restrict__ cand, const int32_t* __restrict__ count,
                                                             int count_cols, int capacity, int cap2, int n2s, double thresh,
                                                             unsigned long long* __restrict__ gkeys, float4* __restrict__ sbox,
                                                             int32_t* __restrict__ sidx, unsigned char* __restrict__ keep,
@@ -1780,7 +1783,8 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     // whole, and a 16 384-key bitonic sort in global memory took 180 us per step: those launches get the large reservation
     const int n2s = min(cap2, num_classes <= 8 ? 16384 : kSortSmemKeys);
     const size_t smem = (size_t)n2s * 8 + (size_t)kBucketClasses * 4 + (size_t)n2s * 2;
-    err = set_smem_once((const void*)sort_kernel, smem);
+    const bool two_per_sm = n > 148 && smem <= 100 * 1024 && !getenv("YV3_SORT_ONE_PER_SM");
+    err = two_per_sm ? set_smem_once((const void*)sort_kernel<2>, smem) : set_smem_once((const void*)sort_kernel<1>, smem);
     if (err != cudaSuccess) return err;
     err = cudaMemsetAsync(ws.wl_count, 0, 3 * sizeof(int32_t), stream);          // two queue counters, the dispatch ticket
     if (err != cudaSuccess) return err;
@@ -1802,7 +1806,9 @@ cudaError_t launch_nms(const float* cand, const int32_t* count, int count_cols, 
     err = set_smem_once((const void*)nms_warp_kernel, sizeof(WarpNmsSmem) * (kWarpNmsDevThreads / 32));
     if (err != cudaSuccess) return err;
     if (!(skip & 1))
-    sort_kernel<<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, n2s, thresh, ws.keys, ws.sbox,
+    if (two_per_sm) sort_kernel<2><<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, n2s, thresh, ws.keys, ws.sbox,
+                                                   ws.sidx, keep, ws.wl, wl_large, ws.wl_count, ws.kspill, dispatch, num_classes > 8 ? 1 : 0);
+    else sort_kernel<1><<<n, kSortThreads, smem, stream>>>(cand, count, count_cols, capacity, cap2, n2s, thresh, ws.keys, ws.sbox,
                                                    ws.sidx, keep, ws.wl, wl_large, ws.wl_count, ws.kspill, dispatch, num_classes > 8 ? 1 : 0);
     err = cudaGetLastError();
     if (err != cudaSuccess) return err;
